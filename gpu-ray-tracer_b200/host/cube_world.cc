@@ -1,0 +1,144 @@
+#include "cube_world.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <fstream>
+#include <sstream>
+#include <stdexcept>
+
+#include "mini_json.h"
+#include "perlin.h"
+
+namespace procedural {
+
+namespace {
+// defaults: src/procedural/cube_world.cc:15-21
+const int kDefaultSeed = 42;
+const int kDefaultGridSize = 8;
+const int kDefaultWidth = 640;
+const int kDefaultHeight = 480;
+const float kDefaultFov = M_PI / 4;
+const float kDefaultUnitLen = 200;
+const float kDefaultAmplitude = 1.0f;
+
+rtb::Float3 read_vec3(const mini_json::Value& v) { return {v.at(0).as_float(), v.at(1).as_float(), v.at(2).as_float()}; }
+rtb::Float4 read_vec4(const mini_json::Value& v) {
+    return {v.at(0).as_float(), v.at(1).as_float(), v.at(2).as_float(), v.at(3).as_float()};
+}
+}  // namespace
+
+rtracer::FlatScene generate_from_text(const std::string& json_text, const WorldOverrides& ov) {
+    std::shared_ptr<mini_json::Value> root = mini_json::parse_text(json_text);
+    const mini_json::Value& doc = *root;
+    if (!doc.is_object()) throw std::runtime_error("world json: top level is not an object");
+
+    int seed = kDefaultSeed, grid_size = kDefaultGridSize, width = kDefaultWidth, height = kDefaultHeight;
+    float fov = kDefaultFov, unit_length = kDefaultUnitLen;
+    if (doc.has("seed")) seed = doc.at("seed").as_int();
+    if (doc.has("grid_size")) grid_size = doc.at("grid_size").as_int();
+    if (doc.has("width")) width = doc.at("width").as_int();
+    if (doc.has("height")) height = doc.at("height").as_int();
+    if (doc.has("fov")) fov = (float)(doc.at("fov").as_double() * M_PI) / 180;  // degrees -> radians (:57)
+    if (doc.has("unit_length")) unit_length = (float)doc.at("unit_length").as_double();
+    if (ov.width > 0) width = ov.width;
+    if (ov.height > 0) height = ov.height;
+    if (ov.grid_size > 0) grid_size = ov.grid_size;
+
+    (void)doc.at("atlas").as_string();  // required key in the reference (:64); the atlas is never sampled
+    rtracer::Camera cam(fov, unit_length, width, height);
+    rtracer::SceneBuilder builder;
+
+    // cube meshes, one per "cubes" entry (:70-114)
+    int n_cubes = 0;
+    const float inv255 = 1.0f / UINT8_MAX;
+    if (doc.has("cubes")) {
+        const mini_json::Value& cubes = doc.at("cubes");
+        n_cubes = (int)cubes.size();
+        for (int i = 0; i < n_cubes; i++) {
+            const mini_json::Value& cube = cubes.at((size_t)i);
+            rtracer::Material mat;
+            rtracer::TextureCoords coords;  // degenerate: texture mapping is a TODO in the reference (:79-81)
+            if (cube.has("Ke")) mat.set_Ke(inv255 * read_vec4(cube.at("Ke")));
+            if (cube.has("Ka")) mat.set_Ka(inv255 * read_vec4(cube.at("Ka")));
+            if (cube.has("Kd")) mat.set_Kd(inv255 * read_vec4(cube.at("Kd")));
+            if (cube.has("Ks")) mat.set_Ks(inv255 * read_vec4(cube.at("Ks")));
+            if (cube.has("Kt")) mat.set_Kt(read_vec4(cube.at("Kt")));
+            if (cube.has("Kr")) mat.set_Kr(read_vec4(cube.at("Kr")));
+            if (cube.has("alpha")) mat.set_alpha((float)cube.at("alpha").as_double());
+            if (cube.has("eta")) mat.set_eta((float)cube.at("eta").as_double());
+            builder.build_cube(.999f, coords, mat);
+        }
+    }
+
+    // lights (:116-138)
+    if (doc.has("lights")) {
+        const mini_json::Value& lights = doc.at("lights");
+        if (lights.has("directional")) {
+            const mini_json::Value& d = lights.at("directional");
+            for (size_t i = 0; i < d.size(); i++)
+                builder.add_directional_light(read_vec3(d.at(i).at("dir")), inv255 * read_vec4(d.at(i).at("col")));
+        }
+        if (lights.has("point")) {
+            const mini_json::Value& p = lights.at("point");
+            for (size_t i = 0; i < p.size(); i++)
+                builder.add_point_light(read_vec3(p.at(i).at("pos")), inv255 * read_vec4(p.at(i).at("col")));
+        }
+    }
+
+    // Perlin height field -> stacked unit cubes (:140-170)
+    float amplitude = kDefaultAmplitude;
+    if (doc.has("amplitude")) amplitude = (float)doc.at("amplitude").as_double();
+    std::vector<float> last_heights((size_t)grid_size * grid_size, 0.0f);
+    float max_height = 0.0f;
+    for (int c = 0; c < n_cubes; c++) {
+        Perlin perlin(seed, (grid_size + 4) / 5);
+        perlin.set_amplitude(amplitude);
+        perlin.set_period((float)grid_size);
+        for (int i = 0; i < grid_size; i++) {
+            for (int j = 0; j < grid_size; j++) {
+                float x = i - grid_size / 2.0f;
+                float z = j - grid_size / 2.0f;
+                float y_off = std::floor(0.5f * (perlin.sample((float)i, (float)j, 0.0f) + amplitude)) + 1;
+                for (int d = 0; d < y_off; d++) {
+                    float y = last_heights[(size_t)i * grid_size + j] + d;
+                    int tid = builder.add_trans(builder.get_mesh_builder(c));
+                    builder.get_transformation(tid).set_position({x, y, z});
+                }
+                last_heights[(size_t)i * grid_size + j] += y_off;
+                max_height = std::max(max_height, last_heights[(size_t)i * grid_size + j]);
+            }
+        }
+    }
+
+    // camera pose (:172-173): note the angle is 45 RADIANS about +x
+    cam.set_position({0.0f, max_height + 10.0f, -(float)grid_size / 2});
+    cam.set_orientation(rtb::quat_axis_angle({1.0f, 0.0f, 0.0f}, 45));
+
+    rtracer::FlatScene fs = builder.build_flat_scene(width, height, cam);
+
+    // finish_env (:177-191)
+    if (doc.has("ambience")) {
+        rtb::Float4 a = read_vec4(doc.at("ambience"));
+        fs.env.ambience[0] = a.x; fs.env.ambience[1] = a.y; fs.env.ambience[2] = a.z; fs.env.ambience[3] = a.w;
+    }
+    if (doc.has("depth")) fs.env.depth = doc.at("depth").as_int();
+    if (ov.depth >= 0) fs.env.depth = ov.depth;
+    if (doc.has("distance_attenuation")) {
+        const mini_json::Value& a = doc.at("distance_attenuation");
+        fs.env.dist_atten[0] = (float)a.at("constant_term").as_double();
+        fs.env.dist_atten[1] = (float)a.at("linear_term").as_double();
+        fs.env.dist_atten[2] = (float)a.at("quadratic_term").as_double();
+    }
+    return fs;
+}
+
+rtracer::FlatScene generate(const std::string& config_path, const WorldOverrides& ov) {
+    std::ifstream ifs(config_path.c_str());
+    if (!ifs) throw std::runtime_error("cannot open scene file: " + config_path);
+    std::stringstream ss;
+    ss << ifs.rdbuf();
+    return generate_from_text(ss.str(), ov);
+}
+
+}  // namespace procedural

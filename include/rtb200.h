@@ -1,0 +1,228 @@
+/* rtb200.h — C ABI of the B200-native ray-traversal engine (librtb200.so).
+ *
+ * Drop-in boundary for the reference's hot path. The reference (wtzhang23/gpu-ray-tracer) has no
+ * FFI layer; its seam is the C++ free-function API in include/raytracer.h:18-28 fed by
+ * SceneBuilder::build_gpu_scene (include/scene_builder.h:115). Every entry point below names the
+ * reference interface it replaces. Plain pointers and sizes only; all functions return 0 on
+ * success or an RtStatus error code (the reference's assert(rv == 0) / unchecked calls become
+ * return codes, src/raytracer.cu:83,115; include/gputils/alloc.h:18-19) and never abort.
+ *
+ * All arithmetic types follow the reference: fp32 geometry/shading, RGBA8 canvas packed as
+ * R<<24 | G<<16 | B<<8 | A in an int32 at buffer[y*W + x] (src/rayenv/color.cu:24-26,
+ * src/rayenv/canvas.cu:9-12).
+ */
+#ifndef RTB200_H
+#define RTB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum RtStatus {
+    RT_OK = 0,
+    RT_ERR_INVALID_ARG = 1,
+    RT_ERR_CUDA = 2,
+    RT_ERR_NO_DEVICE = 3,
+    RT_ERR_OUT_OF_MEMORY = 4,
+    RT_ERR_NO_BVH = 5,
+    RT_ERR_LIMIT = 6
+} RtStatus;
+
+/* rprimitives::Material (include/rayprimitives/material.h:14-27): 6 RGBA vectors + alpha + eta. */
+typedef struct RtMaterial {
+    float Ke[4], Ka[4], Kd[4], Ks[4], Kt[4], Kr[4];
+    float alpha, eta;
+} RtMaterial;
+
+/* rprimitives::{gpu,cpu}::TriInner (include/rayprimitives/gpu/trimesh.cuh:25-53): vertex index
+ * triple, per-triangle material, TextureCoords reduced to its `degenerate` flag (the atlas is
+ * never sampled, src/rayprimitives/phong.cu:19-23). */
+typedef struct RtTriangle {
+    int32_t v[3];
+    int32_t tex_degenerate;
+    RtMaterial mat;
+} RtTriangle;
+
+/* rprimitives::Entity pose (include/rayprimitives/entity.h:16-30): quaternion (i,j,k,r) + position. */
+typedef struct RtPose {
+    float rot[4];
+    float pos[3];
+} RtPose;
+
+/* One Trimesh hitable (MeshBuilder, include/scene_builder.h:29-49): its own pose and a
+ * [tri_begin, tri_end) range into the triangle array. */
+typedef struct RtMesh {
+    RtPose pose;
+    int32_t tri_begin, tri_end;
+} RtMesh;
+
+/* renv::Transformation (include/rayenv/transformation.h:13-23): pose + hitable index. */
+typedef struct RtInstance {
+    RtPose pose;
+    int32_t mesh;
+} RtInstance;
+
+enum { RT_LIGHT_POINT = 0, RT_LIGHT_DIRECTIONAL = 1 };
+/* PointLight / DirLight (include/rayprimitives/gpu/light.cuh:17-67). `v` is the position for a
+ * point light and the NORMALISED shine direction for a directional one (set_shine_dir normalises).
+ * Order matters for float summation: point lights first, then directional
+ * (src/scene_builder.cu:61-81). */
+typedef struct RtLight {
+    int32_t kind;
+    float color[4];
+    float v[3];
+} RtLight;
+
+/* renv::Camera (include/rayenv/camera.h:15-36, src/rayenv/camera.cu:6-9,32-42). */
+typedef struct RtCamera {
+    RtPose pose;
+    float global_near;
+    float unit_to_pixels;
+    float canvas_width, canvas_height;
+} RtCamera;
+
+/* renv::Environment scalars (include/rayenv/environment.h:19-49). depth <= 9 (RayFrame[10],
+ * src/rayenv/scene.cu:25,96). */
+typedef struct RtEnv {
+    float ambience[4];
+    float dist_atten[3];
+    int32_t depth;
+} RtEnv;
+
+typedef struct RtSceneDesc {
+    const float* vertices; /* n_vertices * 3 */
+    const float* normals;  /* n_vertices * 3 (SceneBuilder::generate_normals, src/scene_builder.cc:11-29) */
+    int32_t n_vertices;
+    const RtTriangle* triangles;
+    int32_t n_triangles;
+    const RtMesh* meshes;
+    int32_t n_meshes;
+    const RtInstance* instances;
+    int32_t n_instances;
+    const RtLight* lights;
+    int32_t n_lights;
+    RtCamera camera;
+    RtEnv env;
+    int32_t width, height;
+} RtSceneDesc;
+
+typedef struct RtScene RtScene; /* opaque; owns all device memory */
+
+/* Which bounce semantics propagate_ray follows. The reference's CUDA and serial paths differ for
+ * reflective / refractive materials; RT_SEMANTICS_GPU restates
+ * renv::gpu::propagate_ray (src/rayenv/scene.cu:92-188), RT_SEMANTICS_CPU restates
+ * renv::cpu::Scene::propagate_helper (src/rayenv/scene.cu:222-268). */
+enum { RT_SEMANTICS_GPU = 0, RT_SEMANTICS_CPU = 1 };
+
+enum {
+    RT_RENDER_REBUILD_BVH = 1,   /* rebuild the BVH inside the call (reference timing scope) */
+    RT_RENDER_NO_BVH = 2,        /* `-r/--unoptimize`: brute force over instances, src/rayenv/scene.cu:48-52 */
+    RT_RENDER_CANVAS_DEVICE = 4, /* `canvas` is a device pointer (no D2H copy) */
+    RT_RENDER_SORT_RAYS = 8,     /* sort secondary rays between bounces */
+    RT_RENDER_TILED_OUTPUT = 16  /* write only this rank's tiles, compacted (multi-GPU) */
+};
+
+typedef struct RtRenderParams {
+    int32_t flags;
+    int32_t semantics;
+    /* Multi-GPU screen-space sharding: this process renders tiles t with t % world == rank. */
+    int32_t rank, world;
+    int32_t tile_w, tile_h;
+} RtRenderParams;
+
+typedef struct RtFrameStats {
+    uint64_t rays_total;      /* closest-hit queries = the reference's cast_ray calls */
+    uint64_t rays_primary;
+    uint64_t rays_shadow;
+    uint64_t rays_secondary;
+    uint64_t nodes_visited;   /* only filled by the stats build of the kernels */
+    uint64_t tris_tested;     /* exact (reference-arithmetic) triangle tests */
+    uint64_t prims_prefiltered; /* conservative candidate tests */
+    float ms_build;           /* CUDA-event time of the BVH build inside this call (0 if none) */
+    float ms_trace;           /* CUDA-event time of ray generation + traversal + shading */
+    float ms_total;           /* CUDA-event time of everything incl. canvas copy */
+    int32_t waves;            /* wavefront iterations (bounce levels) executed */
+    int32_t kernel_launches;  /* kernels launched by this call */
+} RtFrameStats;
+
+typedef struct RtBuildStats {
+    int32_t n_prims;          /* world-space triangles (instances x mesh triangles) */
+    int32_t n_bvh2_nodes;     /* 2*n_prims - 1 */
+    int32_t n_bvh8_nodes;
+    int32_t kernel_launches;
+    float ms_build;
+} RtBuildStats;
+
+typedef struct RtHit {
+    int32_t instance; /* renv::Transformation index, -1 on miss */
+    int32_t triangle; /* index within the instance's mesh */
+    float t;
+    float normal[3];
+    float color[4];   /* propagate_ray result for rt_debug_cast */
+} RtHit;
+
+/* Device selection for this process (one process per GPU). */
+int rt_init(int device_ordinal);
+int rt_device_count(int* out);
+
+/* Replaces the upload half of SceneBuilder::build_gpu_scene (src/scene_builder.cu:83-179):
+ * flat arrays in, no device-side `new`, no managed memory. */
+int rt_scene_create(const RtSceneDesc* desc, RtScene** out);
+/* Replaces Scene::free (include/rayenv/gpu/scene.h:55-69). */
+int rt_scene_destroy(RtScene* scene);
+
+/* Host writes to the managed Scene in the reference (camera motion src/main.cc:140-179,
+ * Environment setters include/rayenv/environment.h:36-53). */
+int rt_scene_set_camera(RtScene* scene, const RtCamera* cam);
+int rt_scene_set_env(RtScene* scene, const RtEnv* env);
+int rt_scene_set_instances(RtScene* scene, const RtInstance* instances, int32_t n_instances);
+int rt_scene_set_canvas_size(RtScene* scene, int32_t width, int32_t height);
+
+/* Replaces rtracer::gpu::create_bvh + ropt::gpu::BVH::BVH (src/raytracer.cu:76-89,
+ * src/rayopt/bvh.cu:74-91) and BVH::free (src/rayopt/bvh.cu:93-96). */
+int rt_bvh_build(RtScene* scene, RtBuildStats* stats);
+int rt_bvh_free(RtScene* scene);
+
+/* Replaces rtracer::gpu::update_scene(scene, kernel_dim, optimize) (src/raytracer.cu:102-120):
+ * (re)build the BVH when optimize != 0, trace the frame, synchronise, leave the RGBA8 frame in
+ * host_canvas (width*height int32). kernel_dim is accepted for compatibility and advisory. */
+int rt_update_scene(RtScene* scene, int32_t kernel_dim, int32_t optimize, uint32_t* host_canvas);
+
+/* Full-control render entry (tile sharding, device-resident canvas, stats). */
+int rt_render(RtScene* scene, const RtRenderParams* params, uint32_t* canvas, RtFrameStats* stats);
+
+/* Multi-GPU helper: number of uint32 pixels rt_render writes with RT_RENDER_TILED_OUTPUT, and the
+ * de-interleave of `world` gathered slabs back into a row-major canvas (both device pointers). */
+int rt_tiled_slab_pixels(RtScene* scene, const RtRenderParams* params, int64_t* out_pixels);
+int rt_untile(RtScene* scene, const RtRenderParams* params, const uint32_t* gathered_dev, uint32_t* canvas_dev);
+
+/* Parity hooks. Primary-ray closest hit per pixel (row-major y*W+x), host outputs. The reference's
+ * Isect carries no ids (include/rayprimitives/isect.h:15-24); these are derived the same way the
+ * oracle derives them. */
+int rt_trace_primary(RtScene* scene, int32_t use_bvh, int32_t* instance, int32_t* triangle, float* t);
+/* renv::gpu::cast_ray on caller-provided rays (src/rayenv/scene.cu:42-73). origins/dirs: n*3 floats,
+ * directions are normalised like the rmath::Ray constructor does (include/raymath/geometry.h:216). */
+int rt_cast_rays(RtScene* scene, int32_t use_bvh, const float* origins, const float* dirs, int32_t n,
+                 int32_t* instance, int32_t* triangle, float* t);
+/* Replaces rtracer::gpu::debug_cast (src/raytracer.cu:91-100) without device printf. */
+int rt_debug_cast(RtScene* scene, int32_t x, int32_t y, int32_t semantics, RtHit* out);
+
+/* LBVH inspection for the bit-exact host comparison: any pointer may be NULL. Sizes: codes/perm
+ * n_prims; parent/left/right/boxes for 2*n_prims-1 BVH2 nodes (boxes: 6 floats each). */
+int rt_bvh_download(RtScene* scene, uint64_t* morton, int32_t* perm, int32_t* left, int32_t* right,
+                    int32_t* parent, float* boxes, float* scene_bounds6);
+int rt_bvh8_download(RtScene* scene, void* nodes80, int32_t max_nodes, int32_t* n_nodes, int32_t* prim_index,
+                     int32_t max_prims, int32_t* n_prim_refs);
+
+/* Measured memory peaks used by bench.py for the L2 roofline (resident-working-set read). */
+int rt_measure_l2_bandwidth(int64_t bytes, int32_t iters, float* gbps);
+
+const char* rt_last_error_string(void);
+const char* rt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

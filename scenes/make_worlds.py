@@ -1,0 +1,53 @@
+#!/usr/bin/env python3
+"""Writes the benchmark/parity scene files scenes/*.json in the reference's world*.json schema
+(keys: /root/reference/src/procedural/cube_world.cc:44-61,64,71-107,117-138,142-143,178-190).
+
+The parameter sets below describe the same worlds as the reference's shipped world1/2/4/8/16,
+world8_stress and config files (grid size, materials, lights, camera); tests/test_loader.py checks
+that the loader output for each is bit-identical to the reference loader's output for its own
+file (tests/golden/scene_dumps.json). Larger `grid*` worlds are stress scenes with no reference
+counterpart."""
+import json
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+DIRT = {"Ka": [100, 100, 100, 255], "Kd": [210, 105, 0, 30]}
+GRASS = {"Ka": [0, 255, 0, 255], "Kd": [124, 252, 0, 255]}
+LIGHTS = {"point": [{"pos": [0.0, 10.0, 0.0], "col": [255, 255, 255, 255]}],
+          "directional": [{"dir": [0.0, -1.0, 1.0], "col": [128, 128, 128, 255]}]}
+
+
+def world(grid, cubes, unit_length=200, depth=2, **extra):
+    w = {"seed": 42, "grid_size": grid, "amplitude": 4.0, "width": 640, "height": 480, "fov": 45,
+         "unit_length": unit_length, "depth": depth, "ambience": [0.5, 0.5, 0.5, 1],
+         "distance_attenuation": {"constant_term": 0.1, "linear_term": 0.4, "quadratic_term": 0.8},
+         "atlas": "assets/sus.png", "cubes": cubes, "lights": LIGHTS}
+    w.update(extra)
+    return w
+
+
+GLASS = dict(GRASS, Kt=[0.6, 0.6, 0.6, 1.0], eta=0.8)
+STRESS_GRASS = {"Ka": [60, 120, 0, 255], "Kd": [124, 252, 0, 255]}
+MIRROR = {"Ka": [120, 120, 120, 255], "Kr": [0.8, 0.8, 0.8, 1], "Ks": [255, 255, 255, 255], "alpha": 0.7}
+
+WORLDS = {
+    "world1": world(1, [DIRT, GLASS]),
+    "world2": world(2, [DIRT, GRASS]),
+    "world4": world(4, [DIRT, GRASS]),
+    "world8": world(8, [DIRT, GRASS]),
+    "world16": world(16, [DIRT, GRASS]),
+    "world8_stress": world(8, [DIRT, STRESS_GRASS, MIRROR], unit_length=1000),
+    "config": world(16, [dict(DIRT, Kd=[210, 105, 0, 255], alpha=0.8), GRASS]),
+    # stress content beyond the reference's shipped files (same schema)
+    "grid64": world(64, [DIRT, GRASS]),
+    "grid64_mixed": world(64, [DIRT, STRESS_GRASS, MIRROR, GLASS], depth=9),
+    "grid128": world(128, [DIRT, GRASS]),
+}
+
+if __name__ == "__main__":
+    for name, w in WORLDS.items():
+        with open(os.path.join(HERE, name + ".json"), "w") as f:
+            json.dump(w, f, indent=1)
+            f.write("\n")
+        print("wrote", name)
