@@ -4,7 +4,7 @@
 #define ORACLE_SHIM_RAPIDJSON_DOCUMENT_H
 #include <memory>
 #include <istream>
-#include "mini_json.h"
+#include "../../../../gpu-ray-tracer_b200/host/mini_json.h"
 namespace rapidjson {
 typedef unsigned SizeType;
 class IStreamWrapper;
