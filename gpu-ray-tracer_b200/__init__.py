@@ -23,7 +23,7 @@ CUDA_LIB_PATH = os.path.join(_HERE, "librtb200.so")
 
 RT_SEMANTICS_GPU, RT_SEMANTICS_CPU = 0, 1
 RT_RENDER_REBUILD_BVH, RT_RENDER_NO_BVH, RT_RENDER_CANVAS_DEVICE = 1, 2, 4
-RT_RENDER_SORT_RAYS, RT_RENDER_TILED_OUTPUT = 8, 16
+RT_RENDER_SORT_RAYS, RT_RENDER_TILED_OUTPUT, RT_RENDER_STATS = 8, 16, 32
 
 
 class RtMaterial(C.Structure):
@@ -147,7 +147,7 @@ def cuda_lib():
         lib.rt_cast_rays.argtypes = [vp, i32, vp, vp, i32, vp, vp, vp]
         lib.rt_debug_cast.argtypes = [vp, i32, i32, i32, C.POINTER(RtHit)]
         lib.rt_bvh_download.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
-        lib.rt_bvh8_download.argtypes = [vp, vp, i32, i32p, vp, i32, i32p]
+        lib.rt_bvh8_download.argtypes = [vp, vp, i32, i32p, vp, vp, i32, i32p]
         lib.rt_measure_l2_bandwidth.argtypes = [C.c_int64, i32, f32p]
         lib.rt_last_error_string.restype = C.c_char_p
         lib.rt_version.restype = C.c_char_p
@@ -202,3 +202,131 @@ class World:
             self.close()
         except Exception:
             pass
+
+
+class Scene:
+    """A scene resident on one GPU. Mirrors the reference's per-frame entry points:
+    ``update_scene`` (rtracer::gpu::update_scene, src/raytracer.cu:102-120) and ``debug_cast``
+    (src/raytracer.cu:91-100), plus the full-control ``render`` and the parity hooks."""
+
+    def __init__(self, world, device=0):
+        lib = cuda_lib()
+        _check(lib.rt_init(device), "rt_init")
+        self.world = world
+        self.device = device
+        h = C.c_void_p()
+        _check(lib.rt_scene_create(C.byref(world.desc), C.byref(h)), "rt_scene_create")
+        self._h = h
+        self.width, self.height = world.width, world.height
+
+    # -- host writes the reference does on its managed Scene
+    def set_camera(self, cam):
+        _check(cuda_lib().rt_scene_set_camera(self._h, C.byref(cam)), "rt_scene_set_camera")
+
+    def set_env(self, env):
+        _check(cuda_lib().rt_scene_set_env(self._h, C.byref(env)), "rt_scene_set_env")
+
+    def set_instances(self, instances, n):
+        _check(cuda_lib().rt_scene_set_instances(self._h, instances, n), "rt_scene_set_instances")
+
+    def set_canvas_size(self, w, h):
+        _check(cuda_lib().rt_scene_set_canvas_size(self._h, w, h), "rt_scene_set_canvas_size")
+        self.width, self.height = w, h
+
+    # -- BVH
+    def build_bvh(self):
+        st = RtBuildStats()
+        _check(cuda_lib().rt_bvh_build(self._h, C.byref(st)), "rt_bvh_build")
+        return st.as_dict()
+
+    def free_bvh(self):
+        _check(cuda_lib().rt_bvh_free(self._h), "rt_bvh_free")
+
+    # -- frames
+    def update_scene(self, kernel_dim=16, optimize=True, out=None):
+        canvas = out if out is not None else np.empty((self.height, self.width), np.uint32)
+        _check(cuda_lib().rt_update_scene(self._h, kernel_dim, 1 if optimize else 0, canvas.ctypes.data), "rt_update_scene")
+        return canvas
+
+    def params(self, flags=0, semantics=RT_SEMANTICS_GPU, rank=0, world=1, tile_w=0, tile_h=0):
+        return RtRenderParams(flags, semantics, rank, world, tile_w, tile_h)
+
+    def render(self, flags=0, semantics=RT_SEMANTICS_GPU, rank=0, world=1, tile_w=0, tile_h=0, out=None, out_ptr=None):
+        """Returns (canvas, stats). out: a host uint32 array to fill; out_ptr: a raw pointer (host, or
+        device with RT_RENDER_CANVAS_DEVICE) — then canvas is None."""
+        p = self.params(flags, semantics, rank, world, tile_w, tile_h)
+        st = RtFrameStats()
+        canvas = None
+        if out_ptr is None:
+            if flags & RT_RENDER_TILED_OUTPUT:
+                canvas = out if out is not None else np.empty(self.tiled_slab_pixels(p), np.uint32)
+            else:
+                canvas = out if out is not None else np.empty((self.height, self.width), np.uint32)
+            out_ptr = canvas.ctypes.data
+        _check(cuda_lib().rt_render(self._h, C.byref(p), out_ptr, C.byref(st)), "rt_render")
+        return canvas, st.as_dict()
+
+    def tiled_slab_pixels(self, params):
+        n = C.c_int64()
+        _check(cuda_lib().rt_tiled_slab_pixels(self._h, C.byref(params), C.byref(n)), "rt_tiled_slab_pixels")
+        return n.value
+
+    def untile(self, params, gathered_dev_ptr, canvas_dev_ptr):
+        _check(cuda_lib().rt_untile(self._h, C.byref(params), gathered_dev_ptr, canvas_dev_ptr), "rt_untile")
+
+    # -- parity hooks
+    def trace_primary(self, use_bvh=1):
+        n = self.width * self.height
+        inst = np.empty(n, np.int32); tri = np.empty(n, np.int32); t = np.empty(n, np.float32)
+        _check(cuda_lib().rt_trace_primary(self._h, use_bvh, inst.ctypes.data, tri.ctypes.data, t.ctypes.data),
+               "rt_trace_primary")
+        return inst, tri, t
+
+    def cast_rays(self, origins, dirs, use_bvh=1):
+        o = np.ascontiguousarray(origins, np.float32); d = np.ascontiguousarray(dirs, np.float32)
+        n = o.shape[0]
+        inst = np.empty(n, np.int32); tri = np.empty(n, np.int32); t = np.empty(n, np.float32)
+        _check(cuda_lib().rt_cast_rays(self._h, use_bvh, o.ctypes.data, d.ctypes.data, n, inst.ctypes.data,
+                                       tri.ctypes.data, t.ctypes.data), "rt_cast_rays")
+        return inst, tri, t
+
+    def debug_cast(self, x, y, semantics=RT_SEMANTICS_GPU):
+        h = RtHit()
+        _check(cuda_lib().rt_debug_cast(self._h, x, y, semantics, C.byref(h)), "rt_debug_cast")
+        return h
+
+    def download_bvh(self):
+        lib = cuda_lib()
+        nn, npr = C.c_int32(), C.c_int32()
+        _check(lib.rt_bvh8_download(self._h, None, 0, C.byref(nn), None, None, 0, C.byref(npr)), "rt_bvh8_download")
+        n, n8 = npr.value, nn.value
+        out = dict(n_prims=n, n_nodes8=n8)
+        out["morton"] = np.zeros(n, np.uint64); out["perm"] = np.zeros(n, np.int32)
+        out["left"] = np.zeros(max(n - 1, 0), np.int32); out["right"] = np.zeros(max(n - 1, 0), np.int32)
+        out["parent"] = np.zeros(max(2 * n - 1, 0), np.int32)
+        out["node_boxes"] = np.zeros((max(2 * n - 1, 0), 6), np.float32); out["bounds"] = np.zeros(6, np.float32)
+        _check(lib.rt_bvh_download(self._h, out["morton"].ctypes.data, out["perm"].ctypes.data, out["left"].ctypes.data,
+                                   out["right"].ctypes.data, out["parent"].ctypes.data, out["node_boxes"].ctypes.data,
+                                   out["bounds"].ctypes.data), "rt_bvh_download")
+        out["nodes8"] = np.zeros((n8, 20), np.uint32); out["prims8"] = np.zeros((n, 12), np.float32)
+        out["prim_order8"] = np.zeros(n, np.int32)
+        _check(lib.rt_bvh8_download(self._h, out["nodes8"].ctypes.data, n8, C.byref(nn), out["prims8"].ctypes.data,
+                                    out["prim_order8"].ctypes.data, n, C.byref(npr)), "rt_bvh8_download")
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None):
+            cuda_lib().rt_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def measure_l2_bandwidth(nbytes=32 << 20, iters=50):
+    g = C.c_float()
+    _check(cuda_lib().rt_measure_l2_bandwidth(nbytes, iters, C.byref(g)), "rt_measure_l2_bandwidth")
+    return g.value

@@ -1,0 +1,764 @@
+// rt_bvh_build.cu — GPU LBVH build and collapse into the compressed BVH8.
+//
+// Replaces rtracer::gpu::create_bvh / create_boxes (src/raytracer.cu:54-89) and
+// ropt::gpu::BVH::BVH: gen_morton + gen_numbers + thrust::sort_by_key + reorder + the per-level
+// build_bvh_layer launches (src/rayopt/bvh.cu:11-91). Pipeline (all on one stream, no host
+// round trips, no allocation after the first frame):
+//
+//   k_flatten      world-space triangles + inflated AABBs + scene bounds      (create_boxes)
+//   k_morton       63-bit quantised Morton code of each centroid, iota        (gen_morton, gen_numbers)
+//   radix sort     8 x (k_radix_hist, k_radix_scan, k_radix_scatter), LSD, stable (thrust::sort_by_key)
+//   k_karras       binary radix tree topology, Karras 2012                    (build_bvh_layer)
+//   k_refit        bottom-up AABB union with arrival counters                 (merge_into)
+//   k_collapse     level-by-level BVH2 -> BVH8, quantisation, slot assignment, leaf-ordered triangles
+//
+// Every step is deterministic (stable sort, exact min/max, fixed float evaluation order with
+// -fmad=false), so the result is bit-identical to the sequential host build in oracle/lbvh_host.c
+// that tests/test_bvh_build.py compares it against.
+#include <cooperative_groups.h>
+
+#include "rt_bvh.cuh"
+#include "rt_internal.h"
+
+namespace cg = cooperative_groups;
+using namespace rtd;
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// ---------------------------------------------------------------- flatten
+__device__ __forceinline__ int float_flip(float f) {  // order-preserving float -> int
+    int i = __float_as_int(f);
+    return i >= 0 ? i : i ^ 0x7fffffff;
+}
+__device__ __forceinline__ float float_unflip(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+__global__ void k_bounds_init(int* bounds) {
+    if (threadIdx.x < 3) bounds[threadIdx.x] = 0x7fffffff;
+    else if (threadIdx.x < 6) bounds[threadIdx.x] = (int)0x80000000;
+}
+
+// One thread per world-space triangle p = prim_offset[inst] + k.
+__global__ void k_flatten(SceneView s, const int* __restrict__ prim_offset, int n_prims, float4* __restrict__ prim_world,
+                          float* __restrict__ prim_box, int* __restrict__ bounds) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (p < n_prims) {
+        int a = 0, b = s.n_insts;  // last instance with prim_offset[inst] <= p
+        while (b - a > 1) {
+            int m = (a + b) >> 1;
+            if (prim_offset[m] <= p) a = m; else b = m;
+        }
+        int inst = a;
+        const InstRec& I = s.insts[inst];
+        const MeshRec& M = s.meshes[I.mesh];
+        int tri = M.tri_begin + (p - prim_offset[inst]);
+        const TriRec T = s.tris[tri];
+        float3 w[3];
+        const int vid[3] = {T.v0, T.v1, T.v2};
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            float4 v = s.verts[vid[k]];
+            w[k] = rtx::point_from_local(I.pose, rtx::point_from_local(M.pose, rtx::mk3(v.x, v.y, v.z)));
+        }
+        float3 e1 = rtx::sub3(w[1], w[0]), e2 = rtx::sub3(w[2], w[0]);
+        float L = ((fabsf(e1.x) + fabsf(e1.y)) + fabsf(e1.z)) + ((fabsf(e2.x) + fabsf(e2.y)) + fabsf(e2.z));
+        prim_world[3 * (size_t)p + 0] = make_float4(w[0].x, w[0].y, w[0].z, __int_as_float(inst));
+        prim_world[3 * (size_t)p + 1] = make_float4(e1.x, e1.y, e1.z, __int_as_float(tri));
+        prim_world[3 * (size_t)p + 2] = make_float4(e2.x, e2.y, e2.z, L);
+        lo[0] = fminf(fminf(w[0].x, w[1].x), w[2].x); hi[0] = fmaxf(fmaxf(w[0].x, w[1].x), w[2].x);
+        lo[1] = fminf(fminf(w[0].y, w[1].y), w[2].y); hi[1] = fmaxf(fmaxf(w[0].y, w[1].y), w[2].y);
+        lo[2] = fminf(fminf(w[0].z, w[1].z), w[2].z); hi[2] = fmaxf(fmaxf(w[0].z, w[1].z), w[2].z);
+        // stored box = tight box inflated by the acceptance margin of tri_filter plus coordinate rounding
+        float amax = fmaxf(fmaxf(fmaxf(fabsf(lo[0]), fabsf(hi[0])), fmaxf(fabsf(lo[1]), fabsf(hi[1]))),
+                           fmaxf(fabsf(lo[2]), fabsf(hi[2])));
+        float m = (2e-4f + 4e-5f * L) + 1e-6f * amax;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            prim_box[6 * (size_t)p + k] = lo[k] - m;
+            prim_box[6 * (size_t)p + 3 + k] = hi[k] + m;
+        }
+    }
+    // block reduce of the TIGHT bounds, then one atomic per block and component
+    __shared__ int s_lo[3][kThreads / 32], s_hi[3][kThreads / 32];
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        int l = float_flip(lo[k]), h = float_flip(hi[k]);
+        for (int o = 16; o; o >>= 1) {
+            l = min(l, __shfl_xor_sync(0xffffffffu, l, o));
+            h = max(h, __shfl_xor_sync(0xffffffffu, h, o));
+        }
+        if (lane == 0) { s_lo[k][warp] = l; s_hi[k][warp] = h; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        int k = threadIdx.x % 3;
+        bool is_hi = threadIdx.x >= 3;
+        int v = is_hi ? s_hi[k][0] : s_lo[k][0];
+        for (int w2 = 1; w2 < kThreads / 32; w2++) v = is_hi ? max(v, s_hi[k][w2]) : min(v, s_lo[k][w2]);
+        if (is_hi) atomicMax(&bounds[3 + k], v); else atomicMin(&bounds[k], v);
+    }
+}
+
+// ---------------------------------------------------------------- Morton codes
+__device__ __forceinline__ unsigned long long expand21(unsigned long long v) {
+    v &= 0x1fffffull;
+    v = (v | v << 32) & 0x001f00000000ffffull;
+    v = (v | v << 16) & 0x001f0000ff0000ffull;
+    v = (v | v << 8) & 0x100f00f00f00f00full;
+    v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+}
+
+__global__ void k_morton(const float* __restrict__ prim_box, const float4* __restrict__ prim_world, int n_prims,
+                         const int* __restrict__ bounds, unsigned long long* __restrict__ keys, int* __restrict__ vals,
+                         float* __restrict__ bounds_f) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    float blo[3], bhi[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) { blo[k] = float_unflip(bounds[k]); bhi[k] = float_unflip(bounds[3 + k]); }
+    if (p == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) { bounds_f[k] = blo[k]; bounds_f[3 + k] = bhi[k]; }
+    }
+    if (p >= n_prims) return;
+    // centroid of the tight box, recomputed from the triangle so it does not depend on the margin
+    float4 p0 = prim_world[3 * (size_t)p], p1 = prim_world[3 * (size_t)p + 1], p2 = prim_world[3 * (size_t)p + 2];
+    float v0[3] = {p0.x, p0.y, p0.z}, e1[3] = {p1.x, p1.y, p1.z}, e2[3] = {p2.x, p2.y, p2.z};
+    unsigned long long q[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        float a = v0[k], b = v0[k] + e1[k], c = v0[k] + e2[k];
+        float lo = fminf(fminf(a, b), c), hi = fmaxf(fmaxf(a, b), c);
+        float cen = (lo + hi) * 0.5f;
+        float ext = bhi[k] - blo[k];
+        float n = ext > 0.0f ? (cen - blo[k]) / ext : 0.0f;
+        float sc = n * 2097152.0f;
+        sc = fminf(fmaxf(sc, 0.0f), 2097151.0f);
+        q[k] = (unsigned long long)(unsigned)sc;
+    }
+    keys[p] = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
+    vals[p] = p;
+    (void)prim_box;
+}
+
+// ---------------------------------------------------------------- LSD radix sort (8 bits/pass, stable)
+constexpr int kRadixTile = 2048;  // keys per block: 256 threads, 8 warps x 256 consecutive keys
+constexpr int kBins = 256;
+
+__global__ void k_radix_hist(const unsigned long long* __restrict__ keys, int n, int shift, unsigned* __restrict__ hist,
+                             int n_blocks) {
+    __shared__ unsigned sh[kBins];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    int base = blockIdx.x * kRadixTile;
+    for (int i = threadIdx.x; i < kRadixTile; i += kThreads) {
+        int idx = base + i;
+        if (idx < n) atomicAdd(&sh[(unsigned)(keys[idx] >> shift) & 0xffu], 1u);
+    }
+    __syncthreads();
+    hist[(size_t)threadIdx.x * n_blocks + blockIdx.x] = sh[threadIdx.x];  // bin-major for the scan
+}
+
+// Exclusive scan over kBins * n_blocks counters (bin-major), one block.
+__global__ void k_radix_scan(unsigned* __restrict__ hist, int total) {
+    __shared__ unsigned warp_sum[kThreads / 32];
+    __shared__ unsigned carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < total; base += kThreads) {
+        int idx = base + threadIdx.x;
+        unsigned v = idx < total ? hist[idx] : 0u;
+        unsigned x = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_sum[warp] = x;
+        __syncthreads();
+        unsigned woff = 0;
+        for (int w = 0; w < warp; w++) woff += warp_sum[w];
+        unsigned c = carry;
+        if (idx < total) hist[idx] = c + woff + x - v;
+        __syncthreads();
+        if (threadIdx.x == kThreads - 1) carry = c + woff + x;
+        __syncthreads();
+    }
+}
+
+__global__ void k_radix_scatter(const unsigned long long* __restrict__ keys_in, const int* __restrict__ vals_in, int n,
+                                int shift, const unsigned* __restrict__ hist, int n_blocks,
+                                unsigned long long* __restrict__ keys_out, int* __restrict__ vals_out) {
+    __shared__ unsigned wcount[kThreads / 32][kBins];  // per-warp digit counts, then running offsets
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (kThreads / 32) * kBins; i += kThreads) (&wcount[0][0])[i] = 0;
+    __syncthreads();
+    int wbase = blockIdx.x * kRadixTile + warp * (kRadixTile / (kThreads / 32));
+    constexpr int kIters = kRadixTile / (kThreads / 32) / 32;
+    unsigned long long k[kIters];
+    int v[kIters];
+#pragma unroll
+    for (int it = 0; it < kIters; it++) {
+        int idx = wbase + it * 32 + lane;
+        bool ok = idx < n;
+        k[it] = ok ? keys_in[idx] : ~0ull;
+        v[it] = ok ? vals_in[idx] : 0;
+        unsigned d = (unsigned)(k[it] >> shift) & 0xffu;
+        unsigned act = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+            unsigned peers = __match_any_sync(act, d);
+            if (lane == (31 - __clz((int)peers))) wcount[warp][d] += (unsigned)__popc(peers);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // thread d: turn counts into block-local exclusive offsets across warps, plus the global base
+        unsigned d = threadIdx.x;
+        unsigned run = hist[(size_t)d * n_blocks + blockIdx.x];
+        for (int w = 0; w < kThreads / 32; w++) {
+            unsigned c = wcount[w][d];
+            wcount[w][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < kIters; it++) {
+        int idx = wbase + it * 32 + lane;
+        bool ok = idx < n;
+        unsigned d = (unsigned)(k[it] >> shift) & 0xffu;
+        unsigned act = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+            unsigned peers = __match_any_sync(act, d);
+            unsigned rank = (unsigned)__popc(peers & ((1u << lane) - 1u));
+            unsigned pos = wcount[warp][d] + rank;
+            keys_out[pos] = k[it];
+            vals_out[pos] = v[it];
+            __syncwarp(act);
+            if (lane == (31 - __clz((int)peers))) wcount[warp][d] += (unsigned)__popc(peers);
+        }
+        __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------- Karras 2012 hierarchy
+// Node ids: internal 0..n-2 (root 0), leaf of sorted position j = n-1+j.
+__device__ __forceinline__ int delta(const unsigned long long* __restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    unsigned long long a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz(i ^ j);
+    return __clzll((long long)(a ^ b));
+}
+
+__global__ void k_karras(const unsigned long long* __restrict__ keys, int n, int* __restrict__ left, int* __restrict__ right,
+                         int* __restrict__ parent, int* __restrict__ range_lo, int* __restrict__ range_hi) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) > 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int lo = min(i, j), hi = max(i, j);
+    int lc = (lo == gamma) ? (n - 1 + gamma) : gamma;
+    int rc = (hi == gamma + 1) ? (n - 1 + gamma + 1) : (gamma + 1);
+    left[i] = lc;
+    right[i] = rc;
+    parent[lc] = i;
+    parent[rc] = i;
+    range_lo[i] = lo;
+    range_hi[i] = hi;
+    if (i == 0) parent[0] = -1;
+}
+
+// One thread per leaf climbs; the second arrival at a node unions its children.
+__global__ void k_refit(const int* __restrict__ sorted_prim, const float* __restrict__ prim_box, int n,
+                        const int* __restrict__ left, const int* __restrict__ right, const int* __restrict__ parent,
+                        unsigned* __restrict__ arrive, float* __restrict__ node_box) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    int p = sorted_prim[j];
+    int node = n - 1 + j;
+#pragma unroll
+    for (int k = 0; k < 6; k++) node_box[6 * (size_t)node + k] = prim_box[6 * (size_t)p + k];
+    if (n == 1) return;
+    __threadfence();
+    int cur = parent[node];
+    while (cur >= 0) {
+        if (atomicAdd(&arrive[cur], 1u) == 0u) return;
+        __threadfence();
+        int l = left[cur], r = right[cur];
+        volatile const float* bl = node_box + 6 * (size_t)l;
+        volatile const float* br = node_box + 6 * (size_t)r;
+        float o[6];
+#pragma unroll
+        for (int k = 0; k < 3; k++) { o[k] = fminf(bl[k], br[k]); o[3 + k] = fmaxf(bl[3 + k], br[3 + k]); }
+#pragma unroll
+        for (int k = 0; k < 6; k++) node_box[6 * (size_t)cur + k] = o[k];
+        __threadfence();
+        cur = parent[cur];
+    }
+}
+
+// ---------------------------------------------------------------- BVH2 -> BVH8 collapse
+struct CollapseArgs {
+    int n;                 // primitives
+    const int* left; const int* right; const int* range_lo; const int* range_hi;
+    const float* node_box; // 6 floats per BVH2 node
+    const int* sorted_prim;
+    const float4* prim_world;
+    uint4* nodes8;         // out
+    float4* prims8;        // out
+    int* prim_order8;      // out: sorted position of each BVH8 triangle slot
+    int* level_a; int* level_b;  // BVH2 ids of the nodes of the current / next level
+    int* slots;            // 8 ints per node of the current level: BVH2 child id per slot or -1
+    int* counts;           // 2 ints per node of the current level: inner children, leaf triangles
+    int* block_tot;        // [2 parities][gridDim.x][2]
+    int* result;           // [0] = n_nodes8, [1] = n_prims emitted, [2] = levels, [3] = max level width
+};
+
+__device__ __forceinline__ int node_size(const CollapseArgs& a, int id) {
+    return id >= a.n - 1 ? 1 : a.range_hi[id] - a.range_lo[id] + 1;
+}
+__device__ __forceinline__ int node_first(const CollapseArgs& a, int id) { return id >= a.n - 1 ? id - (a.n - 1) : a.range_lo[id]; }
+__device__ __forceinline__ float half_area(const float* b) {
+    float dx = b[3] - b[0], dy = b[4] - b[1], dz = b[5] - b[2];
+    return (dx * dy + dy * dz) + dz * dx;
+}
+
+// Children of one BVH8 node and their slots. Rule: start from the two BVH2 children; while fewer
+// than 8, replace the child of largest half-area among those covering more than 3 triangles by
+// its own two children (left in place, right appended); ties go to the earlier child. Slots:
+// greedy assignment maximising (child centroid - node centroid) . octant direction of the slot.
+__device__ void collapse_children(const CollapseArgs& a, int root, int slot_child[8], int& n_inner, int& n_leaf_prims) {
+    int ch[8];
+    int nc = 0;
+    if (root >= a.n - 1 || node_size(a, root) <= 3) {
+        ch[nc++] = root;  // degenerate tree: the whole scene is one leaf
+    } else {
+        ch[nc++] = a.left[root];
+        ch[nc++] = a.right[root];
+        while (nc < 8) {
+            int best = -1;
+            float best_area = -1.0f;
+            for (int i = 0; i < nc; i++) {
+                if (node_size(a, ch[i]) <= 3) continue;
+                float ar = half_area(a.node_box + 6 * (size_t)ch[i]);
+                if (ar > best_area) { best_area = ar; best = i; }
+            }
+            if (best < 0) break;
+            int c = ch[best];
+            ch[best] = a.left[c];
+            ch[nc++] = a.right[c];
+        }
+    }
+    const float* nb = a.node_box + 6 * (size_t)root;
+    float ncx = (nb[0] + nb[3]) * 0.5f, ncy = (nb[1] + nb[4]) * 0.5f, ncz = (nb[2] + nb[5]) * 0.5f;
+    float cost[8][8];
+    for (int i = 0; i < nc; i++) {
+        const float* cb = a.node_box + 6 * (size_t)ch[i];
+        float dx = (cb[0] + cb[3]) * 0.5f - ncx, dy = (cb[1] + cb[4]) * 0.5f - ncy, dz = (cb[2] + cb[5]) * 0.5f - ncz;
+        for (int s = 0; s < 8; s++)
+            cost[i][s] = (((s & 1) ? dx : -dx) + ((s & 2) ? dy : -dy)) + ((s & 4) ? dz : -dz);
+    }
+    for (int s = 0; s < 8; s++) slot_child[s] = -1;
+    unsigned child_done = 0, slot_done = 0;
+    for (int it = 0; it < nc; it++) {
+        int bi = -1, bs = -1;
+        float bc = -INFINITY;
+        for (int i = 0; i < nc; i++) {
+            if (child_done & (1u << i)) continue;
+            for (int s = 0; s < 8; s++) {
+                if (slot_done & (1u << s)) continue;
+                if (bi < 0 || cost[i][s] > bc) { bc = cost[i][s]; bi = i; bs = s; }
+            }
+        }
+        child_done |= 1u << bi;
+        slot_done |= 1u << bs;
+        slot_child[bs] = ch[bi];
+    }
+    n_inner = 0;
+    n_leaf_prims = 0;
+    for (int s = 0; s < 8; s++) {
+        if (slot_child[s] < 0) continue;
+        int sz = node_size(a, slot_child[s]);
+        if (sz > 3) n_inner++; else n_leaf_prims += sz;
+    }
+}
+
+__device__ void write_node8(const CollapseArgs& a, int root, int node_idx, const int slot_child[8], int child_base,
+                            int prim_base, int* next_list) {
+    const float* nb = a.node_box + 6 * (size_t)root;
+    float org[3] = {nb[0], nb[1], nb[2]};
+    unsigned eb[3];
+    float scale[3], inv_scale[3];
+    for (int k = 0; k < 3; k++) {
+        float ext = nb[3 + k] - nb[k];
+        float f = ext / 255.0f;
+        unsigned bits = __float_as_uint(f);
+        unsigned e = (bits >> 23) & 0xffu;
+        if (bits & 0x7fffffu) e += 1u;
+        if (e < 1u) e = 1u;
+        if (e > 253u) e = 253u;
+        float sc = __uint_as_float(e << 23);
+        if (org[k] + 255.0f * sc < nb[3 + k] && e < 253u) { e += 1u; sc = __uint_as_float(e << 23); }
+        eb[k] = e;
+        scale[k] = sc;
+        inv_scale[k] = __uint_as_float((254u - e) << 23);
+    }
+    unsigned imask = 0;
+    unsigned meta[8], qlo[3][8], qhi[3][8];
+    int inner_rank = 0, prim_off = 0;
+    for (int s = 0; s < 8; s++) {
+        meta[s] = 0;
+        for (int k = 0; k < 3; k++) { qlo[k][s] = 0; qhi[k][s] = 0; }
+        int c = slot_child[s];
+        if (c < 0) continue;
+        const float* cb = a.node_box + 6 * (size_t)c;
+        for (int k = 0; k < 3; k++) {
+            float ql = floorf((cb[k] - org[k]) * inv_scale[k]);
+            ql = fminf(fmaxf(ql, 0.0f), 255.0f);
+            while (ql > 0.0f && org[k] + ql * scale[k] > cb[k]) ql -= 1.0f;
+            float qh = ceilf((cb[3 + k] - org[k]) * inv_scale[k]);
+            qh = fminf(fmaxf(qh, 0.0f), 255.0f);
+            while (qh < 255.0f && org[k] + qh * scale[k] < cb[3 + k]) qh += 1.0f;
+            qlo[k][s] = (unsigned)ql;
+            qhi[k][s] = (unsigned)qh;
+        }
+        int sz = node_size(a, c);
+        if (sz > 3) {
+            imask |= 1u << s;
+            meta[s] = 0x20u | (24u + (unsigned)s);
+            next_list[inner_rank] = c;
+            inner_rank++;
+        } else {
+            unsigned unary = sz == 1 ? 1u : (sz == 2 ? 3u : 7u);
+            meta[s] = (unary << 5) | (unsigned)prim_off;
+            int first = node_first(a, c);
+            for (int j = 0; j < sz; j++) {
+                int dst = prim_base + prim_off + j;
+                int p = a.sorted_prim[first + j];
+                a.prim_order8[dst] = first + j;
+                a.prims8[3 * (size_t)dst + 0] = a.prim_world[3 * (size_t)p + 0];
+                a.prims8[3 * (size_t)dst + 1] = a.prim_world[3 * (size_t)p + 1];
+                a.prims8[3 * (size_t)dst + 2] = a.prim_world[3 * (size_t)p + 2];
+            }
+            prim_off += sz;
+        }
+    }
+    auto pack4 = [](const unsigned* b) { return b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24); };
+    uint4 q0, q1, q2, q3, q4;
+    q0.x = __float_as_uint(org[0]); q0.y = __float_as_uint(org[1]); q0.z = __float_as_uint(org[2]);
+    q0.w = eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24);
+    q1.x = (unsigned)child_base; q1.y = (unsigned)prim_base; q1.z = pack4(meta); q1.w = pack4(meta + 4);
+    q2.x = pack4(qlo[0]); q2.y = pack4(qlo[0] + 4); q2.z = pack4(qlo[1]); q2.w = pack4(qlo[1] + 4);
+    q3.x = pack4(qlo[2]); q3.y = pack4(qlo[2] + 4); q3.z = pack4(qhi[0]); q3.w = pack4(qhi[0] + 4);
+    q4.x = pack4(qhi[1]); q4.y = pack4(qhi[1] + 4); q4.z = pack4(qhi[2]); q4.w = pack4(qhi[2] + 4);
+    uint4* out = a.nodes8 + 5 * (size_t)node_idx;
+    out[0] = q0; out[1] = q1; out[2] = q2; out[3] = q3; out[4] = q4;
+}
+
+// Cooperative kernel: all levels in one launch, two grid barriers per level. Blocks own
+// contiguous chunks of the level so that the per-level exclusive scan (which fixes child_base
+// and prim_base, i.e. the memory order of the whole tree) follows node order deterministically.
+__global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ int s_warp[2][kThreads / 32];
+    __shared__ int s_carry[2];
+    __shared__ int s_base[2];
+    const int G = gridDim.x, B = blockDim.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int level_n = 1, level_base = 0, prim_total = 0, levels = 0, max_width = 1;
+    if (blockIdx.x == 0 && threadIdx.x == 0) a.level_a[0] = 0;
+    grid.sync();
+    while (level_n > 0) {
+        int parity = levels & 1;
+        int* cur = parity ? a.level_b : a.level_a;
+        int* next = parity ? a.level_a : a.level_b;
+        int* btot = a.block_tot + (size_t)parity * G * 2;
+        int per_block = (level_n + G - 1) / G;
+        int c0 = min(level_n, blockIdx.x * per_block), c1 = min(level_n, c0 + per_block);
+        // phase A: children + counts
+        int my_inner = 0, my_prims = 0;
+        for (int t = c0 + threadIdx.x; t < c1; t += B) {
+            int sc[8], ni, np;
+            collapse_children(a, cur[t], sc, ni, np);
+            for (int s = 0; s < 8; s++) a.slots[8 * (size_t)t + s] = sc[s];
+            a.counts[2 * (size_t)t] = ni;
+            a.counts[2 * (size_t)t + 1] = np;
+            my_inner += ni;
+            my_prims += np;
+        }
+        for (int o = 16; o; o >>= 1) {
+            my_inner += __shfl_xor_sync(0xffffffffu, my_inner, o);
+            my_prims += __shfl_xor_sync(0xffffffffu, my_prims, o);
+        }
+        if (lane == 0) { s_warp[0][warp] = my_inner; s_warp[1][warp] = my_prims; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int ti = 0, tp = 0;
+            for (int w = 0; w < B / 32; w++) { ti += s_warp[0][w]; tp += s_warp[1][w]; }
+            btot[2 * blockIdx.x] = ti;
+            btot[2 * blockIdx.x + 1] = tp;
+        }
+        grid.sync();
+        // phase B: block offsets (every block sums the totals of the blocks before it), ordered scan, emit
+        int pre_i = 0, pre_p = 0, tot_i = 0, tot_p = 0;
+        for (int b = threadIdx.x; b < G; b += B) {
+            int vi = btot[2 * b], vp = btot[2 * b + 1];
+            tot_i += vi; tot_p += vp;
+            if (b < (int)blockIdx.x) { pre_i += vi; pre_p += vp; }
+        }
+        for (int o = 16; o; o >>= 1) {
+            pre_i += __shfl_xor_sync(0xffffffffu, pre_i, o);
+            pre_p += __shfl_xor_sync(0xffffffffu, pre_p, o);
+            tot_i += __shfl_xor_sync(0xffffffffu, tot_i, o);
+            tot_p += __shfl_xor_sync(0xffffffffu, tot_p, o);
+        }
+        __syncthreads();
+        if (lane == 0) { s_warp[0][warp] = pre_i; s_warp[1][warp] = pre_p; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int pi = 0, pp = 0;
+            for (int w = 0; w < B / 32; w++) { pi += s_warp[0][w]; pp += s_warp[1][w]; }
+            s_carry[0] = pi; s_carry[1] = pp;
+        }
+        __syncthreads();
+        if (lane == 0) { s_warp[0][warp] = tot_i; s_warp[1][warp] = tot_p; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int ti = 0, tp = 0;
+            for (int w = 0; w < B / 32; w++) { ti += s_warp[0][w]; tp += s_warp[1][w]; }
+            s_base[0] = ti; s_base[1] = tp;
+        }
+        __syncthreads();
+        const int level_inner = s_base[0], level_prims = s_base[1];
+        const int next_base = level_base + level_n;
+        for (int t0 = c0; t0 < c1; t0 += B) {
+            int t = t0 + threadIdx.x;
+            int ni = 0, np = 0;
+            if (t < c1) { ni = a.counts[2 * (size_t)t]; np = a.counts[2 * (size_t)t + 1]; }
+            int xi = ni, xp = np;
+            for (int o = 1; o < 32; o <<= 1) {
+                int yi = __shfl_up_sync(0xffffffffu, xi, o), yp = __shfl_up_sync(0xffffffffu, xp, o);
+                if (lane >= o) { xi += yi; xp += yp; }
+            }
+            __syncthreads();
+            if (lane == 31) { s_warp[0][warp] = xi; s_warp[1][warp] = xp; }
+            __syncthreads();
+            int wi = 0, wp = 0;
+            for (int w = 0; w < warp; w++) { wi += s_warp[0][w]; wp += s_warp[1][w]; }
+            int ci = s_carry[0], cp = s_carry[1];
+            if (t < c1) {
+                int sc[8];
+                for (int s = 0; s < 8; s++) sc[s] = a.slots[8 * (size_t)t + s];
+                // child_base indexes nodes8 (absolute); the next-level list is relative to next_base
+                int rel_child = ci + wi + xi - ni;
+                write_node8(a, cur[t], level_base + t, sc, next_base + rel_child, prim_total + cp + wp + xp - np,
+                            next + rel_child);
+            }
+            __syncthreads();
+            if (threadIdx.x == B - 1) { s_carry[0] = ci + wi + xi; s_carry[1] = cp + wp + xp; }
+            __syncthreads();
+        }
+        level_base = next_base;
+        prim_total += level_prims;
+        level_n = level_inner;
+        levels++;
+        if (level_n > max_width) max_width = level_n;
+        grid.sync();
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        a.result[0] = level_base;
+        a.result[1] = prim_total;
+        a.result[2] = levels;
+        a.result[3] = max_width;
+    }
+}
+
+}  // namespace
+
+namespace rth {
+
+static inline int grid_for(int n, int per = kThreads) { return n > 0 ? (n + per - 1) / per : 1; }
+
+int build_bvh(RtScene* sc, RtBuildStats* stats) {
+    Bvh& b = sc->bvh;
+    b.valid = false;
+    cudaStream_t st = sc->stream;
+    int launches0 = sc->kernel_launches;
+    // prefix of triangle counts per instance (host; instances change only through rt_scene_set_instances)
+    std::vector<int> off((size_t)sc->n_instances + 1);
+    long long total = 0;
+    for (int i = 0; i < sc->n_instances; i++) {
+        off[i] = (int)total;
+        total += sc->mesh_tri_count[sc->instances[i].mesh];
+        if (total > 0x3fffffffLL) { set_error("too many world-space triangles"); return RT_ERR_LIMIT; }
+    }
+    off[sc->n_instances] = (int)total;
+    int n = (int)total;
+    b.n_prims = n;
+    b.n_bvh2_nodes = n > 0 ? 2 * n - 1 : 0;
+    b.n_nodes8 = 0;
+    if (stats) { stats->n_prims = n; stats->n_bvh2_nodes = b.n_bvh2_nodes; stats->n_bvh8_nodes = 0; stats->kernel_launches = 0; stats->ms_build = 0.f; }
+    RT_CUDA(cudaEventRecord(sc->ev[0], st));
+    if (int rc = update_instance_boxes(sc)) return rc;
+    if (n == 0) {
+        b.valid = true;
+        RT_CUDA(cudaEventRecord(sc->ev[1], st));
+        RT_CUDA(cudaStreamSynchronize(st));
+        return RT_OK;
+    }
+    int nb = (n + kRadixTile - 1) / kRadixTile;
+    int max_nodes8 = n;  // every BVH8 node owns >= 1 BVH2 internal node with > 3 triangles (or is the root)
+    if (b.work.reserve(sizeof(int) * ((size_t)sc->n_instances + 1)) || b.prim_world.reserve(sizeof(float4) * 3 * (size_t)n) ||
+        b.prim_box.reserve(sizeof(float) * 6 * (size_t)n) || b.scene_bounds.reserve(64) ||
+        b.keys_a.reserve(8 * (size_t)n) || b.keys_b.reserve(8 * (size_t)n) || b.vals_a.reserve(4 * (size_t)n) ||
+        b.vals_b.reserve(4 * (size_t)n) || b.hist.reserve(sizeof(unsigned) * kBins * (size_t)nb) ||
+        b.left.reserve(4 * (size_t)n) || b.right.reserve(4 * (size_t)n) || b.parent.reserve(4 * 2 * (size_t)n) ||
+        b.range_lo.reserve(4 * (size_t)n) || b.range_hi.reserve(4 * (size_t)n) || b.flags.reserve(4 * (size_t)n) ||
+        b.node_box.reserve(sizeof(float) * 6 * 2 * (size_t)n) || b.nodes8.reserve(sizeof(uint4) * 5 * (size_t)max_nodes8) ||
+        b.prims8.reserve(sizeof(float4) * 3 * (size_t)n) || b.prim_order8.reserve(4 * (size_t)n))
+        return RT_ERR_OUT_OF_MEMORY;
+    RT_CUDA(cudaMemcpyAsync(b.work.p, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice, st));
+    SceneView v = make_view(sc, false);
+    int* bounds_i = b.scene_bounds.as<int>();
+    float* bounds_f = (float*)(bounds_i + 8);
+    k_bounds_init<<<1, 32, 0, st>>>(bounds_i);
+    k_flatten<<<grid_for(n), kThreads, 0, st>>>(v, b.work.as<int>(), n, b.prim_world.as<float4>(), b.prim_box.as<float>(), bounds_i);
+    k_morton<<<grid_for(n), kThreads, 0, st>>>(b.prim_box.as<float>(), b.prim_world.as<float4>(), n, bounds_i,
+                                               b.keys_a.as<unsigned long long>(), b.vals_a.as<int>(), bounds_f);
+    sc->kernel_launches += 3;
+    unsigned long long* kin = b.keys_a.as<unsigned long long>();
+    unsigned long long* kout = b.keys_b.as<unsigned long long>();
+    int* vin = b.vals_a.as<int>();
+    int* vout = b.vals_b.as<int>();
+    for (int pass = 0; pass < 8; pass++) {
+        int shift = pass * 8;
+        k_radix_hist<<<nb, kThreads, 0, st>>>(kin, n, shift, b.hist.as<unsigned>(), nb);
+        k_radix_scan<<<1, kThreads, 0, st>>>(b.hist.as<unsigned>(), kBins * nb);
+        k_radix_scatter<<<nb, kThreads, 0, st>>>(kin, vin, n, shift, b.hist.as<unsigned>(), nb, kout, vout);
+        sc->kernel_launches += 3;
+        std::swap(kin, kout);
+        std::swap(vin, vout);
+    }
+    b.sorted_keys = kin;  // 8 passes: back in keys_a / vals_a
+    b.sorted_vals = vin;
+    if (n > 1) {
+        k_karras<<<grid_for(n - 1), kThreads, 0, st>>>(kin, n, b.left.as<int>(), b.right.as<int>(), b.parent.as<int>(),
+                                                       b.range_lo.as<int>(), b.range_hi.as<int>());
+        sc->kernel_launches++;
+    }
+    RT_CUDA(cudaMemsetAsync(b.flags.p, 0, 4 * (size_t)n, st));
+    k_refit<<<grid_for(n), kThreads, 0, st>>>(vin, b.prim_box.as<float>(), n, b.left.as<int>(), b.right.as<int>(),
+                                              b.parent.as<int>(), b.flags.as<unsigned>(), b.node_box.as<float>());
+    sc->kernel_launches++;
+    // collapse
+    int blocks_per_sm = 0;
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_collapse, kThreads, 0));
+    if (blocks_per_sm < 1) { set_error("k_collapse cannot be made resident"); return RT_ERR_CUDA; }
+    int G = sc->sm_count * (blocks_per_sm > 2 ? 2 : blocks_per_sm);
+    int want = (n / 4 + kThreads - 1) / kThreads;
+    if (want < 1) want = 1;
+    if (G > want) G = want;
+    size_t level_cap = (size_t)n + 8;
+    size_t wbytes = sizeof(int) * (level_cap * 2 + level_cap * 8 + level_cap * 2 + (size_t)G * 4 + 16);
+    static_assert(sizeof(int) == 4, "int");
+    if (b.collapse_scratch.reserve(wbytes)) return RT_ERR_OUT_OF_MEMORY;
+    int* w = b.collapse_scratch.as<int>();
+    CollapseArgs a;
+    a.n = n;
+    a.left = b.left.as<int>(); a.right = b.right.as<int>(); a.range_lo = b.range_lo.as<int>(); a.range_hi = b.range_hi.as<int>();
+    a.node_box = b.node_box.as<float>();
+    a.sorted_prim = vin;
+    a.prim_world = b.prim_world.as<float4>();
+    a.nodes8 = b.nodes8.as<uint4>();
+    a.prims8 = b.prims8.as<float4>();
+    a.prim_order8 = b.prim_order8.as<int>();
+    a.level_a = w; w += level_cap;
+    a.level_b = w; w += level_cap;
+    a.slots = w; w += level_cap * 8;
+    a.counts = w; w += level_cap * 2;
+    a.block_tot = w; w += (size_t)G * 4;
+    a.result = w;
+    void* args[] = {&a};
+    RT_CUDA(cudaLaunchCooperativeKernel((void*)k_collapse, dim3(G), dim3(kThreads), args, 0, st));
+    sc->kernel_launches++;
+    int result[4];
+    RT_CUDA(cudaMemcpyAsync(result, a.result, sizeof(result), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaEventRecord(sc->ev[1], st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    RT_CUDA(cudaGetLastError());
+    b.n_nodes8 = result[0];
+    if (result[1] != n) { set_error("BVH8 collapse emitted a wrong number of triangles"); return RT_ERR_CUDA; }
+    if (result[2] > RT_STACK_SIZE) { set_error("BVH8 deeper than the traversal stack"); return RT_ERR_LIMIT; }
+    b.valid = true;
+    if (stats) {
+        stats->n_bvh8_nodes = b.n_nodes8;
+        stats->kernel_launches = sc->kernel_launches - launches0;
+        float ms = 0.f;
+        RT_CUDA(cudaEventElapsedTime(&ms, sc->ev[0], sc->ev[1]));
+        stats->ms_build = ms;
+    }
+    return RT_OK;
+}
+
+}  // namespace rth
+
+extern "C" {
+
+int rt_bvh_download(RtScene* sc, uint64_t* morton, int32_t* perm, int32_t* left, int32_t* right, int32_t* parent,
+                    float* boxes, float* scene_bounds6) {
+    if (!sc) { rth::set_error("null scene"); return RT_ERR_INVALID_ARG; }
+    rth::Bvh& b = sc->bvh;
+    if (!b.valid) { rth::set_error("no BVH built"); return RT_ERR_NO_BVH; }
+    size_t n = (size_t)b.n_prims;
+    if (n == 0) return RT_OK;
+    cudaStream_t st = sc->stream;
+    if (morton) RT_CUDA(cudaMemcpyAsync(morton, b.sorted_keys, 8 * n, cudaMemcpyDeviceToHost, st));
+    if (perm) RT_CUDA(cudaMemcpyAsync(perm, b.sorted_vals, 4 * n, cudaMemcpyDeviceToHost, st));
+    if (left && n > 1) RT_CUDA(cudaMemcpyAsync(left, b.left.p, 4 * (n - 1), cudaMemcpyDeviceToHost, st));
+    if (right && n > 1) RT_CUDA(cudaMemcpyAsync(right, b.right.p, 4 * (n - 1), cudaMemcpyDeviceToHost, st));
+    if (parent && n > 1) RT_CUDA(cudaMemcpyAsync(parent, b.parent.p, 4 * (2 * n - 1), cudaMemcpyDeviceToHost, st));
+    if (boxes) RT_CUDA(cudaMemcpyAsync(boxes, b.node_box.p, 24 * (2 * n - 1), cudaMemcpyDeviceToHost, st));
+    if (scene_bounds6) RT_CUDA(cudaMemcpyAsync(scene_bounds6, (const char*)b.scene_bounds.p + 32, 24, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
+int rt_bvh8_download(RtScene* sc, void* nodes80, int32_t max_nodes, int32_t* n_nodes, void* prims48, int32_t* prim_order,
+                     int32_t max_prims, int32_t* n_prims) {
+    if (!sc) { rth::set_error("null scene"); return RT_ERR_INVALID_ARG; }
+    rth::Bvh& b = sc->bvh;
+    if (!b.valid) { rth::set_error("no BVH built"); return RT_ERR_NO_BVH; }
+    if (n_nodes) *n_nodes = b.n_nodes8;
+    if (n_prims) *n_prims = b.n_prims;
+    cudaStream_t st = sc->stream;
+    if (nodes80) {
+        if (max_nodes < b.n_nodes8) { rth::set_error("node buffer too small"); return RT_ERR_INVALID_ARG; }
+        if (b.n_nodes8) RT_CUDA(cudaMemcpyAsync(nodes80, b.nodes8.p, 80 * (size_t)b.n_nodes8, cudaMemcpyDeviceToHost, st));
+    }
+    if (prims48 || prim_order) {
+        if (max_prims < b.n_prims) { rth::set_error("triangle buffer too small"); return RT_ERR_INVALID_ARG; }
+        if (prims48 && b.n_prims) RT_CUDA(cudaMemcpyAsync(prims48, b.prims8.p, 48 * (size_t)b.n_prims, cudaMemcpyDeviceToHost, st));
+        if (prim_order && b.n_prims) RT_CUDA(cudaMemcpyAsync(prim_order, b.prim_order8.p, 4 * (size_t)b.n_prims, cudaMemcpyDeviceToHost, st));
+    }
+    RT_CUDA(cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
+}  // extern "C"

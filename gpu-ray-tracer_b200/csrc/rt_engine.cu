@@ -1,0 +1,902 @@
+// rt_engine.cu — scene upload, frame driver and render kernels of librtb200.so.
+//
+// Replaces, behind the C ABI of include/rtb200.h:
+//   SceneBuilder::build_gpu_scene upload half     src/scene_builder.cu:83-179   -> rt_scene_create
+//   rtracer::gpu::update_scene / create_bvh       src/raytracer.cu:76-120       -> rt_update_scene / rt_render
+//   rtracer::gpu::trace (megakernel)              src/raytracer.cu:17-43        -> k_primary + k_shade + k_bounce
+//   rtracer::gpu::debug / debug_cast              src/raytracer.cu:45-52,91-100 -> rt_debug_cast
+//   gputils (managed memory, blocking copies)     include/gputils/alloc.h       -> DevBuf, one stream, async copies
+//
+// Frame = wavefront pipeline on one stream:
+//   k_primary  persistent warps pull 8x4-pixel tiles from a counter, generate camera rays
+//              (Camera::at), find the closest hit through the BVH8, write black for misses and
+//              append hits to a queue with one warp-aggregated atomic (ballot + popc + shuffle).
+//   k_shade    one thread per queued hit: normal, Phong, shadow rays through the same BVH8;
+//              pixels whose material spawns no secondary ray are finished here, the others get a
+//              path slot (RayFrame stack in HBM) and enter the bounce queue.
+//   k_bounce   one wave per launch: cast the top frame's ray of every live path, shade, run the
+//              reference's REFLECT/REFRACT state machine, compact survivors into the next queue.
+// There is no CPU fallback anywhere in this library.
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+#include "rt_bvh.cuh"
+#include "rt_hostprep.h"
+#include "rt_internal.h"
+#include "rt_shade.cuh"
+
+using namespace rtd;
+
+// ---------------------------------------------------------------- errors, buffers
+namespace rth {
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+    g_err = std::string(cudaGetErrorName(e)) + ": " + cudaGetErrorString(e) + " in " + what + " (" + file + ":" +
+            std::to_string(line) + ")";
+    if (e == cudaErrorMemoryAllocation) return RT_ERR_OUT_OF_MEMORY;
+    if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) return RT_ERR_NO_DEVICE;
+    return RT_ERR_CUDA;
+}
+int DevBuf::reserve(size_t bytes) {
+    if (bytes <= cap && p) return 0;
+    if (bytes == 0) bytes = 16;
+    release();
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) { p = nullptr; cap = 0; return cuda_fail(e, "cudaMalloc", __FILE__, __LINE__); }
+    cap = bytes;
+    return 0;
+}
+void DevBuf::release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+}
+void Bvh::release() {
+    DevBuf* all[] = {&prim_world, &prim_box, &scene_bounds, &keys_a, &keys_b, &vals_a, &vals_b, &hist, &left, &right,
+                     &parent, &range_lo, &range_hi, &flags, &node_box, &nodes8, &prims8, &prim_order8, &work,
+                     &collapse_scratch};
+    for (DevBuf* b : all) b->release();
+    valid = false;
+}
+}  // namespace rth
+using rth::set_error;
+
+namespace {
+
+constexpr int kThreads = 256;
+static int g_device = -1;
+static int g_sm_count = 148;
+
+// ---------------------------------------------------------------- screen tiling
+// Work unit = one 8x4-pixel warp tile. Screen tiles of tile_w x tile_h pixels are dealt round-robin
+// to `world` ranks; a rank enumerates the warp tiles of the screen tiles it owns.
+struct TileMap {
+    int W, H, tile_w, tile_h, tiles_x, n_tiles, rank, world, n_owned, sub_x, sub_per_tile, tiled_out;
+    __host__ __device__ int n_work() const { return n_owned * sub_per_tile; }
+    // lane -> pixel; returns false for pixels outside the canvas
+    __host__ __device__ bool locate(int q, int lane, int& x, int& y, int& out) const {
+        int k = q / sub_per_tile, sidx = q - k * sub_per_tile;
+        int T = k * world + rank;
+        int tx = T % tiles_x, ty = T / tiles_x;
+        int sx = sidx % sub_x, sy = sidx / sub_x;
+        int lx = sx * 8 + (lane & 7), ly = sy * 4 + (lane >> 3);
+        x = tx * tile_w + lx;
+        y = ty * tile_h + ly;
+        out = tiled_out ? (k * tile_h + ly) * tile_w + lx : y * W + x;
+        return x < W && y < H;
+    }
+};
+
+static int make_tilemap(const RtScene* sc, const RtRenderParams* p, TileMap& m) {
+    int tw = 32, th = 16, rank = 0, world = 1, tiled = 0;
+    if (p) {
+        if (p->tile_w > 0) tw = p->tile_w;
+        if (p->tile_h > 0) th = p->tile_h;
+        if (p->world > 1) { world = p->world; rank = p->rank; }
+        tiled = (p->flags & RT_RENDER_TILED_OUTPUT) ? 1 : 0;
+    }
+    if (tw % 8 || th % 4 || tw <= 0 || th <= 0 || rank < 0 || rank >= world) {
+        set_error("tile_w must be a multiple of 8, tile_h a multiple of 4, 0 <= rank < world");
+        return RT_ERR_INVALID_ARG;
+    }
+    m.W = sc->width; m.H = sc->height; m.tile_w = tw; m.tile_h = th;
+    m.tiles_x = (m.W + tw - 1) / tw;
+    m.n_tiles = m.tiles_x * ((m.H + th - 1) / th);
+    m.rank = rank; m.world = world;
+    m.n_owned = m.n_tiles > rank ? (m.n_tiles - rank + world - 1) / world : 0;
+    m.sub_x = tw / 8;
+    m.sub_per_tile = m.sub_x * (th / 4);
+    m.tiled_out = tiled;
+    return RT_OK;
+}
+static long long slab_pixels(const TileMap& m) {
+    long long per_rank = (m.n_tiles + m.world - 1) / m.world;
+    return per_rank * m.tile_w * m.tile_h;
+}
+
+// ---------------------------------------------------------------- device counters
+// d_counters layout (unsigned long long[32]):
+enum { C_WORK0 = 0, C_HITQ = 1, C_WORK1 = 2, C_PATHS = 3, C_QUEUE_A = 4, C_QUEUE_B = 5, C_WORK2 = 6,
+       C_RAYS_PRIMARY = 8, C_RAYS_SHADOW = 9, C_RAYS_SECONDARY = 10, C_NODES = 11, C_PRIMS = 12, C_EXACT = 13, C_N = 32 };
+
+__device__ __forceinline__ void flush_counts(unsigned long long* ctr, const RayCounts& rc, const TravStats& ts, bool stats) {
+    unsigned v[6] = {rc.primary, rc.shadow, rc.secondary, ts.nodes, ts.prims, ts.exact};
+    int n = stats ? 6 : 3;
+    for (int i = 0; i < n; i++) {
+        unsigned x = v[i];
+        for (int o = 16; o; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        if ((threadIdx.x & 31) == 0 && x) atomicAdd(&ctr[C_RAYS_PRIMARY + i], (unsigned long long)x);
+    }
+}
+
+struct HitRec {  // 32 bytes
+    int out_index, xy, inst, tri;
+    float t, u, v, t_local;
+};
+
+// ---------------------------------------------------------------- instance boxes (create_boxes, src/raytracer.cu:54-74)
+// BoundingBox::from_local (src/rayopt/bounding_box.cu:51-60) refits only the transformed min and
+// max corners — reproduced as is, because the reference culls instances by exactly this box.
+__global__ void k_instance_boxes(InstRec* insts, int n, const MeshRec* meshes, const float* mesh_box) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    InstRec I = insts[i];
+    instance_box(I, meshes, mesh_box);
+    for (int k = 0; k < 6; k++) insts[i].box[k] = I.box[k];
+    insts[i].box_ok = I.box_ok;
+}
+
+// ---------------------------------------------------------------- tracer selection
+enum { TR_BVH_BOX = 0, TR_BRUTE = 1, TR_BVH_NOBOX = 2, TR_BRUTE_BOX = 3 };
+template <int MODE> struct TracerOf;
+template <> struct TracerOf<TR_BVH_BOX> {
+    typedef BvhTracer T;
+    __device__ static T make(const SceneView* s, TravStats* st) { T t; t.s = s; t.use_box = true; t.st = st; return t; }
+};
+template <> struct TracerOf<TR_BVH_NOBOX> {
+    typedef BvhTracer T;
+    __device__ static T make(const SceneView* s, TravStats* st) { T t; t.s = s; t.use_box = false; t.st = st; return t; }
+};
+template <> struct TracerOf<TR_BRUTE> {
+    typedef BruteTracer T;
+    __device__ static T make(const SceneView* s, TravStats*) { T t; t.s = s; t.use_box = false; return t; }
+};
+template <> struct TracerOf<TR_BRUTE_BOX> {
+    typedef BruteTracer T;
+    __device__ static T make(const SceneView* s, TravStats*) { T t; t.s = s; t.use_box = true; return t; }
+};
+
+// ---------------------------------------------------------------- wave 0: primary rays
+// IDS == true: parity hook (rt_trace_primary) — writes (instance, triangle-in-mesh, t) per pixel.
+template <int MODE, bool STATS, bool IDS>
+__global__ void __launch_bounds__(kThreads) k_primary(SceneView s, TileMap tm, unsigned long long* ctr, HitRec* hitq,
+                                                     uint32_t* canvas, int* id_inst, int* id_tri, float* id_t) {
+    TravStats ts = {0, 0, 0};
+    RayCounts rc = {0, 0, 0};
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
+    const int lane = threadIdx.x & 31;
+    const int n_work = tm.n_work();
+    for (;;) {
+        int q = 0;
+        if (lane == 0) q = (int)atomicAdd(&ctr[C_WORK0], 1ull);
+        q = __shfl_sync(0xffffffffu, q, 0);
+        if (q >= n_work) break;
+        int x, y, out;
+        bool valid = tm.locate(q, lane, x, y, out);
+        Hit h;
+        hit_reset(h);
+        bool hit = false;
+        if (valid) {
+            rtx::Ray r = rtx::camera_ray(s.cam, (float)x, (float)y);
+            rc.primary++;
+            hit = tr.closest(r, h);
+        }
+        if (IDS) {
+            if (valid) {
+                int p = y * tm.W + x;
+                id_inst[p] = hit ? h.inst : -1;
+                id_tri[p] = hit ? h.tri - s.meshes[s.insts[h.inst].mesh].tri_begin : -1;
+                id_t[p] = h.t;
+            }
+            continue;
+        }
+        if (valid && !hit) canvas[out] = 0u;  // pack_color(0,0,0,0)
+        // warp-aggregated append of the hits
+        unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (m) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(&ctr[C_HITQ], (unsigned long long)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (hit) {
+                HitRec rec;
+                rec.out_index = out; rec.xy = x | (y << 16); rec.inst = h.inst; rec.tri = h.tri;
+                rec.t = h.t; rec.u = h.u; rec.v = h.v; rec.t_local = h.t_local;
+                hitq[base + __popc(m & ((1u << lane) - 1u))] = rec;
+            }
+        }
+    }
+    flush_counts(ctr, rc, ts, STATS);
+}
+
+// ---------------------------------------------------------------- wave 0: shading of primary hits
+template <int MODE, bool STATS>
+__global__ void __launch_bounds__(kThreads) k_shade(SceneView s, unsigned long long* ctr, const HitRec* hitq, uint32_t* canvas,
+                                                   unsigned char* paths, int path_stride, int* queue) {
+    TravStats ts = {0, 0, 0};
+    RayCounts rc = {0, 0, 0};
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
+    const int n = (int)ctr[C_HITQ];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        HitRec rec = hitq[i];
+        Hit h;
+        h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
+        rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
+        int mat_id = s.tris[h.tri].mat;
+        const MatRec& m = s.mats[mat_id];
+        if (s.depth > 0 && (m.reflective || m.refractive)) {
+            // the pixel continues: give it a path slot; k_bounce shades this hit as its first step
+            int slot = (int)atomicAdd(&ctr[C_PATHS], 1ull);
+            PathHead* head = (PathHead*)(paths + (size_t)slot * path_stride);
+            Frame* frames = (Frame*)(head + 1);
+            PathHead hd;
+            hd.acc = rtx::mk4(0.f, 0.f, 0.f, 0.f);
+            hd.out_index = rec.out_index; hd.stack_top = 0; hd.isect_mat = mat_id; hd.pending = 1;
+            hd.hit = h; hd.pad0 = hd.pad1 = 0;
+            *head = hd;
+            Frame f;
+            frame_init_root(f, r, s.depth);
+            frames[0] = f;
+            int qi = (int)atomicAdd(&ctr[C_QUEUE_A], 1ull);
+            queue[qi] = slot;
+            continue;
+        }
+        // no secondary rays: acc = 0 + 1 * illuminate, clamp, pack (src/raytracer.cu:36-41)
+        float3 nrm = hit_normal(s, h);
+        float4 c = illuminate(s, tr, r, h.t, nrm, m, rc);
+        canvas[rec.out_index] = rtx::pack_color(c);
+    }
+    flush_counts(ctr, rc, ts, STATS);
+}
+
+// ---------------------------------------------------------------- waves >= 1: bounce
+template <int MODE, bool STATS>
+__global__ void __launch_bounds__(kThreads) k_bounce(SceneView s, unsigned long long* ctr, int ctr_in, int ctr_out,
+                                                    const int* queue_in, int* queue_out, uint32_t* canvas,
+                                                    unsigned char* paths, int path_stride) {
+    TravStats ts = {0, 0, 0};
+    RayCounts rc = {0, 0, 0};
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
+    const int n = (int)ctr[ctr_in];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int slot = queue_in[i];
+        PathHead* head = (PathHead*)(paths + (size_t)slot * path_stride);
+        Frame* frames = (Frame*)(head + 1);
+        float4 acc = head->acc;
+        int stack_top = head->stack_top, isect_mat = head->isect_mat;
+        Hit h;
+        bool hit;
+        if (head->pending) {
+            h = head->hit;
+            hit = true;
+            head->pending = 0;
+        } else {
+            rtx::Ray r = frames[stack_top].ray;
+            rc.secondary++;
+            hit = tr.closest(r, h);
+        }
+        bool alive = path_advance(s, tr, frames, stack_top, isect_mat, acc, hit, h, rc);
+        if (alive) {
+            head->acc = acc;
+            head->stack_top = stack_top;
+            head->isect_mat = isect_mat;
+            int qi = (int)atomicAdd(&ctr[ctr_out], 1ull);
+            queue_out[qi] = slot;
+        } else {
+            canvas[head->out_index] = rtx::pack_color(acc);
+        }
+    }
+    flush_counts(ctr, rc, ts, STATS);
+}
+
+// ---------------------------------------------------------------- one thread per pixel, whole ray tree
+// Used for `-r` (RT_RENDER_NO_BVH), for RT_SEMANTICS_CPU and by rt_debug_cast.
+template <int MODE, int SEM>
+__global__ void __launch_bounds__(kThreads) k_mega(SceneView s, TileMap tm, unsigned long long* ctr, uint32_t* canvas) {
+    TravStats ts = {0, 0, 0};
+    RayCounts rc = {0, 0, 0};
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, nullptr);
+    const int lane = threadIdx.x & 31;
+    const int n_work = tm.n_work();
+    for (;;) {
+        int q = 0;
+        if (lane == 0) q = (int)atomicAdd(&ctr[C_WORK0], 1ull);
+        q = __shfl_sync(0xffffffffu, q, 0);
+        if (q >= n_work) break;
+        int x, y, out;
+        if (!tm.locate(q, lane, x, y, out)) continue;
+        rtx::Ray r = rtx::camera_ray(s.cam, (float)x, (float)y);
+        float4 c;
+        if (SEM == RT_SEMANTICS_CPU) {
+            CpuIsect is;
+            is.time = INFINITY; is.norm = rtx::mk3(0.f, 0.f, 0.f); is.mat = 0;
+            float last_time = 0.f;
+            c = propagate_cpu_rec(s, tr, r, is, last_time, 0, s.depth, 0, rc);
+        } else {
+            c = propagate_gpu(s, tr, r, rc);
+        }
+        canvas[out] = rtx::pack_color(c);
+    }
+    flush_counts(ctr, rc, ts, false);
+}
+
+template <int MODE>
+__global__ void k_cast_rays(SceneView s, const float* origins, const float* dirs, int n, int* inst, int* tri, float* t) {
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, nullptr);
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    rtx::Ray r = rtx::ray_make(rtx::mk3(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]),
+                               rtx::mk3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]));
+    Hit h;
+    bool hit = tr.closest(r, h);
+    inst[i] = hit ? h.inst : -1;
+    tri[i] = hit ? h.tri - s.meshes[s.insts[h.inst].mesh].tri_begin : -1;
+    t[i] = h.t;
+}
+
+template <int MODE, int SEM>
+__global__ void k_debug(SceneView s, int x, int y, RtHit* out) {
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, nullptr);
+    RayCounts rc = {0, 0, 0};
+    rtx::Ray r = rtx::camera_ray(s.cam, (float)x, (float)y);
+    Hit h;
+    bool hit = tr.closest(r, h);
+    RtHit o;
+    o.instance = hit ? h.inst : -1;
+    o.triangle = hit ? h.tri - s.meshes[s.insts[h.inst].mesh].tri_begin : -1;
+    o.t = h.t;
+    float3 n = hit ? hit_normal(s, h) : rtx::mk3(0.f, 0.f, 0.f);
+    o.normal[0] = n.x; o.normal[1] = n.y; o.normal[2] = n.z;
+    float4 c;
+    if (SEM == RT_SEMANTICS_CPU) {
+        CpuIsect is;
+        is.time = INFINITY; is.norm = rtx::mk3(0.f, 0.f, 0.f); is.mat = 0;
+        float last_time = 0.f;
+        c = propagate_cpu_rec(s, tr, r, is, last_time, 0, s.depth, 0, rc);
+    } else {
+        c = propagate_gpu(s, tr, r, rc);
+    }
+    o.color[0] = c.x; o.color[1] = c.y; o.color[2] = c.z; o.color[3] = c.w;
+    *out = o;
+}
+
+// De-interleave `world` gathered slabs into a row-major canvas (after the NCCL all-gather).
+__global__ void k_untile(TileMap tm, long long slab, const uint32_t* gathered, uint32_t* canvas) {
+    long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= (long long)tm.W * tm.H) return;
+    int x = (int)(p % tm.W), y = (int)(p / tm.W);
+    int tx = x / tm.tile_w, ty = y / tm.tile_h;
+    int T = ty * tm.tiles_x + tx;
+    int rank = T % tm.world, k = T / tm.world;
+    int lx = x - tx * tm.tile_w, ly = y - ty * tm.tile_h;
+    canvas[p] = gathered[(long long)rank * slab + ((long long)k * tm.tile_h + ly) * tm.tile_w + lx];
+}
+
+// Resident-working-set read bandwidth (the L2 roofline denominator).
+__global__ void k_l2_read(const uint4* buf, long long n16, int iters, unsigned* sink) {
+    unsigned acc = 0;
+    long long stride = (long long)gridDim.x * blockDim.x;
+    for (int it = 0; it < iters; it++)
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+            uint4 v = __ldcg(buf + i);
+            acc ^= v.x ^ v.y ^ v.z ^ v.w;
+        }
+    if (acc == 0x12345678u) *sink = acc;
+}
+
+static int upload_instances(RtScene* sc) {
+    std::vector<InstRec> recs = rth::prepare_instances(sc->instances.data(), (int)sc->instances.size());
+    if (sc->d_insts.reserve(sizeof(InstRec) * std::max<size_t>(recs.size(), 1))) return RT_ERR_OUT_OF_MEMORY;
+    if (!recs.empty())
+        RT_CUDA(cudaMemcpyAsync(sc->d_insts.p, recs.data(), sizeof(InstRec) * recs.size(), cudaMemcpyHostToDevice, sc->stream));
+    RT_CUDA(cudaStreamSynchronize(sc->stream));  // recs is a temporary
+    sc->boxes_valid = false;
+    sc->bvh.valid = false;
+    return RT_OK;
+}
+
+template <class T>
+static int upload(rth::DevBuf& b, const std::vector<T>& v, cudaStream_t st) {
+    if (b.reserve(sizeof(T) * std::max<size_t>(v.size(), 1))) return RT_ERR_OUT_OF_MEMORY;
+    if (!v.empty()) RT_CUDA(cudaMemcpyAsync(b.p, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice, st));
+    return RT_OK;
+}
+
+}  // namespace
+
+namespace rth {
+
+int update_instance_boxes(RtScene* sc) {
+    if (sc->boxes_valid) return RT_OK;
+    if (sc->n_instances > 0) {
+        k_instance_boxes<<<(sc->n_instances + kThreads - 1) / kThreads, kThreads, 0, sc->stream>>>(
+            sc->d_insts.as<InstRec>(), sc->n_instances, sc->d_meshes.as<MeshRec>(), sc->d_mesh_box.as<float>());
+        sc->kernel_launches++;
+        RT_CUDA(cudaGetLastError());
+    }
+    sc->boxes_valid = true;
+    return RT_OK;
+}
+
+SceneView make_view(const RtScene* sc, bool with_bvh) {
+    SceneView v;
+    std::memset(&v, 0, sizeof v);
+    v.verts = sc->d_verts.as<float4>();
+    v.norms = sc->d_norms.as<float4>();
+    v.tris = sc->d_tris.as<TriRec>();
+    v.meshes = sc->d_meshes.as<MeshRec>();
+    v.insts = sc->d_insts.as<InstRec>();
+    v.mats = sc->d_mats.as<MatRec>();
+    v.lights = sc->d_lights.as<LightRec>();
+    v.n_insts = sc->n_instances;
+    v.n_lights = sc->n_lights;
+    if (with_bvh && sc->bvh.valid) {
+        v.n_prims = sc->bvh.n_prims;
+        v.nodes = sc->bvh.nodes8.as<uint4>();
+        v.prims = sc->bvh.prims8.as<float4>();
+    }
+    const RtCamera& c = sc->camera;
+    v.cam = rtx::camera_basis(c.pose.rot, c.pose.pos, c.global_near, c.unit_to_pixels, c.canvas_width, c.canvas_height);
+    v.ambience = make_float4(sc->env.ambience[0], sc->env.ambience[1], sc->env.ambience[2], sc->env.ambience[3]);
+    v.dist_c0 = sc->env.dist_atten[0]; v.dist_c1 = sc->env.dist_atten[1]; v.dist_c2 = sc->env.dist_atten[2];
+    v.depth = sc->env.depth;
+    v.width = sc->width; v.height = sc->height;
+    v.any_refractive = sc->any_refractive;
+    v.any_secondary = sc->any_secondary;
+    return v;
+}
+
+}  // namespace rth
+
+// ================================================================ C ABI
+extern "C" {
+
+const char* rt_last_error_string(void) { return rth::g_err.c_str(); }
+const char* rt_version(void) { return "rtb200 0.1 (sm_100a)"; }
+
+int rt_device_count(int* out) {
+    if (!out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { *out = 0; return rth::cuda_fail(e, "cudaGetDeviceCount", __FILE__, __LINE__); }
+    *out = n;
+    return RT_OK;
+}
+
+int rt_init(int device) {
+    int n = 0;
+    if (int rc = rt_device_count(&n)) return rc;
+    if (n <= 0) { set_error("no CUDA device: this library has no CPU fallback"); return RT_ERR_NO_DEVICE; }
+    if (device < 0 || device >= n) { set_error("device ordinal out of range"); return RT_ERR_INVALID_ARG; }
+    RT_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    RT_CUDA(cudaGetDeviceProperties(&prop, device));
+    g_device = device;
+    g_sm_count = prop.multiProcessorCount;
+    return RT_OK;
+}
+
+int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
+    if (!d || !out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    *out = nullptr;
+    if (g_device < 0) { if (int rc = rt_init(0)) return rc; }
+    if (d->n_vertices < 0 || d->n_triangles < 0 || d->n_meshes < 0 || d->n_instances < 0 || d->n_lights < 0 ||
+        d->width <= 0 || d->height <= 0 || d->width > 65535 || d->height > 65535) {
+        set_error("negative count or canvas size out of range (1..65535)");
+        return RT_ERR_INVALID_ARG;
+    }
+    if ((d->n_vertices && (!d->vertices || !d->normals)) || (d->n_triangles && !d->triangles) || (d->n_meshes && !d->meshes) ||
+        (d->n_instances && !d->instances) || (d->n_lights && !d->lights)) {
+        set_error("null array with non-zero count");
+        return RT_ERR_INVALID_ARG;
+    }
+    if (d->env.depth < 0 || d->env.depth >= RT_MAX_FRAMES) {  // RayFrame frames[MAX_DEPTH], scene.cu:25,96
+        set_error("depth must be in 0..9 (the reference's RayFrame[10] stack)");
+        return RT_ERR_LIMIT;
+    }
+    for (int i = 0; i < d->n_triangles; i++)
+        for (int k = 0; k < 3; k++)
+            if (d->triangles[i].v[k] < 0 || d->triangles[i].v[k] >= d->n_vertices) { set_error("triangle vertex index out of range"); return RT_ERR_INVALID_ARG; }
+    for (int i = 0; i < d->n_meshes; i++)
+        if (d->meshes[i].tri_begin < 0 || d->meshes[i].tri_end < d->meshes[i].tri_begin || d->meshes[i].tri_end > d->n_triangles) { set_error("mesh triangle range out of range"); return RT_ERR_INVALID_ARG; }
+    for (int i = 0; i < d->n_instances; i++)
+        if (d->instances[i].mesh < 0 || d->instances[i].mesh >= d->n_meshes) { set_error("instance mesh index out of range"); return RT_ERR_INVALID_ARG; }
+
+    RtScene* sc = new (std::nothrow) RtScene();
+    if (!sc) { set_error("host allocation failed"); return RT_ERR_OUT_OF_MEMORY; }
+    auto fail = [&](int rc) { rt_scene_destroy(sc); return rc; };
+    sc->sm_count = g_sm_count;
+    cudaError_t e = cudaStreamCreateWithFlags(&sc->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__));
+    for (int i = 0; i < 6; i++) {
+        e = cudaEventCreate(&sc->ev[i]);
+        if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaEventCreate", __FILE__, __LINE__));
+    }
+    sc->n_vertices = d->n_vertices; sc->n_triangles = d->n_triangles; sc->n_meshes = d->n_meshes;
+    sc->n_instances = d->n_instances; sc->n_lights = d->n_lights;
+    sc->camera = d->camera; sc->env = d->env; sc->width = d->width; sc->height = d->height;
+    sc->instances.assign(d->instances, d->instances + d->n_instances);
+    sc->meshes.assign(d->meshes, d->meshes + d->n_meshes);
+
+    rth::HostScene hs;
+    rth::prepare_host_scene(d, hs);
+    sc->any_refractive = hs.any_refractive;
+    sc->any_secondary = hs.any_secondary;
+    sc->n_materials = (int)hs.mats.size();
+    sc->mesh_tri_count = hs.mesh_tri_count;
+    int rc;
+    if ((rc = upload(sc->d_verts, hs.verts, sc->stream)) || (rc = upload(sc->d_norms, hs.norms, sc->stream)) ||
+        (rc = upload(sc->d_tris, hs.tris, sc->stream)) || (rc = upload(sc->d_mats, hs.mats, sc->stream)) ||
+        (rc = upload(sc->d_meshes, hs.meshes, sc->stream)) || (rc = upload(sc->d_mesh_box, hs.mesh_box, sc->stream)) ||
+        (rc = upload(sc->d_lights, hs.lights, sc->stream)))
+        return fail(rc);
+    if (sc->d_counters.reserve(sizeof(unsigned long long) * C_N)) return fail(RT_ERR_OUT_OF_MEMORY);
+    if ((rc = upload_instances(sc))) return fail(rc);
+    e = cudaStreamSynchronize(sc->stream);
+    if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaStreamSynchronize", __FILE__, __LINE__));
+    *out = sc;
+    return RT_OK;
+}
+
+int rt_scene_destroy(RtScene* sc) {
+    if (!sc) return RT_OK;
+    if (sc->stream) cudaStreamSynchronize(sc->stream);
+    rth::DevBuf* all[] = {&sc->d_verts, &sc->d_norms, &sc->d_tris, &sc->d_meshes, &sc->d_insts, &sc->d_mats, &sc->d_lights,
+                          &sc->d_mesh_box, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
+                          &sc->d_queue_b, &sc->d_ids};
+    for (rth::DevBuf* b : all) b->release();
+    sc->bvh.release();
+    for (int i = 0; i < 6; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
+    if (sc->stream) cudaStreamDestroy(sc->stream);
+    delete sc;
+    return RT_OK;
+}
+
+int rt_scene_set_camera(RtScene* sc, const RtCamera* cam) {
+    if (!sc || !cam) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    sc->camera = *cam;
+    return RT_OK;
+}
+int rt_scene_set_env(RtScene* sc, const RtEnv* env) {
+    if (!sc || !env) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    if (env->depth < 0 || env->depth >= RT_MAX_FRAMES) { set_error("depth must be in 0..9"); return RT_ERR_LIMIT; }
+    sc->env = *env;
+    return RT_OK;
+}
+int rt_scene_set_instances(RtScene* sc, const RtInstance* inst, int32_t n) {
+    if (!sc || n < 0 || (n && !inst)) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    for (int i = 0; i < n; i++)
+        if (inst[i].mesh < 0 || inst[i].mesh >= sc->n_meshes) { set_error("instance mesh index out of range"); return RT_ERR_INVALID_ARG; }
+    sc->instances.assign(inst, inst + n);
+    sc->n_instances = n;
+    return upload_instances(sc);
+}
+int rt_scene_set_canvas_size(RtScene* sc, int32_t w, int32_t h) {
+    if (!sc || w <= 0 || h <= 0 || w > 65535 || h > 65535) { set_error("invalid canvas size"); return RT_ERR_INVALID_ARG; }
+    sc->width = w; sc->height = h;
+    sc->camera.canvas_width = (float)w;
+    sc->camera.canvas_height = (float)h;
+    return RT_OK;
+}
+
+int rt_bvh_build(RtScene* sc, RtBuildStats* stats) {
+    if (!sc) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
+    return rth::build_bvh(sc, stats);
+}
+int rt_bvh_free(RtScene* sc) {
+    if (!sc) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
+    sc->bvh.release();
+    return RT_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------- frame driver
+namespace {
+
+template <class K>
+static int persistent_grid(K kernel, int sm_count) {
+    int per_sm = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+    return sm_count * per_sm;
+}
+
+template <int MODE, bool STATS>
+static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uint32_t* canvas, int* waves) {
+    cudaStream_t st = sc->stream;
+    unsigned long long* ctr = sc->d_counters.as<unsigned long long>();
+    long long n_pix = (long long)tm.n_work() * 32;
+    if (sc->d_hitq.reserve(sizeof(HitRec) * (size_t)std::max<long long>(n_pix, 1))) return RT_ERR_OUT_OF_MEMORY;
+    int g0 = persistent_grid(k_primary<MODE, STATS, false>, sc->sm_count);
+    k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr);
+    sc->kernel_launches++;
+    *waves = 1;
+    int path_stride = (int)(sizeof(PathHead) + sizeof(Frame) * (size_t)(v.depth + 1));
+    unsigned long long n_hits = 0;
+    if (v.any_secondary && v.depth > 0) {
+        // paths are allocated for the hits actually found (one 8-byte read-back)
+        RT_CUDA(cudaMemcpyAsync(&n_hits, ctr + C_HITQ, 8, cudaMemcpyDeviceToHost, st));
+        RT_CUDA(cudaStreamSynchronize(st));
+        size_t cap = (size_t)std::max<unsigned long long>(n_hits, 1);
+        if (sc->d_paths.reserve(cap * path_stride) || sc->d_queue_a.reserve(4 * cap) || sc->d_queue_b.reserve(4 * cap))
+            return RT_ERR_OUT_OF_MEMORY;
+    }
+    int g1 = persistent_grid(k_shade<MODE, STATS>, sc->sm_count);
+    k_shade<MODE, STATS><<<g1, kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(), canvas, sc->d_paths.as<unsigned char>(),
+                                                 path_stride, sc->d_queue_a.as<int>());
+    sc->kernel_launches++;
+    if (v.any_secondary && v.depth > 0) {
+        int g2 = persistent_grid(k_bounce<MODE, STATS>, sc->sm_count);
+        int in = C_QUEUE_A, outc = C_QUEUE_B;
+        int* qin = sc->d_queue_a.as<int>();
+        int* qout = sc->d_queue_b.as<int>();
+        for (;;) {
+            unsigned long long live = 0;
+            RT_CUDA(cudaMemcpyAsync(&live, ctr + in, 8, cudaMemcpyDeviceToHost, st));
+            RT_CUDA(cudaStreamSynchronize(st));
+            if (live == 0) break;
+            RT_CUDA(cudaMemsetAsync(ctr + outc, 0, 8, st));
+            k_bounce<MODE, STATS><<<g2, kThreads, 0, st>>>(v, ctr, in, outc, qin, qout, canvas, sc->d_paths.as<unsigned char>(), path_stride);
+            sc->kernel_launches++;
+            (*waves)++;
+            std::swap(in, outc);
+            std::swap(qin, qout);
+            if (*waves > 4096) { set_error("bounce waves did not terminate"); return RT_ERR_LIMIT; }
+        }
+    }
+    RT_CUDA(cudaGetLastError());
+    return RT_OK;
+}
+
+template <int MODE>
+static int run_mega(RtScene* sc, const SceneView& v, const TileMap& tm, uint32_t* canvas, int semantics) {
+    unsigned long long* ctr = sc->d_counters.as<unsigned long long>();
+    if (semantics == RT_SEMANTICS_CPU) {
+        RT_CUDA(cudaDeviceSetLimit(cudaLimitStackSize, 32 * 1024));  // propagate_helper recursion
+        int g = persistent_grid(k_mega<MODE, RT_SEMANTICS_CPU>, sc->sm_count);
+        k_mega<MODE, RT_SEMANTICS_CPU><<<g, kThreads, 0, sc->stream>>>(v, tm, ctr, canvas);
+    } else {
+        int g = persistent_grid(k_mega<MODE, RT_SEMANTICS_GPU>, sc->sm_count);
+        k_mega<MODE, RT_SEMANTICS_GPU><<<g, kThreads, 0, sc->stream>>>(v, tm, ctr, canvas);
+    }
+    sc->kernel_launches++;
+    RT_CUDA(cudaGetLastError());
+    return RT_OK;
+}
+
+static int ensure_bvh(RtScene* sc, bool rebuild, RtFrameStats* stats) {
+    if (sc->bvh.valid && !rebuild) return RT_OK;
+    RtBuildStats bs;
+    if (int rc = rth::build_bvh(sc, &bs)) return rc;
+    if (stats) stats->ms_build = bs.ms_build;
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_tiled_slab_pixels(RtScene* sc, const RtRenderParams* p, int64_t* out) {
+    if (!sc || !out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    TileMap tm;
+    if (int rc = make_tilemap(sc, p, tm)) return rc;
+    *out = slab_pixels(tm);
+    return RT_OK;
+}
+
+int rt_untile(RtScene* sc, const RtRenderParams* p, const uint32_t* gathered, uint32_t* canvas) {
+    if (!sc || !gathered || !canvas) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    TileMap tm;
+    if (int rc = make_tilemap(sc, p, tm)) return rc;
+    long long n = (long long)tm.W * tm.H;
+    k_untile<<<(unsigned)((n + kThreads - 1) / kThreads), kThreads, 0, sc->stream>>>(tm, slab_pixels(tm), gathered, canvas);
+    sc->kernel_launches++;
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaStreamSynchronize(sc->stream));
+    return RT_OK;
+}
+
+int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFrameStats* stats) {
+    if (!sc || !canvas) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    RtRenderParams p;
+    std::memset(&p, 0, sizeof p);
+    if (params) p = *params;
+    if (p.semantics != RT_SEMANTICS_GPU && p.semantics != RT_SEMANTICS_CPU) { set_error("unknown semantics"); return RT_ERR_INVALID_ARG; }
+    RtFrameStats fs;
+    std::memset(&fs, 0, sizeof fs);
+    TileMap tm;
+    if (int rc = make_tilemap(sc, &p, tm)) return rc;
+    cudaStream_t st = sc->stream;
+    int launches0 = sc->kernel_launches;
+    const bool no_bvh = (p.flags & RT_RENDER_NO_BVH) != 0;
+    const bool want_stats = (p.flags & RT_RENDER_STATS) != 0;
+    RT_CUDA(cudaEventRecord(sc->ev[2], st));
+    if (!no_bvh) {
+        if (int rc = ensure_bvh(sc, (p.flags & RT_RENDER_REBUILD_BVH) != 0, &fs)) return rc;
+    } else {
+        if (int rc = rth::update_instance_boxes(sc)) return rc;
+    }
+    long long out_pixels = tm.tiled_out ? slab_pixels(tm) : (long long)tm.W * tm.H;
+    uint32_t* dcanvas = canvas;
+    if (!(p.flags & RT_RENDER_CANVAS_DEVICE)) {
+        if (sc->d_canvas.reserve(4 * (size_t)out_pixels)) return RT_ERR_OUT_OF_MEMORY;
+        dcanvas = sc->d_canvas.as<uint32_t>();
+    }
+    unsigned long long* ctr = sc->d_counters.as<unsigned long long>();
+    RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long) * C_N, st));
+    if (tm.tiled_out || tm.world > 1) RT_CUDA(cudaMemsetAsync(dcanvas, 0, 4 * (size_t)out_pixels, st));
+    RT_CUDA(cudaEventRecord(sc->ev[3], st));
+    SceneView v = rth::make_view(sc, !no_bvh);
+    int waves = 1, rc = RT_OK;
+    if (no_bvh) rc = run_mega<TR_BRUTE>(sc, v, tm, dcanvas, p.semantics);
+    else if (p.semantics == RT_SEMANTICS_CPU) rc = run_mega<TR_BVH_BOX>(sc, v, tm, dcanvas, p.semantics);
+    else if (want_stats) rc = run_wavefront<TR_BVH_BOX, true>(sc, v, tm, dcanvas, &waves);
+    else rc = run_wavefront<TR_BVH_BOX, false>(sc, v, tm, dcanvas, &waves);
+    if (rc) return rc;
+    RT_CUDA(cudaEventRecord(sc->ev[4], st));
+    unsigned long long host_ctr[C_N];
+    RT_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof host_ctr, cudaMemcpyDeviceToHost, st));
+    if (!(p.flags & RT_RENDER_CANVAS_DEVICE))
+        RT_CUDA(cudaMemcpyAsync(canvas, dcanvas, 4 * (size_t)out_pixels, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaEventRecord(sc->ev[5], st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    fs.rays_primary = host_ctr[C_RAYS_PRIMARY];
+    fs.rays_shadow = host_ctr[C_RAYS_SHADOW];
+    fs.rays_secondary = host_ctr[C_RAYS_SECONDARY];
+    fs.rays_total = fs.rays_primary + fs.rays_shadow + fs.rays_secondary;
+    fs.nodes_visited = host_ctr[C_NODES];
+    fs.prims_prefiltered = host_ctr[C_PRIMS];
+    fs.tris_tested = host_ctr[C_EXACT];
+    RT_CUDA(cudaEventElapsedTime(&fs.ms_trace, sc->ev[3], sc->ev[4]));
+    RT_CUDA(cudaEventElapsedTime(&fs.ms_total, sc->ev[2], sc->ev[5]));
+    fs.waves = waves;
+    fs.kernel_launches = sc->kernel_launches - launches0;
+    if (stats) *stats = fs;
+    return RT_OK;
+}
+
+int rt_update_scene(RtScene* sc, int32_t kernel_dim, int32_t optimize, uint32_t* host_canvas) {
+    (void)kernel_dim;  // the reference's block edge (-d); grid shapes here are fixed by the SM count
+    RtRenderParams p;
+    std::memset(&p, 0, sizeof p);
+    p.flags = optimize ? RT_RENDER_REBUILD_BVH : RT_RENDER_NO_BVH;  // the reference rebuilds every frame (src/raytracer.cu:104-107)
+    p.semantics = RT_SEMANTICS_GPU;
+    return rt_render(sc, &p, host_canvas, nullptr);
+}
+
+static int tracer_mode(RtScene* sc, int use_bvh, int* mode) {
+    switch (use_bvh) {
+        case 1: *mode = TR_BVH_BOX; break;
+        case 0: *mode = TR_BRUTE; break;
+        case 2: *mode = TR_BVH_NOBOX; break;
+        case 3: *mode = TR_BRUTE_BOX; break;
+        default: set_error("use_bvh must be 0 (brute force), 1 (BVH8 + leaf-box rule), 2 (BVH8 only), 3 (brute force + leaf-box rule)"); return RT_ERR_INVALID_ARG;
+    }
+    if (*mode == TR_BVH_BOX || *mode == TR_BVH_NOBOX) return ensure_bvh(sc, false, nullptr);
+    return rth::update_instance_boxes(sc);
+}
+
+int rt_trace_primary(RtScene* sc, int32_t use_bvh, int32_t* instance, int32_t* triangle, float* t) {
+    if (!sc || !instance || !triangle || !t) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    int mode;
+    if (int rc = tracer_mode(sc, use_bvh, &mode)) return rc;
+    size_t n = (size_t)sc->width * sc->height;
+    if (sc->d_ids.reserve(12 * n)) return RT_ERR_OUT_OF_MEMORY;
+    int* di = sc->d_ids.as<int>();
+    int* dt = di + n;
+    float* dtt = (float*)(di + 2 * n);
+    TileMap tm;
+    if (int rc = make_tilemap(sc, nullptr, tm)) return rc;
+    unsigned long long* ctr = sc->d_counters.as<unsigned long long>();
+    cudaStream_t st = sc->stream;
+    RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long) * C_N, st));
+    SceneView v = rth::make_view(sc, true);
+    int g = sc->sm_count * 4;
+    switch (mode) {
+        case TR_BVH_BOX: k_primary<TR_BVH_BOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt); break;
+        case TR_BVH_NOBOX: k_primary<TR_BVH_NOBOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt); break;
+        case TR_BRUTE: k_primary<TR_BRUTE, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt); break;
+        default: k_primary<TR_BRUTE_BOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt); break;
+    }
+    sc->kernel_launches++;
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(instance, di, 4 * n, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(triangle, dt, 4 * n, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(t, dtt, 4 * n, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
+int rt_cast_rays(RtScene* sc, int32_t use_bvh, const float* origins, const float* dirs, int32_t n, int32_t* instance,
+                 int32_t* triangle, float* t) {
+    if (!sc || n < 0 || (n && (!origins || !dirs || !instance || !triangle || !t))) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    if (n == 0) return RT_OK;
+    int mode;
+    if (int rc = tracer_mode(sc, use_bvh, &mode)) return rc;
+    size_t nn = (size_t)n;
+    if (sc->d_ids.reserve(12 * nn + 24 * nn)) return RT_ERR_OUT_OF_MEMORY;
+    int* di = sc->d_ids.as<int>();
+    int* dt = di + nn;
+    float* dtt = (float*)(di + 2 * nn);
+    float* d_o = dtt + nn;
+    float* d_d = d_o + 3 * nn;
+    cudaStream_t st = sc->stream;
+    RT_CUDA(cudaMemcpyAsync(d_o, origins, 12 * nn, cudaMemcpyHostToDevice, st));
+    RT_CUDA(cudaMemcpyAsync(d_d, dirs, 12 * nn, cudaMemcpyHostToDevice, st));
+    SceneView v = rth::make_view(sc, true);
+    int g = (n + kThreads - 1) / kThreads;
+    switch (mode) {
+        case TR_BVH_BOX: k_cast_rays<TR_BVH_BOX><<<g, kThreads, 0, st>>>(v, d_o, d_d, n, di, dt, dtt); break;
+        case TR_BVH_NOBOX: k_cast_rays<TR_BVH_NOBOX><<<g, kThreads, 0, st>>>(v, d_o, d_d, n, di, dt, dtt); break;
+        case TR_BRUTE: k_cast_rays<TR_BRUTE><<<g, kThreads, 0, st>>>(v, d_o, d_d, n, di, dt, dtt); break;
+        default: k_cast_rays<TR_BRUTE_BOX><<<g, kThreads, 0, st>>>(v, d_o, d_d, n, di, dt, dtt); break;
+    }
+    sc->kernel_launches++;
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(instance, di, 4 * nn, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(triangle, dt, 4 * nn, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(t, dtt, 4 * nn, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
+int rt_debug_cast(RtScene* sc, int32_t x, int32_t y, int32_t semantics, RtHit* out) {
+    if (!sc || !out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    if (x < 0 || y < 0 || x >= sc->width || y >= sc->height) { set_error("pixel outside the canvas"); return RT_ERR_INVALID_ARG; }
+    if (int rc = ensure_bvh(sc, false, nullptr)) return rc;
+    if (sc->d_ids.reserve(sizeof(RtHit))) return RT_ERR_OUT_OF_MEMORY;
+    SceneView v = rth::make_view(sc, true);
+    cudaStream_t st = sc->stream;
+    if (semantics == RT_SEMANTICS_CPU) {
+        RT_CUDA(cudaDeviceSetLimit(cudaLimitStackSize, 32 * 1024));
+        k_debug<TR_BVH_BOX, RT_SEMANTICS_CPU><<<1, 1, 0, st>>>(v, x, y, sc->d_ids.as<RtHit>());
+    } else {
+        k_debug<TR_BVH_BOX, RT_SEMANTICS_GPU><<<1, 1, 0, st>>>(v, x, y, sc->d_ids.as<RtHit>());
+    }
+    sc->kernel_launches++;
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(out, sc->d_ids.p, sizeof(RtHit), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
+int rt_measure_l2_bandwidth(int64_t bytes, int32_t iters, float* gbps) {
+    if (!gbps || bytes < 4096 || iters < 1) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    if (g_device < 0) { if (int rc = rt_init(0)) return rc; }
+    void* buf = nullptr;
+    unsigned* sink = nullptr;
+    RT_CUDA(cudaMalloc(&buf, (size_t)bytes));
+    RT_CUDA(cudaMalloc((void**)&sink, 4));
+    RT_CUDA(cudaMemset(buf, 1, (size_t)bytes));
+    cudaEvent_t e0, e1;
+    RT_CUDA(cudaEventCreate(&e0));
+    RT_CUDA(cudaEventCreate(&e1));
+    long long n16 = bytes / 16;
+    int grid = g_sm_count * 8;
+    k_l2_read<<<grid, kThreads>>>((const uint4*)buf, n16, 2, sink);  // warm the cache
+    RT_CUDA(cudaEventRecord(e0));
+    k_l2_read<<<grid, kThreads>>>((const uint4*)buf, n16, iters, sink);
+    RT_CUDA(cudaEventRecord(e1));
+    RT_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    RT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    *gbps = (float)((double)n16 * 16.0 * iters / (ms * 1e-3) / 1e9);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(buf);
+    cudaFree(sink);
+    return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,86 @@
+// rt_internal.h — host-side state shared by the translation units of librtb200.so.
+#ifndef RTB200_INTERNAL_H
+#define RTB200_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "rtb200.h"
+#include "rt_scene.cuh"
+
+namespace rth {
+
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define RT_CUDA(call)                                                          \
+    do {                                                                       \
+        cudaError_t _e = (call);                                               \
+        if (_e != cudaSuccess) return rth::cuda_fail(_e, #call, __FILE__, __LINE__); \
+    } while (0)
+
+// Grow-only device buffer (gputils::create_buffer / copy_to_gpu replacement, include/gputils/alloc.h:14-22:
+// plain cudaMalloc, no managed memory; reused across frames instead of malloc/free per frame).
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes);
+    void release();
+    template <class T> T* as() const { return (T*)p; }
+};
+
+struct Bvh {
+    bool valid = false;
+    int n_prims = 0;
+    int n_bvh2_nodes = 0;
+    int n_nodes8 = 0;
+    DevBuf prim_world;   // float4[3*n_prims]  world-space triangles in input (instance-major) order
+    DevBuf prim_box;     // float[6*n_prims]   inflated prim AABBs
+    DevBuf scene_bounds; // float[6] (+ atomics scratch)
+    DevBuf keys_a, keys_b, vals_a, vals_b;  // radix sort ping-pong
+    DevBuf hist;         // radix histograms
+    DevBuf left, right, parent, range_lo, range_hi, flags;  // BVH2 topology
+    DevBuf node_box;     // float[6*(2n-1)]
+    DevBuf nodes8;       // uint4[5*n_nodes8]
+    DevBuf prims8;       // float4[3*n_prims] in BVH8 leaf order
+    DevBuf prim_order8;  // int[n_prims] sorted-order index per BVH8 prim slot
+    const unsigned long long* sorted_keys = nullptr;  // into keys_a/keys_b after the last pass
+    const int* sorted_vals = nullptr;
+    DevBuf work;         // per-instance triangle prefix
+    DevBuf collapse_scratch;  // level lists, slots, counts, block totals
+    void release();
+};
+
+}  // namespace rth
+
+struct RtScene {
+    // host copies (instances can be replaced; the rest is immutable after create)
+    std::vector<RtInstance> instances;
+    std::vector<RtMesh> meshes;
+    int n_vertices = 0, n_triangles = 0, n_meshes = 0, n_instances = 0, n_lights = 0, n_materials = 0;
+    RtCamera camera;
+    RtEnv env;
+    int width = 0, height = 0;
+    int any_refractive = 0, any_secondary = 0;
+    std::vector<int> mesh_tri_count;
+    // device
+    rth::DevBuf d_verts, d_norms, d_tris, d_meshes, d_insts, d_mats, d_lights, d_mesh_box;
+    rth::DevBuf d_canvas, d_counters, d_hitq, d_paths, d_queue_a, d_queue_b, d_ids;
+    rth::Bvh bvh;
+    bool boxes_valid = false;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int sm_count = 148;
+    int kernel_launches = 0;  // running count, sampled around each API call
+};
+
+namespace rth {
+int build_bvh(RtScene* sc, RtBuildStats* stats);          // rt_bvh.cu
+int update_instance_boxes(RtScene* sc);                    // rt_engine.cu
+rtd::SceneView make_view(const RtScene* sc, bool with_bvh);
+}  // namespace rth
+
+#endif

@@ -121,7 +121,8 @@ enum {
     RT_RENDER_NO_BVH = 2,        /* `-r/--unoptimize`: brute force over instances, src/rayenv/scene.cu:48-52 */
     RT_RENDER_CANVAS_DEVICE = 4, /* `canvas` is a device pointer (no D2H copy) */
     RT_RENDER_SORT_RAYS = 8,     /* sort secondary rays between bounces */
-    RT_RENDER_TILED_OUTPUT = 16  /* write only this rank's tiles, compacted (multi-GPU) */
+    RT_RENDER_TILED_OUTPUT = 16, /* write only this rank's tiles, compacted (multi-GPU) */
+    RT_RENDER_STATS = 32         /* count nodes / triangle tests per frame (slower kernels) */
 };
 
 typedef struct RtRenderParams {
@@ -200,7 +201,9 @@ int rt_untile(RtScene* scene, const RtRenderParams* params, const uint32_t* gath
 
 /* Parity hooks. Primary-ray closest hit per pixel (row-major y*W+x), host outputs. The reference's
  * Isect carries no ids (include/rayprimitives/isect.h:15-24); these are derived the same way the
- * oracle derives them. */
+ * oracle derives them. use_bvh: 1 = BVH8 traversal with the reference's leaf-box rule (the BVH
+ * path), 0 = brute force over all instances (`-r`), 2 = BVH8 traversal without the leaf-box rule,
+ * 3 = brute force with the leaf-box rule. */
 int rt_trace_primary(RtScene* scene, int32_t use_bvh, int32_t* instance, int32_t* triangle, float* t);
 /* renv::gpu::cast_ray on caller-provided rays (src/rayenv/scene.cu:42-73). origins/dirs: n*3 floats,
  * directions are normalised like the rmath::Ray constructor does (include/raymath/geometry.h:216). */
@@ -213,8 +216,10 @@ int rt_debug_cast(RtScene* scene, int32_t x, int32_t y, int32_t semantics, RtHit
  * n_prims; parent/left/right/boxes for 2*n_prims-1 BVH2 nodes (boxes: 6 floats each). */
 int rt_bvh_download(RtScene* scene, uint64_t* morton, int32_t* perm, int32_t* left, int32_t* right,
                     int32_t* parent, float* boxes, float* scene_bounds6);
-int rt_bvh8_download(RtScene* scene, void* nodes80, int32_t max_nodes, int32_t* n_nodes, int32_t* prim_index,
-                     int32_t max_prims, int32_t* n_prim_refs);
+/* BVH8: nodes80 = 80 bytes per node, prims48 = 48 bytes per triangle in leaf order, prim_order =
+ * sorted (Morton) position of each leaf-order triangle. */
+int rt_bvh8_download(RtScene* scene, void* nodes80, int32_t max_nodes, int32_t* n_nodes, void* prims48,
+                     int32_t* prim_order, int32_t max_prims, int32_t* n_prims);
 
 /* Measured memory peaks used by bench.py for the L2 roofline (resident-working-set read). */
 int rt_measure_l2_bandwidth(int64_t bytes, int32_t iters, float* gbps);

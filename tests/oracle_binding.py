@@ -115,3 +115,54 @@ class OracleScene:
             self.close()
         except Exception:
             pass
+
+
+# ---- host LBVH / BVH8 reference build (oracle/lbvh_host.c) ----
+class OracleBvh:
+    def __init__(self, world):
+        l = lib()
+        vp = C.c_void_p
+        l.or_bvh_build.argtypes = [vp]
+        l.or_bvh_build.restype = vp
+        l.or_bvh_free.argtypes = [vp]
+        for name in ("n_prims", "n_nodes8", "levels"):
+            f = getattr(l, "or_bvh_" + name)
+            f.argtypes = [vp]
+            f.restype = C.c_int32
+        for name in ("morton", "perm", "left", "right", "parent", "node_boxes", "bounds", "nodes8", "prims8", "prim_order8"):
+            f = getattr(l, "or_bvh_" + name)
+            f.argtypes = [vp]
+            f.restype = vp
+        self.world = world
+        self._h = l.or_bvh_build(C.addressof(world.desc))
+        n = self.n_prims = l.or_bvh_n_prims(self._h)
+        self.n_nodes8 = l.or_bvh_n_nodes8(self._h)
+        self.levels = l.or_bvh_levels(self._h)
+
+        def arr(name, dtype, count):
+            if count <= 0:
+                return np.zeros(0, dtype)
+            p = getattr(l, "or_bvh_" + name)(self._h)
+            return np.ctypeslib.as_array(C.cast(p, C.POINTER(np.ctypeslib.as_ctypes_type(dtype))), shape=(count,)).copy()
+
+        self.morton = arr("morton", np.uint64, n)
+        self.perm = arr("perm", np.int32, n)
+        self.left = arr("left", np.int32, max(n - 1, 0))
+        self.right = arr("right", np.int32, max(n - 1, 0))
+        self.parent = arr("parent", np.int32, max(2 * n - 1, 0))
+        self.node_boxes = arr("node_boxes", np.float32, 6 * max(2 * n - 1, 0)).reshape(-1, 6)
+        self.bounds = arr("bounds", np.float32, 6)
+        self.nodes8 = arr("nodes8", np.uint32, 20 * self.n_nodes8).reshape(-1, 20)
+        self.prims8 = arr("prims8", np.float32, 12 * n).reshape(-1, 12)
+        self.prim_order8 = arr("prim_order8", np.int32, n)
+
+    def close(self):
+        if self._h:
+            lib().or_bvh_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

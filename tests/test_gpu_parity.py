@@ -1,0 +1,215 @@
+"""-m gpu: the CUDA engine, called through the C ABI, against the oracle and the golden fixtures
+the unmodified reference produced (tests/golden/). Integer ids bit-exact, t bit-exact (tolerance
+stated where looser), canvases bit-exact against the oracle."""
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+from conftest import WORLDS, N_INSTANCES, golden, scene_path
+
+pytestmark = pytest.mark.gpu
+
+# north_star tolerances
+ID_MATCH_MIN = 0.9999
+T_REL_TOL = 1e-4
+RMSE_MAX = 1e-3
+
+
+def rmse(a, b):
+    def ch(c):
+        return np.stack([(c >> s) & 0xff for s in (24, 16, 8, 0)], -1).astype(np.float64) / 255.0
+    return float(np.sqrt(np.mean((ch(a) - ch(b)) ** 2)))
+
+
+@pytest.fixture(scope="module")
+def scenes(pkg, gpu_ok):
+    cache = {}
+
+    def get(name, **kw):
+        key = (name, tuple(sorted(kw.items())))
+        if key not in cache:
+            w = pkg.World(scene_path(name), **kw)
+            cache[key] = (w, pkg.Scene(w))
+        return cache[key]
+    yield get
+    for w, s in cache.values():
+        s.close()
+
+
+@pytest.mark.parametrize("name", WORLDS)
+def test_primary_ids_vs_reference_golden(pkg, scenes, name):
+    """Closest-hit (instance, triangle, t) of every primary ray equals what the unmodified
+    reference's serial path produced (tests/golden/*.npz)."""
+    w, s = scenes(name)
+    assert w.n_instances == N_INSTANCES[name]
+    meta, g = golden(name)
+    inst, tri, t = s.trace_primary(use_bvh=1)
+    same = (inst == g["inst"]) & (tri == g["tri"])
+    assert same.mean() >= ID_MATCH_MIN
+    assert same.all(), f"{(~same).sum()} primary rays differ"
+    tg = g["t_bits"].view(np.float32)
+    hit = inst >= 0
+    assert np.all(np.abs(t[hit] - tg[hit]) <= T_REL_TOL * np.abs(tg[hit]))
+    assert (t.view(np.uint32) == g["t_bits"]).all()
+    if "inst_bf" in g:
+        inst0, tri0, t0 = s.trace_primary(use_bvh=0)  # `-r`: brute force, no leaf-box rule
+        assert (inst0 == g["inst_bf"]).all() and (tri0 == g["tri_bf"]).all()
+        assert (t0.view(np.uint32) == g["t_bf_bits"]).all()
+
+
+@pytest.mark.parametrize("name", WORLDS)
+def test_tracer_variants_agree(pkg, scenes, name):
+    """BVH8 traversal == brute force, with and without the reference's leaf-box rule."""
+    w, s = scenes(name)
+    a = s.trace_primary(use_bvh=1)
+    b = s.trace_primary(use_bvh=3)
+    for x, y in zip(a, b):
+        assert (x.view(np.uint32) == y.view(np.uint32)).all()
+    if w.n_instances <= 400:
+        c = s.trace_primary(use_bvh=2)
+        d = s.trace_primary(use_bvh=0)
+        for x, y in zip(c, d):
+            assert (x.view(np.uint32) == y.view(np.uint32)).all()
+
+
+@pytest.mark.parametrize("name", WORLDS)
+def test_canvas_cpu_semantics_vs_reference_golden(pkg, scenes, name):
+    """RT_SEMANTICS_CPU frame == the canvas the reference's serial path rendered."""
+    w, s = scenes(name)
+    meta, g = golden(name)
+    canvas, st = s.render(semantics=pkg.RT_SEMANTICS_CPU)
+    h, nz = ob.canvas_hash(canvas)
+    assert rmse(canvas, g["canvas"]) <= RMSE_MAX
+    assert (canvas == g["canvas"]).all()
+    assert "%016x" % h == meta["hash"] and nz == meta["nonzero"]
+
+
+@pytest.mark.parametrize("name", WORLDS + ["grid64_mixed"])
+def test_canvas_gpu_semantics_vs_oracle(pkg, scenes, name):
+    """Wavefront pipeline (reference CUDA semantics) == oracle's restatement of propagate_ray."""
+    w, s = scenes(name)
+    o = ob.OracleScene(w)
+    oc, ost = o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    canvas, st = s.render(flags=pkg.RT_RENDER_REBUILD_BVH | pkg.RT_RENDER_STATS)
+    assert rmse(canvas, oc) <= RMSE_MAX
+    assert (canvas == oc).all(), f"{(canvas != oc).sum()} pixels differ"
+    assert st["rays_primary"] == ost["rays_primary"]
+    assert st["rays_shadow"] == ost["rays_shadow"]
+    assert st["rays_secondary"] == ost["rays_secondary"]
+    assert st["rays_total"] == ost["rays_total"]
+    # the one-thread-per-pixel kernel over brute force (`-r`) gives the same frame
+    if w.n_instances <= 100:
+        c2, _ = s.render(flags=pkg.RT_RENDER_NO_BVH)
+        oc2, _ = o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=0)
+        assert (c2 == oc2).all()
+    # update_scene: the reference-shaped call
+    c3 = s.update_scene(16, True)
+    assert (c3 == oc).all()
+
+
+@pytest.mark.parametrize("name", ["world1", "world4", "world16", "world8_stress"])
+def test_bvh_build_bit_exact_vs_host(pkg, scenes, name):
+    """GPU LBVH (Morton, radix sort, Karras, refit) and BVH8 collapse == the sequential host build."""
+    w, s = scenes(name)
+    s.build_bvh()
+    d = s.download_bvh()
+    hb = ob.OracleBvh(w)
+    assert d["n_prims"] == hb.n_prims and d["n_nodes8"] == hb.n_nodes8
+    assert (d["bounds"] == hb.bounds).all()
+    assert (d["morton"] == hb.morton).all()
+    assert (d["perm"] == hb.perm).all()
+    assert (d["left"] == hb.left).all() and (d["right"] == hb.right).all()
+    assert (d["parent"][1:] == hb.parent[1:]).all()
+    assert (d["node_boxes"].view(np.uint32) == hb.node_boxes.view(np.uint32)).all()
+    assert (d["prim_order8"] == hb.prim_order8).all()
+    assert (d["nodes8"] == hb.nodes8).all()
+    assert (d["prims8"].view(np.uint32) == hb.prims8.view(np.uint32)).all()
+
+
+def test_random_rays_vs_oracle(pkg, scenes):
+    """Incoherent rays, rays aimed at triangle edges / vertices, axis-parallel and degenerate rays."""
+    w, s = scenes("world8")
+    o = ob.OracleScene(w)
+    rng = np.random.default_rng(7)
+    n = 20000
+    org = rng.uniform(-6, 6, (n, 3)).astype(np.float32)
+    org[:, 1] = rng.uniform(0, 14, n)
+    d = rng.standard_normal((n, 3)).astype(np.float32)
+    boxes = o.instance_boxes()
+    # aim a third of the rays at cube corners / edge midpoints (silhouette and diagonal cases)
+    k = n // 3
+    pick = rng.integers(0, len(boxes), k)
+    corner = np.where(rng.integers(0, 2, (k, 3)) == 1, boxes[pick, 3:], boxes[pick, :3])
+    mid = rng.integers(0, 3, k)
+    centre = 0.5 * (boxes[pick, :3] + boxes[pick, 3:])
+    corner[np.arange(k), mid] = np.where(rng.integers(0, 2, k) == 1, centre[np.arange(k), mid], corner[np.arange(k), mid])
+    d[:k] = corner - org[:k]
+    d[k:k + 300] = np.eye(3, dtype=np.float32)[rng.integers(0, 3, 300)] * rng.choice([-1, 1], (300, 1))
+    d[k + 300:k + 310] = 0
+    oi, ot, otime = o.cast_rays(org, d, use_bvh=1)
+    gi, gt, gtime = s.cast_rays(org, d, use_bvh=1)
+    assert (gi == oi).all() and (gt == ot).all()
+    assert (gtime.view(np.uint32) == otime.view(np.uint32)).all()
+    assert (oi >= 0).sum() > n // 10
+
+
+def test_resolution_and_depth_overrides(pkg, gpu_ok):
+    """BASELINE configs change width/height/depth through the JSON keys; parity holds there too."""
+    w = pkg.World(scene_path("world8_stress"), width=333, height=217, depth=5)
+    s = pkg.Scene(w)
+    o = ob.OracleScene(w)
+    oc, ost = o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    c, st = s.render()
+    assert (c == oc).all() and st["rays_total"] == ost["rays_total"]
+    assert st["waves"] >= 3
+    s.close()
+
+
+def test_tiled_sharding_reassembles(pkg, scenes):
+    """world ranks render disjoint tiles; concatenated slabs + rt_untile == the single-GPU frame
+    (emulated on one device: ranks run one after another)."""
+    import torch
+    w, s = scenes("world4")
+    full, _ = s.render()
+    world = 3
+    p0 = s.params(flags=pkg.RT_RENDER_TILED_OUTPUT | pkg.RT_RENDER_CANVAS_DEVICE, world=world, tile_w=32, tile_h=16)
+    slab = s.tiled_slab_pixels(p0)
+    gathered = torch.zeros(world * slab, dtype=torch.int32, device="cuda")
+    for r in range(world):
+        s.render(flags=pkg.RT_RENDER_TILED_OUTPUT | pkg.RT_RENDER_CANVAS_DEVICE, rank=r, world=world, tile_w=32, tile_h=16,
+                 out_ptr=gathered.data_ptr() + 4 * r * slab)
+    out = torch.zeros(w.height * w.width, dtype=torch.int32, device="cuda")
+    s.untile(p0, gathered.data_ptr(), out.data_ptr())
+    got = out.cpu().numpy().view(np.uint32).reshape(w.height, w.width)
+    assert (got == full).all()
+
+
+def test_debug_cast_and_errors(pkg, scenes):
+    w, s = scenes("world4")
+    o = ob.OracleScene(w)
+    inst, tri, t = o.trace_primary(use_bvh=1)
+    p = int(np.flatnonzero(inst >= 0)[100])
+    x, y = p % w.width, p // w.width
+    h = s.debug_cast(x, y)
+    assert h.instance == inst[p] and h.triangle == tri[p] and np.float32(h.t) == t[p]
+    with pytest.raises(RuntimeError):
+        s.debug_cast(-1, 0)
+    with pytest.raises(RuntimeError):
+        s.render(tile_w=7)
+    lib = pkg.cuda_lib()
+    assert lib.rt_scene_create(None, None) == 1
+    assert b"null" in lib.rt_last_error_string()
+
+
+def test_empty_scene_and_single_triangle(pkg, gpu_ok):
+    """Edge cases: no instances at all; one triangle (LBVH with a single leaf)."""
+    C = pkg.C
+    w = pkg.World(scene_path("world1"), width=64, height=48)
+    d = w.desc
+    n_keep = d.n_instances
+    d.n_instances = 0
+    s = pkg.Scene(w)
+    c, st = s.render()
+    assert not c.any() and st["rays_total"] == 64 * 48
+    s.close()
+    d.n_instances = n_keep
