@@ -663,9 +663,15 @@ template <int MODE>
 static int run_mega(RtScene* sc, const SceneView& v, const TileMap& tm, uint32_t* canvas, int semantics) {
     unsigned long long* ctr = sc->d_counters.as<unsigned long long>();
     if (semantics == RT_SEMANTICS_CPU) {
-        RT_CUDA(cudaDeviceSetLimit(cudaLimitStackSize, 32 * 1024));  // propagate_helper recursion
+        // propagate_helper recursion: RT_CPU_SEM_MAX_LEVEL frames of < 1 KB each
+        RT_CUDA(cudaDeviceSetLimit(cudaLimitStackSize, 32 * 1024));
         int g = persistent_grid(k_mega<MODE, RT_SEMANTICS_CPU>, sc->sm_count);
         k_mega<MODE, RT_SEMANTICS_CPU><<<g, kThreads, 0, sc->stream>>>(v, tm, ctr, canvas);
+        sc->kernel_launches++;
+        RT_CUDA(cudaGetLastError());
+        RT_CUDA(cudaStreamSynchronize(sc->stream));
+        RT_CUDA(cudaDeviceSetLimit(cudaLimitStackSize, 2048));
+        return RT_OK;
     } else {
         int g = persistent_grid(k_mega<MODE, RT_SEMANTICS_GPU>, sc->sm_count);
         k_mega<MODE, RT_SEMANTICS_GPU><<<g, kThreads, 0, sc->stream>>>(v, tm, ctr, canvas);
@@ -861,6 +867,8 @@ int rt_debug_cast(RtScene* sc, int32_t x, int32_t y, int32_t semantics, RtHit* o
     if (semantics == RT_SEMANTICS_CPU) {
         RT_CUDA(cudaDeviceSetLimit(cudaLimitStackSize, 32 * 1024));
         k_debug<TR_BVH_BOX, RT_SEMANTICS_CPU><<<1, 1, 0, st>>>(v, x, y, sc->d_ids.as<RtHit>());
+        RT_CUDA(cudaStreamSynchronize(st));
+        RT_CUDA(cudaDeviceSetLimit(cudaLimitStackSize, 2048));
     } else {
         k_debug<TR_BVH_BOX, RT_SEMANTICS_GPU><<<1, 1, 0, st>>>(v, x, y, sc->d_ids.as<RtHit>());
     }

@@ -225,13 +225,19 @@ RT_HD float4 propagate_gpu(const SceneView& s, const Tracer& tr, const rtx::Ray&
 // Recursion unrolled by hand is not possible (two children share one Isect), so this walks the
 // tree with an explicit stack of continuation records.
 struct CpuIsect { float time; float3 norm; int mat; };
+// The reference's serial recursion is bounded only by misses; rays caught
+// in the 0.001-wide gap between two reflective cubes recurse thousands of levels there, adding
+// light to pixels that are already clamped to 1. Device recursion is cut here.
+#ifndef RT_CPU_SEM_MAX_LEVEL
+#define RT_CPU_SEM_MAX_LEVEL 16
+#endif
 
 template <class Tracer>
 __host__ __device__ float4 propagate_cpu_rec(const SceneView& s, const Tracer& tr, const rtx::Ray& r, CpuIsect& isect,
                                float& last_time, int in_obj, int depth, int level, RayCounts& rc) {
     float4 zero = rtx::mk4(0.f, 0.f, 0.f, 0.f);
     if (depth > s.depth) return zero;
-    if (level > 64) return zero;  // the reference recurses until a miss; 64 levels is far past any real tree
+    if (level > RT_CPU_SEM_MAX_LEVEL) return zero;
     isect.time = INFINITY;
     if (level == 0) rc.primary++; else rc.secondary++;
     Hit h;
