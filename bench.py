@@ -1,0 +1,363 @@
+#!/usr/bin/env python3
+"""bench.py — Mrays/s of the ray-traversal hot path on B200 (contract: see DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--scene world16] ...
+
+A step is one frame = BVH rebuild + trace, the scope of the reference's bench()
+(/root/reference/src/main.cc:210-216 -> rtracer::gpu::update_scene, src/raytracer.cu:102-120).
+Default workload: world16.json at 3840x2160, depth 9 (BASELINE.json configs[3], the headline).
+
+  value : frame with everything resident in HBM (canvas stays on the device)
+  e2e   : the same frame through the C ABI with HOST buffers — instances and camera uploaded,
+          canvas copied back into pinned host memory — inside the timed region
+  N > 1 : screen tiles dealt round-robin to the ranks, scene + BVH replicated, one NCCL
+          all-gather of the RGBA8 slabs per frame and a de-interleave kernel ("strong" scaling)
+
+`--impl reference` times the reference's own serial CPU path (oracle/_ref/ref_cpu, built from the
+unmodified sources; falls back to the oracle port) on a bounded sample of the same workload.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s (all rays: primary + shadow + secondary closest-hit queries)"
+UNIT = "Mrays/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scene", default="world16")
+    ap.add_argument("--width", type=int, default=3840)
+    ap.add_argument("--height", type=int, default=2160)
+    ap.add_argument("--depth", type=int, default=9)
+    ap.add_argument("--grid-size", type=int, default=0)
+    ap.add_argument("--tile-w", type=int, default=32)
+    ap.add_argument("--tile-h", type=int, default=16)
+    ap.add_argument("--keep-bvh", action="store_true", help="do not rebuild the BVH every frame")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline leg")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return "%s.json %dx%d depth %d%s" % (a.scene, a.width, a.height, a.depth,
+                                          (" grid %d" % a.grid_size) if a.grid_size else "")
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ reference CPU arm
+def cpu_reference_run(a, budget_s, frames=1):
+    """Times the reference's serial path on a bounded sample of the workload: the same scene and
+    depth at a reduced resolution (rows/cols scaled by the same factor) so that one frame takes
+    about budget_s/frames seconds. Returns (Mrays/s, kind, cores, sample, seconds)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import rtb200_loader
+    pkg = rtb200_loader.load()
+    import oracle_binding as ob
+    ref_cpu = os.path.join(ROOT, "oracle", "_ref", "ref_cpu")
+    scene_json = os.path.join(ROOT, "scenes", a.scene + ".json")
+    # ~1.0e5 rays/s/core on world16 for the reference's serial path; pick a
+    # resolution whose ray count fits the budget, then measure — the estimate only sizes the sample
+    est_rays_per_s = {"world16": 0.9e5, "config": 0.9e5, "world8_stress": 1.4e5, "world8": 3.0e5}.get(a.scene, 5e5)
+    full_pixels = a.width * a.height
+    frac = min(1.0, (est_rays_per_s * budget_s / frames) / (2.0 * full_pixels))
+    scale = frac ** 0.5
+    w = max(64, int(a.width * scale) // 8 * 8)
+    h = max(48, int(a.height * scale) // 4 * 4)
+    world = pkg.World(scene_json, width=w, height=h, depth=a.depth, grid_size=a.grid_size)
+    # ray count of the sample = closest-hit queries of the serial path (counted by the oracle port)
+    _, st = ob.OracleScene(world).render(semantics=pkg.RT_SEMANTICS_CPU, use_bvh=1)
+    rays = st["rays_total"]
+    if os.path.exists(ref_cpu):
+        cfg = json.load(open(scene_json))
+        cfg.update(width=w, height=h, depth=a.depth)
+        if a.grid_size:
+            cfg["grid_size"] = a.grid_size
+        with tempfile.NamedTemporaryFile("w", suffix=".json", delete=False) as f:
+            json.dump(cfg, f)
+            tmp = f.name
+        try:
+            out = subprocess.run([ref_cpu, tmp, "--frames", str(frames)], capture_output=True, text=True, check=True).stdout
+            info = json.loads(out.strip().splitlines()[-1])
+            secs = info["ms_median"] * 1e-3
+        finally:
+            os.unlink(tmp)
+        kind, cores = "reference", 1
+    else:
+        t0 = time.perf_counter()
+        for _ in range(frames):
+            ob.OracleScene(world).render(semantics=pkg.RT_SEMANTICS_CPU, use_bvh=1, threads=1)
+        secs = (time.perf_counter() - t0) / frames
+        kind, cores = "port", 1
+    sample = "%s %dx%d depth %d, %d frame(s) of rtracer::cpu::update_scene (BVH build + trace), %d rays/frame, %.2f s/frame" % (
+        a.scene, w, h, a.depth, frames, rays, secs)
+    return rays / secs / 1e6, kind, cores, sample, secs
+
+
+def run_reference_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    total = a.steps + a.warmup
+    per_step = max(1.0, min(8.0, 150.0 / max(total, 1)))
+    vals, kind, cores, sample = [], "port", 1, ""
+    t_all = 0.0
+    for i in range(total):
+        v, kind, cores, sample, secs = cpu_reference_run(a, per_step, frames=1)
+        if i >= a.warmup:
+            vals.append(v)
+            t_all += secs
+    value = sum(vals) / len(vals)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * t_all / max(len(vals), 1), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic (procedural world, seed 42)",
+            "config": {"workload": workload_name(a), "sample": sample},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                             "host_cores": os.cpu_count()},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------ our arm
+def hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+    import rtb200_loader
+    pkg = rtb200_loader.load()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    wfile = pkg.World(os.path.join(ROOT, "scenes", a.scene + ".json"), width=a.width, height=a.height, depth=a.depth,
+                      grid_size=a.grid_size)
+    scene = pkg.Scene(wfile, device=local_rank)
+    W, H = wfile.width, wfile.height
+    base = 0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH
+    dev_flags = base | pkg.RT_RENDER_CANVAS_DEVICE | (pkg.RT_RENDER_TILED_OUTPUT if world > 1 else 0)
+    params = scene.params(flags=dev_flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h)
+    canvas_dev = torch.zeros(H * W, dtype=torch.int32, device="cuda")
+    host_canvas = torch.zeros(H * W, dtype=torch.int32).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    slab_t = gathered = None
+    if world > 1:
+        slab = scene.tiled_slab_pixels(params)
+        slab_t = torch.zeros(slab, dtype=torch.int32, device="cuda")
+        gathered = torch.zeros(world * slab, dtype=torch.int32, device="cuda")
+    desc = wfile.desc
+    h2d = C.sizeof(pkg.RtInstance) * desc.n_instances + C.sizeof(pkg.RtCamera)
+
+    def frame_device(flags=dev_flags):
+        """One frame, canvas left in HBM (rank-local tiles gathered and de-interleaved when N > 1)."""
+        if world == 1:
+            _, st = scene.render(flags=flags, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=canvas_dev.data_ptr())
+            return st, st["kernel_launches"]
+        _, st = scene.render(flags=flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=slab_t.data_ptr())
+        dist.all_gather_into_tensor(gathered, slab_t)
+        torch.cuda.current_stream().synchronize()
+        scene.untile(params, gathered.data_ptr(), canvas_dev.data_ptr())
+        return st, st["kernel_launches"] + 1
+
+    def frame_e2e():
+        """The call a user of the reference makes per frame, with host buffers on both sides."""
+        scene.set_instances(desc.instances, desc.n_instances)
+        scene.set_camera(desc.camera)
+        if world == 1:
+            _, st = scene.render(flags=base, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=host_canvas.data_ptr())
+            return st
+        st, _ = frame_device()
+        if rank == 0:
+            host_canvas.copy_(canvas_dev, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        return st
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, sampler=None):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        total_ms, out = 0.0, []
+        barrier()
+        if sampler:
+            sampler.start()
+        for _ in range(steps):
+            flush.zero_()            # L2 flush between timed iterations (untimed)
+            torch.cuda.synchronize()
+            ev0.record()
+            out.append(fn())
+            ev1.record()
+            ev1.synchronize()
+            total_ms += ev0.elapsed_time(ev1)
+        clocks = sampler.stop() if sampler else None
+        barrier()
+        if world > 1:
+            t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            total_ms = float(t.item())
+        return total_ms, out, clocks
+
+    for _ in range(max(a.warmup, 3)):
+        frame_device()
+        frame_e2e()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ms_dev, outs, clocks = timed(frame_device, a.steps, sampler)
+    ms_e2e, outs_e2e, _ = timed(frame_e2e, a.steps)
+
+    # rays: every rank counts its own tiles
+    rays_local = sum(o[0]["rays_total"] for o in outs)
+    launches = sum(o[1] for o in outs)
+    if world > 1:
+        t = torch.tensor([rays_local, launches], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t)
+        rays_all, launches_all = int(t[0].item()), int(t[1].item())
+    else:
+        rays_all, launches_all = rays_local, launches
+    rays_per_frame = rays_all / a.steps
+    value = rays_all / (ms_dev * 1e-3) / 1e6
+    e2e_value = rays_all / (ms_e2e * 1e-3) / 1e6
+
+    if rank == 0:
+        st = [o[0] for o in outs]
+        avg = lambda k: sum(s[k] for s in st) / len(st)
+        # one stats frame for nodes / triangle tests per ray (slower kernels, untimed)
+        sflags = (dev_flags | pkg.RT_RENDER_STATS)
+        sst, _ = frame_device(sflags)
+        peak, peak_src = hbm_peak()
+        l2_peak = pkg.measure_l2_bandwidth(32 << 20, 40)
+        # dominant kernel and its algorithmic HBM bytes per launch (DESIGN.md "Roofline"):
+        #   k_primary: 4 B per missed pixel (canvas) + 32 B per hit (hit queue write)
+        #   k_shade  : 32 B per hit (queue read) + 4 B per hit (canvas)
+        pix_local = sst["rays_primary"]
+        hits = sst["n_hits"]
+        kernels = {"k_primary": (avg("ms_primary"), 4.0 * (pix_local - hits) + 32.0 * hits),
+                   "k_shade": (avg("ms_shade"), 36.0 * hits)}
+        dom = max(kernels, key=lambda k: kernels[k][0])
+        dom_ms, dom_bytes = kernels[dom]
+        achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+        l2_bytes = 80.0 * sst["nodes_visited"] + 48.0 * sst["prims_prefiltered"]
+        ms_trace = avg("ms_trace")
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms,
+                    "note": "scene + BVH8 (< 2 MB) are L1/L2-resident; the kernel is issue/latency-bound, not HBM-bound",
+                    "l2": {"bytes_per_frame": l2_bytes, "achieved": l2_bytes / (ms_trace * 1e-3) / 1e9,
+                           "peak": l2_peak, "unit": "GB/s", "frac": l2_bytes / (ms_trace * 1e-3) / 1e9 / l2_peak,
+                           "peak_source": "rt_measure_l2_bandwidth (32 MiB resident read, measured in this run)",
+                           "nodes_per_ray": sst["nodes_visited"] / max(sst["rays_total"], 1),
+                           "tri_filters_per_ray": sst["prims_prefiltered"] / max(sst["rays_total"], 1),
+                           "exact_tests_per_ray": sst["tris_tested"] / max(sst["rays_total"], 1)}}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+                "ms_per_step": ms_dev / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic (procedural world, seed 42)",
+                "config": {"workload": workload_name(a), "rays_per_frame": rays_per_frame, "instances": desc.n_instances,
+                           "triangles": sst_prims(scene), "step": "BVH rebuild + trace" if not a.keep_bvh else "trace (BVH kept)",
+                           "l2": "flushed between timed iterations (256 MiB write)",
+                           "sharding": "screen tiles %dx%d round-robin over %d rank(s)" % (a.tile_w, a.tile_h, world)},
+                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / a.steps, "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": 4 * W * H},
+                "gpu_launches": launches_all, "clocks": clocks,
+                "breakdown_ms": {"build": avg("ms_build"), "trace": ms_trace, "k_primary": avg("ms_primary"),
+                                 "k_shade": avg("ms_shade"), "k_bounce": avg("ms_bounce"), "waves": st[0]["waves"]},
+                "roofline": roofline}
+        if world == 1 and not a.no_cpu_baseline:
+            v, kind, cores, sample, _ = cpu_reference_run(a, a.cpu_seconds)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                                    "host_cores": os.cpu_count()}
+        print(json.dumps(line), flush=True)
+    scene.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def sst_prims(scene):
+    try:
+        return scene.build_bvh()["n_prims"]
+    except Exception:
+        return None
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        return run_reference_arm(a)
+    return run_ours(a)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

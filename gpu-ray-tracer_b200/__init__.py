@@ -78,7 +78,8 @@ class RtFrameStats(C.Structure):
     _fields_ = [("rays_total", C.c_uint64), ("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64),
                 ("rays_secondary", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("prims_prefiltered", C.c_uint64), ("ms_build", C.c_float), ("ms_trace", C.c_float),
-                ("ms_total", C.c_float), ("waves", C.c_int32), ("kernel_launches", C.c_int32)]
+                ("ms_total", C.c_float), ("waves", C.c_int32), ("kernel_launches", C.c_int32),
+                ("ms_primary", C.c_float), ("ms_shade", C.c_float), ("ms_bounce", C.c_float), ("n_hits", C.c_int32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

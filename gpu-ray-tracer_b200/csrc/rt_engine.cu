@@ -519,7 +519,7 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
     sc->sm_count = g_sm_count;
     cudaError_t e = cudaStreamCreateWithFlags(&sc->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__));
-    for (int i = 0; i < 6; i++) {
+    for (int i = 0; i < 10; i++) {
         e = cudaEventCreate(&sc->ev[i]);
         if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaEventCreate", __FILE__, __LINE__));
     }
@@ -557,7 +557,7 @@ int rt_scene_destroy(RtScene* sc) {
                           &sc->d_queue_b, &sc->d_ids};
     for (rth::DevBuf* b : all) b->release();
     sc->bvh.release();
-    for (int i = 0; i < 6; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
+    for (int i = 0; i < 10; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
     if (sc->stream) cudaStreamDestroy(sc->stream);
     delete sc;
     return RT_OK;
@@ -621,6 +621,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     int g0 = persistent_grid(k_primary<MODE, STATS, false>, sc->sm_count);
     k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr);
     sc->kernel_launches++;
+    RT_CUDA(cudaEventRecord(sc->ev[6], st));
     *waves = 1;
     int path_stride = (int)(sizeof(PathHead) + sizeof(Frame) * (size_t)(v.depth + 1));
     unsigned long long n_hits = 0;
@@ -636,6 +637,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     k_shade<MODE, STATS><<<g1, kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(), canvas, sc->d_paths.as<unsigned char>(),
                                                  path_stride, sc->d_queue_a.as<int>());
     sc->kernel_launches++;
+    RT_CUDA(cudaEventRecord(sc->ev[7], st));
     if (v.any_secondary && v.depth > 0) {
         int g2 = persistent_grid(k_bounce<MODE, STATS>, sc->sm_count);
         int in = C_QUEUE_A, outc = C_QUEUE_B;
@@ -745,6 +747,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     RT_CUDA(cudaEventRecord(sc->ev[3], st));
     SceneView v = rth::make_view(sc, !no_bvh);
     int waves = 1, rc = RT_OK;
+    const bool wavefront = !no_bvh && p.semantics == RT_SEMANTICS_GPU;
     if (no_bvh) rc = run_mega<TR_BRUTE>(sc, v, tm, dcanvas, p.semantics);
     else if (p.semantics == RT_SEMANTICS_CPU) rc = run_mega<TR_BVH_BOX>(sc, v, tm, dcanvas, p.semantics);
     else if (want_stats) rc = run_wavefront<TR_BVH_BOX, true>(sc, v, tm, dcanvas, &waves);
@@ -766,6 +769,12 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     fs.tris_tested = host_ctr[C_EXACT];
     RT_CUDA(cudaEventElapsedTime(&fs.ms_trace, sc->ev[3], sc->ev[4]));
     RT_CUDA(cudaEventElapsedTime(&fs.ms_total, sc->ev[2], sc->ev[5]));
+    if (wavefront) {
+        RT_CUDA(cudaEventElapsedTime(&fs.ms_primary, sc->ev[3], sc->ev[6]));
+        RT_CUDA(cudaEventElapsedTime(&fs.ms_shade, sc->ev[6], sc->ev[7]));
+        RT_CUDA(cudaEventElapsedTime(&fs.ms_bounce, sc->ev[7], sc->ev[4]));
+        fs.n_hits = (int32_t)host_ctr[C_HITQ];
+    }
     fs.waves = waves;
     fs.kernel_launches = sc->kernel_launches - launches0;
     if (stats) *stats = fs;

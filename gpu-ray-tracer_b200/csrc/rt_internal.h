@@ -72,7 +72,7 @@ struct RtScene {
     rth::Bvh bvh;
     bool boxes_valid = false;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     int sm_count = 148;
     int kernel_launches = 0;  // running count, sampled around each API call
 };

@@ -146,6 +146,10 @@ typedef struct RtFrameStats {
     float ms_total;           /* CUDA-event time of everything incl. canvas copy */
     int32_t waves;            /* wavefront iterations (bounce levels) executed */
     int32_t kernel_launches;  /* kernels launched by this call */
+    float ms_primary;         /* CUDA-event time of k_primary (ray generation + closest-hit traversal) */
+    float ms_shade;           /* CUDA-event time of k_shade (shadow-ray traversal + Phong) */
+    float ms_bounce;          /* CUDA-event time of all k_bounce waves (incl. the per-wave read-backs) */
+    int32_t n_hits;           /* primary rays that hit something */
 } RtFrameStats;
 
 typedef struct RtBuildStats {

@@ -84,10 +84,13 @@ def test_canvas_cpu_semantics_vs_reference_golden(pkg, scenes, name):
     assert "%016x" % h == meta["hash"] and nz == meta["nonzero"]
 
 
+MIXED = dict(width=160, height=120, grid_size=16, depth=4)  # sized for the oracle (seconds)
+
+
 @pytest.mark.parametrize("name", WORLDS + ["grid64_mixed"])
 def test_canvas_gpu_semantics_vs_oracle(pkg, scenes, name):
     """Wavefront pipeline (reference CUDA semantics) == oracle's restatement of propagate_ray."""
-    w, s = scenes(name)
+    w, s = scenes(name, **(MIXED if name == "grid64_mixed" else {}))
     o = ob.OracleScene(w)
     oc, ost = o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
     canvas, st = s.render(flags=pkg.RT_RENDER_REBUILD_BVH | pkg.RT_RENDER_STATS)
