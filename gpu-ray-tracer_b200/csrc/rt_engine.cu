@@ -221,8 +221,8 @@ __global__ void __launch_bounds__(kThreads) k_primary(SceneView s, TileMap tm, u
 }
 
 // ---------------------------------------------------------------- wave 0: shading of primary hits
-template <int MODE, bool STATS>
-__global__ void __launch_bounds__(kThreads) k_shade(SceneView s, unsigned long long* ctr, const HitRec* hitq, uint32_t* canvas,
+template <int MODE, bool STATS, bool OPAQUE_ONLY>
+__global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned long long* ctr, const HitRec* hitq, uint32_t* canvas,
                                                    unsigned char* paths, int path_stride, int* queue) {
     TravStats ts = {0, 0, 0};
     RayCounts rc = {0, 0, 0};
@@ -235,7 +235,7 @@ __global__ void __launch_bounds__(kThreads) k_shade(SceneView s, unsigned long l
         rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
         int mat_id = s.tris[h.tri].mat;
         const MatRec& m = s.mats[mat_id];
-        if (s.depth > 0 && (m.reflective || m.refractive)) {
+        if (!OPAQUE_ONLY && s.depth > 0 && (m.reflective || m.refractive)) {
             // the pixel continues: give it a path slot; k_bounce shades this hit as its first step
             int slot = (int)atomicAdd(&ctr[C_PATHS], 1ull);
             PathHead* head = (PathHead*)(paths + (size_t)slot * path_stride);
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(kThreads) k_shade(SceneView s, unsigned long l
         }
         // no secondary rays: acc = 0 + 1 * illuminate, clamp, pack (src/raytracer.cu:36-41)
         float3 nrm = hit_normal(s, h);
-        float4 c = illuminate(s, tr, r, h.t, nrm, m, rc);
+        float4 c = illuminate<OPAQUE_ONLY>(s, tr, r, h.t, nrm, m, rc);
         canvas[rec.out_index] = rtx::pack_color(c);
     }
     flush_counts(ctr, rc, ts, STATS);
@@ -633,9 +633,14 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         if (sc->d_paths.reserve(cap * path_stride) || sc->d_queue_a.reserve(4 * cap) || sc->d_queue_b.reserve(4 * cap))
             return RT_ERR_OUT_OF_MEMORY;
     }
-    int g1 = persistent_grid(k_shade<MODE, STATS>, sc->sm_count);
-    k_shade<MODE, STATS><<<g1, kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(), canvas, sc->d_paths.as<unsigned char>(),
-                                                 path_stride, sc->d_queue_a.as<int>());
+    if (!v.any_secondary) {  // no Kr / Kt anywhere: any-hit shadow rays only, every pixel ends here
+        int g1 = persistent_grid(k_shade<MODE, STATS, true>, sc->sm_count);
+        k_shade<MODE, STATS, true><<<g1, kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, 0, nullptr);
+    } else {
+        int g1 = persistent_grid(k_shade<MODE, STATS, false>, sc->sm_count);
+        k_shade<MODE, STATS, false><<<g1, kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(), canvas,
+                                                            sc->d_paths.as<unsigned char>(), path_stride, sc->d_queue_a.as<int>());
+    }
     sc->kernel_launches++;
     RT_CUDA(cudaEventRecord(sc->ev[7], st));
     if (v.any_secondary && v.depth > 0) {

@@ -17,6 +17,14 @@
 #include <stdint.h>
 
 #define RT_HD __host__ __device__ __forceinline__
+// Out-of-line on the device: the exact paths are large (precise sqrt / divide sequences) and are
+// reached by few lanes at a time; one copy per kernel keeps the traversal loop inside the
+// instruction cache (k_shade was 199 KB of SASS with everything inlined, stall_no_instruction 8.0).
+#ifdef __CUDACC__
+#define RT_HD_NOINLINE inline __host__ __device__ __noinline__
+#else
+#define RT_HD_NOINLINE inline
+#endif
 
 // include/raymath/linear.h:15 — `constexpr double THRESHOLD = 1E-5f`: an fp32 value widened to
 // double; comparing an fp32 operand against it is the same as comparing against the fp32 constant.
@@ -96,7 +104,7 @@ RT_HD Quat qmul(Quat a, Quat o) {  // geometry.h:163-170 (Hamilton product, this
     return r;
 }
 // geometry.h:176-181 operator*(Quat, Vec3): sandwich product, then the input length restored.
-RT_HD float3 qrotate(Quat q, float3 v) {
+RT_HD_NOINLINE float3 qrotate(Quat q, float3 v) {
     float length = len3(v);
     Quat qv = {v.x, v.y, v.z, 0.0f};
     Quat prod = qmul(qmul(qnormalized(q), qv), qinverse(q));
@@ -191,7 +199,7 @@ RT_HD float3 ref_refract(float3 dir, float3 norm, float index_from, float index_
 // powf as the reference's host build evaluates it (glibc: correctly rounded in all but a
 // vanishing fraction of cases): a double-precision pow rounded once to fp32. Only reached for
 // refractive materials (trans_atten / calc_shadow_atten) and specular terms; pow(x, 0) == 1.
-RT_HD float ref_powf(float x, float y) {
+RT_HD_NOINLINE float ref_powf(float x, float y) {
     if (y == 0.0f) return 1.0f;
     if (y == 1.0f) return x;
     return (float)pow((double)x, (double)y);

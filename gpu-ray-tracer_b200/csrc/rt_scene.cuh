@@ -104,7 +104,7 @@ struct InstCtx {
     int box_pass;      // BoundingBox::intersects on the instance's leaf box
 };
 
-RT_HD void inst_ctx_load(const SceneView& s, const rtx::Ray& r, int inst, bool use_box, InstCtx& c) {
+RT_HD_NOINLINE void inst_ctx_load(const SceneView& s, const rtx::Ray& r, int inst, bool use_box, InstCtx& c) {
     const InstRec& I = s.insts[inst];
     c.inst = inst;
     c.box_pass = use_box ? (rtx::ref_box_intersects(I.box, I.box_ok != 0, r) ? 1 : 0) : 1;
@@ -123,7 +123,7 @@ RT_HD void inst_ctx_load(const SceneView& s, const rtx::Ray& r, int inst, bool u
 // instance times are compared in mesh-local units like Trimesh::hit_local does; across instances
 // after rescaling. Exact ties go to the lower (instance, triangle) index, i.e. the one the
 // reference's index-ordered loops reach first.
-RT_HD bool exact_candidate(const SceneView& s, const rtx::Ray& r, int inst, int tri, bool use_box, InstCtx& ctx,
+RT_HD_NOINLINE bool exact_candidate(const SceneView& s, const rtx::Ray& r, int inst, int tri, bool use_box, InstCtx& ctx,
                            Hit& best) {
     if (ctx.inst != inst) inst_ctx_load(s, r, inst, use_box, ctx);
     if (!ctx.box_pass) return false;
@@ -147,7 +147,7 @@ RT_HD bool exact_candidate(const SceneView& s, const rtx::Ray& r, int inst, int 
 // back through the mesh pose (HitHandle dtor, hitable.cu:20-26) and the instance pose
 // (cast_local, scene.cu:35-38). The reference recomputes it on every accepted candidate; only
 // the last one survives, so it is evaluated once per closest hit here.
-RT_HD float3 hit_normal(const SceneView& s, const Hit& h) {
+RT_HD_NOINLINE float3 hit_normal(const SceneView& s, const Hit& h) {
     const TriRec T = s.tris[h.tri];
     float4 n0 = s.norms[T.v0], n1 = s.norms[T.v1], n2 = s.norms[T.v2];
     float bary0 = 1.0f - h.u - h.v;

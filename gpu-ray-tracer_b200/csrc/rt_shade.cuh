@@ -26,15 +26,18 @@ RT_HD float dist_atten(const SceneView& s, float dist) {
 // casts that walks through refractive occluders. When no material in the scene is refractive the
 // loop body runs once and only asks "is the closest hit within max_t", which an any-hit query
 // answers exactly, so that case terminates on the first accepted occluder.
-template <class Tracer>
+// OPAQUE_ONLY (compile time): the caller guarantees !s.any_refractive, so the closest-hit loop is
+// not even instantiated (k_shade's code size and registers).
+template <bool OPAQUE_ONLY, class Tracer>
 RT_HD float4 light_attenuate(const SceneView& s, const Tracer& tr, const LightRec& L, const rtx::Ray& to_light,
                              float max_t, RayCounts& rc) {
     float4 rv = L.color;
     rtx::Ray cur = rtx::ray_make(rtx::ray_at(to_light, RT_THR), to_light.d);
-    if (!s.any_refractive) {
+    if (OPAQUE_ONLY || !s.any_refractive) {
         rc.shadow++;
         return tr.occluded(cur, max_t) ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : rv;
     }
+    if (OPAQUE_ONLY) return rv;
     for (;;) {
         Hit sh;
         rc.shadow++;
@@ -52,21 +55,25 @@ RT_HD float4 light_attenuate(const SceneView& s, const Tracer& tr, const LightRe
     }
 }
 
-// PointLight::shine / DirLight::shine (light.cu:63-77)
-template <class Tracer>
+// PointLight::shine / DirLight::shine (light.cu:63-77). One call site of light_attenuate for both
+// kinds (the traversal is inlined there); the arithmetic per kind is the reference's.
+template <bool OPAQUE_ONLY, class Tracer>
 RT_HD float4 light_shine(const SceneView& s, const Tracer& tr, const LightRec& L, float3 hit_pos, float3& dir_to_light,
                          RayCounts& rc) {
-    if (L.kind == 0) {
+    float max_t = INFINITY, da = 1.0f;
+    const bool point = L.kind == 0;
+    if (point) {
         float3 disp = rtx::sub3(L.v, hit_pos);
         float dist = rtx::len3(disp);
-        float da = dist_atten(s, dist);
+        da = dist_atten(s, dist);
         dir_to_light = rtx::normalized3(disp);
-        rtx::Ray to_light = rtx::ray_make(hit_pos, dir_to_light);
-        return rtx::scale4(da, light_attenuate(s, tr, L, to_light, dist, rc));
+        max_t = dist;
+    } else {
+        dir_to_light = rtx::neg3(L.v);
     }
-    dir_to_light = rtx::neg3(L.v);
     rtx::Ray to_light = rtx::ray_make(hit_pos, dir_to_light);
-    return light_attenuate(s, tr, L, to_light, INFINITY, rc);
+    float4 a = light_attenuate<OPAQUE_ONLY>(s, tr, L, to_light, max_t, rc);
+    return point ? rtx::scale4(da, a) : a;
 }
 
 // phong (phong.cu:14-33); the texture branch is empty in the reference.
@@ -80,14 +87,14 @@ RT_HD float4 phong(const MatRec& m, float3 norm, float4 incoming, float3 ray_dir
 }
 
 // org_light + illuminate (phong.cu:35-53)
-template <class Tracer>
+template <bool OPAQUE_ONLY = false, class Tracer>
 RT_HD float4 illuminate(const SceneView& s, const Tracer& tr, const rtx::Ray& ray, float t, float3 norm,
                         const MatRec& m, RayCounts& rc) {
     float4 sum = rtx::add4(m.Ke, rtx::mul4(m.Ka, s.ambience));
     float3 hit_pos = rtx::ray_at(ray, t);
     for (int i = 0; i < s.n_lights; i++) {
         float3 dir_to_light;
-        float4 incoming = light_shine(s, tr, s.lights[i], hit_pos, dir_to_light, rc);
+        float4 incoming = light_shine<OPAQUE_ONLY>(s, tr, s.lights[i], hit_pos, dir_to_light, rc);
         sum = rtx::add4(sum, phong(m, norm, incoming, ray.d, dir_to_light));
     }
     return sum;
