@@ -144,6 +144,7 @@ def cuda_lib():
         lib.rt_render.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(RtFrameStats)]
         lib.rt_tiled_slab_pixels.argtypes = [vp, C.POINTER(RtRenderParams), C.POINTER(C.c_int64)]
         lib.rt_untile.argtypes = [vp, C.POINTER(RtRenderParams), vp, vp]
+        lib.rt_tile_map.argtypes = [i32, i32, i32, i32, i32, i32, vp, C.POINTER(C.c_int64)]
         lib.rt_trace_primary.argtypes = [vp, i32, vp, vp, vp]
         lib.rt_cast_rays.argtypes = [vp, i32, vp, vp, i32, vp, vp, vp]
         lib.rt_debug_cast.argtypes = [vp, i32, i32, i32, C.POINTER(RtHit)]
@@ -331,3 +332,11 @@ def measure_l2_bandwidth(nbytes=32 << 20, iters=50):
     g = C.c_float()
     _check(cuda_lib().rt_measure_l2_bandwidth(nbytes, iters, C.byref(g)), "rt_measure_l2_bandwidth")
     return g.value
+
+
+def tile_map(width, height, tile_w=32, tile_h=16, rank=0, world=1):
+    """Host-only: (slab index per pixel or -1, slab size) — the tile map the kernels use."""
+    idx = np.empty(width * height, np.int64)
+    n = C.c_int64()
+    _check(cuda_lib().rt_tile_map(width, height, tile_w, tile_h, rank, world, idx.ctypes.data, C.byref(n)), "rt_tile_map")
+    return idx.reshape(height, width), n.value

@@ -708,6 +708,26 @@ int rt_tiled_slab_pixels(RtScene* sc, const RtRenderParams* p, int64_t* out) {
     return RT_OK;
 }
 
+int rt_tile_map(int32_t width, int32_t height, int32_t tile_w, int32_t tile_h, int32_t rank, int32_t world,
+                int64_t* slab_index, int64_t* slab_pix) {
+    if (width <= 0 || height <= 0 || !slab_index) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    RtScene dims;  // only width/height are read
+    dims.width = width; dims.height = height;
+    RtRenderParams p;
+    std::memset(&p, 0, sizeof p);
+    p.flags = RT_RENDER_TILED_OUTPUT; p.rank = rank; p.world = world; p.tile_w = tile_w; p.tile_h = tile_h;
+    TileMap tm;
+    if (int rc = make_tilemap(&dims, &p, tm)) return rc;
+    for (long long i = 0; i < (long long)width * height; i++) slab_index[i] = -1;
+    for (int q = 0; q < tm.n_work(); q++)
+        for (int lane = 0; lane < 32; lane++) {
+            int x, y, out;
+            if (tm.locate(q, lane, x, y, out)) slab_index[(long long)y * width + x] = out;
+        }
+    if (slab_pix) *slab_pix = slab_pixels(tm);
+    return RT_OK;
+}
+
 int rt_untile(RtScene* sc, const RtRenderParams* p, const uint32_t* gathered, uint32_t* canvas) {
     if (!sc || !gathered || !canvas) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
     TileMap tm;

@@ -203,6 +203,11 @@ int rt_render(RtScene* scene, const RtRenderParams* params, uint32_t* canvas, Rt
 int rt_tiled_slab_pixels(RtScene* scene, const RtRenderParams* params, int64_t* out_pixels);
 int rt_untile(RtScene* scene, const RtRenderParams* params, const uint32_t* gathered_dev, uint32_t* canvas_dev);
 
+/* Host-only (no GPU needed): the tile map the kernels use. For every pixel (row-major) writes the
+ * index rank `rank` stores it at inside its slab, or -1 if another rank owns the pixel. */
+int rt_tile_map(int32_t width, int32_t height, int32_t tile_w, int32_t tile_h, int32_t rank, int32_t world,
+                int64_t* slab_index, int64_t* slab_pixels);
+
 /* Parity hooks. Primary-ray closest hit per pixel (row-major y*W+x), host outputs. The reference's
  * Isect carries no ids (include/rayprimitives/isect.h:15-24); these are derived the same way the
  * oracle derives them. use_bvh: 1 = BVH8 traversal with the reference's leaf-box rule (the BVH
