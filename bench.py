@@ -290,12 +290,12 @@ def run_ours(a):
     value = rays_all / (ms_dev * 1e-3) / 1e6
     e2e_value = rays_all / (ms_e2e * 1e-3) / 1e6
 
+    # one stats frame for nodes / triangle tests per ray (slower kernels, untimed). Every rank takes
+    # part: the frame contains the all-gather.
+    sst, _ = frame_device(dev_flags | pkg.RT_RENDER_STATS)
     if rank == 0:
         st = [o[0] for o in outs]
         avg = lambda k: sum(s[k] for s in st) / len(st)
-        # one stats frame for nodes / triangle tests per ray (slower kernels, untimed)
-        sflags = (dev_flags | pkg.RT_RENDER_STATS)
-        sst, _ = frame_device(sflags)
         peak, peak_src = hbm_peak()
         l2_peak = pkg.measure_l2_bandwidth(32 << 20, 40)
         # dominant kernel and its algorithmic HBM bytes per launch (DESIGN.md "Roofline"):
