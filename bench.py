@@ -59,49 +59,53 @@ def workload_name(a):
 
 # ------------------------------------------------------------------ clocks
 class ClockSampler:
-    """SM clock and throttle reasons DURING the timed region, sampled through NVML every few
-    milliseconds (the nvidia-smi query of B200_PROFILING.md reads the same counters; its 100 ms
-    period is longer than a whole timed region here)."""
+    """SM clock and throttle reasons DURING the timed region: the nvidia-smi query loop of
+    B200_PROFILING.md in a separate process (an in-process NVML thread was measured to add 2.5 ms to
+    every multi-rank step), spawned before warm-up so that it is already streaming when the timed
+    region starts. Samples are tagged with their arrival time and only those inside the region kept."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index = index
-        self.sm, self.reasons, self.max_mhz = [], set(), None
-        self._stop = threading.Event()
-        self._thread = None
-
-    def _loop(self):
+        self.rows, self.t0, self.t1, self.proc = [], None, None, None
+        period = os.environ.get("BENCH_CLOCK_PERIOD_MS", "20")
         try:
-            import pynvml as nv
-            nv.nvmlInit()
-            h = nv.nvmlDeviceGetHandleByIndex(self.index)
-            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
-            names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
-                     "hw_power_brake_slowdown": 0x80}
-            while not self._stop.is_set():
-                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
-                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                for k, bit in names.items():
-                    if r & bit:
-                        self.reasons.add(k)
-                time.sleep(0.002)
-        except Exception as e:  # no NVML: report that no samples were taken
-            self.error = repr(e)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", period],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
 
     def start(self):
-        self._thread = threading.Thread(target=self._loop, daemon=True)
-        self._thread.start()
-        time.sleep(0.05)
+        self.t0 = time.time()
 
     def stop(self):
-        self._stop.set()
-        if self._thread:
-            self._thread.join(timeout=2)
-        if not self.sm:
-            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0,
-                    "error": getattr(self, "error", None)}
-        s = sorted(self.sm)
-        return {"sm_mhz": s[len(s) // 2], "sm_min_mhz": s[0], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+        self.t1 = time.time()
+        time.sleep(0.05)
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons, n_all = [], [], set(), len(self.rows)
+        for t, r in self.rows:
+            if self.t0 is None or not (self.t0 <= t <= self.t1 + 0.03):
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "samples_outside_region": n_all}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_min_mhz": sm[0], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm), "region_ms": 1e3 * (self.t1 - self.t0)}
 
 
 # ------------------------------------------------------------------ reference CPU arm
@@ -270,10 +274,10 @@ def run_ours(a):
             total_ms = float(t.item())
         return total_ms, out, clocks
 
+    sampler = ClockSampler(local_rank) if rank == 0 and not os.environ.get("BENCH_NO_CLOCKS") else None
     for _ in range(max(a.warmup, 3)):
         frame_device()
         frame_e2e()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     ms_dev, outs, clocks = timed(frame_device, a.steps, sampler)
     ms_e2e, outs_e2e, _ = timed(frame_e2e, a.steps)
 
