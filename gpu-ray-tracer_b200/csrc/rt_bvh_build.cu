@@ -113,9 +113,11 @@ __device__ __forceinline__ unsigned long long expand21(unsigned long long v) {
     return v;
 }
 
+// key_shift: 0 keeps the 63-bit code; 31 keeps its top 32 bits (scenes up to 2^20 triangles: four
+// radix passes instead of eight; equal prefixes fall back to the triangle index like equal codes do).
 __global__ void k_morton(const float* __restrict__ prim_box, const float4* __restrict__ prim_world, int n_prims,
                          const int* __restrict__ bounds, unsigned long long* __restrict__ keys, int* __restrict__ vals,
-                         float* __restrict__ bounds_f) {
+                         float* __restrict__ bounds_f, int key_shift) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     float blo[3], bhi[3];
 #pragma unroll
@@ -140,7 +142,7 @@ __global__ void k_morton(const float* __restrict__ prim_box, const float4* __res
         sc = fminf(fmaxf(sc, 0.0f), 2097151.0f);
         q[k] = (unsigned long long)(unsigned)sc;
     }
-    keys[p] = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
+    keys[p] = ((expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2])) >> key_shift;
     vals[p] = p;
     (void)prim_box;
 }
@@ -190,10 +192,15 @@ __global__ void k_radix_scan(unsigned* __restrict__ hist, int total) {
     }
 }
 
+// FUSED_SCAN: `hist` holds raw per-block counts and every block derives its own global offsets
+// (few blocks: cheaper than a separate single-block scan launch); otherwise `hist` was scanned by
+// k_radix_scan.
+template <bool FUSED_SCAN>
 __global__ void k_radix_scatter(const unsigned long long* __restrict__ keys_in, const int* __restrict__ vals_in, int n,
                                 int shift, const unsigned* __restrict__ hist, int n_blocks,
                                 unsigned long long* __restrict__ keys_out, int* __restrict__ vals_out) {
     __shared__ unsigned wcount[kThreads / 32][kBins];  // per-warp digit counts, then running offsets
+    __shared__ unsigned s_wtot[kThreads / 32];
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < (kThreads / 32) * kBins; i += kThreads) (&wcount[0][0])[i] = 0;
     __syncthreads();
@@ -216,9 +223,30 @@ __global__ void k_radix_scatter(const unsigned long long* __restrict__ keys_in, 
         __syncwarp();
     }
     __syncthreads();
+    unsigned gbase;
+    if (FUSED_SCAN) {  // exclusive scan over (digit, block) in bin-major order, evaluated at (d, blockIdx.x)
+        unsigned d = threadIdx.x, tot = 0, before = 0;
+        for (int b2 = 0; b2 < n_blocks; b2++) {
+            unsigned c = hist[(size_t)d * n_blocks + b2];
+            tot += c;
+            if (b2 < (int)blockIdx.x) before += c;
+        }
+        unsigned x = tot;
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) s_wtot[warp] = x;
+        __syncthreads();
+        unsigned woff = 0;
+        for (int w = 0; w < warp; w++) woff += s_wtot[w];
+        gbase = woff + x - tot + before;
+    } else {
+        gbase = hist[(size_t)threadIdx.x * n_blocks + blockIdx.x];
+    }
     {   // thread d: turn counts into block-local exclusive offsets across warps, plus the global base
         unsigned d = threadIdx.x;
-        unsigned run = hist[(size_t)d * n_blocks + blockIdx.x];
+        unsigned run = gbase;
         for (int w = 0; w < kThreads / 32; w++) {
             unsigned c = wcount[w][d];
             wcount[w][d] = run;
@@ -350,20 +378,28 @@ __device__ void collapse_children(const CollapseArgs& a, int root, int slot_chil
     if (root >= a.n - 1 || node_size(a, root) <= 3) {
         ch[nc++] = root;  // degenerate tree: the whole scene is one leaf
     } else {
-        ch[nc++] = a.left[root];
-        ch[nc++] = a.right[root];
+        // area[i] < 0 marks a child that cannot be opened (<= 3 triangles); sizes and areas are
+        // read once per child so that the selection loop runs out of registers
+        float area[8];
+        auto put = [&](int slot, int id) {
+            ch[slot] = id;
+            area[slot] = node_size(a, id) <= 3 ? -1.0f : half_area(a.node_box + 6 * (size_t)id);
+        };
+        put(0, a.left[root]);
+        put(1, a.right[root]);
+        nc = 2;
         while (nc < 8) {
             int best = -1;
             float best_area = -1.0f;
-            for (int i = 0; i < nc; i++) {
-                if (node_size(a, ch[i]) <= 3) continue;
-                float ar = half_area(a.node_box + 6 * (size_t)ch[i]);
-                if (ar > best_area) { best_area = ar; best = i; }
-            }
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                if (i < nc && area[i] > best_area) { best_area = area[i]; best = i; }
             if (best < 0) break;
             int c = ch[best];
-            ch[best] = a.left[c];
-            ch[nc++] = a.right[c];
+            int l = a.left[c], r = a.right[c];
+            put(best, l);
+            put(nc, r);
+            nc++;
         }
     }
     const float* nb = a.node_box + 6 * (size_t)root;
@@ -596,7 +632,7 @@ namespace rth {
 
 static inline int grid_for(int n, int per = kThreads) { return n > 0 ? (n + per - 1) / per : 1; }
 
-int build_bvh(RtScene* sc, RtBuildStats* stats) {
+int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     Bvh& b = sc->bvh;
     b.valid = false;
     cudaStream_t st = sc->stream;
@@ -640,23 +676,31 @@ int build_bvh(RtScene* sc, RtBuildStats* stats) {
     float* bounds_f = (float*)(bounds_i + 8);
     k_bounds_init<<<1, 32, 0, st>>>(bounds_i);
     k_flatten<<<grid_for(n), kThreads, 0, st>>>(v, b.work.as<int>(), n, b.prim_world.as<float4>(), b.prim_box.as<float>(), bounds_i);
+    const int key_shift = n <= (1 << 20) ? 31 : 0;
+    const int n_passes = key_shift ? 4 : 8;
     k_morton<<<grid_for(n), kThreads, 0, st>>>(b.prim_box.as<float>(), b.prim_world.as<float4>(), n, bounds_i,
-                                               b.keys_a.as<unsigned long long>(), b.vals_a.as<int>(), bounds_f);
+                                               b.keys_a.as<unsigned long long>(), b.vals_a.as<int>(), bounds_f, key_shift);
     sc->kernel_launches += 3;
     unsigned long long* kin = b.keys_a.as<unsigned long long>();
     unsigned long long* kout = b.keys_b.as<unsigned long long>();
     int* vin = b.vals_a.as<int>();
     int* vout = b.vals_b.as<int>();
-    for (int pass = 0; pass < 8; pass++) {
+    const bool fused_scan = nb <= 64;
+    for (int pass = 0; pass < n_passes; pass++) {
         int shift = pass * 8;
         k_radix_hist<<<nb, kThreads, 0, st>>>(kin, n, shift, b.hist.as<unsigned>(), nb);
-        k_radix_scan<<<1, kThreads, 0, st>>>(b.hist.as<unsigned>(), kBins * nb);
-        k_radix_scatter<<<nb, kThreads, 0, st>>>(kin, vin, n, shift, b.hist.as<unsigned>(), nb, kout, vout);
-        sc->kernel_launches += 3;
+        if (fused_scan) {
+            k_radix_scatter<true><<<nb, kThreads, 0, st>>>(kin, vin, n, shift, b.hist.as<unsigned>(), nb, kout, vout);
+            sc->kernel_launches += 2;
+        } else {
+            k_radix_scan<<<1, kThreads, 0, st>>>(b.hist.as<unsigned>(), kBins * nb);
+            k_radix_scatter<false><<<nb, kThreads, 0, st>>>(kin, vin, n, shift, b.hist.as<unsigned>(), nb, kout, vout);
+            sc->kernel_launches += 3;
+        }
         std::swap(kin, kout);
         std::swap(vin, vout);
     }
-    b.sorted_keys = kin;  // 8 passes: back in keys_a / vals_a
+    b.sorted_keys = kin;  // even number of passes: back in keys_a / vals_a
     b.sorted_vals = vin;
     if (n > 1) {
         k_karras<<<grid_for(n - 1), kThreads, 0, st>>>(kin, n, b.left.as<int>(), b.right.as<int>(), b.parent.as<int>(),
@@ -698,18 +742,26 @@ int build_bvh(RtScene* sc, RtBuildStats* stats) {
     void* args[] = {&a};
     RT_CUDA(cudaLaunchCooperativeKernel((void*)k_collapse, dim3(G), dim3(kThreads), args, 0, st));
     sc->kernel_launches++;
-    int result[4];
-    RT_CUDA(cudaMemcpyAsync(result, a.result, sizeof(result), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(sc->h_pinned + 32, a.result, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaEventRecord(sc->ev[1], st));
-    RT_CUDA(cudaStreamSynchronize(st));
     RT_CUDA(cudaGetLastError());
+    b.valid = true;  // provisional until finish_build() has looked at the result
+    b.build_launches = sc->kernel_launches - launches0;
+    if (!sync) return RT_OK;
+    RT_CUDA(cudaStreamSynchronize(st));
+    return finish_build(sc, stats);
+}
+
+int finish_build(RtScene* sc, RtBuildStats* stats) {
+    Bvh& b = sc->bvh;
+    if (b.n_prims == 0) return RT_OK;
+    const int* result = (const int*)(sc->h_pinned + 32);
     b.n_nodes8 = result[0];
-    if (result[1] != n) { set_error("BVH8 collapse emitted a wrong number of triangles"); return RT_ERR_CUDA; }
-    if (result[2] > RT_STACK_SIZE) { set_error("BVH8 deeper than the traversal stack"); return RT_ERR_LIMIT; }
-    b.valid = true;
+    if (result[1] != b.n_prims) { b.valid = false; set_error("BVH8 collapse emitted a wrong number of triangles"); return RT_ERR_CUDA; }
+    if (result[2] > RT_STACK_SIZE) { b.valid = false; set_error("BVH8 deeper than the traversal stack"); return RT_ERR_LIMIT; }
     if (stats) {
         stats->n_bvh8_nodes = b.n_nodes8;
-        stats->kernel_launches = sc->kernel_launches - launches0;
+        stats->kernel_launches = b.build_launches;
         float ms = 0.f;
         RT_CUDA(cudaEventElapsedTime(&ms, sc->ev[0], sc->ev[1]));
         stats->ms_build = ms;

@@ -542,6 +542,9 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
         (rc = upload(sc->d_lights, hs.lights, sc->stream)))
         return fail(rc);
     if (sc->d_counters.reserve(sizeof(unsigned long long) * C_N)) return fail(RT_ERR_OUT_OF_MEMORY);
+    e = cudaHostAlloc((void**)&sc->h_pinned, 64 * sizeof(unsigned long long), cudaHostAllocDefault);
+    if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaHostAlloc", __FILE__, __LINE__));
+    std::memset(sc->h_pinned, 0, 64 * sizeof(unsigned long long));
     if ((rc = upload_instances(sc))) return fail(rc);
     e = cudaStreamSynchronize(sc->stream);
     if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaStreamSynchronize", __FILE__, __LINE__));
@@ -559,6 +562,7 @@ int rt_scene_destroy(RtScene* sc) {
     sc->bvh.release();
     for (int i = 0; i < 10; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
     if (sc->stream) cudaStreamDestroy(sc->stream);
+    if (sc->h_pinned) cudaFreeHost(sc->h_pinned);
     delete sc;
     return RT_OK;
 }
@@ -688,11 +692,13 @@ static int run_mega(RtScene* sc, const SceneView& v, const TileMap& tm, uint32_t
     return RT_OK;
 }
 
-static int ensure_bvh(RtScene* sc, bool rebuild, RtFrameStats* stats) {
+// built == nullptr: blocking build. Otherwise the build is only enqueued and *built tells the
+// caller to run rth::finish_build() after its own stream synchronisation.
+static int ensure_bvh(RtScene* sc, bool rebuild, bool* built) {
+    if (built) *built = false;
     if (sc->bvh.valid && !rebuild) return RT_OK;
-    RtBuildStats bs;
-    if (int rc = rth::build_bvh(sc, &bs)) return rc;
-    if (stats) stats->ms_build = bs.ms_build;
+    if (int rc = rth::build_bvh(sc, nullptr, built == nullptr)) return rc;
+    if (built) *built = true;
     return RT_OK;
 }
 
@@ -754,9 +760,10 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     int launches0 = sc->kernel_launches;
     const bool no_bvh = (p.flags & RT_RENDER_NO_BVH) != 0;
     const bool want_stats = (p.flags & RT_RENDER_STATS) != 0;
+    bool built = false;
     RT_CUDA(cudaEventRecord(sc->ev[2], st));
     if (!no_bvh) {
-        if (int rc = ensure_bvh(sc, (p.flags & RT_RENDER_REBUILD_BVH) != 0, &fs)) return rc;
+        if (int rc = ensure_bvh(sc, (p.flags & RT_RENDER_REBUILD_BVH) != 0, &built)) return rc;
     } else {
         if (int rc = rth::update_instance_boxes(sc)) return rc;
     }
@@ -779,12 +786,17 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     else rc = run_wavefront<TR_BVH_BOX, false>(sc, v, tm, dcanvas, &waves);
     if (rc) return rc;
     RT_CUDA(cudaEventRecord(sc->ev[4], st));
-    unsigned long long host_ctr[C_N];
-    RT_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof host_ctr, cudaMemcpyDeviceToHost, st));
+    unsigned long long* host_ctr = sc->h_pinned;
+    RT_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof(unsigned long long) * C_N, cudaMemcpyDeviceToHost, st));
     if (!(p.flags & RT_RENDER_CANVAS_DEVICE))
         RT_CUDA(cudaMemcpyAsync(canvas, dcanvas, 4 * (size_t)out_pixels, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaEventRecord(sc->ev[5], st));
     RT_CUDA(cudaStreamSynchronize(st));
+    if (built) {
+        RtBuildStats bs;
+        if (int rc2 = rth::finish_build(sc, &bs)) return rc2;
+        fs.ms_build = bs.ms_build;
+    }
     fs.rays_primary = host_ctr[C_RAYS_PRIMARY];
     fs.rays_shadow = host_ctr[C_RAYS_SHADOW];
     fs.rays_secondary = host_ctr[C_RAYS_SECONDARY];

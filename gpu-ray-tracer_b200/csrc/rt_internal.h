@@ -37,6 +37,7 @@ struct Bvh {
     int n_prims = 0;
     int n_bvh2_nodes = 0;
     int n_nodes8 = 0;
+    int build_launches = 0;
     DevBuf prim_world;   // float4[3*n_prims]  world-space triangles in input (instance-major) order
     DevBuf prim_box;     // float[6*n_prims]   inflated prim AABBs
     DevBuf scene_bounds; // float[6] (+ atomics scratch)
@@ -73,12 +74,15 @@ struct RtScene {
     bool boxes_valid = false;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    unsigned long long* h_pinned = nullptr;  // 64 x u64 of pinned host memory: [0,32) frame counters, [32,36) build result
     int sm_count = 148;
     int kernel_launches = 0;  // running count, sampled around each API call
 };
 
 namespace rth {
-int build_bvh(RtScene* sc, RtBuildStats* stats);          // rt_bvh.cu
+// sync = false: everything is enqueued, finish_build() must run after the next stream synchronisation
+int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync = true);   // rt_bvh_build.cu
+int finish_build(RtScene* sc, RtBuildStats* stats);
 int update_instance_boxes(RtScene* sc);                    // rt_engine.cu
 rtd::SceneView make_view(const RtScene* sc, bool with_bvh);
 }  // namespace rth

@@ -381,7 +381,9 @@ OrBvh* or_bvh_build(const RtSceneDesc* d) {
     if (n == 0) return b;
     flatten(b, d);
     KeyIdx* ki = (KeyIdx*)malloc(sizeof(KeyIdx) * (size_t)n);
-    for (int p = 0; p < n; p++) { ki[p].key = morton_of(b, p); ki[p].idx = p; }
+    /* scenes up to 2^20 triangles keep the top 32 bits of the 63-bit code (four radix passes on the GPU) */
+    int key_shift = n <= (1 << 20) ? 31 : 0;
+    for (int p = 0; p < n; p++) { ki[p].key = morton_of(b, p) >> key_shift; ki[p].idx = p; }
     qsort(ki, (size_t)n, sizeof(KeyIdx), cmp_keyidx);
     for (int j = 0; j < n; j++) { b->morton[j] = ki[j].key; b->perm[j] = ki[j].idx; }
     free(ki);
