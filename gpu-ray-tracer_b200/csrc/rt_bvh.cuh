@@ -137,15 +137,51 @@ RT_HD RayPrep ray_prep(const rtx::Ray& r) {
 
 RT_HD unsigned byte_of(unsigned w, int i) { return (w >> (8 * i)) & 0xffu; }
 
+// Byte i of w as the float 1 + q * 2^-15 (q in mantissa bits 8..15): one PRMT on the device, no
+// integer-to-float conversion (I2F issues at a quarter of the FFMA rate and was the co-bottleneck
+// of the node test). With A = 2^15 * a and B = b - A, fma(f, A, B) = q * a + b.
+// `one` must hold 0x3f800000 where the compiler cannot fold it (SceneView::one_bits, a kernel
+// parameter): PRMT takes
+// a single immediate, and with the constant as the immediate the selector was re-materialised from
+// a uniform register for every byte (55 extra MOV/IMAD per node in the first version).
+template <int I>
+RT_HD float qfloat(unsigned w, unsigned one) {
+#ifdef __CUDA_ARCH__
+    unsigned r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(one), "n"(0x7604 | (I << 4)));
+    return __uint_as_float(r);
+#else
+    return hd_u2f(one | (byte_of(w, I) << 8));
+#endif
+}
+// byte I of w, zero-extended: one PRMT with an immediate selector
+template <int I>
+RT_HD unsigned qbyte(unsigned w) {
+#ifdef __CUDA_ARCH__
+    unsigned r;
+    asm("prmt.b32 %0, %1, 0, %2;" : "=r"(r) : "r"(w), "n"(0x4440 | I));
+    return r;
+#else
+    return byte_of(w, I);
+#endif
+}
+
 // Tests the 8 quantised child boxes of one node. Returns the hit mask in traversal layout:
 // bits 24..31 inner children at position 24 + (slot ^ octinv), bits 0..23 leaf triangles.
+// Conservative: the entry distance is biased down and the exit distance up by more than the
+// rounding of the fused multiply-adds, so a box the exact slab test would hit is never missed.
 RT_HD unsigned node_children_hits(const uint4 q0, const uint4 q1, const uint4 q2, const uint4 q3, const uint4 q4,
-                                  const RayPrep& rp, float tcull) {
+                                  const RayPrep& rp, float tcull, const unsigned one) {
     float px = hd_u2f(q0.x), py = hd_u2f(q0.y), pz = hd_u2f(q0.z);
-    float sx = hd_u2f((q0.w & 0xffu) << 23), sy = hd_u2f(((q0.w >> 8) & 0xffu) << 23),
-          sz = hd_u2f(((q0.w >> 16) & 0xffu) << 23);
-    float aix = sx * rp.idir.x, aiy = sy * rp.idir.y, aiz = sz * rp.idir.z;
-    float aox = (px - rp.o.x) * rp.idir.x, aoy = (py - rp.o.y) * rp.idir.y, aoz = (pz - rp.o.z) * rp.idir.z;
+    // 2^15 * 2^(e-127): exponent byte + 15
+    float sx = hd_u2f(((q0.w & 0xffu) + 15u) << 23), sy = hd_u2f((((q0.w >> 8) & 0xffu) + 15u) << 23),
+          sz = hd_u2f((((q0.w >> 16) & 0xffu) + 15u) << 23);
+    float Ax = sx * rp.idir.x, Ay = sy * rp.idir.y, Az = sz * rp.idir.z;
+    float bx = (px - rp.o.x) * rp.idir.x, by = (py - rp.o.y) * rp.idir.y, bz = (pz - rp.o.z) * rp.idir.z;
+    float Bx = bx - Ax, By = by - Ay, Bz = bz - Az;
+    const float kSlack = 2.384185791015625e-07f;  // 2^-22
+    float dx = (fabsf(Ax) + fabsf(bx)) * kSlack, dy = (fabsf(Ay) + fabsf(by)) * kSlack, dz = (fabsf(Az) + fabsf(bz)) * kSlack;
+    float B0x = Bx - dx, B1x = Bx + dx, B0y = By - dy, B1y = By + dy, B0z = Bz - dz, B1z = Bz + dz;
     bool nx = rp.idir.x < 0.0f, ny = rp.idir.y < 0.0f, nz = rp.idir.z < 0.0f;
     unsigned hits = 0;
 #pragma unroll
@@ -156,22 +192,24 @@ RT_HD unsigned node_children_hits(const uint4 q0, const uint4 q1, const uint4 q2
         unsigned nearx = nx ? hix : lox, farx = nx ? lox : hix;
         unsigned neary = ny ? hiy : loy, fary = ny ? loy : hiy;
         unsigned nearz = nz ? hiz : loz, farz = nz ? loz : hiz;
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            unsigned meta = byte_of(meta4, i);
-            float t0x = fmaf((float)byte_of(nearx, i), aix, aox), t1x = fmaf((float)byte_of(farx, i), aix, aox);
-            float t0y = fmaf((float)byte_of(neary, i), aiy, aoy), t1y = fmaf((float)byte_of(fary, i), aiy, aoy);
-            float t0z = fmaf((float)byte_of(nearz, i), aiz, aoz), t1z = fmaf((float)byte_of(farz, i), aiz, aoz);
-            float tmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));
-            float tmax = fminf(fminf(t1x, t1y), fminf(t1z, tcull));
-            // 1 + 2^-21: slack for the rounding of the six fused multiply-adds (robust slab test)
-            bool hit = meta != 0u && tmin <= tmax * 1.0000005f + 1e-30f;
-            if (hit) {
-                unsigned is_inner = ((meta & 0x18u) == 0x18u) ? 1u : 0u;  // offsets 24..31 mark inner slots
-                unsigned pos = is_inner ? ((meta ^ rp.octinv) & 31u) : (meta & 31u);
-                hits |= (meta >> 5) << pos;
-            }
+        // four children at once: inner slots (offsets 24..31) get their position XORed with the
+        // ray octant, leaves keep their triangle offset; empty slots have zero child bits
+        unsigned is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        unsigned inner_mask4 = (is_inner4 >> 4) * 0xffu;
+        unsigned bit_index4 = (meta4 ^ (rp.octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+        unsigned child_bits4 = (meta4 >> 5) & 0x07070707u;
+#define RT_CHILD(I)                                                                                          \
+        {                                                                                                    \
+            float t0x = fmaf(qfloat<I>(nearx, one), Ax, B0x), t1x = fmaf(qfloat<I>(farx, one), Ax, B1x);      \
+            float t0y = fmaf(qfloat<I>(neary, one), Ay, B0y), t1y = fmaf(qfloat<I>(fary, one), Ay, B1y);      \
+            float t0z = fmaf(qfloat<I>(nearz, one), Az, B0z), t1z = fmaf(qfloat<I>(farz, one), Az, B1z);      \
+            float tmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));                                           \
+            float tmax = fminf(fminf(t1x, t1y), fminf(t1z, tcull));                                          \
+            unsigned bits = qbyte<I>(child_bits4) << qbyte<I>(bit_index4);                                   \
+            if (tmin <= tmax) hits |= bits;                                                                  \
         }
+        RT_CHILD(0) RT_CHILD(1) RT_CHILD(2) RT_CHILD(3)
+#undef RT_CHILD
     }
     return hits;
 }
@@ -205,7 +243,7 @@ RT_HD bool bvh_query(const SceneView& s, const rtx::Ray& r, bool use_box, float 
             const uint4* np = s.nodes + (size_t)(ng.x + rel) * 5;
             uint4 q0 = ldg4u(np), q1 = ldg4u(np + 1), q2 = ldg4u(np + 2), q3 = ldg4u(np + 3), q4 = ldg4u(np + 4);
             if (st) st->nodes++;
-            unsigned h = node_children_hits(q0, q1, q2, q3, q4, rp, tcull);
+            unsigned h = node_children_hits(q0, q1, q2, q3, q4, rp, tcull, s.one_bits);
             ng.x = q1.x; ng.y = (h & 0xff000000u) | (q0.w >> 24);
             tg.x = q1.y; tg.y = h & 0x00ffffffu;
         } else {

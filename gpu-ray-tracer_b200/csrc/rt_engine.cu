@@ -260,6 +260,65 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
     flush_counts(ctr, rc, ts, STATS);
 }
 
+// ---------------------------------------------------------------- wave 0, all-opaque scenes: split shading
+// k_shade keeps ray setup, traversal, the exact tests and Phong in one instruction stream (50 KB of
+// SASS, stall_no_instruction 2.6 warps per issue). When no material spawns secondary rays the same
+// work runs as three tight kernels: shadow-ray generation, any-hit traversal, Phong + pack.
+struct ShadowRec { float4 o_maxt, d; };  // 32 bytes; stored light-major: index = light * n_hits + hit
+
+__global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, const unsigned long long* ctr, const HitRec* hitq,
+                                                        ShadowRec* shq) {
+    const int n = (int)ctr[C_HITQ];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        HitRec rec = hitq[i];
+        rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
+        float3 hit_pos = rtx::ray_at(r, rec.t);
+        for (int l = 0; l < s.n_lights; l++) {
+            float3 dir;
+            float max_t, da;
+            light_setup(s, s.lights[l], hit_pos, dir, max_t, da);
+            rtx::Ray cur = shadow_ray(hit_pos, dir);
+            ShadowRec q;
+            q.o_maxt = make_float4(cur.o.x, cur.o.y, cur.o.z, max_t);
+            q.d = make_float4(cur.d.x, cur.d.y, cur.d.z, 0.f);
+            shq[(size_t)l * n + i] = q;
+        }
+    }
+}
+
+template <int MODE, bool STATS>
+__global__ void __launch_bounds__(kThreads) k_shadow(SceneView s, unsigned long long* ctr, const ShadowRec* shq,
+                                                    unsigned char* occl) {
+    TravStats ts = {0, 0, 0};
+    RayCounts rc = {0, 0, 0};
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
+    const long long n = (long long)ctr[C_HITQ] * s.n_lights;
+    for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (long long)gridDim.x * blockDim.x) {
+        ShadowRec q = shq[j];
+        rtx::Ray r;
+        r.o = rtx::mk3(q.o_maxt.x, q.o_maxt.y, q.o_maxt.z);
+        r.d = rtx::mk3(q.d.x, q.d.y, q.d.z);
+        rc.shadow++;
+        occl[j] = tr.occluded(r, q.o_maxt.w) ? 1 : 0;
+    }
+    flush_counts(ctr, rc, ts, STATS);
+}
+
+__global__ void __launch_bounds__(kThreads) k_resolve(SceneView s, const unsigned long long* ctr, const HitRec* hitq,
+                                                     const unsigned char* occl, uint32_t* canvas) {
+    const int n = (int)ctr[C_HITQ];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        HitRec rec = hitq[i];
+        Hit h;
+        h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
+        rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
+        const MatRec& m = s.mats[s.tris[h.tri].mat];
+        float3 nrm = hit_normal(s, h);
+        float4 c = illuminate_resolved(s, r, h.t, nrm, m, [&](int l) { return occl[(size_t)l * n + i] != 0; });
+        canvas[rec.out_index] = rtx::pack_color(c);
+    }
+}
+
 // ---------------------------------------------------------------- waves >= 1: bounce
 template <int MODE, bool STATS>
 __global__ void __launch_bounds__(kThreads) k_bounce(SceneView s, unsigned long long* ctr, int ctr_in, int ctr_out,
@@ -454,6 +513,7 @@ SceneView make_view(const RtScene* sc, bool with_bvh) {
     v.width = sc->width; v.height = sc->height;
     v.any_refractive = sc->any_refractive;
     v.any_secondary = sc->any_secondary;
+    v.one_bits = 0x3f800000u;
     return v;
 }
 
@@ -557,7 +617,7 @@ int rt_scene_destroy(RtScene* sc) {
     if (sc->stream) cudaStreamSynchronize(sc->stream);
     rth::DevBuf* all[] = {&sc->d_verts, &sc->d_norms, &sc->d_tris, &sc->d_meshes, &sc->d_insts, &sc->d_mats, &sc->d_lights,
                           &sc->d_mesh_box, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
-                          &sc->d_queue_b, &sc->d_ids};
+                          &sc->d_queue_b, &sc->d_ids, &sc->d_shadowq, &sc->d_occl};
     for (rth::DevBuf* b : all) b->release();
     sc->bvh.release();
     for (int i = 0; i < 10; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
@@ -627,6 +687,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     sc->kernel_launches++;
     RT_CUDA(cudaEventRecord(sc->ev[6], st));
     *waves = 1;
+    sc->split_shade_used = false;
     int path_stride = (int)(sizeof(PathHead) + sizeof(Frame) * (size_t)(v.depth + 1));
     unsigned long long n_hits = 0;
     if (v.any_secondary && v.depth > 0) {
@@ -637,7 +698,21 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         if (sc->d_paths.reserve(cap * path_stride) || sc->d_queue_a.reserve(4 * cap) || sc->d_queue_b.reserve(4 * cap))
             return RT_ERR_OUT_OF_MEMORY;
     }
-    if (!v.any_secondary) {  // no Kr / Kt anywhere: any-hit shadow rays only, every pixel ends here
+    if (!v.any_secondary && !sc->fused_shade) {
+        // no Kr / Kt anywhere: every pixel ends after its shadow rays -> gen / any-hit traverse / resolve
+        size_t cap = (size_t)std::max<long long>(n_pix, 1) * (size_t)std::max(v.n_lights, 1);
+        if (sc->d_shadowq.reserve(sizeof(ShadowRec) * cap) || sc->d_occl.reserve(cap)) return RT_ERR_OUT_OF_MEMORY;
+        k_shadow_gen<<<persistent_grid(k_shadow_gen, sc->sm_count), kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(),
+                                                                                      sc->d_shadowq.as<ShadowRec>());
+        RT_CUDA(cudaEventRecord(sc->ev[8], st));
+        k_shadow<MODE, STATS><<<persistent_grid(k_shadow<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
+            v, ctr, sc->d_shadowq.as<ShadowRec>(), sc->d_occl.as<unsigned char>());
+        RT_CUDA(cudaEventRecord(sc->ev[9], st));
+        k_resolve<<<persistent_grid(k_resolve, sc->sm_count), kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(),
+                                                                                sc->d_occl.as<unsigned char>(), canvas);
+        sc->kernel_launches += 2;
+        sc->split_shade_used = true;
+    } else if (!v.any_secondary) {
         int g1 = persistent_grid(k_shade<MODE, STATS, true>, sc->sm_count);
         k_shade<MODE, STATS, true><<<g1, kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, 0, nullptr);
     } else {
@@ -760,6 +835,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     int launches0 = sc->kernel_launches;
     const bool no_bvh = (p.flags & RT_RENDER_NO_BVH) != 0;
     const bool want_stats = (p.flags & RT_RENDER_STATS) != 0;
+    sc->fused_shade = (p.flags & RT_RENDER_FUSED_SHADE) != 0;
     bool built = false;
     RT_CUDA(cudaEventRecord(sc->ev[2], st));
     if (!no_bvh) {
@@ -809,6 +885,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     if (wavefront) {
         RT_CUDA(cudaEventElapsedTime(&fs.ms_primary, sc->ev[3], sc->ev[6]));
         RT_CUDA(cudaEventElapsedTime(&fs.ms_shade, sc->ev[6], sc->ev[7]));
+        if (sc->split_shade_used) RT_CUDA(cudaEventElapsedTime(&fs.ms_shadow, sc->ev[8], sc->ev[9]));
         RT_CUDA(cudaEventElapsedTime(&fs.ms_bounce, sc->ev[7], sc->ev[4]));
         fs.n_hits = (int32_t)host_ctr[C_HITQ];
     }

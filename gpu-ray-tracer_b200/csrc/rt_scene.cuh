@@ -59,6 +59,7 @@ struct SceneView {
     int width, height;
     int any_refractive;  // some material has Kt > 0: shadow rays need the closest-hit loop
     int any_secondary;   // some material has Kr > 0 or Kt > 0
+    unsigned one_bits;   // 0x3f800000, kept opaque to the compiler (rt_bvh.cuh qfloat)
 };
 
 // create_boxes (src/raytracer.cu:54-74): world box of an instance = from_local(from_local(mesh box,

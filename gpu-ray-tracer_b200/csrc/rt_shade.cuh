@@ -22,17 +22,16 @@ RT_HD float dist_atten(const SceneView& s, float dist) {
     return quad < 1.0f ? 1.0f : 1.0f / quad;
 }
 
-// Light::attenuate (light.cu:29-61): shadow ray from hit + THRESHOLD*L, a loop of CLOSEST-hit
-// casts that walks through refractive occluders. When no material in the scene is refractive the
-// loop body runs once and only asks "is the closest hit within max_t", which an any-hit query
-// answers exactly, so that case terminates on the first accepted occluder.
+// Light::attenuate (light.cu:29-61): `cur` is the shadow ray (see shadow_ray()), then a loop of
+// CLOSEST-hit casts that walks through refractive occluders. When no material in the scene is
+// refractive the loop body runs once and only asks "is the closest hit within max_t", which an
+// any-hit query answers exactly, so that case terminates on the first accepted occluder.
 // OPAQUE_ONLY (compile time): the caller guarantees !s.any_refractive, so the closest-hit loop is
-// not even instantiated (k_shade's code size and registers).
+// not even instantiated (code size and registers).
 template <bool OPAQUE_ONLY, class Tracer>
-RT_HD float4 light_attenuate(const SceneView& s, const Tracer& tr, const LightRec& L, const rtx::Ray& to_light,
-                             float max_t, RayCounts& rc) {
+RT_HD float4 light_attenuate(const SceneView& s, const Tracer& tr, const LightRec& L, rtx::Ray cur, float max_t,
+                             RayCounts& rc) {
     float4 rv = L.color;
-    rtx::Ray cur = rtx::ray_make(rtx::ray_at(to_light, RT_THR), to_light.d);
     if (OPAQUE_ONLY || !s.any_refractive) {
         rc.shadow++;
         return tr.occluded(cur, max_t) ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : rv;
@@ -55,14 +54,12 @@ RT_HD float4 light_attenuate(const SceneView& s, const Tracer& tr, const LightRe
     }
 }
 
-// PointLight::shine / DirLight::shine (light.cu:63-77). One call site of light_attenuate for both
-// kinds (the traversal is inlined there); the arithmetic per kind is the reference's.
-template <bool OPAQUE_ONLY, class Tracer>
-RT_HD float4 light_shine(const SceneView& s, const Tracer& tr, const LightRec& L, float3 hit_pos, float3& dir_to_light,
-                         RayCounts& rc) {
-    float max_t = INFINITY, da = 1.0f;
-    const bool point = L.kind == 0;
-    if (point) {
+// PointLight::shine / DirLight::shine (light.cu:63-77), the part before attenuate(): direction to
+// the light, distance limit and distance attenuation.
+RT_HD void light_setup(const SceneView& s, const LightRec& L, float3 hit_pos, float3& dir_to_light, float& max_t, float& da) {
+    max_t = INFINITY;
+    da = 1.0f;
+    if (L.kind == 0) {
         float3 disp = rtx::sub3(L.v, hit_pos);
         float dist = rtx::len3(disp);
         da = dist_atten(s, dist);
@@ -71,9 +68,22 @@ RT_HD float4 light_shine(const SceneView& s, const Tracer& tr, const LightRec& L
     } else {
         dir_to_light = rtx::neg3(L.v);
     }
+}
+// The Ray handed to attenuate() (Ray ctor normalises) and the shadow ray attenuate() starts from
+// it: origin moved THRESHOLD along the direction, direction normalised once more (light.cu:31-33).
+RT_HD rtx::Ray shadow_ray(float3 hit_pos, float3 dir_to_light) {
     rtx::Ray to_light = rtx::ray_make(hit_pos, dir_to_light);
-    float4 a = light_attenuate<OPAQUE_ONLY>(s, tr, L, to_light, max_t, rc);
-    return point ? rtx::scale4(da, a) : a;
+    return rtx::ray_make(rtx::ray_at(to_light, RT_THR), to_light.d);
+}
+
+// One call site of light_attenuate for both kinds (the traversal is inlined there).
+template <bool OPAQUE_ONLY, class Tracer>
+RT_HD float4 light_shine(const SceneView& s, const Tracer& tr, const LightRec& L, float3 hit_pos, float3& dir_to_light,
+                         RayCounts& rc) {
+    float max_t, da;
+    light_setup(s, L, hit_pos, dir_to_light, max_t, da);
+    float4 a = light_attenuate<OPAQUE_ONLY>(s, tr, L, shadow_ray(hit_pos, dir_to_light), max_t, rc);
+    return L.kind == 0 ? rtx::scale4(da, a) : a;
 }
 
 // phong (phong.cu:14-33); the texture branch is empty in the reference.
@@ -95,6 +105,25 @@ RT_HD float4 illuminate(const SceneView& s, const Tracer& tr, const rtx::Ray& ra
     for (int i = 0; i < s.n_lights; i++) {
         float3 dir_to_light;
         float4 incoming = light_shine<OPAQUE_ONLY>(s, tr, s.lights[i], hit_pos, dir_to_light, rc);
+        sum = rtx::add4(sum, phong(m, norm, incoming, ray.d, dir_to_light));
+    }
+    return sum;
+}
+
+// illuminate for the split pipeline of all-opaque scenes: the shadow rays of this hit were traced
+// by k_shadow; occluded(i) tells whether light i is blocked. Same operations as illuminate<true>.
+template <class Occluded>
+RT_HD float4 illuminate_resolved(const SceneView& s, const rtx::Ray& ray, float t, float3 norm, const MatRec& m,
+                                 Occluded occluded) {
+    float4 sum = rtx::add4(m.Ke, rtx::mul4(m.Ka, s.ambience));
+    float3 hit_pos = rtx::ray_at(ray, t);
+    for (int i = 0; i < s.n_lights; i++) {
+        const LightRec& L = s.lights[i];
+        float3 dir_to_light;
+        float max_t, da;
+        light_setup(s, L, hit_pos, dir_to_light, max_t, da);
+        float4 a = occluded(i) ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : L.color;
+        float4 incoming = L.kind == 0 ? rtx::scale4(da, a) : a;
         sum = rtx::add4(sum, phong(m, norm, incoming, ray.d, dir_to_light));
     }
     return sum;

@@ -122,7 +122,8 @@ enum {
     RT_RENDER_CANVAS_DEVICE = 4, /* `canvas` is a device pointer (no D2H copy) */
     RT_RENDER_SORT_RAYS = 8,     /* sort secondary rays between bounces */
     RT_RENDER_TILED_OUTPUT = 16, /* write only this rank's tiles, compacted (multi-GPU) */
-    RT_RENDER_STATS = 32         /* count nodes / triangle tests per frame (slower kernels) */
+    RT_RENDER_STATS = 32,        /* count nodes / triangle tests per frame (slower kernels) */
+    RT_RENDER_FUSED_SHADE = 64   /* all-opaque scenes: one fused shading kernel instead of gen / shadow / resolve */
 };
 
 typedef struct RtRenderParams {
@@ -150,6 +151,7 @@ typedef struct RtFrameStats {
     float ms_shade;           /* CUDA-event time of k_shade (shadow-ray traversal + Phong) */
     float ms_bounce;          /* CUDA-event time of all k_bounce waves (incl. the per-wave read-backs) */
     int32_t n_hits;           /* primary rays that hit something */
+    float ms_shadow;          /* CUDA-event time of k_shadow (any-hit traversal of the shadow-ray queue; part of ms_shade) */
 } RtFrameStats;
 
 typedef struct RtBuildStats {

@@ -38,6 +38,7 @@ static void fill_view(EmuScene* e, const RtSceneDesc* d, const uint32_t* nodes8,
     v.dist_c0 = d->env.dist_atten[0]; v.dist_c1 = d->env.dist_atten[1]; v.dist_c2 = d->env.dist_atten[2];
     v.depth = d->env.depth; v.width = d->width; v.height = d->height;
     v.any_refractive = e->hs.any_refractive; v.any_secondary = e->hs.any_secondary;
+    v.one_bits = 0x3f800000u;
 }
 
 template <class F>

@@ -108,6 +108,9 @@ def test_canvas_gpu_semantics_vs_oracle(pkg, scenes, name):
     # update_scene: the reference-shaped call
     c3 = s.update_scene(16, True)
     assert (c3 == oc).all()
+    # all-opaque scenes shade through gen / shadow / resolve by default; the fused kernel agrees
+    c4, st4 = s.render(flags=pkg.RT_RENDER_FUSED_SHADE)
+    assert (c4 == oc).all() and st4["rays_total"] == ost["rays_total"]
 
 
 @pytest.mark.parametrize("name", ["world1", "world4", "world16", "world8_stress"])
