@@ -368,80 +368,146 @@ __device__ __forceinline__ float half_area(const float* b) {
     return (dx * dy + dy * dz) + dz * dx;
 }
 
-// Children of one BVH8 node and their slots. Rule: start from the two BVH2 children; while fewer
-// than 8, replace the child of largest half-area among those covering more than 3 triangles by
-// its own two children (left in place, right appended); ties go to the earlier child. Slots:
-// greedy assignment maximising (child centroid - node centroid) . octant direction of the slot.
-__device__ void collapse_children(const CollapseArgs& a, int root, int slot_child[8], int& n_inner, int& n_leaf_prims) {
-    int ch[8];
-    int nc = 0;
-    if (root >= a.n - 1 || node_size(a, root) <= 3) {
-        ch[nc++] = root;  // degenerate tree: the whole scene is one leaf
+// ---- 8 lanes per BVH8 node (4 nodes per warp). Every shuffle below is executed by all 32 lanes
+// with uniform trip counts; `width = 8` keeps the exchange inside one node's lane group. ----
+#define FULL 0xffffffffu
+__device__ __forceinline__ int g_shfl(int v, int src) { return __shfl_sync(FULL, v, src, 8); }
+__device__ __forceinline__ float g_shflf(float v, int src) { return __shfl_sync(FULL, v, src, 8); }
+__device__ __forceinline__ int g_sum(int v) {
+    v += __shfl_xor_sync(FULL, v, 1, 8);
+    v += __shfl_xor_sync(FULL, v, 2, 8);
+    v += __shfl_xor_sync(FULL, v, 4, 8);
+    return v;
+}
+__device__ __forceinline__ unsigned g_or(unsigned v) {
+    v |= __shfl_xor_sync(FULL, v, 1, 8);
+    v |= __shfl_xor_sync(FULL, v, 2, 8);
+    v |= __shfl_xor_sync(FULL, v, 4, 8);
+    return v;
+}
+// exclusive prefix sum over the 8 lanes of a group
+__device__ __forceinline__ int g_excl(int v, int j) {
+    int x = v;
+    for (int o = 1; o < 8; o <<= 1) {
+        int y = __shfl_up_sync(FULL, x, o, 8);
+        if (j >= o) x += y;
+    }
+    return x - v;
+}
+// argmax of (val, lowest lane on ties) over the group; returns the winning lane, val_out its value
+__device__ __forceinline__ int g_argmax(float val, int j, float& val_out) {
+    int idx = j;
+    for (int o = 1; o < 8; o <<= 1) {
+        float ov = __shfl_xor_sync(FULL, val, o, 8);
+        int oi = __shfl_xor_sync(FULL, idx, o, 8);
+        if (ov > val || (ov == val && oi < idx)) { val = ov; idx = oi; }
+    }
+    val_out = val;
+    return idx;
+}
+
+// Children of one BVH8 node and their slots, computed by the 8 lanes of a group (lane j holds list
+// position j). Rule (identical to the sequential host build): start from the two BVH2 children;
+// while fewer than 8, replace the child of largest half-area among those covering more than 3
+// triangles by its own two children (left in place, right appended); ties go to the earlier child.
+// Slots: greedy assignment maximising (child centroid - node centroid) . octant direction of the
+// slot, scanning children then slots with a strict comparison. On return lane s holds the BVH2 id
+// in slot s (or -1), and n_inner / n_leaf_prims are group-uniform.
+__device__ int collapse_children_g(const CollapseArgs& a, int root, int j, int& n_inner, int& n_leaf_prims) {
+    int ch = -1;          // BVH2 id at list position j
+    float area = -2.0f;   // -2: empty position, -1: cannot be opened, >= 0: half-area
+    int nc;
+    auto load = [&](int id) {
+        ch = id;
+        area = node_size(a, id) <= 3 ? -1.0f : half_area(a.node_box + 6 * (size_t)id);
+    };
+    const bool single = root >= a.n - 1 || node_size(a, root) <= 3;  // whole scene is one leaf
+    if (single) {
+        if (j == 0) { ch = root; area = -1.0f; }
+        nc = 1;
     } else {
-        // area[i] < 0 marks a child that cannot be opened (<= 3 triangles); sizes and areas are
-        // read once per child so that the selection loop runs out of registers
-        float area[8];
-        auto put = [&](int slot, int id) {
-            ch[slot] = id;
-            area[slot] = node_size(a, id) <= 3 ? -1.0f : half_area(a.node_box + 6 * (size_t)id);
-        };
-        put(0, a.left[root]);
-        put(1, a.right[root]);
+        if (j == 0) load(a.left[root]);
+        if (j == 1) load(a.right[root]);
         nc = 2;
-        while (nc < 8) {
-            int best = -1;
-            float best_area = -1.0f;
-#pragma unroll
-            for (int i = 0; i < 8; i++)
-                if (i < nc && area[i] > best_area) { best_area = area[i]; best = i; }
-            if (best < 0) break;
-            int c = ch[best];
-            int l = a.left[c], r = a.right[c];
-            put(best, l);
-            put(nc, r);
+    }
+#pragma unroll 1
+    for (int it = 0; it < 6; it++) {
+        float best_area;
+        int best = g_argmax(area, j, best_area);
+        int c = g_shfl(ch, best);
+        bool open = best_area >= 0.0f && nc < 8;  // group-uniform
+        if (open) {
+            if (j == best) load(a.left[c]);
+            if (j == nc) load(a.right[c]);
             nc++;
         }
     }
-    const float* nb = a.node_box + 6 * (size_t)root;
-    float ncx = (nb[0] + nb[3]) * 0.5f, ncy = (nb[1] + nb[4]) * 0.5f, ncz = (nb[2] + nb[5]) * 0.5f;
-    float cost[8][8];
-    for (int i = 0; i < nc; i++) {
-        const float* cb = a.node_box + 6 * (size_t)ch[i];
-        float dx = (cb[0] + cb[3]) * 0.5f - ncx, dy = (cb[1] + cb[4]) * 0.5f - ncy, dz = (cb[2] + cb[5]) * 0.5f - ncz;
-        for (int s = 0; s < 8; s++)
-            cost[i][s] = (((s & 1) ? dx : -dx) + ((s & 2) ? dy : -dy)) + ((s & 4) ? dz : -dz);
-    }
-    for (int s = 0; s < 8; s++) slot_child[s] = -1;
-    unsigned child_done = 0, slot_done = 0;
-    for (int it = 0; it < nc; it++) {
-        int bi = -1, bs = -1;
-        float bc = -INFINITY;
-        for (int i = 0; i < nc; i++) {
-            if (child_done & (1u << i)) continue;
-            for (int s = 0; s < 8; s++) {
-                if (slot_done & (1u << s)) continue;
-                if (bi < 0 || cost[i][s] > bc) { bc = cost[i][s]; bi = i; bs = s; }
-            }
+    // cost row of this lane's child
+    float cost[8];
+    {
+        const float* nb = a.node_box + 6 * (size_t)root;
+        float ncx = (nb[0] + nb[3]) * 0.5f, ncy = (nb[1] + nb[4]) * 0.5f, ncz = (nb[2] + nb[5]) * 0.5f;
+        float dx = 0.f, dy = 0.f, dz = 0.f;
+        if (ch >= 0) {
+            const float* cb = a.node_box + 6 * (size_t)ch;
+            dx = (cb[0] + cb[3]) * 0.5f - ncx; dy = (cb[1] + cb[4]) * 0.5f - ncy; dz = (cb[2] + cb[5]) * 0.5f - ncz;
         }
-        child_done |= 1u << bi;
-        slot_done |= 1u << bs;
-        slot_child[bs] = ch[bi];
+#pragma unroll
+        for (int s = 0; s < 8; s++) cost[s] = (((s & 1) ? dx : -dx) + ((s & 2) ? dy : -dy)) + ((s & 4) ? dz : -dz);
     }
-    n_inner = 0;
-    n_leaf_prims = 0;
-    for (int s = 0; s < 8; s++) {
-        if (slot_child[s] < 0) continue;
-        int sz = node_size(a, slot_child[s]);
-        if (sz > 3) n_inner++; else n_leaf_prims += sz;
+    // greedy assignment, one (child, slot) pair per round
+    unsigned slot_done = 0;
+    bool mine_done = ch < 0;
+    int my_slot = -1;
+#pragma unroll 1
+    for (int it = 0; it < 8; it++) {
+        // this lane's best free slot (lowest slot on ties)
+        float bv = -INFINITY;
+        int bs = -1;
+#pragma unroll
+        for (int s = 0; s < 8; s++)
+            if (!(slot_done & (1u << s)) && (bs < 0 || cost[s] > bv)) { bv = cost[s]; bs = s; }
+        // lanes that are done or empty must never win: key below every real value, NaN-free
+        float key = mine_done ? -INFINITY : bv;
+        int cand = mine_done ? 8 + j : j;  // done lanes sort after live ones on ties at -inf
+        // argmax over lanes with ties to the lowest live lane
+        float kv = key;
+        int ki = cand;
+        for (int o = 1; o < 8; o <<= 1) {
+            float ov = __shfl_xor_sync(FULL, kv, o, 8);
+            int oi = __shfl_xor_sync(FULL, ki, o, 8);
+            if (ov > kv || (ov == kv && oi < ki)) { kv = ov; ki = oi; }
+        }
+        bool any = ki < 8;  // a live lane won
+        int wslot = g_shfl(bs, ki & 7);
+        if (any) {
+            if (j == ki) { my_slot = bs; mine_done = true; }
+            slot_done |= 1u << wslot;
+        }
     }
+    // lane s <- child assigned to slot s
+    int child_of_slot = -1;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        int sk = g_shfl(my_slot, k);
+        int ck = g_shfl(ch, k);
+        if (sk == j) child_of_slot = ck;
+    }
+    int sz = child_of_slot >= 0 ? node_size(a, child_of_slot) : 0;
+    n_inner = g_sum(sz > 3 ? 1 : 0);
+    n_leaf_prims = g_sum(sz > 3 ? 0 : sz);
+    return child_of_slot;
 }
 
-__device__ void write_node8(const CollapseArgs& a, int root, int node_idx, const int slot_child[8], int child_base,
-                            int prim_base, int* next_list) {
+// Lane s of the group quantises and emits slot s of one BVH8 node; lanes 0 and 4 store the packed
+// words. `c` = BVH2 id in this lane's slot or -1.
+__device__ void write_node8_g(const CollapseArgs& a, int root, int node_idx, int c, int j, int child_base, int prim_base,
+                              int* next_list, bool valid) {
     const float* nb = a.node_box + 6 * (size_t)root;
     float org[3] = {nb[0], nb[1], nb[2]};
     unsigned eb[3];
     float scale[3], inv_scale[3];
+#pragma unroll
     for (int k = 0; k < 3; k++) {
         float ext = nb[3 + k] - nb[k];
         float f = ext / 255.0f;
@@ -456,15 +522,11 @@ __device__ void write_node8(const CollapseArgs& a, int root, int node_idx, const
         scale[k] = sc;
         inv_scale[k] = __uint_as_float((254u - e) << 23);
     }
-    unsigned imask = 0;
-    unsigned meta[8], qlo[3][8], qhi[3][8];
-    int inner_rank = 0, prim_off = 0;
-    for (int s = 0; s < 8; s++) {
-        meta[s] = 0;
-        for (int k = 0; k < 3; k++) { qlo[k][s] = 0; qhi[k][s] = 0; }
-        int c = slot_child[s];
-        if (c < 0) continue;
+    unsigned q[6] = {0, 0, 0, 0, 0, 0};
+    int sz = 0;
+    if (c >= 0) {
         const float* cb = a.node_box + 6 * (size_t)c;
+#pragma unroll
         for (int k = 0; k < 3; k++) {
             float ql = floorf((cb[k] - org[k]) * inv_scale[k]);
             ql = fminf(fmaxf(ql, 0.0f), 255.0f);
@@ -472,40 +534,58 @@ __device__ void write_node8(const CollapseArgs& a, int root, int node_idx, const
             float qh = ceilf((cb[3 + k] - org[k]) * inv_scale[k]);
             qh = fminf(fmaxf(qh, 0.0f), 255.0f);
             while (qh < 255.0f && org[k] + qh * scale[k] < cb[3 + k]) qh += 1.0f;
-            qlo[k][s] = (unsigned)ql;
-            qhi[k][s] = (unsigned)qh;
+            q[k] = (unsigned)ql;
+            q[3 + k] = (unsigned)qh;
         }
-        int sz = node_size(a, c);
-        if (sz > 3) {
-            imask |= 1u << s;
-            meta[s] = 0x20u | (24u + (unsigned)s);
-            next_list[inner_rank] = c;
-            inner_rank++;
+        sz = node_size(a, c);
+    }
+    const bool inner = sz > 3;
+    const int inner_rank = g_excl(inner ? 1 : 0, j);
+    const int prim_off = g_excl(inner ? 0 : sz, j);
+    unsigned meta = 0;
+    if (c >= 0) {
+        if (inner) {
+            meta = 0x20u | (24u + (unsigned)j);
+            if (valid) next_list[inner_rank] = c;
         } else {
             unsigned unary = sz == 1 ? 1u : (sz == 2 ? 3u : 7u);
-            meta[s] = (unary << 5) | (unsigned)prim_off;
+            meta = (unary << 5) | (unsigned)prim_off;
             int first = node_first(a, c);
-            for (int j = 0; j < sz; j++) {
-                int dst = prim_base + prim_off + j;
-                int p = a.sorted_prim[first + j];
-                a.prim_order8[dst] = first + j;
-                a.prims8[3 * (size_t)dst + 0] = a.prim_world[3 * (size_t)p + 0];
-                a.prims8[3 * (size_t)dst + 1] = a.prim_world[3 * (size_t)p + 1];
-                a.prims8[3 * (size_t)dst + 2] = a.prim_world[3 * (size_t)p + 2];
+            for (int t = 0; t < sz; t++) {
+                int dst = prim_base + prim_off + t;
+                int p = a.sorted_prim[first + t];
+                if (valid) {
+                    a.prim_order8[dst] = first + t;
+                    a.prims8[3 * (size_t)dst + 0] = a.prim_world[3 * (size_t)p + 0];
+                    a.prims8[3 * (size_t)dst + 1] = a.prim_world[3 * (size_t)p + 1];
+                    a.prims8[3 * (size_t)dst + 2] = a.prim_world[3 * (size_t)p + 2];
+                }
             }
-            prim_off += sz;
         }
     }
-    auto pack4 = [](const unsigned* b) { return b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24); };
-    uint4 q0, q1, q2, q3, q4;
-    q0.x = __float_as_uint(org[0]); q0.y = __float_as_uint(org[1]); q0.z = __float_as_uint(org[2]);
-    q0.w = eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24);
-    q1.x = (unsigned)child_base; q1.y = (unsigned)prim_base; q1.z = pack4(meta); q1.w = pack4(meta + 4);
-    q2.x = pack4(qlo[0]); q2.y = pack4(qlo[0] + 4); q2.z = pack4(qlo[1]); q2.w = pack4(qlo[1] + 4);
-    q3.x = pack4(qlo[2]); q3.y = pack4(qlo[2] + 4); q3.z = pack4(qhi[0]); q3.w = pack4(qhi[0] + 4);
-    q4.x = pack4(qhi[1]); q4.y = pack4(qhi[1] + 4); q4.z = pack4(qhi[2]); q4.w = pack4(qhi[2] + 4);
-    uint4* out = a.nodes8 + 5 * (size_t)node_idx;
-    out[0] = q0; out[1] = q1; out[2] = q2; out[3] = q3; out[4] = q4;
+    const unsigned imask = g_or(inner ? (1u << j) : 0u);
+    // byte j of each 8-byte array: OR the shifted bytes of lanes 0..3 / 4..7 into one word each
+    const int sh = 8 * (j & 3);
+    auto pack = [&](unsigned v) {
+        unsigned w = v << sh;
+        w |= __shfl_xor_sync(FULL, w, 1, 8);
+        w |= __shfl_xor_sync(FULL, w, 2, 8);
+        return w;  // lanes 0..3 hold the low word, lanes 4..7 the high word
+    };
+    unsigned wm = pack(meta), w0 = pack(q[0]), w1 = pack(q[1]), w2 = pack(q[2]), w3 = pack(q[3]), w4 = pack(q[4]), w5 = pack(q[5]);
+    if (!valid) return;
+    unsigned* out = (unsigned*)(a.nodes8 + 5 * (size_t)node_idx);
+    if (j == 0) {
+        out[0] = __float_as_uint(org[0]); out[1] = __float_as_uint(org[1]); out[2] = __float_as_uint(org[2]);
+        out[3] = eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24);
+        out[4] = (unsigned)child_base; out[5] = (unsigned)prim_base;
+    }
+    if (j == 0 || j == 4) {
+        int h = j >> 2;  // 0: low words, 1: high words
+        out[6 + h] = wm;
+        out[8 + h] = w0; out[10 + h] = w1; out[12 + h] = w2;
+        out[14 + h] = w3; out[16 + h] = w4; out[18 + h] = w5;
+    }
 }
 
 // Cooperative kernel: all levels in one launch, two grid barriers per level. Blocks own
@@ -528,16 +608,23 @@ __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
         int* btot = a.block_tot + (size_t)parity * G * 2;
         int per_block = (level_n + G - 1) / G;
         int c0 = min(level_n, blockIdx.x * per_block), c1 = min(level_n, c0 + per_block);
-        // phase A: children + counts
+        // phase A: children + counts, 8 lanes per node
+        const int group = threadIdx.x >> 3, j = threadIdx.x & 7, groups = B >> 3;
         int my_inner = 0, my_prims = 0;
-        for (int t = c0 + threadIdx.x; t < c1; t += B) {
-            int sc[8], ni, np;
-            collapse_children(a, cur[t], sc, ni, np);
-            for (int s = 0; s < 8; s++) a.slots[8 * (size_t)t + s] = sc[s];
-            a.counts[2 * (size_t)t] = ni;
-            a.counts[2 * (size_t)t + 1] = np;
-            my_inner += ni;
-            my_prims += np;
+        for (int base = c0; base < c1; base += groups) {
+            int t = base + group;
+            bool valid = t < c1;
+            int ni, np;
+            int child = collapse_children_g(a, cur[valid ? t : c0], j, ni, np);
+            if (valid) {
+                a.slots[8 * (size_t)t + j] = child;
+                if (j == 0) {
+                    a.counts[2 * (size_t)t] = ni;
+                    a.counts[2 * (size_t)t + 1] = np;
+                    my_inner += ni;
+                    my_prims += np;
+                }
+            }
         }
         for (int o = 16; o; o >>= 1) {
             my_inner += __shfl_xor_sync(0xffffffffu, my_inner, o);
@@ -600,16 +687,22 @@ __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
             for (int w = 0; w < warp; w++) { wi += s_warp[0][w]; wp += s_warp[1][w]; }
             int ci = s_carry[0], cp = s_carry[1];
             if (t < c1) {
-                int sc[8];
-                for (int s = 0; s < 8; s++) sc[s] = a.slots[8 * (size_t)t + s];
-                // child_base indexes nodes8 (absolute); the next-level list is relative to next_base
-                int rel_child = ci + wi + xi - ni;
-                write_node8(a, cur[t], level_base + t, sc, next_base + rel_child, prim_total + cp + wp + xp - np,
-                            next + rel_child);
+                // child_base indexes nodes8 (absolute); prim_base indexes prims8
+                a.counts[2 * (size_t)t] = next_base + (ci + wi + xi - ni);
+                a.counts[2 * (size_t)t + 1] = prim_total + cp + wp + xp - np;
             }
             __syncthreads();
             if (threadIdx.x == B - 1) { s_carry[0] = ci + wi + xi; s_carry[1] = cp + wp + xp; }
             __syncthreads();
+        }
+        __syncthreads();
+        for (int base = c0; base < c1; base += groups) {
+            int t = base + group;
+            bool valid = t < c1;
+            int tt = valid ? t : c0;
+            int child_base = a.counts[2 * (size_t)tt];
+            write_node8_g(a, cur[tt], level_base + tt, a.slots[8 * (size_t)tt + j], j, child_base, a.counts[2 * (size_t)tt + 1],
+                          next + (child_base - next_base), valid);
         }
         level_base = next_base;
         prim_total += level_prims;
