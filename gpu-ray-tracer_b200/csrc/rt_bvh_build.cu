@@ -415,15 +415,27 @@ __device__ __forceinline__ int g_argmax(float val, int j, float& val_out) {
 // in slot s (or -1), and n_inner / n_leaf_prims are group-uniform.
 __device__ int collapse_children_g(const CollapseArgs& a, int root, int j, int& n_inner, int& n_leaf_prims) {
     int ch = -1;          // BVH2 id at list position j
+    int cl = -1, cr = -1; // its two children, fetched together with it (one memory round trip per opening)
     float area = -2.0f;   // -2: empty position, -1: cannot be opened, >= 0: half-area
+    float cb[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     int nc;
     auto load = [&](int id) {
         ch = id;
-        area = node_size(a, id) <= 3 ? -1.0f : half_area(a.node_box + 6 * (size_t)id);
+        const float* bx = a.node_box + 6 * (size_t)id;
+#pragma unroll
+        for (int k = 0; k < 6; k++) cb[k] = bx[k];
+        if (id >= a.n - 1) {  // single triangle
+            area = -1.0f;
+        } else {
+            int lo = a.range_lo[id], hi = a.range_hi[id];
+            cl = a.left[id];
+            cr = a.right[id];
+            area = (hi - lo + 1) <= 3 ? -1.0f : half_area(cb);
+        }
     };
     const bool single = root >= a.n - 1 || node_size(a, root) <= 3;  // whole scene is one leaf
     if (single) {
-        if (j == 0) { ch = root; area = -1.0f; }
+        if (j == 0) { load(root); area = -1.0f; }
         nc = 1;
     } else {
         if (j == 0) load(a.left[root]);
@@ -434,11 +446,11 @@ __device__ int collapse_children_g(const CollapseArgs& a, int root, int j, int& 
     for (int it = 0; it < 6; it++) {
         float best_area;
         int best = g_argmax(area, j, best_area);
-        int c = g_shfl(ch, best);
+        int l = g_shfl(cl, best), r = g_shfl(cr, best);
         bool open = best_area >= 0.0f && nc < 8;  // group-uniform
         if (open) {
-            if (j == best) load(a.left[c]);
-            if (j == nc) load(a.right[c]);
+            if (j == best) load(l);
+            if (j == nc) load(r);
             nc++;
         }
     }
@@ -449,7 +461,6 @@ __device__ int collapse_children_g(const CollapseArgs& a, int root, int j, int& 
         float ncx = (nb[0] + nb[3]) * 0.5f, ncy = (nb[1] + nb[4]) * 0.5f, ncz = (nb[2] + nb[5]) * 0.5f;
         float dx = 0.f, dy = 0.f, dz = 0.f;
         if (ch >= 0) {
-            const float* cb = a.node_box + 6 * (size_t)ch;
             dx = (cb[0] + cb[3]) * 0.5f - ncx; dy = (cb[1] + cb[4]) * 0.5f - ncy; dz = (cb[2] + cb[5]) * 0.5f - ncz;
         }
 #pragma unroll
@@ -588,11 +599,27 @@ __device__ void write_node8_g(const CollapseArgs& a, int root, int node_idx, int
     }
 }
 
+// Grid barrier for the cooperative launch (all blocks co-resident): one arrival counter that only
+// grows, so no reset race; cheaper than cooperative_groups' grid.sync() at these block counts.
+__device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned n_blocks, unsigned& epoch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        epoch++;
+        __threadfence();
+        atomicAdd(counter, 1u);
+        const unsigned target = epoch * n_blocks;
+        while (*(volatile unsigned*)counter < target) {}
+        __threadfence();
+    }
+    __syncthreads();
+}
+
 // Cooperative kernel: all levels in one launch, two grid barriers per level. Blocks own
 // contiguous chunks of the level so that the per-level exclusive scan (which fixes child_base
 // and prim_base, i.e. the memory order of the whole tree) follows node order deterministically.
 __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
-    cg::grid_group grid = cg::this_grid();
+    unsigned epoch = 0;
+    unsigned* bar = (unsigned*)(a.result + 8);  // zeroed by the host before the launch
     __shared__ int s_warp[2][kThreads / 32];
     __shared__ int s_carry[2];
     __shared__ int s_base[2];
@@ -600,7 +627,7 @@ __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int level_n = 1, level_base = 0, prim_total = 0, levels = 0, max_width = 1;
     if (blockIdx.x == 0 && threadIdx.x == 0) a.level_a[0] = 0;
-    grid.sync();
+    grid_barrier(bar, gridDim.x, epoch);
     while (level_n > 0) {
         int parity = levels & 1;
         int* cur = parity ? a.level_b : a.level_a;
@@ -638,7 +665,7 @@ __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
             btot[2 * blockIdx.x] = ti;
             btot[2 * blockIdx.x + 1] = tp;
         }
-        grid.sync();
+        grid_barrier(bar, gridDim.x, epoch);
         // phase B: block offsets (every block sums the totals of the blocks before it), ordered scan, emit
         int pre_i = 0, pre_p = 0, tot_i = 0, tot_p = 0;
         for (int b = threadIdx.x; b < G; b += B) {
@@ -709,7 +736,7 @@ __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
         level_n = level_inner;
         levels++;
         if (level_n > max_width) max_width = level_n;
-        grid.sync();
+        grid_barrier(bar, gridDim.x, epoch);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         a.result[0] = level_base;
@@ -809,7 +836,7 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k_collapse, kThreads, 0));
     if (blocks_per_sm < 1) { set_error("k_collapse cannot be made resident"); return RT_ERR_CUDA; }
     int G = sc->sm_count * (blocks_per_sm > 2 ? 2 : blocks_per_sm);
-    int want = (n / 4 + kThreads - 1) / kThreads;
+    int want = (n / 4 * 8 + kThreads - 1) / kThreads;  // 8 lanes per BVH8 node, about n/4 nodes on the widest level
     if (want < 1) want = 1;
     if (G > want) G = want;
     size_t level_cap = (size_t)n + 8;
@@ -832,6 +859,7 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     a.counts = w; w += level_cap * 2;
     a.block_tot = w; w += (size_t)G * 4;
     a.result = w;
+    RT_CUDA(cudaMemsetAsync(a.result, 0, 16 * sizeof(int), st));
     void* args[] = {&a};
     RT_CUDA(cudaLaunchCooperativeKernel((void*)k_collapse, dim3(G), dim3(kThreads), args, 0, st));
     sc->kernel_launches++;
