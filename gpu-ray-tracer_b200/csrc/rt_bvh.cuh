@@ -39,6 +39,9 @@ namespace rtd {
 // distances by rounding of the local-frame transforms only (relative ~1e-6)
 #define RT_TCULL_REL 1.0001f
 #define RT_TCULL_ABS 1e-4f
+#ifndef RT_POSTPONE_PCT
+#define RT_POSTPONE_PCT 0   /* measured: no gain on coherent primary / shadow rays (profiles/r1_summary.md) */
+#endif
 
 RT_HD int hd_clz(unsigned x) {
 #ifdef __CUDA_ARCH__
@@ -250,6 +253,20 @@ RT_HD bool bvh_query(const SceneView& s, const rtx::Ray& r, bool use_box, float 
             tg = ng;
             ng.x = 0u; ng.y = 0u;
         }
+#ifdef __CUDA_ARCH__
+        // Triangle postponing (Ylitie et al. 2017, §4.3): when only a few lanes of the warp have
+        // triangles to test and this lane still has nodes to visit, park the triangle group on the
+        // stack and keep traversing, so that triangle tests run with more lanes active. The order
+        // of tests does not change the result (closest hit with index tie rules / any hit).
+        if (RT_POSTPONE_PCT > 0 && tg.y != 0u && ng.y > 0x00ffffffu && sp < RT_STACK_SIZE - 2) {
+            unsigned act = __activemask();
+            int with_tris = __popc(__ballot_sync(act, tg.y != 0u));
+            if (with_tris * 100 < __popc(act) * RT_POSTPONE_PCT) {
+                stack[sp++] = tg;
+                tg.y = 0u;
+            }
+        }
+#endif
         while (tg.y) {
             unsigned k = (unsigned)hd_ctz(tg.y);
             tg.y &= tg.y - 1u;

@@ -260,66 +260,197 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
     flush_counts(ctr, rc, ts, STATS);
 }
 
-// ---------------------------------------------------------------- wave 0, all-opaque scenes: split shading
-// k_shade keeps ray setup, traversal, the exact tests and Phong in one instruction stream (50 KB of
-// SASS, stall_no_instruction 2.6 warps per issue). When no material spawns secondary rays the same
-// work runs as three tight kernels: shadow-ray generation, any-hit traversal, Phong + pack.
-struct ShadowRec { float4 o_maxt, d; };  // 32 bytes; stored light-major: index = light * n_hits + hit
+// ---------------------------------------------------------------- split shading (every wave)
+// The fused kernels (k_shade / k_bounce below, RT_RENDER_FUSED_SHADE) keep ray setup, traversal,
+// the exact tests, Phong and the bounce state machine in one instruction stream (50-80 KB of
+// SASS, stall_no_instruction 2.6 warps per issue). By default the same work runs as tight kernels:
+//   k_shadow_gen   one shadow ray per (hit, light)                    no traversal
+//   k_shadow       any-hit traversal, or Light::attenuate's closest-hit loop when a material refracts
+//   k_resolve      Phong + pack (wave 0; starts a path where the material reflects / refracts)
+//   k_path_trace   closest hit of each live path's next ray          (waves >= 1)
+//   k_path_advance Phong + the RayFrame state machine                (waves >= 1), no traversal
+struct ShadowRec { float4 o_maxt, d; };  // 32 bytes; stored light-major: index = light * n + hit; max_t < 0: no ray
 
-__global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, const unsigned long long* ctr, const HitRec* hitq,
-                                                        ShadowRec* shq) {
-    const int n = (int)ctr[C_HITQ];
+__device__ __forceinline__ Frame* path_frames(unsigned char* paths, int path_stride, int slot, PathHead** head) {
+    *head = (PathHead*)(paths + (size_t)slot * path_stride);
+    return (Frame*)(*head + 1);
+}
+
+// PATHS == false: hits of camera rays (wave 0). PATHS == true: hits of path rays; rec.out_index is
+// the path slot and rec.inst < 0 marks a miss (no shadow rays).
+template <bool PATHS>
+__global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, const unsigned long long* ctr, int ctr_n,
+                                                        const HitRec* hitq, ShadowRec* shq, unsigned char* paths,
+                                                        int path_stride) {
+    const int n = (int)ctr[ctr_n];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         HitRec rec = hitq[i];
-        rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
-        float3 hit_pos = rtx::ray_at(r, rec.t);
+        rtx::Ray r;
+        bool hit = true;
+        if (PATHS) {
+            hit = rec.inst >= 0;
+            PathHead* head;
+            Frame* frames = path_frames(paths, path_stride, rec.out_index, &head);
+            if (hit) r = frames[head->stack_top].ray;
+        } else {
+            r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
+        }
+        float3 hit_pos = hit ? rtx::ray_at(r, rec.t) : rtx::mk3(0.f, 0.f, 0.f);
         for (int l = 0; l < s.n_lights; l++) {
-            float3 dir;
-            float max_t, da;
-            light_setup(s, s.lights[l], hit_pos, dir, max_t, da);
-            rtx::Ray cur = shadow_ray(hit_pos, dir);
             ShadowRec q;
-            q.o_maxt = make_float4(cur.o.x, cur.o.y, cur.o.z, max_t);
-            q.d = make_float4(cur.d.x, cur.d.y, cur.d.z, 0.f);
+            q.o_maxt = make_float4(0.f, 0.f, 0.f, -1.f);
+            q.d = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (hit) {
+                float3 dir;
+                float max_t, da;
+                light_setup(s, s.lights[l], hit_pos, dir, max_t, da);
+                rtx::Ray cur = shadow_ray(hit_pos, dir);
+                q.o_maxt = make_float4(cur.o.x, cur.o.y, cur.o.z, max_t);
+                q.d = make_float4(cur.d.x, cur.d.y, cur.d.z, 0.f);
+            }
             shq[(size_t)l * n + i] = q;
         }
     }
 }
 
-template <int MODE, bool STATS>
-__global__ void __launch_bounds__(kThreads) k_shadow(SceneView s, unsigned long long* ctr, const ShadowRec* shq,
-                                                    unsigned char* occl) {
+// LOOP == false: occl[j] = 1 when anything blocks the ray within max_t (any-hit).
+// LOOP == true : att4[j] = Light::attenuate's result (closest-hit walk through refractive occluders).
+template <int MODE, bool STATS, bool LOOP>
+__global__ void __launch_bounds__(kThreads) k_shadow(SceneView s, unsigned long long* ctr, int ctr_n, const ShadowRec* shq,
+                                                    unsigned char* occl, float4* att4) {
     TravStats ts = {0, 0, 0};
     RayCounts rc = {0, 0, 0};
     typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
-    const long long n = (long long)ctr[C_HITQ] * s.n_lights;
+    const long long n_hits = (long long)ctr[ctr_n];
+    const long long n = n_hits * s.n_lights;
     for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (long long)gridDim.x * blockDim.x) {
         ShadowRec q = shq[j];
+        if (q.o_maxt.w < 0.f) continue;
         rtx::Ray r;
         r.o = rtx::mk3(q.o_maxt.x, q.o_maxt.y, q.o_maxt.z);
         r.d = rtx::mk3(q.d.x, q.d.y, q.d.z);
-        rc.shadow++;
-        occl[j] = tr.occluded(r, q.o_maxt.w) ? 1 : 0;
+        if (LOOP) {
+            att4[j] = light_attenuate_loop(s, tr, s.lights[(int)(j / n_hits)], r, q.o_maxt.w, rc);
+        } else {
+            rc.shadow++;
+            occl[j] = tr.occluded(r, q.o_maxt.w) ? 1 : 0;
+        }
     }
     flush_counts(ctr, rc, ts, STATS);
 }
 
-__global__ void __launch_bounds__(kThreads) k_resolve(SceneView s, const unsigned long long* ctr, const HitRec* hitq,
-                                                     const unsigned char* occl, uint32_t* canvas) {
+// What Light::attenuate returned for (light l, hit i of n), from whichever k_shadow variant ran.
+struct AttenLookup {
+    const unsigned char* occl;
+    const float4* att4;
+    size_t n, i;
+    __device__ __forceinline__ float4 operator()(int l, const LightRec& L) const {
+        size_t j = (size_t)l * n + i;
+        if (att4) return att4[j];
+        return occl[j] ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : L.color;
+    }
+};
+
+// SECONDARY == true: hits on reflective / refractive materials become paths (their first
+// RayFrame transitions run here) and are queued for the bounce waves.
+template <bool SECONDARY>
+__global__ void __launch_bounds__(kThreads) k_resolve(SceneView s, unsigned long long* ctr, const HitRec* hitq,
+                                                     const unsigned char* occl, const float4* att4, uint32_t* canvas,
+                                                     unsigned char* paths, int path_stride, int* queue) {
     const int n = (int)ctr[C_HITQ];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         HitRec rec = hitq[i];
         Hit h;
         h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
         rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
-        const MatRec& m = s.mats[s.tris[h.tri].mat];
+        int mat_id = s.tris[h.tri].mat;
+        const MatRec& m = s.mats[mat_id];
+        AttenLookup att = {occl, att4, (size_t)n, (size_t)i};
+        if (SECONDARY && (m.reflective || m.refractive)) {
+            int slot = (int)atomicAdd(&ctr[C_PATHS], 1ull);
+            PathHead* head;
+            Frame* frames = path_frames(paths, path_stride, slot, &head);
+            Frame f;
+            frame_init_root(f, r, s.depth);
+            frames[0] = f;
+            int stack_top = 0, isect_mat = mat_id;
+            float4 acc = rtx::mk4(0.f, 0.f, 0.f, 0.f);
+            bool alive = path_advance_with(
+                s, [&](const rtx::Ray& ray, float t, float3 nn, const MatRec& mm) { return illuminate_resolved(s, ray, t, nn, mm, att); },
+                frames, stack_top, isect_mat, acc, true, h);
+            if (alive) {
+                PathHead hd;
+                hd.acc = acc; hd.out_index = rec.out_index; hd.stack_top = stack_top; hd.isect_mat = isect_mat;
+                hd.pending = 0; hd.hit = h; hd.pad0 = hd.pad1 = 0;
+                *head = hd;
+                queue[(int)atomicAdd(&ctr[C_QUEUE_A], 1ull)] = slot;
+            } else {
+                canvas[rec.out_index] = rtx::pack_color(acc);
+            }
+            continue;
+        }
+        // no secondary rays: acc = 0 + 1 * illuminate, clamp, pack (src/raytracer.cu:36-41)
         float3 nrm = hit_normal(s, h);
-        float4 c = illuminate_resolved(s, r, h.t, nrm, m, [&](int l) { return occl[(size_t)l * n + i] != 0; });
+        float4 c = illuminate_resolved(s, r, h.t, nrm, m, att);
         canvas[rec.out_index] = rtx::pack_color(c);
     }
 }
 
-// ---------------------------------------------------------------- waves >= 1: bounce
+// waves >= 1: closest hit of every live path's pending ray (frames[stack_top].ray)
+template <int MODE, bool STATS>
+__global__ void __launch_bounds__(kThreads) k_path_trace(SceneView s, unsigned long long* ctr, int ctr_in, const int* queue_in,
+                                                        unsigned char* paths, int path_stride, HitRec* whit) {
+    TravStats ts = {0, 0, 0};
+    RayCounts rc = {0, 0, 0};
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
+    const int n = (int)ctr[ctr_in];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int slot = queue_in[i];
+        PathHead* head;
+        Frame* frames = path_frames(paths, path_stride, slot, &head);
+        rtx::Ray r = frames[head->stack_top].ray;
+        Hit h;
+        rc.secondary++;
+        bool hit = tr.closest(r, h);
+        HitRec rec;
+        rec.out_index = slot; rec.xy = 0; rec.inst = hit ? h.inst : -1; rec.tri = h.tri;
+        rec.t = h.t; rec.u = h.u; rec.v = h.v; rec.t_local = h.t_local;
+        whit[i] = rec;
+    }
+    flush_counts(ctr, rc, ts, STATS);
+}
+
+// waves >= 1: shade the hit from the traced shadow rays, run the RayFrame transitions, requeue or finish
+__global__ void __launch_bounds__(kThreads) k_path_advance(SceneView s, unsigned long long* ctr, int ctr_in, int ctr_out,
+                                                          const HitRec* whit, const unsigned char* occl, const float4* att4,
+                                                          int* queue_out, uint32_t* canvas, unsigned char* paths,
+                                                          int path_stride) {
+    const int n = (int)ctr[ctr_in];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        HitRec rec = whit[i];
+        int slot = rec.out_index;
+        PathHead* head;
+        Frame* frames = path_frames(paths, path_stride, slot, &head);
+        float4 acc = head->acc;
+        int stack_top = head->stack_top, isect_mat = head->isect_mat;
+        Hit h;
+        h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
+        AttenLookup att = {occl, att4, (size_t)n, (size_t)i};
+        bool alive = path_advance_with(
+            s, [&](const rtx::Ray& ray, float t, float3 nn, const MatRec& mm) { return illuminate_resolved(s, ray, t, nn, mm, att); },
+            frames, stack_top, isect_mat, acc, rec.inst >= 0, h);
+        if (alive) {
+            head->acc = acc;
+            head->stack_top = stack_top;
+            head->isect_mat = isect_mat;
+            queue_out[(int)atomicAdd(&ctr[ctr_out], 1ull)] = slot;
+        } else {
+            canvas[head->out_index] = rtx::pack_color(acc);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- waves >= 1, fused variant (RT_RENDER_FUSED_SHADE)
 template <int MODE, bool STATS>
 __global__ void __launch_bounds__(kThreads) k_bounce(SceneView s, unsigned long long* ctr, int ctr_in, int ctr_out,
                                                     const int* queue_in, int* queue_out, uint32_t* canvas,
@@ -689,41 +820,61 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     *waves = 1;
     sc->split_shade_used = false;
     int path_stride = (int)(sizeof(PathHead) + sizeof(Frame) * (size_t)(v.depth + 1));
+    const bool secondary = v.any_secondary && v.depth > 0;
+    const bool loop = v.any_refractive != 0;  // shadow rays walk through refractive occluders
     unsigned long long n_hits = 0;
-    if (v.any_secondary && v.depth > 0) {
-        // paths are allocated for the hits actually found (one 8-byte read-back)
+    size_t hit_cap = (size_t)std::max<long long>(n_pix, 1);
+    if (secondary) {
+        // paths and shadow queues are allocated for the hits actually found (one 8-byte read-back)
         RT_CUDA(cudaMemcpyAsync(&n_hits, ctr + C_HITQ, 8, cudaMemcpyDeviceToHost, st));
         RT_CUDA(cudaStreamSynchronize(st));
-        size_t cap = (size_t)std::max<unsigned long long>(n_hits, 1);
-        if (sc->d_paths.reserve(cap * path_stride) || sc->d_queue_a.reserve(4 * cap) || sc->d_queue_b.reserve(4 * cap))
+        hit_cap = (size_t)std::max<unsigned long long>(n_hits, 1);
+        if (sc->d_paths.reserve(hit_cap * path_stride) || sc->d_queue_a.reserve(4 * hit_cap) || sc->d_queue_b.reserve(4 * hit_cap))
             return RT_ERR_OUT_OF_MEMORY;
     }
-    if (!v.any_secondary && !sc->fused_shade) {
-        // no Kr / Kt anywhere: every pixel ends after its shadow rays -> gen / any-hit traverse / resolve
-        size_t cap = (size_t)std::max<long long>(n_pix, 1) * (size_t)std::max(v.n_lights, 1);
-        if (sc->d_shadowq.reserve(sizeof(ShadowRec) * cap) || sc->d_occl.reserve(cap)) return RT_ERR_OUT_OF_MEMORY;
-        k_shadow_gen<<<persistent_grid(k_shadow_gen, sc->sm_count), kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(),
-                                                                                      sc->d_shadowq.as<ShadowRec>());
+    unsigned char* occl = nullptr;
+    float4* att4 = nullptr;
+    ShadowRec* shq = nullptr;
+    if (!sc->fused_shade) {
+        size_t cap = hit_cap * (size_t)std::max(v.n_lights, 1);
+        if (sc->d_shadowq.reserve(sizeof(ShadowRec) * cap) || sc->d_occl.reserve((loop ? sizeof(float4) : 1) * cap))
+            return RT_ERR_OUT_OF_MEMORY;
+        shq = sc->d_shadowq.as<ShadowRec>();
+        if (loop) att4 = sc->d_occl.as<float4>(); else occl = sc->d_occl.as<unsigned char>();
+    }
+    // one any-hit / closest-loop traversal of the n * n_lights shadow rays in shq
+    auto trace_shadows = [&](int ctr_n) {
+        if (loop) k_shadow<MODE, STATS, true><<<persistent_grid(k_shadow<MODE, STATS, true>, sc->sm_count), kThreads, 0, st>>>(
+            v, ctr, ctr_n, shq, occl, att4);
+        else k_shadow<MODE, STATS, false><<<persistent_grid(k_shadow<MODE, STATS, false>, sc->sm_count), kThreads, 0, st>>>(
+            v, ctr, ctr_n, shq, occl, att4);
+        sc->kernel_launches++;
+    };
+    HitRec* hitq = sc->d_hitq.as<HitRec>();
+    unsigned char* paths = sc->d_paths.as<unsigned char>();
+    if (!sc->fused_shade) {
+        k_shadow_gen<false><<<persistent_grid(k_shadow_gen<false>, sc->sm_count), kThreads, 0, st>>>(v, ctr, C_HITQ, hitq, shq, nullptr, 0);
+        sc->kernel_launches++;
         RT_CUDA(cudaEventRecord(sc->ev[8], st));
-        k_shadow<MODE, STATS><<<persistent_grid(k_shadow<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
-            v, ctr, sc->d_shadowq.as<ShadowRec>(), sc->d_occl.as<unsigned char>());
+        trace_shadows(C_HITQ);
         RT_CUDA(cudaEventRecord(sc->ev[9], st));
-        k_resolve<<<persistent_grid(k_resolve, sc->sm_count), kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(),
-                                                                                sc->d_occl.as<unsigned char>(), canvas);
-        sc->kernel_launches += 2;
+        if (secondary)
+            k_resolve<true><<<persistent_grid(k_resolve<true>, sc->sm_count), kThreads, 0, st>>>(
+                v, ctr, hitq, occl, att4, canvas, paths, path_stride, sc->d_queue_a.as<int>());
+        else
+            k_resolve<false><<<persistent_grid(k_resolve<false>, sc->sm_count), kThreads, 0, st>>>(
+                v, ctr, hitq, occl, att4, canvas, nullptr, 0, nullptr);
         sc->split_shade_used = true;
     } else if (!v.any_secondary) {
         int g1 = persistent_grid(k_shade<MODE, STATS, true>, sc->sm_count);
-        k_shade<MODE, STATS, true><<<g1, kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, 0, nullptr);
+        k_shade<MODE, STATS, true><<<g1, kThreads, 0, st>>>(v, ctr, hitq, canvas, nullptr, 0, nullptr);
     } else {
         int g1 = persistent_grid(k_shade<MODE, STATS, false>, sc->sm_count);
-        k_shade<MODE, STATS, false><<<g1, kThreads, 0, st>>>(v, ctr, sc->d_hitq.as<HitRec>(), canvas,
-                                                            sc->d_paths.as<unsigned char>(), path_stride, sc->d_queue_a.as<int>());
+        k_shade<MODE, STATS, false><<<g1, kThreads, 0, st>>>(v, ctr, hitq, canvas, paths, path_stride, sc->d_queue_a.as<int>());
     }
     sc->kernel_launches++;
     RT_CUDA(cudaEventRecord(sc->ev[7], st));
-    if (v.any_secondary && v.depth > 0) {
-        int g2 = persistent_grid(k_bounce<MODE, STATS>, sc->sm_count);
+    if (secondary) {
         int in = C_QUEUE_A, outc = C_QUEUE_B;
         int* qin = sc->d_queue_a.as<int>();
         int* qout = sc->d_queue_b.as<int>();
@@ -733,8 +884,20 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
             RT_CUDA(cudaStreamSynchronize(st));
             if (live == 0) break;
             RT_CUDA(cudaMemsetAsync(ctr + outc, 0, 8, st));
-            k_bounce<MODE, STATS><<<g2, kThreads, 0, st>>>(v, ctr, in, outc, qin, qout, canvas, sc->d_paths.as<unsigned char>(), path_stride);
-            sc->kernel_launches++;
+            if (sc->fused_shade) {
+                k_bounce<MODE, STATS><<<persistent_grid(k_bounce<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
+                    v, ctr, in, outc, qin, qout, canvas, paths, path_stride);
+                sc->kernel_launches++;
+            } else {
+                // the wave-0 hit queue is consumed; it now holds this wave's hits
+                k_path_trace<MODE, STATS><<<persistent_grid(k_path_trace<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
+                    v, ctr, in, qin, paths, path_stride, hitq);
+                k_shadow_gen<true><<<persistent_grid(k_shadow_gen<true>, sc->sm_count), kThreads, 0, st>>>(v, ctr, in, hitq, shq, paths, path_stride);
+                trace_shadows(in);
+                k_path_advance<<<persistent_grid(k_path_advance, sc->sm_count), kThreads, 0, st>>>(
+                    v, ctr, in, outc, hitq, occl, att4, qout, canvas, paths, path_stride);
+                sc->kernel_launches += 3;
+            }
             (*waves)++;
             std::swap(in, outc);
             std::swap(qin, qout);

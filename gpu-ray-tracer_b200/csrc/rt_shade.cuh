@@ -22,21 +22,11 @@ RT_HD float dist_atten(const SceneView& s, float dist) {
     return quad < 1.0f ? 1.0f : 1.0f / quad;
 }
 
-// Light::attenuate (light.cu:29-61): `cur` is the shadow ray (see shadow_ray()), then a loop of
-// CLOSEST-hit casts that walks through refractive occluders. When no material in the scene is
-// refractive the loop body runs once and only asks "is the closest hit within max_t", which an
-// any-hit query answers exactly, so that case terminates on the first accepted occluder.
-// OPAQUE_ONLY (compile time): the caller guarantees !s.any_refractive, so the closest-hit loop is
-// not even instantiated (code size and registers).
-template <bool OPAQUE_ONLY, class Tracer>
-RT_HD float4 light_attenuate(const SceneView& s, const Tracer& tr, const LightRec& L, rtx::Ray cur, float max_t,
-                             RayCounts& rc) {
+// The closest-hit loop of Light::attenuate (light.cu:34-60) on its own (k_shadow<LOOP>).
+template <class Tracer>
+RT_HD float4 light_attenuate_loop(const SceneView& s, const Tracer& tr, const LightRec& L, rtx::Ray cur, float max_t,
+                                  RayCounts& rc) {
     float4 rv = L.color;
-    if (OPAQUE_ONLY || !s.any_refractive) {
-        rc.shadow++;
-        return tr.occluded(cur, max_t) ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : rv;
-    }
-    if (OPAQUE_ONLY) return rv;
     for (;;) {
         Hit sh;
         rc.shadow++;
@@ -52,6 +42,24 @@ RT_HD float4 light_attenuate(const SceneView& s, const Tracer& tr, const LightRe
         cur = rtx::ray_make(rtx::ray_at(cur, sh.t), cur.d);
         max_t -= sh.t;
     }
+}
+
+// Light::attenuate (light.cu:29-61): `cur` is the shadow ray (see shadow_ray()), then a loop of
+// CLOSEST-hit casts that walks through refractive occluders. When no material in the scene is
+// refractive the loop body runs once and only asks "is the closest hit within max_t", which an
+// any-hit query answers exactly, so that case terminates on the first accepted occluder.
+// OPAQUE_ONLY (compile time): the caller guarantees !s.any_refractive, so the closest-hit loop is
+// not even instantiated (code size and registers).
+template <bool OPAQUE_ONLY, class Tracer>
+RT_HD float4 light_attenuate(const SceneView& s, const Tracer& tr, const LightRec& L, rtx::Ray cur, float max_t,
+                             RayCounts& rc) {
+    float4 rv = L.color;
+    if (OPAQUE_ONLY || !s.any_refractive) {
+        rc.shadow++;
+        return tr.occluded(cur, max_t) ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : rv;
+    }
+    if (OPAQUE_ONLY) return rv;
+    return light_attenuate_loop(s, tr, L, cur, max_t, rc);
 }
 
 // PointLight::shine / DirLight::shine (light.cu:63-77), the part before attenuate(): direction to
@@ -110,11 +118,12 @@ RT_HD float4 illuminate(const SceneView& s, const Tracer& tr, const rtx::Ray& ra
     return sum;
 }
 
-// illuminate for the split pipeline of all-opaque scenes: the shadow rays of this hit were traced
-// by k_shadow; occluded(i) tells whether light i is blocked. Same operations as illuminate<true>.
-template <class Occluded>
+// illuminate for the split pipelines: the shadow rays of this hit were traced by k_shadow;
+// atten(i) is what Light::attenuate returned for light i (the light colour, zero when blocked,
+// or the colour filtered by the refractive occluders). Same operations as illuminate().
+template <class Atten>
 RT_HD float4 illuminate_resolved(const SceneView& s, const rtx::Ray& ray, float t, float3 norm, const MatRec& m,
-                                 Occluded occluded) {
+                                 Atten atten) {
     float4 sum = rtx::add4(m.Ke, rtx::mul4(m.Ka, s.ambience));
     float3 hit_pos = rtx::ray_at(ray, t);
     for (int i = 0; i < s.n_lights; i++) {
@@ -122,7 +131,7 @@ RT_HD float4 illuminate_resolved(const SceneView& s, const rtx::Ray& ray, float 
         float3 dir_to_light;
         float max_t, da;
         light_setup(s, L, hit_pos, dir_to_light, max_t, da);
-        float4 a = occluded(i) ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : L.color;
+        float4 a = atten(i, L);
         float4 incoming = L.kind == 0 ? rtx::scale4(da, a) : a;
         sum = rtx::add4(sum, phong(m, norm, incoming, ray.d, dir_to_light));
     }
@@ -168,9 +177,11 @@ RT_HD void frame_init_root(Frame& f, const rtx::Ray& r, int depth) {
 // reference keeps one Isect for the whole ray tree and reads isect.mat in the REFLECT/REFRACT
 // cases after deeper bounces may have overwritten it.
 // `frames` may point to local or global memory (one path per thread either way).
-template <class Tracer>
-RT_HD bool path_advance(const SceneView& s, const Tracer& tr, Frame* frames, int& stack_top, int& isect_mat,
-                        float4& acc, bool hit, const Hit& h, RayCounts& rc) {
+// `illum(ray, t, normal, material)` returns illuminate() of the hit: traced in place (path_advance)
+// or assembled from shadow rays a previous kernel traced (the split bounce pipeline).
+template <class Illum>
+RT_HD bool path_advance_with(const SceneView& s, Illum illum, Frame* frames, int& stack_top, int& isect_mat,
+                             float4& acc, bool hit, const Hit& h) {
     if (hit) {
         Frame& top = frames[stack_top];
         int mat_id = s.tris[h.tri].mat;
@@ -192,7 +203,7 @@ RT_HD bool path_advance(const SceneView& s, const Tracer& tr, Frame* frames, int
             stack_top--;
         }
         isect_mat = mat_id;
-        acc = rtx::add4(acc, rtx::mul4(atten, illuminate(s, tr, ray, h.t, n, m, rc)));
+        acc = rtx::add4(acc, rtx::mul4(atten, illum(ray, h.t, n, m)));
     } else {
         stack_top--;
     }
@@ -237,6 +248,14 @@ RT_HD bool path_advance(const SceneView& s, const Tracer& tr, Frame* frames, int
         }
     }
     return false;
+}
+
+template <class Tracer>
+RT_HD bool path_advance(const SceneView& s, const Tracer& tr, Frame* frames, int& stack_top, int& isect_mat,
+                        float4& acc, bool hit, const Hit& h, RayCounts& rc) {
+    return path_advance_with(
+        s, [&](const rtx::Ray& ray, float t, float3 n, const MatRec& m) { return illuminate(s, tr, ray, t, n, m, rc); },
+        frames, stack_top, isect_mat, acc, hit, h);
 }
 
 // Whole pixel in one thread (rt_debug_cast and the host-side harness): propagate_ray verbatim.
