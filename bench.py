@@ -304,11 +304,12 @@ def run_ours(a):
         l2_peak = pkg.measure_l2_bandwidth(32 << 20, 40)
         # dominant kernel and its algorithmic HBM bytes per launch (DESIGN.md "Roofline"):
         #   k_primary: 4 B per missed pixel (canvas) + 32 B per hit (hit queue write)
-        #   k_shade  : 32 B per hit (queue read) + 4 B per hit (canvas)
         pix_local = sst["rays_primary"]
         hits = sst["n_hits"]
+        #   k_shadow : 32 B per traced shadow ray (queue read) + 1 B (occlusion flag)
+        shadow_traced = sst["rays_shadow"] - sst["rays_culled"]
         kernels = {"k_primary": (avg("ms_primary"), 4.0 * (pix_local - hits) + 32.0 * hits),
-                   "k_shade": (avg("ms_shade"), 36.0 * hits)}
+                   "k_shadow": (avg("ms_shadow"), 33.0 * shadow_traced)}
         dom = max(kernels, key=lambda k: kernels[k][0])
         dom_ms, dom_bytes = kernels[dom]
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
@@ -327,7 +328,10 @@ def run_ours(a):
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
                 "ms_per_step": ms_dev / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic (procedural world, seed 42)",
-                "config": {"workload": workload_name(a), "rays_per_frame": rays_per_frame, "instances": desc.n_instances,
+                "config": {"workload": workload_name(a), "rays_per_frame": rays_per_frame,
+                           "rays": "the reference's cast_ray calls for this frame; culled_frac of them (shadow rays of lights "
+                                   "with zero Phong weight) are answered without a traversal",
+                           "culled_frac": sst["rays_culled"] / max(sst["rays_total"], 1), "instances": desc.n_instances,
                            "triangles": sst_prims(scene), "step": "BVH rebuild + trace" if not a.keep_bvh else "trace (BVH kept)",
                            "l2": "flushed between timed iterations (256 MiB write)",
                            "sharding": "screen tiles %dx%d round-robin over %d rank(s)" % (a.tile_w, a.tile_h, world)},
@@ -335,7 +339,8 @@ def run_ours(a):
                         "d2h_bytes_per_step": 4 * W * H},
                 "gpu_launches": launches_all, "clocks": clocks,
                 "breakdown_ms": {"build": avg("ms_build"), "trace": ms_trace, "k_primary": avg("ms_primary"),
-                                 "k_shade": avg("ms_shade"), "k_bounce": avg("ms_bounce"), "waves": st[0]["waves"]},
+                                 "shade": avg("ms_shade"), "k_shadow": avg("ms_shadow"), "bounce_waves": avg("ms_bounce"),
+                                 "waves": st[0]["waves"]},
                 "roofline": roofline}
         if world == 1 and not a.no_cpu_baseline:
             v, kind, cores, sample, _ = cpu_reference_run(a, a.cpu_seconds)

@@ -24,6 +24,7 @@ CUDA_LIB_PATH = os.path.join(_HERE, "librtb200.so")
 RT_SEMANTICS_GPU, RT_SEMANTICS_CPU = 0, 1
 RT_RENDER_REBUILD_BVH, RT_RENDER_NO_BVH, RT_RENDER_CANVAS_DEVICE = 1, 2, 4
 RT_RENDER_SORT_RAYS, RT_RENDER_TILED_OUTPUT, RT_RENDER_STATS, RT_RENDER_FUSED_SHADE = 8, 16, 32, 64
+RT_RENDER_TRACE_UNLIT = 128
 
 
 class RtMaterial(C.Structure):
@@ -79,7 +80,8 @@ class RtFrameStats(C.Structure):
                 ("rays_secondary", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("prims_prefiltered", C.c_uint64), ("ms_build", C.c_float), ("ms_trace", C.c_float),
                 ("ms_total", C.c_float), ("waves", C.c_int32), ("kernel_launches", C.c_int32),
-                ("ms_primary", C.c_float), ("ms_shade", C.c_float), ("ms_bounce", C.c_float), ("n_hits", C.c_int32), ("ms_shadow", C.c_float)]
+                ("ms_primary", C.c_float), ("ms_shade", C.c_float), ("ms_bounce", C.c_float), ("n_hits", C.c_int32), ("ms_shadow", C.c_float),
+                ("rays_culled", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

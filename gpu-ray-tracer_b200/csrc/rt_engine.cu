@@ -119,7 +119,7 @@ static long long slab_pixels(const TileMap& m) {
 // ---------------------------------------------------------------- device counters
 // d_counters layout (unsigned long long[32]):
 enum { C_WORK0 = 0, C_HITQ = 1, C_WORK1 = 2, C_PATHS = 3, C_QUEUE_A = 4, C_QUEUE_B = 5, C_WORK2 = 6,
-       C_RAYS_PRIMARY = 8, C_RAYS_SHADOW = 9, C_RAYS_SECONDARY = 10, C_NODES = 11, C_PRIMS = 12, C_EXACT = 13, C_N = 32 };
+       C_RAYS_PRIMARY = 8, C_RAYS_SHADOW = 9, C_RAYS_SECONDARY = 10, C_NODES = 11, C_PRIMS = 12, C_EXACT = 13, C_RAYS_CULLED = 14, C_N = 32 };
 
 __device__ __forceinline__ void flush_counts(unsigned long long* ctr, const RayCounts& rc, const TravStats& ts, bool stats) {
     unsigned v[6] = {rc.primary, rc.shadow, rc.secondary, ts.nodes, ts.prims, ts.exact};
@@ -129,6 +129,17 @@ __device__ __forceinline__ void flush_counts(unsigned long long* ctr, const RayC
         for (int o = 16; o; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
         if ((threadIdx.x & 31) == 0 && x) atomicAdd(&ctr[C_RAYS_PRIMARY + i], (unsigned long long)x);
     }
+}
+
+// One atomicAdd per converged group of lanes instead of one per lane (same-address atomics
+// serialise in one L2 slice: 2.6 M of them cost k_resolve 0.25 ms on world8_stress at 4K).
+__device__ __forceinline__ int warp_alloc(unsigned long long* counter) {
+    unsigned m = __activemask();
+    int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    unsigned long long base = 0;
+    if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
+    base = __shfl_sync(m, base, leader);
+    return (int)base + __popc(m & ((1u << lane) - 1u));
 }
 
 struct HitRec {  // 32 bytes
@@ -237,7 +248,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
         const MatRec& m = s.mats[mat_id];
         if (!OPAQUE_ONLY && s.depth > 0 && (m.reflective || m.refractive)) {
             // the pixel continues: give it a path slot; k_bounce shades this hit as its first step
-            int slot = (int)atomicAdd(&ctr[C_PATHS], 1ull);
+            int slot = warp_alloc(&ctr[C_PATHS]);
             PathHead* head = (PathHead*)(paths + (size_t)slot * path_stride);
             Frame* frames = (Frame*)(head + 1);
             PathHead hd;
@@ -248,7 +259,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
             Frame f;
             frame_init_root(f, r, s.depth);
             frames[0] = f;
-            int qi = (int)atomicAdd(&ctr[C_QUEUE_A], 1ull);
+            int qi = warp_alloc(&ctr[C_QUEUE_A]);
             queue[qi] = slot;
             continue;
         }
@@ -279,10 +290,11 @@ __device__ __forceinline__ Frame* path_frames(unsigned char* paths, int path_str
 // PATHS == false: hits of camera rays (wave 0). PATHS == true: hits of path rays; rec.out_index is
 // the path slot and rec.inst < 0 marks a miss (no shadow rays).
 template <bool PATHS>
-__global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, const unsigned long long* ctr, int ctr_n,
-                                                        const HitRec* hitq, ShadowRec* shq, unsigned char* paths,
-                                                        int path_stride) {
+__global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned long long* ctr, int ctr_n,
+                                                        const HitRec* hitq, ShadowRec* shq, unsigned char* occl, float4* att4,
+                                                        unsigned char* paths, int path_stride) {
     const int n = (int)ctr[ctr_n];
+    unsigned culled = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         HitRec rec = hitq[i];
         rtx::Ray r;
@@ -296,20 +308,39 @@ __global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, const unsi
             r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
         }
         float3 hit_pos = hit ? rtx::ray_at(r, rec.t) : rtx::mk3(0.f, 0.f, 0.f);
+        float3 nrm = rtx::mk3(0.f, 0.f, 0.f);
+        const MatRec* m = nullptr;
+        if (hit && s.cull_unlit) {
+            Hit h;
+            h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
+            nrm = hit_normal(s, h);
+            m = &s.mats[s.tris[rec.tri].mat];
+        }
         for (int l = 0; l < s.n_lights; l++) {
             ShadowRec q;
             q.o_maxt = make_float4(0.f, 0.f, 0.f, -1.f);
             q.d = make_float4(0.f, 0.f, 0.f, 0.f);
+            size_t j = (size_t)l * n + i;
             if (hit) {
                 float3 dir;
                 float max_t, da;
                 light_setup(s, s.lights[l], hit_pos, dir, max_t, da);
-                rtx::Ray cur = shadow_ray(hit_pos, dir);
-                q.o_maxt = make_float4(cur.o.x, cur.o.y, cur.o.z, max_t);
-                q.d = make_float4(cur.d.x, cur.d.y, cur.d.z, 0.f);
+                if (m && light_unlit(*m, nrm, dir)) {
+                    // never read by the resolve step (same predicate there); defined anyway
+                    culled++;
+                    if (att4) att4[j] = make_float4(0.f, 0.f, 0.f, 0.f); else occl[j] = 1;
+                } else {
+                    rtx::Ray cur = shadow_ray(hit_pos, dir);
+                    q.o_maxt = make_float4(cur.o.x, cur.o.y, cur.o.z, max_t);
+                    q.d = make_float4(cur.d.x, cur.d.y, cur.d.z, 0.f);
+                }
             }
-            shq[(size_t)l * n + i] = q;
+            shq[j] = q;
         }
+    }
+    if (s.cull_unlit) {
+        for (int o = 16; o; o >>= 1) culled += __shfl_xor_sync(0xffffffffu, culled, o);
+        if ((threadIdx.x & 31) == 0 && culled) atomicAdd(&ctr[C_RAYS_CULLED], (unsigned long long)culled);
     }
 }
 
@@ -367,7 +398,7 @@ __global__ void __launch_bounds__(kThreads) k_resolve(SceneView s, unsigned long
         const MatRec& m = s.mats[mat_id];
         AttenLookup att = {occl, att4, (size_t)n, (size_t)i};
         if (SECONDARY && (m.reflective || m.refractive)) {
-            int slot = (int)atomicAdd(&ctr[C_PATHS], 1ull);
+            int slot = warp_alloc(&ctr[C_PATHS]);
             PathHead* head;
             Frame* frames = path_frames(paths, path_stride, slot, &head);
             Frame f;
@@ -383,7 +414,7 @@ __global__ void __launch_bounds__(kThreads) k_resolve(SceneView s, unsigned long
                 hd.acc = acc; hd.out_index = rec.out_index; hd.stack_top = stack_top; hd.isect_mat = isect_mat;
                 hd.pending = 0; hd.hit = h; hd.pad0 = hd.pad1 = 0;
                 *head = hd;
-                queue[(int)atomicAdd(&ctr[C_QUEUE_A], 1ull)] = slot;
+                queue[warp_alloc(&ctr[C_QUEUE_A])] = slot;
             } else {
                 canvas[rec.out_index] = rtx::pack_color(acc);
             }
@@ -443,7 +474,7 @@ __global__ void __launch_bounds__(kThreads) k_path_advance(SceneView s, unsigned
             head->acc = acc;
             head->stack_top = stack_top;
             head->isect_mat = isect_mat;
-            queue_out[(int)atomicAdd(&ctr[ctr_out], 1ull)] = slot;
+            queue_out[warp_alloc(&ctr[ctr_out])] = slot;
         } else {
             canvas[head->out_index] = rtx::pack_color(acc);
         }
@@ -481,7 +512,7 @@ __global__ void __launch_bounds__(kThreads) k_bounce(SceneView s, unsigned long 
             head->acc = acc;
             head->stack_top = stack_top;
             head->isect_mat = isect_mat;
-            int qi = (int)atomicAdd(&ctr[ctr_out], 1ull);
+            int qi = warp_alloc(&ctr[ctr_out]);
             queue_out[qi] = slot;
         } else {
             canvas[head->out_index] = rtx::pack_color(acc);
@@ -644,6 +675,9 @@ SceneView make_view(const RtScene* sc, bool with_bvh) {
     v.width = sc->width; v.height = sc->height;
     v.any_refractive = sc->any_refractive;
     v.any_secondary = sc->any_secondary;
+    // not with refractive materials: a culled ray would have cost the reference an unknown number
+    // of Light::attenuate casts, and rays_shadow must stay the reference's count
+    v.cull_unlit = (sc->cull_ok && !sc->any_refractive && !sc->trace_unlit && !sc->fused_shade) ? 1 : 0;
     v.one_bits = 0x3f800000u;
     return v;
 }
@@ -724,6 +758,7 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
     rth::prepare_host_scene(d, hs);
     sc->any_refractive = hs.any_refractive;
     sc->any_secondary = hs.any_secondary;
+    sc->cull_ok = hs.cull_ok;
     sc->n_materials = (int)hs.mats.size();
     sc->mesh_tri_count = hs.mesh_tri_count;
     int rc;
@@ -853,7 +888,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     HitRec* hitq = sc->d_hitq.as<HitRec>();
     unsigned char* paths = sc->d_paths.as<unsigned char>();
     if (!sc->fused_shade) {
-        k_shadow_gen<false><<<persistent_grid(k_shadow_gen<false>, sc->sm_count), kThreads, 0, st>>>(v, ctr, C_HITQ, hitq, shq, nullptr, 0);
+        k_shadow_gen<false><<<persistent_grid(k_shadow_gen<false>, sc->sm_count), kThreads, 0, st>>>(v, ctr, C_HITQ, hitq, shq, occl, att4, nullptr, 0);
         sc->kernel_launches++;
         RT_CUDA(cudaEventRecord(sc->ev[8], st));
         trace_shadows(C_HITQ);
@@ -892,7 +927,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
                 // the wave-0 hit queue is consumed; it now holds this wave's hits
                 k_path_trace<MODE, STATS><<<persistent_grid(k_path_trace<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, qin, paths, path_stride, hitq);
-                k_shadow_gen<true><<<persistent_grid(k_shadow_gen<true>, sc->sm_count), kThreads, 0, st>>>(v, ctr, in, hitq, shq, paths, path_stride);
+                k_shadow_gen<true><<<persistent_grid(k_shadow_gen<true>, sc->sm_count), kThreads, 0, st>>>(v, ctr, in, hitq, shq, occl, att4, paths, path_stride);
                 trace_shadows(in);
                 k_path_advance<<<persistent_grid(k_path_advance, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, outc, hitq, occl, att4, qout, canvas, paths, path_stride);
@@ -999,6 +1034,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     const bool no_bvh = (p.flags & RT_RENDER_NO_BVH) != 0;
     const bool want_stats = (p.flags & RT_RENDER_STATS) != 0;
     sc->fused_shade = (p.flags & RT_RENDER_FUSED_SHADE) != 0;
+    sc->trace_unlit = (p.flags & RT_RENDER_TRACE_UNLIT) != 0;
     bool built = false;
     RT_CUDA(cudaEventRecord(sc->ev[2], st));
     if (!no_bvh) {
@@ -1037,7 +1073,8 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
         fs.ms_build = bs.ms_build;
     }
     fs.rays_primary = host_ctr[C_RAYS_PRIMARY];
-    fs.rays_shadow = host_ctr[C_RAYS_SHADOW];
+    fs.rays_culled = host_ctr[C_RAYS_CULLED];
+    fs.rays_shadow = host_ctr[C_RAYS_SHADOW] + fs.rays_culled;
     fs.rays_secondary = host_ctr[C_RAYS_SECONDARY];
     fs.rays_total = fs.rays_primary + fs.rays_shadow + fs.rays_secondary;
     fs.nodes_visited = host_ctr[C_NODES];

@@ -4,6 +4,7 @@
 #ifndef RTB200_HOSTPREP_H
 #define RTB200_HOSTPREP_H
 
+#include <cmath>
 #include <cstring>
 #include <map>
 #include <string>
@@ -23,6 +24,7 @@ struct HostScene {
     std::vector<rtd::LightRec> lights;
     std::vector<int> mesh_tri_count;
     int any_refractive = 0, any_secondary = 0;
+    int cull_ok = 1;  // every colour that can enter a light's `incoming` is finite (rt_shade.cuh light_unlit)
 };
 
 inline bool is_identity_rot(const float* q) {
@@ -60,6 +62,8 @@ inline void prepare_host_scene(const RtSceneDesc* d, HostScene& hs) {
             r.alpha = m.alpha; r.eta = m.eta;
             r.reflective = (m.Kr[0] > 0.f || m.Kr[1] > 0.f || m.Kr[2] > 0.f || m.Kr[3] > 0.f) ? 1 : 0;
             r.refractive = (m.Kt[0] > 0.f || m.Kt[1] > 0.f || m.Kt[2] > 0.f || m.Kt[3] > 0.f) ? 1 : 0;
+            for (int k = 0; k < 4; k++)
+                if (!std::isfinite(m.Kd[k]) || !std::isfinite(m.Ks[k]) || !(m.Kt[k] <= 1.0f)) hs.cull_ok = 0;
             if (r.refractive) hs.any_refractive = 1;
             if (r.refractive || r.reflective) hs.any_secondary = 1;
             id = (int)hs.mats.size();
@@ -96,6 +100,8 @@ inline void prepare_host_scene(const RtSceneDesc* d, HostScene& hs) {
         hs.lights[i].kind = d->lights[i].kind;
         hs.lights[i].color = make_float4(d->lights[i].color[0], d->lights[i].color[1], d->lights[i].color[2], d->lights[i].color[3]);
         hs.lights[i].v = make_float3(d->lights[i].v[0], d->lights[i].v[1], d->lights[i].v[2]);
+        for (int k = 0; k < 4; k++)
+            if (!std::isfinite(d->lights[i].color[k])) hs.cull_ok = 0;
     }
 }
 

@@ -65,7 +65,8 @@ struct RtScene {
     RtCamera camera;
     RtEnv env;
     int width = 0, height = 0;
-    int any_refractive = 0, any_secondary = 0;
+    int any_refractive = 0, any_secondary = 0, cull_ok = 0;
+    bool trace_unlit = false;       // RT_RENDER_TRACE_UNLIT
     std::vector<int> mesh_tri_count;
     // device
     rth::DevBuf d_verts, d_norms, d_tris, d_meshes, d_insts, d_mats, d_lights, d_mesh_box;

@@ -59,6 +59,7 @@ struct SceneView {
     int width, height;
     int any_refractive;  // some material has Kt > 0: shadow rays need the closest-hit loop
     int any_secondary;   // some material has Kr > 0 or Kt > 0
+    int cull_unlit;      // skip shadow rays of lights with zero Phong weight (rt_shade.cuh light_unlit)
     unsigned one_bits;   // 0x3f800000, kept opaque to the compiler (rt_bvh.cuh qfloat)
 };
 

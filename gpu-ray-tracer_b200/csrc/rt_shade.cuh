@@ -118,6 +118,16 @@ RT_HD float4 illuminate(const SceneView& s, const Tracer& tr, const rtx::Ray& ra
     return sum;
 }
 
+// A light whose Phong weight is exactly zero: max(L.N, 0) == 0 and Ks == 0 (with alpha >= 0 the
+// specular power is finite, so specular = pow * 0 = 0). phong() then returns (0 + 0) * incoming = 0
+// for every finite `incoming`, lit or shadowed, and sum + 0 == sum: the shadow ray of such a light
+// cannot change the pixel and the split pipelines do not trace it (SceneView::cull_unlit, which
+// the host only sets when every colour that enters `incoming` is finite).
+RT_HD bool light_unlit(const MatRec& m, float3 norm, float3 dir_to_light) {
+    return fmaxf(rtx::dot3(dir_to_light, norm), 0.0f) == 0.0f && m.Ks.x == 0.0f && m.Ks.y == 0.0f && m.Ks.z == 0.0f &&
+           m.Ks.w == 0.0f && m.alpha >= 0.0f;
+}
+
 // illuminate for the split pipelines: the shadow rays of this hit were traced by k_shadow;
 // atten(i) is what Light::attenuate returned for light i (the light colour, zero when blocked,
 // or the colour filtered by the refractive occluders). Same operations as illuminate().
@@ -131,6 +141,7 @@ RT_HD float4 illuminate_resolved(const SceneView& s, const rtx::Ray& ray, float 
         float3 dir_to_light;
         float max_t, da;
         light_setup(s, L, hit_pos, dir_to_light, max_t, da);
+        if (s.cull_unlit && light_unlit(m, norm, dir_to_light)) continue;  // its shadow ray was not traced
         float4 a = atten(i, L);
         float4 incoming = L.kind == 0 ? rtx::scale4(da, a) : a;
         sum = rtx::add4(sum, phong(m, norm, incoming, ray.d, dir_to_light));

@@ -123,7 +123,9 @@ enum {
     RT_RENDER_SORT_RAYS = 8,     /* sort secondary rays between bounces */
     RT_RENDER_TILED_OUTPUT = 16, /* write only this rank's tiles, compacted (multi-GPU) */
     RT_RENDER_STATS = 32,        /* count nodes / triangle tests per frame (slower kernels) */
-    RT_RENDER_FUSED_SHADE = 64   /* all-opaque scenes: one fused shading kernel instead of gen / shadow / resolve */
+    RT_RENDER_FUSED_SHADE = 64,  /* fused shading / bounce kernels instead of the split gen / shadow / resolve pipeline */
+    RT_RENDER_TRACE_UNLIT = 128  /* also trace shadow rays whose Phong weight is exactly zero (the reference does; the
+                                    split pipeline skips them by default: they cannot change a pixel) */
 };
 
 typedef struct RtRenderParams {
@@ -137,7 +139,7 @@ typedef struct RtRenderParams {
 typedef struct RtFrameStats {
     uint64_t rays_total;      /* closest-hit queries = the reference's cast_ray calls */
     uint64_t rays_primary;
-    uint64_t rays_shadow;
+    uint64_t rays_shadow;     /* Light::attenuate casts the reference performs for this frame (traced + rays_culled) */
     uint64_t rays_secondary;
     uint64_t nodes_visited;   /* only filled by the stats build of the kernels */
     uint64_t tris_tested;     /* exact (reference-arithmetic) triangle tests */
@@ -152,6 +154,8 @@ typedef struct RtFrameStats {
     float ms_bounce;          /* CUDA-event time of all k_bounce waves (incl. the per-wave read-backs) */
     int32_t n_hits;           /* primary rays that hit something */
     float ms_shadow;          /* CUDA-event time of k_shadow (any-hit traversal of the shadow-ray queue; part of ms_shade) */
+    uint64_t rays_culled;     /* shadow queries counted in rays_shadow / rays_total that were answered without a
+                                 traversal (zero Phong weight, see RT_RENDER_TRACE_UNLIT) */
 } RtFrameStats;
 
 typedef struct RtBuildStats {

@@ -110,7 +110,12 @@ def test_canvas_gpu_semantics_vs_oracle(pkg, scenes, name):
     assert (c3 == oc).all()
     # all-opaque scenes shade through gen / shadow / resolve by default; the fused kernel agrees
     c4, st4 = s.render(flags=pkg.RT_RENDER_FUSED_SHADE)
-    assert (c4 == oc).all() and st4["rays_total"] == ost["rays_total"]
+    assert (c4 == oc).all() and st4["rays_total"] == ost["rays_total"] and st4["rays_culled"] == 0
+    # shadow rays of lights with zero Phong weight are answered without a traversal by default;
+    # tracing them like the reference does gives the same frame and the same query count
+    c5, st5 = s.render(flags=pkg.RT_RENDER_TRACE_UNLIT)
+    assert (c5 == oc).all() and st5["rays_total"] == ost["rays_total"] and st5["rays_culled"] == 0
+    assert st["rays_culled"] <= st["rays_shadow"]
 
 
 @pytest.mark.parametrize("name", ["world1", "world4", "world16", "world8_stress"])
