@@ -66,6 +66,12 @@ using rth::set_error;
 namespace {
 
 constexpr int kThreads = 256;
+#ifndef RT_SHADOW_MIN_BLOCKS
+#define RT_SHADOW_MIN_BLOCKS 3
+#endif
+#ifndef RT_RESOLVE_MIN_BLOCKS
+#define RT_RESOLVE_MIN_BLOCKS 3
+#endif
 static int g_device = -1;
 static int g_sm_count = 148;
 
@@ -140,6 +146,15 @@ __device__ __forceinline__ int warp_alloc(unsigned long long* counter) {
     if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
     base = __shfl_sync(m, base, leader);
     return (int)base + __popc(m & ((1u << lane) - 1u));
+}
+
+__device__ __forceinline__ unsigned warp_alloc32(unsigned* counter) {
+    unsigned m = __activemask();
+    int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    unsigned base = 0;
+    if (lane == leader) base = atomicAdd(counter, (unsigned)__popc(m));
+    base = __shfl_sync(m, base, leader);
+    return base + __popc(m & ((1u << lane) - 1u));
 }
 
 struct HitRec {  // 32 bytes
@@ -280,7 +295,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
 //   k_resolve      Phong + pack (wave 0; starts a path where the material reflects / refracts)
 //   k_path_trace   closest hit of each live path's next ray          (waves >= 1)
 //   k_path_advance Phong + the RayFrame state machine                (waves >= 1), no traversal
-struct ShadowRec { float4 o_maxt, d; };  // 32 bytes; stored light-major: index = light * n + hit; max_t < 0: no ray
+struct ShadowRec { float4 o_maxt, d; };  // 32 bytes; d.w = hit index (int bits). Light l's rays: shq[l * n .. l * n + shq_count[l])
 
 __device__ __forceinline__ Frame* path_frames(unsigned char* paths, int path_stride, int slot, PathHead** head) {
     *head = (PathHead*)(paths + (size_t)slot * path_stride);
@@ -291,8 +306,9 @@ __device__ __forceinline__ Frame* path_frames(unsigned char* paths, int path_str
 // the path slot and rec.inst < 0 marks a miss (no shadow rays).
 template <bool PATHS>
 __global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned long long* ctr, int ctr_n,
-                                                        const HitRec* hitq, ShadowRec* shq, unsigned char* occl, float4* att4,
-                                                        unsigned char* paths, int path_stride) {
+                                                        const HitRec* hitq, ShadowRec* shq, unsigned* shq_count,
+                                                        unsigned char* occl, float4* att4, unsigned char* paths,
+                                                        int path_stride) {
     const int n = (int)ctr[ctr_n];
     unsigned culled = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -316,28 +332,36 @@ __global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned l
             nrm = hit_normal(s, h);
             m = &s.mats[s.tris[rec.tri].mat];
         }
+        if (!hit) continue;
         for (int l = 0; l < s.n_lights; l++) {
-            ShadowRec q;
-            q.o_maxt = make_float4(0.f, 0.f, 0.f, -1.f);
-            q.d = make_float4(0.f, 0.f, 0.f, 0.f);
-            size_t j = (size_t)l * n + i;
-            if (hit) {
-                float3 dir;
-                float max_t, da;
-                light_setup(s, s.lights[l], hit_pos, dir, max_t, da);
-                if (m && light_unlit(*m, nrm, dir)) {
-                    // never read by the resolve step (same predicate there); defined anyway
-                    culled++;
-                    if (att4) att4[j] = make_float4(0.f, 0.f, 0.f, 0.f); else occl[j] = 1;
-                } else {
-                    rtx::Ray cur = shadow_ray(hit_pos, dir);
-                    q.o_maxt = make_float4(cur.o.x, cur.o.y, cur.o.z, max_t);
-                    q.d = make_float4(cur.d.x, cur.d.y, cur.d.z, 0.f);
+            size_t j = (size_t)l * n + i;  // where the resolve step looks the answer up
+            float3 dir;
+            float max_t, da;
+            light_setup(s, s.lights[l], hit_pos, dir, max_t, da);
+            if (m && light_unlit(*m, nrm, dir)) {
+                // never read by the resolve step (same predicate there); defined anyway
+                culled++;
+                if (att4) att4[j] = make_float4(0.f, 0.f, 0.f, 0.f); else occl[j] = 1;
+                if (!PATHS) {
+                    ShadowRec hole;
+                    hole.o_maxt = make_float4(0.f, 0.f, 0.f, -1.f);
+                    hole.d = make_float4(0.f, 0.f, 0.f, 0.f);
+                    shq[j] = hole;
                 }
+                continue;
             }
-            shq[j] = q;
+            rtx::Ray cur = shadow_ray(hit_pos, dir);
+            ShadowRec q;
+            q.o_maxt = make_float4(cur.o.x, cur.o.y, cur.o.z, max_t);
+            q.d = make_float4(cur.d.x, cur.d.y, cur.d.z, __int_as_float((int)i));
+            // PATHS: dense per-light queues (about half of the path rays miss; the holes left k_shadow
+            // 7-12 active lanes per warp). Wave 0: slot i, so neighbouring lanes keep neighbouring
+            // pixels and no atomics are needed; culled lights leave a hole (max_t < 0).
+            shq[(size_t)l * n + (PATHS ? warp_alloc32(&shq_count[l]) : (unsigned)i)] = q;
         }
     }
+    if (!PATHS && blockIdx.x == 0 && threadIdx.x < s.n_lights)
+        for (int l = threadIdx.x; l < s.n_lights; l += blockDim.x) shq_count[l] = (unsigned)n;
     if (s.cull_unlit) {
         for (int o = 16; o; o >>= 1) culled += __shfl_xor_sync(0xffffffffu, culled, o);
         if ((threadIdx.x & 31) == 0 && culled) atomicAdd(&ctr[C_RAYS_CULLED], (unsigned long long)culled);
@@ -347,21 +371,26 @@ __global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned l
 // LOOP == false: occl[j] = 1 when anything blocks the ray within max_t (any-hit).
 // LOOP == true : att4[j] = Light::attenuate's result (closest-hit walk through refractive occluders).
 template <int MODE, bool STATS, bool LOOP>
-__global__ void __launch_bounds__(kThreads) k_shadow(SceneView s, unsigned long long* ctr, int ctr_n, const ShadowRec* shq,
-                                                    unsigned char* occl, float4* att4) {
+__global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(SceneView s, unsigned long long* ctr, int ctr_n, const ShadowRec* shq,
+                                                       const unsigned* shq_count, unsigned char* occl, float4* att4) {
     TravStats ts = {0, 0, 0};
     RayCounts rc = {0, 0, 0};
     typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
     const long long n_hits = (long long)ctr[ctr_n];
-    const long long n = n_hits * s.n_lights;
-    for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (long long)gridDim.x * blockDim.x) {
-        ShadowRec q = shq[j];
-        if (q.o_maxt.w < 0.f) continue;
+    long long total = 0;
+    for (int l = 0; l < s.n_lights; l++) total += shq_count[l];
+    for (long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x; f < total; f += (long long)gridDim.x * blockDim.x) {
+        int l = 0;
+        long long k = f;
+        for (unsigned c; k >= (long long)(c = shq_count[l]); l++) k -= c;  // light whose queue holds entry f
+        ShadowRec q = shq[(size_t)l * n_hits + k];
+        if (q.o_maxt.w < 0.f) continue;  // wave-0 hole: culled light
+        size_t j = (size_t)l * n_hits + (size_t)__float_as_int(q.d.w);
         rtx::Ray r;
         r.o = rtx::mk3(q.o_maxt.x, q.o_maxt.y, q.o_maxt.z);
         r.d = rtx::mk3(q.d.x, q.d.y, q.d.z);
         if (LOOP) {
-            att4[j] = light_attenuate_loop(s, tr, s.lights[(int)(j / n_hits)], r, q.o_maxt.w, rc);
+            att4[j] = light_attenuate_loop(s, tr, s.lights[l], r, q.o_maxt.w, rc);
         } else {
             rc.shadow++;
             occl[j] = tr.occluded(r, q.o_maxt.w) ? 1 : 0;
@@ -385,7 +414,7 @@ struct AttenLookup {
 // SECONDARY == true: hits on reflective / refractive materials become paths (their first
 // RayFrame transitions run here) and are queued for the bounce waves.
 template <bool SECONDARY>
-__global__ void __launch_bounds__(kThreads) k_resolve(SceneView s, unsigned long long* ctr, const HitRec* hitq,
+__global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_resolve(SceneView s, unsigned long long* ctr, const HitRec* hitq,
                                                      const unsigned char* occl, const float4* att4, uint32_t* canvas,
                                                      unsigned char* paths, int path_stride, int* queue) {
     const int n = (int)ctr[C_HITQ];
@@ -452,7 +481,7 @@ __global__ void __launch_bounds__(kThreads) k_path_trace(SceneView s, unsigned l
 }
 
 // waves >= 1: shade the hit from the traced shadow rays, run the RayFrame transitions, requeue or finish
-__global__ void __launch_bounds__(kThreads) k_path_advance(SceneView s, unsigned long long* ctr, int ctr_in, int ctr_out,
+__global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_path_advance(SceneView s, unsigned long long* ctr, int ctr_in, int ctr_out,
                                                           const HitRec* whit, const unsigned char* occl, const float4* att4,
                                                           int* queue_out, uint32_t* canvas, unsigned char* paths,
                                                           int path_stride) {
@@ -783,7 +812,7 @@ int rt_scene_destroy(RtScene* sc) {
     if (sc->stream) cudaStreamSynchronize(sc->stream);
     rth::DevBuf* all[] = {&sc->d_verts, &sc->d_norms, &sc->d_tris, &sc->d_meshes, &sc->d_insts, &sc->d_mats, &sc->d_lights,
                           &sc->d_mesh_box, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
-                          &sc->d_queue_b, &sc->d_ids, &sc->d_shadowq, &sc->d_occl};
+                          &sc->d_queue_b, &sc->d_ids, &sc->d_shadowq, &sc->d_occl, &sc->d_shq_count};
     for (rth::DevBuf* b : all) b->release();
     sc->bvh.release();
     for (int i = 0; i < 10; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
@@ -872,23 +901,26 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     ShadowRec* shq = nullptr;
     if (!sc->fused_shade) {
         size_t cap = hit_cap * (size_t)std::max(v.n_lights, 1);
-        if (sc->d_shadowq.reserve(sizeof(ShadowRec) * cap) || sc->d_occl.reserve((loop ? sizeof(float4) : 1) * cap))
+        if (sc->d_shadowq.reserve(sizeof(ShadowRec) * cap) || sc->d_occl.reserve((loop ? sizeof(float4) : 1) * cap) ||
+            sc->d_shq_count.reserve(sizeof(unsigned) * (size_t)std::max(v.n_lights, 1)))
             return RT_ERR_OUT_OF_MEMORY;
         shq = sc->d_shadowq.as<ShadowRec>();
         if (loop) att4 = sc->d_occl.as<float4>(); else occl = sc->d_occl.as<unsigned char>();
     }
-    // one any-hit / closest-loop traversal of the n * n_lights shadow rays in shq
+    unsigned* shq_count = sc->d_shq_count.as<unsigned>();
+    const size_t shq_count_bytes = sizeof(unsigned) * (size_t)std::max(v.n_lights, 1);
+    // one any-hit / closest-loop traversal of the shadow rays queued in shq
     auto trace_shadows = [&](int ctr_n) {
         if (loop) k_shadow<MODE, STATS, true><<<persistent_grid(k_shadow<MODE, STATS, true>, sc->sm_count), kThreads, 0, st>>>(
-            v, ctr, ctr_n, shq, occl, att4);
+            v, ctr, ctr_n, shq, shq_count, occl, att4);
         else k_shadow<MODE, STATS, false><<<persistent_grid(k_shadow<MODE, STATS, false>, sc->sm_count), kThreads, 0, st>>>(
-            v, ctr, ctr_n, shq, occl, att4);
+            v, ctr, ctr_n, shq, shq_count, occl, att4);
         sc->kernel_launches++;
     };
     HitRec* hitq = sc->d_hitq.as<HitRec>();
     unsigned char* paths = sc->d_paths.as<unsigned char>();
     if (!sc->fused_shade) {
-        k_shadow_gen<false><<<persistent_grid(k_shadow_gen<false>, sc->sm_count), kThreads, 0, st>>>(v, ctr, C_HITQ, hitq, shq, occl, att4, nullptr, 0);
+        k_shadow_gen<false><<<persistent_grid(k_shadow_gen<false>, sc->sm_count), kThreads, 0, st>>>(v, ctr, C_HITQ, hitq, shq, shq_count, occl, att4, nullptr, 0);
         sc->kernel_launches++;
         RT_CUDA(cudaEventRecord(sc->ev[8], st));
         trace_shadows(C_HITQ);
@@ -927,7 +959,8 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
                 // the wave-0 hit queue is consumed; it now holds this wave's hits
                 k_path_trace<MODE, STATS><<<persistent_grid(k_path_trace<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, qin, paths, path_stride, hitq);
-                k_shadow_gen<true><<<persistent_grid(k_shadow_gen<true>, sc->sm_count), kThreads, 0, st>>>(v, ctr, in, hitq, shq, occl, att4, paths, path_stride);
+                RT_CUDA(cudaMemsetAsync(shq_count, 0, shq_count_bytes, st));
+                k_shadow_gen<true><<<persistent_grid(k_shadow_gen<true>, sc->sm_count), kThreads, 0, st>>>(v, ctr, in, hitq, shq, shq_count, occl, att4, paths, path_stride);
                 trace_shadows(in);
                 k_path_advance<<<persistent_grid(k_path_advance, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, outc, hitq, occl, att4, qout, canvas, paths, path_stride);

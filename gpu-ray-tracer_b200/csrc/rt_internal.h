@@ -71,7 +71,7 @@ struct RtScene {
     // device
     rth::DevBuf d_verts, d_norms, d_tris, d_meshes, d_insts, d_mats, d_lights, d_mesh_box;
     rth::DevBuf d_canvas, d_counters, d_hitq, d_paths, d_queue_a, d_queue_b, d_ids;
-    rth::DevBuf d_shadowq, d_occl;
+    rth::DevBuf d_shadowq, d_occl, d_shq_count;
     bool fused_shade = false;       // RT_RENDER_FUSED_SHADE: one k_shade kernel instead of gen / traverse / resolve
     bool split_shade_used = false;
     rth::Bvh bvh;

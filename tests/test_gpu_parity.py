@@ -224,3 +224,34 @@ def test_empty_scene_and_single_triangle(pkg, gpu_ok):
     assert not c.any() and st["rays_total"] == 64 * 48
     s.close()
     d.n_instances = n_keep
+
+
+@pytest.mark.parametrize("base", ["world4", "world8_stress"])
+def test_many_lights_vs_oracle(pkg, gpu_ok, tmp_path, base):
+    """Seven lights (the shipped worlds have two): per-light shadow queues, culled lights and the
+    bounce waves against the oracle; also a scene without any light."""
+    import json
+    cfg = json.load(open(scene_path(base)))
+    cfg["lights"]["point"] += [{"pos": [x, 6.0, z], "col": [90, 60, 40, 255]} for x, z in ((-3, -2), (3, 1), (0, -4))]
+    cfg["lights"]["directional"] += [{"dir": [1.0, -1.0, 0.0], "col": [40, 40, 80, 255]},
+                                     {"dir": [0.0, 1.0, 0.0], "col": [30, 30, 30, 255]}]
+    p = tmp_path / "lights7.json"
+    p.write_text(json.dumps(cfg))
+    w = pkg.World(str(p), width=320, height=240)
+    s = pkg.Scene(w)
+    o = ob.OracleScene(w)
+    oc, ost = o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    c, st = s.render(flags=pkg.RT_RENDER_REBUILD_BVH)
+    assert (c == oc).all(), f"{(c != oc).sum()} pixels differ"
+    assert st["rays_total"] == ost["rays_total"]
+    c2, st2 = s.render(flags=pkg.RT_RENDER_TRACE_UNLIT)
+    assert (c2 == oc).all() and st2["rays_culled"] == 0 and st2["rays_total"] == ost["rays_total"]
+    s.close()
+    cfg["lights"] = {"point": [], "directional": []}
+    p.write_text(json.dumps(cfg))
+    w = pkg.World(str(p), width=160, height=120)
+    s = pkg.Scene(w)
+    oc, ost = ob.OracleScene(w).render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    c, st = s.render()
+    assert (c == oc).all() and st["rays_total"] == ost["rays_total"]
+    s.close()
