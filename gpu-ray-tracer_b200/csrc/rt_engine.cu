@@ -430,14 +430,13 @@ __global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_resolve(Sce
             int slot = warp_alloc(&ctr[C_PATHS]);
             PathHead* head;
             Frame* frames = path_frames(paths, path_stride, slot, &head);
-            Frame f;
-            frame_init_root(f, r, s.depth);
-            frames[0] = f;
+            Frame top;  // the root frame starts in registers; path_advance_core stores what stays on the stack
+            frame_init_root(top, r, s.depth);
             int stack_top = 0, isect_mat = mat_id;
             float4 acc = rtx::mk4(0.f, 0.f, 0.f, 0.f);
-            bool alive = path_advance_with(
+            bool alive = path_advance_core(
                 s, [&](const rtx::Ray& ray, float t, float3 nn, const MatRec& mm) { return illuminate_resolved(s, ray, t, nn, mm, att); },
-                frames, stack_top, isect_mat, acc, true, h);
+                frames, stack_top, isect_mat, acc, true, h, top, true);
             if (alive) {
                 PathHead hd;
                 hd.acc = acc; hd.out_index = rec.out_index; hd.stack_top = stack_top; hd.isect_mat = isect_mat;

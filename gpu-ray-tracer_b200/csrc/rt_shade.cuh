@@ -190,11 +190,17 @@ RT_HD void frame_init_root(Frame& f, const rtx::Ray& r, int depth) {
 // `frames` may point to local or global memory (one path per thread either way).
 // `illum(ray, t, normal, material)` returns illuminate() of the hit: traced in place (path_advance)
 // or assembled from shadow rays a previous kernel traced (the split bounce pipeline).
+// The frame on top of the stack lives in registers (`top`) while the transitions run and is
+// stored only when another frame goes on top of it or the function returns: the stack is in
+// global memory in the wavefront kernels, and a store followed by dependent loads of the same
+// frame cost k_resolve / k_path_advance most of their time.
+// have_top: `top` already holds frames[stack_top] (not yet stored) on entry.
 template <class Illum>
-RT_HD bool path_advance_with(const SceneView& s, Illum illum, Frame* frames, int& stack_top, int& isect_mat,
-                             float4& acc, bool hit, const Hit& h) {
+RT_HD bool path_advance_core(const SceneView& s, Illum illum, Frame* frames, int& stack_top, int& isect_mat,
+                             float4& acc, bool hit, const Hit& h, Frame& top, bool have_top) {
+    bool dirty = have_top;
     if (hit) {
-        Frame& top = frames[stack_top];
+        if (!have_top) { top = frames[stack_top]; have_top = true; }
         int mat_id = s.tris[h.tri].mat;
         const MatRec& m = s.mats[mat_id];
         float3 n = hit_normal(s, h);
@@ -210,20 +216,27 @@ RT_HD bool path_advance_with(const SceneView& s, Illum illum, Frame* frames, int
             top.hit_pt = rtx::ray_at(ray, h.t);
             top.last_mat = mat_id;
             top.norm = n;
+            dirty = true;
         } else {
             stack_top--;
+            have_top = false;
         }
         isect_mat = mat_id;
         acc = rtx::add4(acc, rtx::mul4(atten, illum(ray, h.t, n, m)));
     } else {
         stack_top--;
+        have_top = false;
     }
     while (stack_top >= 0) {
-        Frame& top = frames[stack_top];
-        if (top.type == FR_NORMAL) return true;
+        if (!have_top) { top = frames[stack_top]; have_top = true; dirty = false; }
+        if (top.type == FR_NORMAL) {
+            if (dirty) frames[stack_top] = top;
+            return true;
+        }
         const MatRec& im = s.mats[isect_mat];
         if (top.type == FR_REFLECT) {
             top.type = FR_REFRACT;
+            dirty = true;
             if (im.reflective) {
                 Frame nt;
                 nt.type = FR_NORMAL;
@@ -235,12 +248,14 @@ RT_HD bool path_advance_with(const SceneView& s, Illum illum, Frame* frames, int
                 nt.hit_pt = rtx::mk3(0.f, 0.f, 0.f);
                 nt.norm = rtx::mk3(0.f, 0.f, 0.f);
                 nt.pad0 = nt.pad1 = 0;
+                frames[stack_top] = top;  // the parent stays below the new frame
                 stack_top++;
-                frames[stack_top] = nt;
+                top = nt;
             }
         } else {  // FR_REFRACT
             if (im.refractive) {
                 top.type = FR_NORMAL;
+                dirty = true;
                 float eta = s.mats[top.last_mat].eta;
                 float n1, n2;
                 if (top.in_obj) { n1 = eta; n2 = 1.0f; } else { n1 = 1.0f; n2 = eta; }
@@ -248,6 +263,7 @@ RT_HD bool path_advance_with(const SceneView& s, Illum illum, Frame* frames, int
                 float3 rd = rtx::ref_refract(top.ray.d, rtx::normalized3(top.norm), n1, n2, tir);
                 if (tir) {
                     stack_top--;
+                    have_top = false;
                 } else {
                     top.ray = rtx::ray_make(top.hit_pt, rd);
                     top.in_obj = !top.in_obj;
@@ -255,10 +271,18 @@ RT_HD bool path_advance_with(const SceneView& s, Illum illum, Frame* frames, int
                 }
             } else {
                 stack_top--;
+                have_top = false;
             }
         }
     }
     return false;
+}
+
+template <class Illum>
+RT_HD bool path_advance_with(const SceneView& s, Illum illum, Frame* frames, int& stack_top, int& isect_mat,
+                             float4& acc, bool hit, const Hit& h) {
+    Frame top;
+    return path_advance_core(s, illum, frames, stack_top, isect_mat, acc, hit, h, top, false);
 }
 
 template <class Tracer>
