@@ -81,10 +81,10 @@ class RtFrameStats(C.Structure):
                 ("prims_prefiltered", C.c_uint64), ("ms_build", C.c_float), ("ms_trace", C.c_float),
                 ("ms_total", C.c_float), ("waves", C.c_int32), ("kernel_launches", C.c_int32),
                 ("ms_primary", C.c_float), ("ms_shade", C.c_float), ("ms_bounce", C.c_float), ("n_hits", C.c_int32), ("ms_shadow", C.c_float),
-                ("rays_culled", C.c_uint64)]
+                ("ms_wave_phase", C.c_float * 4), ("rays_culled", C.c_uint64)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_}
+        return {k: (list(getattr(self, k)) if k == "ms_wave_phase" else getattr(self, k)) for k, _ in self._fields_}
 
 
 class RtBuildStats(C.Structure):

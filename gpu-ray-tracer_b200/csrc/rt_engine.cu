@@ -18,6 +18,8 @@
 //              reference's REFLECT/REFRACT state machine, compact survivors into the next queue.
 // There is no CPU fallback anywhere in this library.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -68,6 +70,9 @@ namespace {
 constexpr int kThreads = 256;
 #ifndef RT_SHADOW_MIN_BLOCKS
 #define RT_SHADOW_MIN_BLOCKS 3
+#endif
+#ifndef RT_WAVES_MIN_BLOCKS
+#define RT_WAVES_MIN_BLOCKS 3
 #endif
 #ifndef RT_RESOLVE_MIN_BLOCKS
 #define RT_RESOLVE_MIN_BLOCKS 3
@@ -125,7 +130,7 @@ static long long slab_pixels(const TileMap& m) {
 // ---------------------------------------------------------------- device counters
 // d_counters layout (unsigned long long[32]):
 enum { C_WORK0 = 0, C_HITQ = 1, C_WORK1 = 2, C_PATHS = 3, C_QUEUE_A = 4, C_QUEUE_B = 5, C_WORK2 = 6,
-       C_RAYS_PRIMARY = 8, C_RAYS_SHADOW = 9, C_RAYS_SECONDARY = 10, C_NODES = 11, C_PRIMS = 12, C_EXACT = 13, C_RAYS_CULLED = 14, C_N = 32 };
+       C_RAYS_PRIMARY = 8, C_RAYS_SHADOW = 9, C_RAYS_SECONDARY = 10, C_NODES = 11, C_PRIMS = 12, C_EXACT = 13, C_RAYS_CULLED = 14, C_WAVES = 15, C_BARRIER = 16, C_PHASE_NS = 20, C_N = 32 };
 
 __device__ __forceinline__ void flush_counts(unsigned long long* ctr, const RayCounts& rc, const TravStats& ts, bool stats) {
     unsigned v[6] = {rc.primary, rc.shadow, rc.secondary, ts.nodes, ts.prims, ts.exact};
@@ -293,8 +298,8 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
 //   k_shadow_gen   one shadow ray per (hit, light)                    no traversal
 //   k_shadow       any-hit traversal, or Light::attenuate's closest-hit loop when a material refracts
 //   k_resolve      Phong + pack (wave 0; starts a path where the material reflects / refracts)
-//   k_path_trace   closest hit of each live path's next ray          (waves >= 1)
-//   k_path_advance Phong + the RayFrame state machine                (waves >= 1), no traversal
+//   k_bounce_waves (waves >= 1, one cooperative launch) per wave: closest hit of each live path's
+//                  next ray / shadow-ray generation / shadow traversal / Phong + RayFrame state machine
 struct ShadowRec { float4 o_maxt, d; };  // 32 bytes; d.w = hit index (int bits). Light l's rays: shq[l * n .. l * n + shq_count[l])
 
 __device__ __forceinline__ Frame* path_frames(unsigned char* paths, int path_stride, int slot, PathHead** head) {
@@ -305,12 +310,9 @@ __device__ __forceinline__ Frame* path_frames(unsigned char* paths, int path_str
 // PATHS == false: hits of camera rays (wave 0). PATHS == true: hits of path rays; rec.out_index is
 // the path slot and rec.inst < 0 marks a miss (no shadow rays).
 template <bool PATHS>
-__global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned long long* ctr, int ctr_n,
-                                                        const HitRec* hitq, ShadowRec* shq, unsigned* shq_count,
-                                                        unsigned char* occl, float4* att4, unsigned char* paths,
-                                                        int path_stride) {
-    const int n = (int)ctr[ctr_n];
-    unsigned culled = 0;
+__device__ __forceinline__ void phase_shadow_gen(const SceneView& s, const int n, const HitRec* hitq, ShadowRec* shq,
+                                                 unsigned* shq_count, unsigned char* occl, float4* att4,
+                                                 unsigned char* paths, int path_stride, unsigned& culled) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         HitRec rec = hitq[i];
         rtx::Ray r;
@@ -362,21 +364,31 @@ __global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned l
     }
     if (!PATHS && blockIdx.x == 0 && threadIdx.x < s.n_lights)
         for (int l = threadIdx.x; l < s.n_lights; l += blockDim.x) shq_count[l] = (unsigned)n;
+}
+
+__device__ __forceinline__ void flush_culled(const SceneView& s, unsigned long long* ctr, unsigned culled) {
     if (s.cull_unlit) {
         for (int o = 16; o; o >>= 1) culled += __shfl_xor_sync(0xffffffffu, culled, o);
         if ((threadIdx.x & 31) == 0 && culled) atomicAdd(&ctr[C_RAYS_CULLED], (unsigned long long)culled);
     }
 }
 
+template <bool PATHS>
+__global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned long long* ctr, int ctr_n,
+                                                        const HitRec* hitq, ShadowRec* shq, unsigned* shq_count,
+                                                        unsigned char* occl, float4* att4, unsigned char* paths,
+                                                        int path_stride) {
+    unsigned culled = 0;
+    phase_shadow_gen<PATHS>(s, (int)ctr[ctr_n], hitq, shq, shq_count, occl, att4, paths, path_stride, culled);
+    flush_culled(s, ctr, culled);
+}
+
 // LOOP == false: occl[j] = 1 when anything blocks the ray within max_t (any-hit).
 // LOOP == true : att4[j] = Light::attenuate's result (closest-hit walk through refractive occluders).
-template <int MODE, bool STATS, bool LOOP>
-__global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(SceneView s, unsigned long long* ctr, int ctr_n, const ShadowRec* shq,
-                                                       const unsigned* shq_count, unsigned char* occl, float4* att4) {
-    TravStats ts = {0, 0, 0};
-    RayCounts rc = {0, 0, 0};
-    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
-    const long long n_hits = (long long)ctr[ctr_n];
+template <bool LOOP, class Tracer>
+__device__ __forceinline__ void phase_shadow(const SceneView& s, const Tracer& tr, RayCounts& rc, const long long n_hits,
+                                             const ShadowRec* shq, const unsigned* shq_count, unsigned char* occl,
+                                             float4* att4) {
     long long total = 0;
     for (int l = 0; l < s.n_lights; l++) total += shq_count[l];
     for (long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x; f < total; f += (long long)gridDim.x * blockDim.x) {
@@ -396,6 +408,15 @@ __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(Scene
             occl[j] = tr.occluded(r, q.o_maxt.w) ? 1 : 0;
         }
     }
+}
+
+template <int MODE, bool STATS, bool LOOP>
+__global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(SceneView s, unsigned long long* ctr, int ctr_n, const ShadowRec* shq,
+                                                       const unsigned* shq_count, unsigned char* occl, float4* att4) {
+    TravStats ts = {0, 0, 0};
+    RayCounts rc = {0, 0, 0};
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
+    phase_shadow<LOOP>(s, tr, rc, (long long)ctr[ctr_n], shq, shq_count, occl, att4);
     flush_counts(ctr, rc, ts, STATS);
 }
 
@@ -456,13 +477,9 @@ __global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_resolve(Sce
 }
 
 // waves >= 1: closest hit of every live path's pending ray (frames[stack_top].ray)
-template <int MODE, bool STATS>
-__global__ void __launch_bounds__(kThreads) k_path_trace(SceneView s, unsigned long long* ctr, int ctr_in, const int* queue_in,
-                                                        unsigned char* paths, int path_stride, HitRec* whit) {
-    TravStats ts = {0, 0, 0};
-    RayCounts rc = {0, 0, 0};
-    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
-    const int n = (int)ctr[ctr_in];
+template <class Tracer>
+__device__ __forceinline__ void phase_path_trace(const SceneView& s, const Tracer& tr, RayCounts& rc, const int n,
+                                                 const int* queue_in, unsigned char* paths, int path_stride, HitRec* whit) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         int slot = queue_in[i];
         PathHead* head;
@@ -476,15 +493,21 @@ __global__ void __launch_bounds__(kThreads) k_path_trace(SceneView s, unsigned l
         rec.t = h.t; rec.u = h.u; rec.v = h.v; rec.t_local = h.t_local;
         whit[i] = rec;
     }
-    flush_counts(ctr, rc, ts, STATS);
+}
+
+// first step of a wave: reset what the later steps of this wave append to (their previous readers,
+// the steps of the wave before, have completed)
+__device__ __forceinline__ void wave_reset(const SceneView& s, unsigned long long* ctr, int ctr_out, unsigned* shq_count) {
+    if (blockIdx.x == 0) {
+        if (threadIdx.x == 0) ctr[ctr_out] = 0ull;
+        for (int l = threadIdx.x; l < s.n_lights; l += blockDim.x) shq_count[l] = 0u;
+    }
 }
 
 // waves >= 1: shade the hit from the traced shadow rays, run the RayFrame transitions, requeue or finish
-__global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_path_advance(SceneView s, unsigned long long* ctr, int ctr_in, int ctr_out,
-                                                          const HitRec* whit, const unsigned char* occl, const float4* att4,
-                                                          int* queue_out, uint32_t* canvas, unsigned char* paths,
-                                                          int path_stride) {
-    const int n = (int)ctr[ctr_in];
+__device__ __forceinline__ void phase_path_advance(const SceneView& s, const int n, unsigned long long* live_out,
+                                                   const HitRec* whit, const unsigned char* occl, const float4* att4,
+                                                   int* queue_out, uint32_t* canvas, unsigned char* paths, int path_stride) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         HitRec rec = whit[i];
         int slot = rec.out_index;
@@ -502,11 +525,90 @@ __global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_path_advanc
             head->acc = acc;
             head->stack_top = stack_top;
             head->isect_mat = isect_mat;
-            queue_out[warp_alloc(&ctr[ctr_out])] = slot;
+            queue_out[warp_alloc(live_out)] = slot;
         } else {
             canvas[head->out_index] = rtx::pack_color(acc);
         }
     }
+}
+
+// All bounce waves in one cooperative launch (every block resident): the four steps of a wave run
+// as phases separated by grid barriers, and the loop ends on the device when a wave leaves no
+// live path. At 640x480 the per-wave launches were host-bound (16 launches, ~20 us each, around
+// kernels that run for 3-10 us); this removes them and the per-wave read-back.
+__device__ __forceinline__ void wave_barrier(unsigned* counter, unsigned n_blocks, unsigned& epoch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        epoch++;
+        __threadfence();
+        atomicAdd(counter, 1u);
+        const unsigned target = epoch * n_blocks;
+        while (*(volatile unsigned*)counter < target) {}
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+struct WaveArgs {
+    unsigned long long* ctr;
+    int* queue_a;
+    int* queue_b;
+    HitRec* whit;
+    ShadowRec* shq;
+    unsigned* shq_count;
+    unsigned char* occl;
+    float4* att4;
+    uint32_t* canvas;
+    unsigned char* paths;
+    int path_stride;
+    int max_waves;
+    unsigned* barrier;  // zeroed before the launch
+};
+
+template <int MODE, bool STATS, bool LOOP>
+__global__ void __launch_bounds__(kThreads, RT_WAVES_MIN_BLOCKS) k_bounce_waves(SceneView s, WaveArgs a) {
+    TravStats ts = {0, 0, 0};
+    RayCounts rc = {0, 0, 0};
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
+    unsigned epoch = 0, culled = 0;
+    int in = C_QUEUE_A, out = C_QUEUE_B;
+    int* qin = a.queue_a;
+    int* qout = a.queue_b;
+    int waves = 0;
+    for (;;) {
+        // written by the previous wave's advance phase (or k_resolve); every thread sees the same value
+        const int n = (int)*(volatile unsigned long long*)&a.ctr[in];
+        if (n == 0 || waves >= a.max_waves) break;
+        // STATS: block 0 accumulates the time between barrier completions per phase (ns)
+        const bool clock = STATS && blockIdx.x == 0 && threadIdx.x == 0;
+        unsigned long long t0 = 0, t1;
+        if (clock) t0 = global_ns();
+        wave_reset(s, a.ctr, out, a.shq_count);
+        phase_path_trace(s, tr, rc, n, qin, a.paths, a.path_stride, a.whit);
+        wave_barrier(a.barrier, gridDim.x, epoch);
+        if (clock) { t1 = global_ns(); a.ctr[C_PHASE_NS + 0] += t1 - t0; t0 = t1; }
+        phase_shadow_gen<true>(s, n, a.whit, a.shq, a.shq_count, a.occl, a.att4, a.paths, a.path_stride, culled);
+        wave_barrier(a.barrier, gridDim.x, epoch);
+        if (clock) { t1 = global_ns(); a.ctr[C_PHASE_NS + 1] += t1 - t0; t0 = t1; }
+        phase_shadow<LOOP>(s, tr, rc, (long long)n, a.shq, a.shq_count, a.occl, a.att4);
+        wave_barrier(a.barrier, gridDim.x, epoch);
+        if (clock) { t1 = global_ns(); a.ctr[C_PHASE_NS + 2] += t1 - t0; t0 = t1; }
+        phase_path_advance(s, n, &a.ctr[out], a.whit, a.occl, a.att4, qout, a.canvas, a.paths, a.path_stride);
+        wave_barrier(a.barrier, gridDim.x, epoch);
+        if (clock) { t1 = global_ns(); a.ctr[C_PHASE_NS + 3] += t1 - t0; }
+        int t = in; in = out; out = t;
+        int* q = qin; qin = qout; qout = q;
+        waves++;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) a.ctr[C_WAVES] = (unsigned long long)waves;
+    flush_counts(a.ctr, rc, ts, STATS);
+    flush_culled(s, a.ctr, culled);
 }
 
 // ---------------------------------------------------------------- waves >= 1, fused variant (RT_RENDER_FUSED_SHADE)
@@ -772,7 +874,7 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
     sc->sm_count = g_sm_count;
     cudaError_t e = cudaStreamCreateWithFlags(&sc->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__));
-    for (int i = 0; i < 10; i++) {
+    for (int i = 0; i < 12; i++) {
         e = cudaEventCreate(&sc->ev[i]);
         if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaEventCreate", __FILE__, __LINE__));
     }
@@ -814,7 +916,7 @@ int rt_scene_destroy(RtScene* sc) {
                           &sc->d_queue_b, &sc->d_ids, &sc->d_shadowq, &sc->d_occl, &sc->d_shq_count};
     for (rth::DevBuf* b : all) b->release();
     sc->bvh.release();
-    for (int i = 0; i < 10; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
+    for (int i = 0; i < 12; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
     if (sc->stream) cudaStreamDestroy(sc->stream);
     if (sc->h_pinned) cudaFreeHost(sc->h_pinned);
     delete sc;
@@ -888,10 +990,13 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     unsigned long long n_hits = 0;
     size_t hit_cap = (size_t)std::max<long long>(n_pix, 1);
     if (secondary) {
-        // paths and shadow queues are allocated for the hits actually found (one 8-byte read-back)
-        RT_CUDA(cudaMemcpyAsync(&n_hits, ctr + C_HITQ, 8, cudaMemcpyDeviceToHost, st));
-        RT_CUDA(cudaStreamSynchronize(st));
-        hit_cap = (size_t)std::max<unsigned long long>(n_hits, 1);
+        // Path stacks for every pixel when that is affordable (no host round trip after k_primary);
+        // otherwise they are allocated for the hits actually found (one 8-byte read-back).
+        if (hit_cap * (size_t)path_stride > ((size_t)4 << 30)) {
+            RT_CUDA(cudaMemcpyAsync(&n_hits, ctr + C_HITQ, 8, cudaMemcpyDeviceToHost, st));
+            RT_CUDA(cudaStreamSynchronize(st));
+            hit_cap = (size_t)std::max<unsigned long long>(n_hits, 1);
+        }
         if (sc->d_paths.reserve(hit_cap * path_stride) || sc->d_queue_a.reserve(4 * hit_cap) || sc->d_queue_b.reserve(4 * hit_cap))
             return RT_ERR_OUT_OF_MEMORY;
     }
@@ -907,7 +1012,6 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         if (loop) att4 = sc->d_occl.as<float4>(); else occl = sc->d_occl.as<unsigned char>();
     }
     unsigned* shq_count = sc->d_shq_count.as<unsigned>();
-    const size_t shq_count_bytes = sizeof(unsigned) * (size_t)std::max(v.n_lights, 1);
     // one any-hit / closest-loop traversal of the shadow rays queued in shq
     auto trace_shadows = [&](int ctr_n) {
         if (loop) k_shadow<MODE, STATS, true><<<persistent_grid(k_shadow<MODE, STATS, true>, sc->sm_count), kThreads, 0, st>>>(
@@ -944,31 +1048,39 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         int in = C_QUEUE_A, outc = C_QUEUE_B;
         int* qin = sc->d_queue_a.as<int>();
         int* qout = sc->d_queue_b.as<int>();
-        for (;;) {
-            unsigned long long live = 0;
-            RT_CUDA(cudaMemcpyAsync(&live, ctr + in, 8, cudaMemcpyDeviceToHost, st));
-            RT_CUDA(cudaStreamSynchronize(st));
-            if (live == 0) break;
-            RT_CUDA(cudaMemsetAsync(ctr + outc, 0, 8, st));
-            if (sc->fused_shade) {
+        if (sc->fused_shade) {
+            for (;;) {
+                unsigned long long live = 0;
+                RT_CUDA(cudaMemcpyAsync(&live, ctr + in, 8, cudaMemcpyDeviceToHost, st));
+                RT_CUDA(cudaStreamSynchronize(st));
+                if (live == 0) break;
+                RT_CUDA(cudaMemsetAsync(ctr + outc, 0, 8, st));
                 k_bounce<MODE, STATS><<<persistent_grid(k_bounce<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, outc, qin, qout, canvas, paths, path_stride);
                 sc->kernel_launches++;
-            } else {
-                // the wave-0 hit queue is consumed; it now holds this wave's hits
-                k_path_trace<MODE, STATS><<<persistent_grid(k_path_trace<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
-                    v, ctr, in, qin, paths, path_stride, hitq);
-                RT_CUDA(cudaMemsetAsync(shq_count, 0, shq_count_bytes, st));
-                k_shadow_gen<true><<<persistent_grid(k_shadow_gen<true>, sc->sm_count), kThreads, 0, st>>>(v, ctr, in, hitq, shq, shq_count, occl, att4, paths, path_stride);
-                trace_shadows(in);
-                k_path_advance<<<persistent_grid(k_path_advance, sc->sm_count), kThreads, 0, st>>>(
-                    v, ctr, in, outc, hitq, occl, att4, qout, canvas, paths, path_stride);
-                sc->kernel_launches += 3;
+                (*waves)++;
+                std::swap(in, outc);
+                std::swap(qin, qout);
+                if (*waves > 4096) { set_error("bounce waves did not terminate"); return RT_ERR_LIMIT; }
             }
-            (*waves)++;
-            std::swap(in, outc);
-            std::swap(qin, qout);
-            if (*waves > 4096) { set_error("bounce waves did not terminate"); return RT_ERR_LIMIT; }
+        } else {
+            // every wave inside one cooperative launch; the wave count comes back with the frame counters
+            WaveArgs wa;
+            wa.ctr = ctr; wa.queue_a = qin; wa.queue_b = qout; wa.whit = hitq; wa.shq = shq; wa.shq_count = shq_count;
+            wa.occl = occl; wa.att4 = att4; wa.canvas = canvas; wa.paths = paths; wa.path_stride = path_stride;
+            wa.max_waves = 4096;
+            wa.barrier = (unsigned*)(ctr + C_BARRIER);  // zeroed with the counters at the start of the frame
+            SceneView vv = v;
+            void* args[] = {&vv, &wa};
+            if (loop) {
+                static const int g = persistent_grid(k_bounce_waves<MODE, STATS, true>, sc->sm_count);
+                RT_CUDA(cudaLaunchCooperativeKernel((void*)k_bounce_waves<MODE, STATS, true>, dim3(g), dim3(kThreads), args, 0, st));
+            } else {
+                static const int g = persistent_grid(k_bounce_waves<MODE, STATS, false>, sc->sm_count);
+                RT_CUDA(cudaLaunchCooperativeKernel((void*)k_bounce_waves<MODE, STATS, false>, dim3(g), dim3(kThreads), args, 0, st));
+            }
+            sc->kernel_launches++;
+            *waves = -1;  // 1 + ctr[C_WAVES], filled in by the caller after the counter read-back
         }
     }
     RT_CUDA(cudaGetLastError());
@@ -1121,7 +1233,9 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
         RT_CUDA(cudaEventElapsedTime(&fs.ms_bounce, sc->ev[7], sc->ev[4]));
         fs.n_hits = (int32_t)host_ctr[C_HITQ];
     }
-    fs.waves = waves;
+    for (int k = 0; k < 4; k++) fs.ms_wave_phase[k] = (float)host_ctr[C_PHASE_NS + k] * 1e-6f;
+    fs.waves = waves >= 0 ? waves : 1 + (int)host_ctr[C_WAVES];
+    if (fs.waves > 4096) { set_error("bounce waves did not terminate"); return RT_ERR_LIMIT; }
     fs.kernel_launches = sc->kernel_launches - launches0;
     if (stats) *stats = fs;
     return RT_OK;

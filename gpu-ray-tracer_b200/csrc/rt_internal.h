@@ -77,8 +77,8 @@ struct RtScene {
     rth::Bvh bvh;
     bool boxes_valid = false;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    unsigned long long* h_pinned = nullptr;  // 64 x u64 of pinned host memory: [0,32) frame counters, [32,36) build result
+    cudaEvent_t ev[12] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    unsigned long long* h_pinned = nullptr;  // 64 x u64 of pinned host memory: [0,32) frame counters, [32,36) build result, [40,42) live counts of the bounce waves
     int sm_count = 148;
     int kernel_launches = 0;  // running count, sampled around each API call
 };

@@ -154,6 +154,8 @@ typedef struct RtFrameStats {
     float ms_bounce;          /* CUDA-event time of all k_bounce waves (incl. the per-wave read-backs) */
     int32_t n_hits;           /* primary rays that hit something */
     float ms_shadow;          /* CUDA-event time of k_shadow (any-hit traversal of the shadow-ray queue; part of ms_shade) */
+    float ms_wave_phase[4];   /* RT_RENDER_STATS: time all bounce waves spent in their four phases (path trace, shadow-ray
+                                 generation, shadow traversal, shade + advance), clocked by block 0 of k_bounce_waves */
     uint64_t rays_culled;     /* shadow queries counted in rays_shadow / rays_total that were answered without a
                                  traversal (zero Phong weight, see RT_RENDER_TRACE_UNLIT) */
 } RtFrameStats;
