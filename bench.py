@@ -223,16 +223,25 @@ def run_ours(a):
     desc = wfile.desc
     h2d = C.sizeof(pkg.RtInstance) * desc.n_instances + C.sizeof(pkg.RtCamera)
 
+    # the engine enqueues on torch's current stream: frame, NCCL all-gather and de-interleave are
+    # stream-ordered, with no host synchronisation inside a step
+    scene.set_stream(torch.cuda.current_stream().cuda_stream)
+    params_async = scene.params(flags=dev_flags | pkg.RT_RENDER_ASYNC, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h)
+
     def frame_device(flags=dev_flags):
-        """One frame, canvas left in HBM (rank-local tiles gathered and de-interleaved when N > 1)."""
+        """One frame, canvas left in HBM (rank-local tiles gathered and de-interleaved when N > 1).
+        Only enqueues; the caller synchronises and then collects the statistics with frame_stats()."""
+        flags |= pkg.RT_RENDER_ASYNC
         if world == 1:
-            _, st = scene.render(flags=flags, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=canvas_dev.data_ptr())
-            return st, st["kernel_launches"]
-        _, st = scene.render(flags=flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=slab_t.data_ptr())
+            scene.render(flags=flags, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=canvas_dev.data_ptr())
+            return
+        scene.render(flags=flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=slab_t.data_ptr())
         dist.all_gather_into_tensor(gathered, slab_t)
-        torch.cuda.current_stream().synchronize()
-        scene.untile(params, gathered.data_ptr(), canvas_dev.data_ptr())
-        return st, st["kernel_launches"] + 1
+        scene.untile(params_async, gathered.data_ptr(), canvas_dev.data_ptr())
+
+    def frame_stats():
+        st = scene.finish()
+        return st, st["kernel_launches"] + (1 if world > 1 else 0)
 
     def frame_e2e():
         """The call a user of the reference makes per frame, with host buffers on both sides."""
@@ -241,11 +250,11 @@ def run_ours(a):
         if world == 1:
             _, st = scene.render(flags=base, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=host_canvas.data_ptr())
             return st
-        st, _ = frame_device()
+        frame_device()
         if rank == 0:
             host_canvas.copy_(canvas_dev, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-        return st
+        torch.cuda.current_stream().synchronize()
+        return frame_stats()[0]
 
     def barrier():
         if world > 1:
@@ -262,9 +271,10 @@ def run_ours(a):
             flush.zero_()            # L2 flush between timed iterations (untimed)
             torch.cuda.synchronize()
             ev0.record()
-            out.append(fn())
+            r = fn()
             ev1.record()
             ev1.synchronize()
+            out.append(r if r is not None else frame_stats())
             total_ms += ev0.elapsed_time(ev1)
         clocks = sampler.stop() if sampler else None
         barrier()
@@ -277,6 +287,8 @@ def run_ours(a):
     sampler = ClockSampler(local_rank) if rank == 0 and not os.environ.get("BENCH_NO_CLOCKS") else None
     for _ in range(max(a.warmup, 3)):
         frame_device()
+        torch.cuda.current_stream().synchronize()
+        frame_stats()
         frame_e2e()
     ms_dev, outs, clocks = timed(frame_device, a.steps, sampler)
     ms_e2e, outs_e2e, _ = timed(frame_e2e, a.steps)
@@ -296,7 +308,9 @@ def run_ours(a):
 
     # one stats frame for nodes / triangle tests per ray (slower kernels, untimed). Every rank takes
     # part: the frame contains the all-gather.
-    sst, _ = frame_device(dev_flags | pkg.RT_RENDER_STATS)
+    frame_device(dev_flags | pkg.RT_RENDER_STATS)
+    torch.cuda.current_stream().synchronize()
+    sst, _ = frame_stats()
     if rank == 0:
         st = [o[0] for o in outs]
         avg = lambda k: sum(s[k] for s in st) / len(st)

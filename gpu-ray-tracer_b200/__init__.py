@@ -25,6 +25,7 @@ RT_SEMANTICS_GPU, RT_SEMANTICS_CPU = 0, 1
 RT_RENDER_REBUILD_BVH, RT_RENDER_NO_BVH, RT_RENDER_CANVAS_DEVICE = 1, 2, 4
 RT_RENDER_SORT_RAYS, RT_RENDER_TILED_OUTPUT, RT_RENDER_STATS, RT_RENDER_FUSED_SHADE = 8, 16, 32, 64
 RT_RENDER_TRACE_UNLIT = 128
+RT_RENDER_ASYNC = 256
 
 
 class RtMaterial(C.Structure):
@@ -146,6 +147,8 @@ def cuda_lib():
         lib.rt_render.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(RtFrameStats)]
         lib.rt_tiled_slab_pixels.argtypes = [vp, C.POINTER(RtRenderParams), C.POINTER(C.c_int64)]
         lib.rt_untile.argtypes = [vp, C.POINTER(RtRenderParams), vp, vp]
+        lib.rt_scene_set_stream.argtypes = [vp, vp, i32]
+        lib.rt_frame_finish.argtypes = [vp, C.POINTER(RtFrameStats)]
         lib.rt_tile_map.argtypes = [i32, i32, i32, i32, i32, i32, vp, C.POINTER(C.c_int64)]
         lib.rt_trace_primary.argtypes = [vp, i32, vp, vp, vp]
         lib.rt_cast_rays.argtypes = [vp, i32, vp, vp, i32, vp, vp, vp]
@@ -268,7 +271,18 @@ class Scene:
                 canvas = out if out is not None else np.empty((self.height, self.width), np.uint32)
             out_ptr = canvas.ctypes.data
         _check(cuda_lib().rt_render(self._h, C.byref(p), out_ptr, C.byref(st)), "rt_render")
-        return canvas, st.as_dict()
+        return canvas, (None if flags & RT_RENDER_ASYNC else st.as_dict())
+
+    def set_stream(self, cuda_stream):
+        """Enqueue all later work of this scene on the caller's CUDA stream (an int handle, e.g.
+        torch.cuda.current_stream().cuda_stream); None returns to the scene's own stream."""
+        _check(cuda_lib().rt_scene_set_stream(self._h, cuda_stream or None, 0 if cuda_stream is None else 1), "rt_scene_set_stream")
+
+    def finish(self):
+        """Waits for the frame started with RT_RENDER_ASYNC and returns its statistics."""
+        st = RtFrameStats()
+        _check(cuda_lib().rt_frame_finish(self._h, C.byref(st)), "rt_frame_finish")
+        return st.as_dict()
 
     def tiled_slab_pixels(self, params):
         n = C.c_int64()

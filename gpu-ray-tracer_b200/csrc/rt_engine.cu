@@ -872,7 +872,8 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
     if (!sc) { set_error("host allocation failed"); return RT_ERR_OUT_OF_MEMORY; }
     auto fail = [&](int rc) { rt_scene_destroy(sc); return rc; };
     sc->sm_count = g_sm_count;
-    cudaError_t e = cudaStreamCreateWithFlags(&sc->stream, cudaStreamNonBlocking);
+    cudaError_t e = cudaStreamCreateWithFlags(&sc->own_stream, cudaStreamNonBlocking);
+    sc->stream = sc->own_stream;
     if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__));
     for (int i = 0; i < 12; i++) {
         e = cudaEventCreate(&sc->ev[i]);
@@ -917,7 +918,7 @@ int rt_scene_destroy(RtScene* sc) {
     for (rth::DevBuf* b : all) b->release();
     sc->bvh.release();
     for (int i = 0; i < 12; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
-    if (sc->stream) cudaStreamDestroy(sc->stream);
+    if (sc->own_stream) cudaStreamDestroy(sc->own_stream);
     if (sc->h_pinned) cudaFreeHost(sc->h_pinned);
     delete sc;
     return RT_OK;
@@ -1159,7 +1160,17 @@ int rt_untile(RtScene* sc, const RtRenderParams* p, const uint32_t* gathered, ui
     k_untile<<<(unsigned)((n + kThreads - 1) / kThreads), kThreads, 0, sc->stream>>>(tm, slab_pixels(tm), gathered, canvas);
     sc->kernel_launches++;
     RT_CUDA(cudaGetLastError());
+    if (!(p && (p->flags & RT_RENDER_ASYNC))) RT_CUDA(cudaStreamSynchronize(sc->stream));
+    return RT_OK;
+}
+
+int rt_scene_set_stream(RtScene* sc, void* stream, int32_t external) {
+    if (!sc) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    if (sc->pending) {
+        if (int rc = rt_frame_finish(sc, nullptr)) return rc;
+    }
     RT_CUDA(cudaStreamSynchronize(sc->stream));
+    sc->stream = external ? (cudaStream_t)stream : sc->own_stream;  // external handle 0 = the legacy default stream
     return RT_OK;
 }
 
@@ -1169,8 +1180,9 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     std::memset(&p, 0, sizeof p);
     if (params) p = *params;
     if (p.semantics != RT_SEMANTICS_GPU && p.semantics != RT_SEMANTICS_CPU) { set_error("unknown semantics"); return RT_ERR_INVALID_ARG; }
-    RtFrameStats fs;
-    std::memset(&fs, 0, sizeof fs);
+    if (sc->pending) {  // an asynchronous frame was never finished: its counters are about to be reused
+        if (int rc = rt_frame_finish(sc, nullptr)) return rc;
+    }
     TileMap tm;
     if (int rc = make_tilemap(sc, &p, tm)) return rc;
     cudaStream_t st = sc->stream;
@@ -1210,7 +1222,22 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     if (!(p.flags & RT_RENDER_CANVAS_DEVICE))
         RT_CUDA(cudaMemcpyAsync(canvas, dcanvas, 4 * (size_t)out_pixels, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaEventRecord(sc->ev[5], st));
-    RT_CUDA(cudaStreamSynchronize(st));
+    sc->pending = true;
+    sc->pend_built = built; sc->pend_wavefront = wavefront; sc->pend_waves = waves; sc->pend_launches0 = launches0;
+    if (p.flags & RT_RENDER_ASYNC) return RT_OK;  // rt_frame_finish() completes the frame
+    return rt_frame_finish(sc, stats);
+}
+
+int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
+    if (!sc) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    if (!sc->pending) { set_error("no frame pending"); return RT_ERR_INVALID_ARG; }
+    sc->pending = false;
+    const bool built = sc->pend_built, wavefront = sc->pend_wavefront;
+    const int waves = sc->pend_waves, launches0 = sc->pend_launches0;
+    unsigned long long* host_ctr = sc->h_pinned;
+    RtFrameStats fs;
+    std::memset(&fs, 0, sizeof fs);
+    RT_CUDA(cudaEventSynchronize(sc->ev[5]));
     if (built) {
         RtBuildStats bs;
         if (int rc2 = rth::finish_build(sc, &bs)) return rc2;

@@ -76,7 +76,11 @@ struct RtScene {
     bool split_shade_used = false;
     rth::Bvh bvh;
     bool boxes_valid = false;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;      // the stream all work of this scene goes to: own_stream or the caller's (rt_scene_set_stream)
+    cudaStream_t own_stream = nullptr;
+    bool pending = false;               // a frame is enqueued and rt_frame_finish() has not run yet
+    bool pend_built = false, pend_wavefront = false;
+    int pend_waves = 0, pend_launches0 = 0;
     cudaEvent_t ev[12] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     unsigned long long* h_pinned = nullptr;  // 64 x u64 of pinned host memory: [0,32) frame counters, [32,36) build result, [40,42) live counts of the bounce waves
     int sm_count = 148;

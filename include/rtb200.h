@@ -124,6 +124,8 @@ enum {
     RT_RENDER_TILED_OUTPUT = 16, /* write only this rank's tiles, compacted (multi-GPU) */
     RT_RENDER_STATS = 32,        /* count nodes / triangle tests per frame (slower kernels) */
     RT_RENDER_FUSED_SHADE = 64,  /* fused shading / bounce kernels instead of the split gen / shadow / resolve pipeline */
+    RT_RENDER_ASYNC = 256,       /* rt_render / rt_untile only enqueue on the scene's stream; rt_frame_finish() waits for
+                                    the frame and returns its statistics (a host canvas is valid only after that) */
     RT_RENDER_TRACE_UNLIT = 128  /* also trace shadow rays whose Phong weight is exactly zero (the reference does; the
                                     split pipeline skips them by default: they cannot change a pixel) */
 };
@@ -205,6 +207,17 @@ int rt_update_scene(RtScene* scene, int32_t kernel_dim, int32_t optimize, uint32
 
 /* Full-control render entry (tile sharding, device-resident canvas, stats). */
 int rt_render(RtScene* scene, const RtRenderParams* params, uint32_t* canvas, RtFrameStats* stats);
+
+/* Stream-ordered use (replaces the reference's default-stream + cudaDeviceSynchronize per frame,
+ * src/raytracer.cu:108-114): rt_scene_set_stream makes every later call of this scene enqueue on the
+ * caller's CUDA stream (external != 0; cudaStream_t as void*, where a null handle is the legacy default
+ * stream) or on the scene's own stream again (external == 0), so a frame
+ * can be ordered against the caller's work (an NCCL all-gather of the tiles, a copy) without host
+ * synchronisation. With RT_RENDER_ASYNC, rt_render returns once the frame is enqueued and `stats`
+ * is not written; rt_frame_finish waits for that frame and fills the statistics. One frame can be
+ * pending per scene; starting another finishes the pending one first. */
+int rt_scene_set_stream(RtScene* scene, void* cuda_stream, int32_t external);
+int rt_frame_finish(RtScene* scene, RtFrameStats* stats);
 
 /* Multi-GPU helper: number of uint32 pixels rt_render writes with RT_RENDER_TILED_OUTPUT, and the
  * de-interleave of `world` gathered slabs back into a row-major canvas (both device pointers). */

@@ -255,3 +255,33 @@ def test_many_lights_vs_oracle(pkg, gpu_ok, tmp_path, base):
     c, st = s.render()
     assert (c == oc).all() and st["rays_total"] == ost["rays_total"]
     s.close()
+
+
+def test_async_frame_and_external_stream(pkg, scenes):
+    """RT_RENDER_ASYNC + rt_frame_finish, on the scene's own stream and on a caller's stream, give
+    the frame and the statistics of the blocking call."""
+    import torch
+    w, s = scenes("world8_stress")
+    ref, st_ref = s.render(flags=pkg.RT_RENDER_REBUILD_BVH)
+    out = np.zeros((s.height, s.width), np.uint32)
+    c, st = s.render(flags=pkg.RT_RENDER_REBUILD_BVH | pkg.RT_RENDER_ASYNC, out=out)
+    assert st is None
+    st = s.finish()
+    assert (out == ref).all() and st["rays_total"] == st_ref["rays_total"] and st["waves"] == st_ref["waves"]
+    with pytest.raises(RuntimeError):
+        s.finish()  # nothing pending
+    stream = torch.cuda.Stream()
+    dev = torch.zeros(s.height * s.width, dtype=torch.int32, device="cuda")
+    s.set_stream(stream.cuda_stream)
+    try:
+        with torch.cuda.stream(stream):
+            s.render(flags=pkg.RT_RENDER_ASYNC | pkg.RT_RENDER_CANVAS_DEVICE, out_ptr=dev.data_ptr())
+            host = dev.cpu()  # ordered after the frame on the same stream
+        st2 = s.finish()
+        assert (host.numpy().view(np.uint32).reshape(ref.shape) == ref).all() and st2["rays_total"] == st_ref["rays_total"]
+        # a second frame without finish(): the pending one is completed implicitly
+        s.render(flags=pkg.RT_RENDER_ASYNC | pkg.RT_RENDER_CANVAS_DEVICE, out_ptr=dev.data_ptr())
+        c3, st3 = s.render()
+        assert (c3 == ref).all()
+    finally:
+        s.set_stream(None)

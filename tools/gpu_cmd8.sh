@@ -1,7 +1,2 @@
 timeout 400 python -m pytest tests -m gpu -q -x 2>&1 | tail -3
-for sc in "world16 3840 2160 9" "world8_stress 3840 2160 2" "world8_stress 640 480 2" "world1 640 480 2"; do
-python tools/profile_frame.py $sc 6 | tail -2 | python -c "
-import sys,ast
-for l in sys.stdin:
-    d=ast.literal_eval(l); print({k:d[k] for k in ('ms_build','ms_trace','ms_primary','ms_shade','ms_shadow','ms_bounce','waves','kernel_launches')})"
-done
+timeout 200 python bench.py --steps 20 --warmup 3 --no-cpu-baseline 2>gpurun_out/err.log | tail -1 | tee gpurun_out/bench_r1_g.log | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['e2e']['ms_per_step'], d['breakdown_ms'], d['gpu_launches'])" || tail gpurun_out/err.log
