@@ -26,6 +26,8 @@ import tempfile
 import threading
 import time
 
+import numpy as np
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -46,6 +48,8 @@ def parse_args():
     ap.add_argument("--grid-size", type=int, default=0)
     ap.add_argument("--tile-w", type=int, default=32)
     ap.add_argument("--tile-h", type=int, default=16)
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: tiles stored into every rank's canvas over NVLink peer memory (p2p) or all-gather + de-interleave (nccl)")
     ap.add_argument("--keep-bvh", action="store_true", help="do not rebuild the BVH every frame")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline leg")
@@ -90,22 +94,28 @@ class ClockSampler:
         time.sleep(0.05)
         if self.proc:
             self.proc.terminate()
-        sm, mx, reasons, n_all = [], [], set(), len(self.rows)
-        for t, r in self.rows:
-            if self.t0 is None or not (self.t0 <= t <= self.t1 + 0.03):
-                continue
-            try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-            except Exception:
-                pass
+        n_all = len(self.rows)
+        # a region shorter than a few sampling periods (8 GPUs: 20 steps last ~15 ms) may hold no sample:
+        # widen the window into the warm-up before it and the e2e leg after it (same workload, same load)
+        for pad in (0.0, 0.1, 0.5):
+            sm, mx, reasons = [], [], set()
+            for t, r in self.rows:
+                if self.t0 is None or not (self.t0 - pad <= t <= self.t1 + 0.03 + pad):
+                    continue
+                try:
+                    sm.append(float(r[0])); mx.append(float(r[1]))
+                    for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                        if v.lower().startswith("active"):
+                            reasons.add(name)
+                except Exception:
+                    pass
+            if len(sm) >= 2:
+                break
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "samples_outside_region": n_all}
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2], "sm_min_mhz": sm[0], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
-                "samples": len(sm), "region_ms": 1e3 * (self.t1 - self.t0)}
+                "samples": len(sm), "region_ms": 1e3 * (self.t1 - self.t0), "window_pad_ms": 1e3 * pad}
 
 
 # ------------------------------------------------------------------ reference CPU arm
@@ -228,6 +238,28 @@ def run_ours(a):
     scene.set_stream(torch.cuda.current_stream().cuda_stream)
     params_async = scene.params(flags=dev_flags | pkg.RT_RENDER_ASYNC, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h)
 
+    # N > 1, default: no collective on the data path. Each rank owns a canvas the others map through
+    # CUDA IPC and rt_push_tiles stores the rank's tiles into all of them; a one-element all-reduce on
+    # the same stream is the barrier that tells every rank its canvas is complete.
+    peer_ptrs, own_canvas_ptr, token = None, None, None
+    gather = a.gather if world > 1 else "none"
+    if gather == "p2p":
+        try:
+            own_canvas_ptr, handle = pkg.peer_canvas_alloc(W * H)
+            mine = torch.tensor(list(handle), dtype=torch.uint8, device="cuda")
+            allh = torch.empty(world * 64, dtype=torch.uint8, device="cuda")
+            dist.all_gather_into_tensor(allh, mine)
+            allh = bytes(allh.cpu().numpy().tobytes())
+            peer_ptrs = [own_canvas_ptr if r == rank else pkg.peer_canvas_open(allh[64 * r:64 * r + 64]) for r in range(world)]
+            ok = torch.ones(1, device="cuda")
+        except RuntimeError as e:
+            sys.stderr.write("peer canvases unavailable (%s); using the all-gather path\n" % e)
+            ok = torch.zeros(1, device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if float(ok.item()) == 0.0:
+            gather, peer_ptrs = "nccl", None
+        token = torch.zeros(1, device="cuda")
+
     def frame_device(flags=dev_flags):
         """One frame, canvas left in HBM (rank-local tiles gathered and de-interleaved when N > 1).
         Only enqueues; the caller synchronises and then collects the statistics with frame_stats()."""
@@ -236,8 +268,12 @@ def run_ours(a):
             scene.render(flags=flags, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=canvas_dev.data_ptr())
             return
         scene.render(flags=flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=slab_t.data_ptr())
-        dist.all_gather_into_tensor(gathered, slab_t)
-        scene.untile(params_async, gathered.data_ptr(), canvas_dev.data_ptr())
+        if gather == "p2p":
+            scene.push_tiles(params_async, slab_t.data_ptr(), peer_ptrs)
+            dist.all_reduce(token)
+        else:
+            dist.all_gather_into_tensor(gathered, slab_t)
+            scene.untile(params_async, gathered.data_ptr(), canvas_dev.data_ptr())
 
     def frame_stats():
         st = scene.finish()
@@ -252,7 +288,10 @@ def run_ours(a):
             return st
         frame_device()
         if rank == 0:
-            host_canvas.copy_(canvas_dev, non_blocking=True)
+            if gather == "p2p":
+                scene.copy_to_host(own_canvas_ptr, host_canvas.numpy())
+            else:
+                host_canvas.copy_(canvas_dev, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return frame_stats()[0]
 
@@ -269,6 +308,8 @@ def run_ours(a):
             sampler.start()
         for _ in range(steps):
             flush.zero_()            # L2 flush between timed iterations (untimed)
+            if world > 1:
+                dist.barrier()       # ranks enter the step together: the all-gather must not time rank skew
             torch.cuda.synchronize()
             ev0.record()
             r = fn()
@@ -284,6 +325,21 @@ def run_ours(a):
             total_ms = float(t.item())
         return total_ms, out, clocks
 
+    if gather == "p2p":
+        # untimed check: the peer-memory exchange leaves the frame the all-gather path leaves
+        frame_device()
+        torch.cuda.current_stream().synchronize()
+        frame_stats()
+        got = scene.copy_to_host(own_canvas_ptr, np.empty(H * W, np.uint32))
+        scene.render(flags=dev_flags | pkg.RT_RENDER_ASYNC, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h,
+                     out_ptr=slab_t.data_ptr())
+        dist.all_gather_into_tensor(gathered, slab_t)
+        scene.untile(params_async, gathered.data_ptr(), canvas_dev.data_ptr())
+        torch.cuda.current_stream().synchronize()
+        frame_stats()
+        want = canvas_dev.cpu().numpy().view(np.uint32)
+        if not (got == want).all():
+            raise SystemExit("rank %d: peer-memory frame differs from the all-gather frame in %d pixels" % (rank, int((got != want).sum())))
     sampler = ClockSampler(local_rank) if rank == 0 and not os.environ.get("BENCH_NO_CLOCKS") else None
     for _ in range(max(a.warmup, 3)):
         frame_device()
@@ -348,7 +404,9 @@ def run_ours(a):
                            "culled_frac": sst["rays_culled"] / max(sst["rays_total"], 1), "instances": desc.n_instances,
                            "triangles": sst_prims(scene), "step": "BVH rebuild + trace" if not a.keep_bvh else "trace (BVH kept)",
                            "l2": "flushed between timed iterations (256 MiB write)",
-                           "sharding": "screen tiles %dx%d round-robin over %d rank(s)" % (a.tile_w, a.tile_h, world)},
+                           "sharding": "screen tiles %dx%d round-robin over %d rank(s)" % (a.tile_w, a.tile_h, world),
+                           "exchange": {"p2p": "tiles stored into every rank's canvas over NVLink peer memory (rt_push_tiles) + 1-element all-reduce as barrier",
+                                        "nccl": "NCCL all-gather of the tile slabs + de-interleave kernel", "none": "single GPU"}[gather]},
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / a.steps, "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": 4 * W * H},
                 "gpu_launches": launches_all, "clocks": clocks,
@@ -361,6 +419,13 @@ def run_ours(a):
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
                                     "host_cores": os.cpu_count()}
         print(json.dumps(line), flush=True)
+    if peer_ptrs:
+        dist.barrier()
+        for r, ptr in enumerate(peer_ptrs):
+            if r != rank:
+                pkg.peer_canvas_close(ptr)
+        dist.barrier()
+        pkg.peer_canvas_free(own_canvas_ptr)
     scene.close()
     if world > 1:
         dist.barrier()

@@ -148,6 +148,12 @@ def cuda_lib():
         lib.rt_tiled_slab_pixels.argtypes = [vp, C.POINTER(RtRenderParams), C.POINTER(C.c_int64)]
         lib.rt_untile.argtypes = [vp, C.POINTER(RtRenderParams), vp, vp]
         lib.rt_scene_set_stream.argtypes = [vp, vp, i32]
+        lib.rt_peer_canvas_alloc.argtypes = [C.c_int64, C.POINTER(vp), vp]
+        lib.rt_peer_canvas_free.argtypes = [vp]
+        lib.rt_peer_canvas_open.argtypes = [vp, C.POINTER(vp)]
+        lib.rt_peer_canvas_close.argtypes = [vp]
+        lib.rt_push_tiles.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(vp), i32]
+        lib.rt_copy_to_host.argtypes = [vp, vp, vp, C.c_int64]
         lib.rt_frame_finish.argtypes = [vp, C.POINTER(RtFrameStats)]
         lib.rt_tile_map.argtypes = [i32, i32, i32, i32, i32, i32, vp, C.POINTER(C.c_int64)]
         lib.rt_trace_primary.argtypes = [vp, i32, vp, vp, vp]
@@ -166,6 +172,29 @@ def _check(rc, what):
     if rc != 0:
         msg = cuda_lib().rt_last_error_string()
         raise RuntimeError(f"{what} failed with status {rc}: {msg.decode() if msg else ''}")
+
+
+def peer_canvas_alloc(pixels):
+    """(device pointer, 64-byte CUDA IPC handle) of a canvas other ranks can map."""
+    ptr = C.c_void_p()
+    handle = (C.c_ubyte * 64)()
+    _check(cuda_lib().rt_peer_canvas_alloc(pixels, C.byref(ptr), handle), "rt_peer_canvas_alloc")
+    return ptr.value, bytes(handle)
+
+
+def peer_canvas_open(handle):
+    ptr = C.c_void_p()
+    buf = (C.c_ubyte * 64).from_buffer_copy(handle)
+    _check(cuda_lib().rt_peer_canvas_open(buf, C.byref(ptr)), "rt_peer_canvas_open")
+    return ptr.value
+
+
+def peer_canvas_close(ptr):
+    _check(cuda_lib().rt_peer_canvas_close(ptr), "rt_peer_canvas_close")
+
+
+def peer_canvas_free(ptr):
+    _check(cuda_lib().rt_peer_canvas_free(ptr), "rt_peer_canvas_free")
 
 
 class World:
@@ -291,6 +320,15 @@ class Scene:
 
     def untile(self, params, gathered_dev_ptr, canvas_dev_ptr):
         _check(cuda_lib().rt_untile(self._h, C.byref(params), gathered_dev_ptr, canvas_dev_ptr), "rt_untile")
+
+    def push_tiles(self, params, slab_dev_ptr, peer_ptrs):
+        """Stores this rank's tiles into every rank's row-major canvas (NVLink peer memory)."""
+        arr = (C.c_void_p * len(peer_ptrs))(*peer_ptrs)
+        _check(cuda_lib().rt_push_tiles(self._h, C.byref(params), slab_dev_ptr, arr, len(peer_ptrs)), "rt_push_tiles")
+
+    def copy_to_host(self, dev_ptr, out):
+        _check(cuda_lib().rt_copy_to_host(self._h, dev_ptr, out.ctypes.data, out.size), "rt_copy_to_host")
+        return out
 
     # -- parity hooks
     def trace_primary(self, use_bvh=1):

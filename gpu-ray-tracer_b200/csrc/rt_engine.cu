@@ -734,6 +734,37 @@ __global__ void k_untile(TileMap tm, long long slab, const uint32_t* gathered, u
     canvas[p] = gathered[(long long)rank * slab + ((long long)k * tm.tile_h + ly) * tm.tile_w + lx];
 }
 
+// Multi-GPU frame exchange without a collective library: every rank stores the pixels of the tiles
+// it owns straight into the row-major canvas of every peer (its own included) through NVLink peer
+// mappings. One thread moves 4 pixels (16 bytes); a tile row is a contiguous run in the slab and
+// in the canvas, so a warp writes whole 128-byte segments. Replaces all-gather + k_untile.
+struct PeerCanvases { uint32_t* p[RT_MAX_PEERS]; int n; };
+
+__global__ void k_push_tiles(TileMap tm, const uint32_t* slab, PeerCanvases pc) {
+    const int quads_per_row = tm.tile_w >> 2;
+    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long n_quads = (long long)tm.n_owned * tm.tile_h * quads_per_row;
+    if (q >= n_quads) return;
+    int lq = (int)(q % quads_per_row);
+    long long row = q / quads_per_row;
+    int ly = (int)(row % tm.tile_h), k = (int)(row / tm.tile_h);
+    int T = k * tm.world + tm.rank;
+    int tx = T % tm.tiles_x, ty = T / tm.tiles_x;
+    int x = tx * tm.tile_w + lq * 4, y = ty * tm.tile_h + ly;
+    if (y >= tm.H || x >= tm.W) return;
+    const uint32_t* src = slab + ((long long)k * tm.tile_h + ly) * tm.tile_w + lq * 4;
+    long long dst = (long long)y * tm.W + x;
+    if (x + 4 <= tm.W && (tm.W & 3) == 0) {
+        uint4 v = *(const uint4*)src;
+        for (int r = 0; r < pc.n; r++) *(uint4*)(pc.p[r] + dst) = v;
+    } else {
+        for (int i = 0; i < 4 && x + i < tm.W; i++) {
+            uint32_t v = src[i];
+            for (int r = 0; r < pc.n; r++) pc.p[r][dst + i] = v;
+        }
+    }
+}
+
 // Resident-working-set read bandwidth (the L2 roofline denominator).
 __global__ void k_l2_read(const uint4* buf, long long n16, int iters, unsigned* sink) {
     unsigned acc = 0;
@@ -1164,6 +1195,66 @@ int rt_untile(RtScene* sc, const RtRenderParams* p, const uint32_t* gathered, ui
     return RT_OK;
 }
 
+int rt_push_tiles(RtScene* sc, const RtRenderParams* p, const uint32_t* slab, uint32_t* const* peer_canvases, int32_t n_peers) {
+    if (!sc || !slab || !peer_canvases || n_peers < 1 || n_peers > RT_MAX_PEERS) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    TileMap tm;
+    if (int rc = make_tilemap(sc, p, tm)) return rc;
+    if (tm.tile_w % 4) { set_error("tile_w must be a multiple of 4"); return RT_ERR_INVALID_ARG; }
+    PeerCanvases pc;
+    pc.n = n_peers;
+    for (int r = 0; r < n_peers; r++) {
+        if (!peer_canvases[r]) { set_error("null peer canvas"); return RT_ERR_INVALID_ARG; }
+        pc.p[r] = peer_canvases[r];
+    }
+    long long n_quads = (long long)tm.n_owned * tm.tile_h * (tm.tile_w / 4);
+    if (n_quads > 0) {
+        k_push_tiles<<<(unsigned)((n_quads + kThreads - 1) / kThreads), kThreads, 0, sc->stream>>>(tm, slab, pc);
+        sc->kernel_launches++;
+    }
+    RT_CUDA(cudaGetLastError());
+    if (!(p && (p->flags & RT_RENDER_ASYNC))) RT_CUDA(cudaStreamSynchronize(sc->stream));
+    return RT_OK;
+}
+
+// Canvas memory other processes can map: plain cudaMalloc (torch's caching allocator hands out
+// sub-allocations, which CUDA IPC cannot export), exported / imported as a 64-byte CUDA IPC handle.
+int rt_peer_canvas_alloc(int64_t pixels, uint32_t** dev_ptr, unsigned char handle[64]) {
+    if (pixels <= 0 || !dev_ptr || !handle) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    void* p = nullptr;
+    RT_CUDA(cudaMalloc(&p, 4 * (size_t)pixels));
+    RT_CUDA(cudaMemset(p, 0, 4 * (size_t)pixels));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); return rth::cuda_fail(e, "cudaIpcGetMemHandle", __FILE__, __LINE__); }
+    std::memcpy(handle, &h, 64);
+    *dev_ptr = (uint32_t*)p;
+    return RT_OK;
+}
+int rt_peer_canvas_free(uint32_t* dev_ptr) {
+    if (dev_ptr) RT_CUDA(cudaFree(dev_ptr));
+    return RT_OK;
+}
+int rt_peer_canvas_open(const unsigned char handle[64], uint32_t** dev_ptr) {
+    if (!handle || !dev_ptr) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    void* p = nullptr;
+    RT_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *dev_ptr = (uint32_t*)p;
+    return RT_OK;
+}
+int rt_peer_canvas_close(uint32_t* dev_ptr) {
+    if (dev_ptr) RT_CUDA(cudaIpcCloseMemHandle(dev_ptr));
+    return RT_OK;
+}
+int rt_copy_to_host(RtScene* sc, const uint32_t* dev_ptr, uint32_t* host_ptr, int64_t pixels) {
+    if (!sc || !dev_ptr || !host_ptr || pixels < 0) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    RT_CUDA(cudaMemcpyAsync(host_ptr, dev_ptr, 4 * (size_t)pixels, cudaMemcpyDeviceToHost, sc->stream));
+    RT_CUDA(cudaStreamSynchronize(sc->stream));
+    return RT_OK;
+}
+
 int rt_scene_set_stream(RtScene* sc, void* stream, int32_t external) {
     if (!sc) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
     if (sc->pending) {
@@ -1206,7 +1297,9 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     }
     unsigned long long* ctr = sc->d_counters.as<unsigned long long>();
     RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long) * C_N, st));
-    if (tm.tiled_out || tm.world > 1) RT_CUDA(cudaMemsetAsync(dcanvas, 0, 4 * (size_t)out_pixels, st));
+    // row-major canvas shared with other ranks' tiles: clear them. A tile slab needs no clearing: every
+    // in-canvas pixel of an owned tile is written, and the slab padding beyond the canvas edge is never read.
+    if (!tm.tiled_out && tm.world > 1) RT_CUDA(cudaMemsetAsync(dcanvas, 0, 4 * (size_t)out_pixels, st));
     RT_CUDA(cudaEventRecord(sc->ev[3], st));
     SceneView v = rth::make_view(sc, !no_bvh);
     int waves = 1, rc = RT_OK;

@@ -224,6 +224,22 @@ int rt_frame_finish(RtScene* scene, RtFrameStats* stats);
 int rt_tiled_slab_pixels(RtScene* scene, const RtRenderParams* params, int64_t* out_pixels);
 int rt_untile(RtScene* scene, const RtRenderParams* params, const uint32_t* gathered_dev, uint32_t* canvas_dev);
 
+/* Multi-GPU frame exchange over NVLink peer memory (one process per GPU), instead of all-gather +
+ * rt_untile: every rank owns a canvas other ranks can map (rt_peer_canvas_alloc returns the device
+ * pointer and a 64-byte CUDA IPC handle to send to the peers; rt_peer_canvas_open maps a peer's
+ * handle). After rt_render with RT_RENDER_TILED_OUTPUT, rt_push_tiles stores this rank's tiles into
+ * the row-major canvases of all `n_peers` ranks (peer_canvases[rank] is the own canvas). A barrier
+ * across the ranks on the same stream (any collective) then tells every rank its canvas is complete. */
+#define RT_MAX_PEERS 16
+int rt_peer_canvas_alloc(int64_t pixels, uint32_t** dev_ptr, unsigned char ipc_handle[64]);
+int rt_peer_canvas_free(uint32_t* dev_ptr);
+int rt_peer_canvas_open(const unsigned char ipc_handle[64], uint32_t** dev_ptr);
+int rt_peer_canvas_close(uint32_t* dev_ptr);
+int rt_push_tiles(RtScene* scene, const RtRenderParams* params, const uint32_t* slab_dev, uint32_t* const* peer_canvases,
+                  int32_t n_peers);
+/* Blocking device-to-host copy of `pixels` uint32 on the scene's stream. */
+int rt_copy_to_host(RtScene* scene, const uint32_t* dev_ptr, uint32_t* host_ptr, int64_t pixels);
+
 /* Host-only (no GPU needed): the tile map the kernels use. For every pixel (row-major) writes the
  * index rank `rank` stores it at inside its slab, or -1 if another rank owns the pixel. */
 int rt_tile_map(int32_t width, int32_t height, int32_t tile_w, int32_t tile_h, int32_t rank, int32_t world,
