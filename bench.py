@@ -73,7 +73,7 @@ class ClockSampler:
 
     def __init__(self, index):
         self.rows, self.t0, self.t1, self.proc = [], None, None, None
-        period = os.environ.get("BENCH_CLOCK_PERIOD_MS", "20")
+        period = os.environ.get("BENCH_CLOCK_PERIOD_MS", "10")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", period],
@@ -85,6 +85,13 @@ class ClockSampler:
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def wait_ready(self, timeout=15.0):
+        """Blocks until nvidia-smi has printed its first row (its start-up takes seconds on an 8-GPU box; a
+        multi-rank timed region of a few tens of milliseconds used to be over before the first sample)."""
+        t_end = time.time() + timeout
+        while self.proc and not self.rows and self.proc.poll() is None and time.time() < t_end:
+            time.sleep(0.02)
 
     def start(self):
         self.t0 = time.time()
@@ -341,6 +348,10 @@ def run_ours(a):
         if not (got == want).all():
             raise SystemExit("rank %d: peer-memory frame differs from the all-gather frame in %d pixels" % (rank, int((got != want).sum())))
     sampler = ClockSampler(local_rank) if rank == 0 and not os.environ.get("BENCH_NO_CLOCKS") else None
+    if sampler:
+        sampler.wait_ready()
+    if world > 1:
+        dist.barrier()
     for _ in range(max(a.warmup, 3)):
         frame_device()
         torch.cuda.current_stream().synchronize()
