@@ -120,6 +120,16 @@ def host_lib():
         lib.rth_world_free.restype = None
         lib.rth_last_error_string.restype = C.c_char_p
         lib.rth_world_dump.argtypes = [C.c_void_p, C.c_char_p]
+        f3, f4 = C.POINTER(C.c_float * 3), C.POINTER(C.c_float * 4)
+        lib.rth_pose_translate_global.argtypes = [C.POINTER(RtPose), f3]
+        lib.rth_pose_translate.argtypes = [C.POINTER(RtPose), f3]
+        lib.rth_pose_rotate.argtypes = [C.POINTER(RtPose), f4]
+        lib.rth_quat_axis_angle.argtypes = [f3, C.c_float, f4]
+        lib.rth_camera_key.argtypes = [C.POINTER(RtCamera), C.c_char]
+        lib.rth_camera_mouse.argtypes = [C.POINTER(RtCamera), C.c_float, C.c_float]
+        for fn in (lib.rth_pose_translate_global, lib.rth_pose_translate, lib.rth_pose_rotate, lib.rth_quat_axis_angle,
+                   lib.rth_camera_mouse):
+            fn.restype = None
         _host = lib
     return _host
 
@@ -227,6 +237,34 @@ class World:
 
     def dump(self, path):
         host_lib().rth_world_dump(self._h, os.fspath(path).encode())
+
+    def apply_moves(self, spec):
+        """Per-frame motion in the reference's arithmetic (include/rtb200_host.h), in place on this world's
+        camera and instances. Comma-separated operations, the grammar of oracle/ref_build/ref_driver.cu
+        --moves: ``w s a d`` (camera keys, src/main.cc:140-165), ``m:xrel:yrel`` (mouse look, main.cc:166-177),
+        ``g:idx:dx:dy:dz`` / ``l:idx:dx:dy:dz`` (Entity::translate_global / translate of instance idx),
+        ``r:idx:ax:ay:az:theta`` (Entity::rotate by Quat(axis, theta)). Pass the result on with
+        Scene.set_camera(world.desc.camera) / Scene.set_instances(world.desc.instances, n)."""
+        lib = host_lib()
+        cam = self.desc.camera
+        for op in filter(None, spec.split(",")):
+            f = op.split(":")
+            if f[0] in "wsad" and len(f) == 1:
+                lib.rth_camera_key(C.byref(cam), f[0].encode())
+            elif f[0] == "m" and len(f) == 3:
+                lib.rth_camera_mouse(C.byref(cam), float(f[1]), float(f[2]))
+            elif f[0] in ("g", "l") and len(f) == 5:
+                pose = self.desc.instances[int(f[1])].pose
+                dp = (C.c_float * 3)(float(f[2]), float(f[3]), float(f[4]))
+                (lib.rth_pose_translate_global if f[0] == "g" else lib.rth_pose_translate)(C.byref(pose), C.byref(dp))
+            elif f[0] == "r" and len(f) == 6:
+                pose = self.desc.instances[int(f[1])].pose
+                axis = (C.c_float * 3)(float(f[2]), float(f[3]), float(f[4]))
+                q = (C.c_float * 4)()
+                lib.rth_quat_axis_angle(C.byref(axis), float(f[5]), C.byref(q))
+                lib.rth_pose_rotate(C.byref(pose), C.byref(q))
+            else:
+                raise ValueError("bad move operation %r" % op)
 
     def close(self):
         if self._h:

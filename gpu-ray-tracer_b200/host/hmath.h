@@ -65,6 +65,54 @@ inline Quat operator*(Quat a, Quat o) {
     return r;
 }
 
+// ---- motion: the operations behind Entity::translate / rotate and the mouse-look
+// of the reference's event loop (include/rayprimitives/entity.h:49-76, src/main.cc:140-179) ----
+inline float qdot(Quat a, Quat b) {
+    float s = 0;
+    s += a.i * b.i;
+    s += a.j * b.j;
+    s += a.k * b.k;
+    s += a.r * b.r;
+    return s;
+}
+// Quat::normalized (geometry.h:158-161) = Vec4::normalized (linear.h:160-168)
+inline Quat qnormalized(Quat q) {
+    float len = std::sqrt(qdot(q, q));
+    if (len > kThreshold) {
+        float inv = 1 / len;
+        return Quat{q.i * inv, q.j * inv, q.k * inv, q.r * inv};
+    }
+    return Quat{0.f, 0.f, 0.f, 0.f};
+}
+// Quat::inverse (geometry.h:145-156)
+inline Quat qinverse(Quat q) {
+    float sq = qdot(q, q);
+    if (sq < kThreshold) return Quat{0.f, 0.f, 0.f, 0.f};
+    float inv = 1 / sq;
+    return Quat{q.i * -inv, q.j * -inv, q.k * -inv, q.r * inv};
+}
+// operator*(Quat, Vec3) (geometry.h:176-181): sandwich product, input length restored
+inline Float3 operator*(Quat q, Float3 v) {
+    float len = length(v);
+    Quat prod = qnormalized(q) * Quat{v.x, v.y, v.z, 0.f} * qinverse(q);
+    return len * normalized(Float3{prod.i, prod.j, prod.k});
+}
+// columns of Quat::to_Mat3 (geometry.h:183-198), normalised twice like Camera::right/up/forward
+// followed by the Ray constructor do (src/rayenv/camera.cu:11-30, geometry.h:216)
+struct Basis { Float3 right, up, forward; };
+inline Basis quat_basis(Quat q) {
+    float len = std::sqrt(qdot(q, q));
+    float ni = q.i / len, nj = q.j / len, nk = q.k / len, nr = q.r / len;
+    float ii = 2.0f * ni * ni, jj = 2.0f * nj * nj, kk = 2.0f * nk * nk;
+    float ri = 2.0f * nr * ni, rj = 2.0f * nr * nj, rk = 2.0f * nr * nk, ij = 2.0f * ni * nj, ik = 2.0f * ni * nk,
+          jk = 2.0f * nj * nk;
+    Basis b;
+    b.right = normalized(normalized(Float3{1 - (jj + kk), ij + rk, ik - rj}));
+    b.up = normalized(normalized(Float3{ij - rk, 1 - (ii + kk), jk + ri}));
+    b.forward = normalized(normalized(Float3{ik + rj, jk - ri, 1 - (ii + jj)}));
+    return b;
+}
+
 }  // namespace rtb
 
 #endif

@@ -1,9 +1,11 @@
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <exception>
 #include <string>
 
 #include "cube_world.h"
+#include "hmath.h"
 #include "rtb200_host.h"
 
 struct RthWorld {
@@ -90,6 +92,51 @@ int rth_world_dump(const RthWorld* w, const char* path) {
     }
     fclose(f);
     return 0;
+}
+
+// ---- motion (declared in rtb200_host.h; reference anchors there) ----
+static rtb::Quat pose_q(const RtPose* p) { return rtb::Quat{p->rot[0], p->rot[1], p->rot[2], p->rot[3]}; }
+static void pose_set_q(RtPose* p, rtb::Quat q) { p->rot[0] = q.i; p->rot[1] = q.j; p->rot[2] = q.k; p->rot[3] = q.r; }
+
+void rth_pose_translate_global(RtPose* pose, const float dp[3]) {
+    rtb::Float3 p = rtb::Float3{pose->pos[0], pose->pos[1], pose->pos[2]} + rtb::Float3{dp[0], dp[1], dp[2]};
+    pose->pos[0] = p.x; pose->pos[1] = p.y; pose->pos[2] = p.z;
+}
+void rth_pose_translate(RtPose* pose, const float dp[3]) {
+    rtb::Float3 l = pose_q(pose) * rtb::Float3{dp[0], dp[1], dp[2]};  // Entity::vec_to_local = o * v
+    const float g[3] = {l.x, l.y, l.z};
+    rth_pose_translate_global(pose, g);
+}
+void rth_pose_rotate(RtPose* pose, const float q[4]) { pose_set_q(pose, rtb::Quat{q[0], q[1], q[2], q[3]} * pose_q(pose)); }
+void rth_quat_axis_angle(const float axis[3], float theta, float out[4]) {
+    rtb::Quat q = rtb::quat_axis_angle(rtb::Float3{axis[0], axis[1], axis[2]}, theta);
+    out[0] = q.i; out[1] = q.j; out[2] = q.k; out[3] = q.r;
+}
+int rth_camera_key(RtCamera* cam, char key) {
+    const float kMoveSpeed = 0.2f;  // MOVE_SPEED, src/main.cc:19
+    float dp[3] = {0.f, 0.f, 0.f};
+    switch (key) {
+        case 'w': dp[2] = kMoveSpeed; break;
+        case 's': dp[2] = -kMoveSpeed; break;
+        case 'a': dp[0] = -kMoveSpeed; break;
+        case 'd': dp[0] = kMoveSpeed; break;
+        default: return 1;
+    }
+    rth_pose_translate(&cam->pose, dp);
+    return 0;
+}
+void rth_camera_mouse(RtCamera* cam, float xrel, float yrel) {
+    const float kRotSpeed = 0.01f;  // ROT_SPEED, src/main.cc:20
+    // Vec<float, 2>::normalized (linear.h:160-168)
+    float s = 0;
+    s += xrel * xrel;
+    s += yrel * yrel;
+    float len = std::sqrt(s);
+    float rx = 0.f, ry = 0.f;
+    if (len > rtb::kThreshold) { float inv = 1 / len; rx = xrel * inv; ry = yrel * inv; }
+    rtb::Basis b = rtb::quat_basis(pose_q(&cam->pose));
+    rtb::Quat rot = rtb::quat_axis_angle(b.up, kRotSpeed * rx) * rtb::quat_axis_angle(b.right, kRotSpeed * ry);
+    pose_set_q(&cam->pose, rot * pose_q(&cam->pose));
 }
 
 }  // extern "C"

@@ -192,12 +192,61 @@ static void dump_ids(renv::cpu::Scene* scene, const std::string& path, bool bvh_
     fclose(f);
 }
 
+// --moves: per-frame motion through the reference's own Entity API before the frame is traced, in the
+// arithmetic of its event loop (src/main.cc:19-20,140-177). Comma-separated operations:
+//   w s a d                  camera key presses: cam.translate(+-MOVE_SPEED along local z / x)
+//   m:xrel:yrel              SDL_MOUSEMOTION: cam.rotate(Quat(up, ROT_SPEED*rx) * Quat(right, ROT_SPEED*ry))
+//   g:idx:dx:dy:dz           trans[idx].translate_global(dp)      (include/rayprimitives/entity.h:49-52)
+//   l:idx:dx:dy:dz           trans[idx].translate(dp)             (entity.h:54-57)
+//   r:idx:ax:ay:az:theta     trans[idx].rotate(Quat(axis, theta)) (entity.h:64-67)
+static void apply_moves(renv::Environment& env, const std::string& spec) {
+    const float MOVE_SPEED = 0.2f, ROT_SPEED = 0.01f;
+    size_t pos = 0;
+    while (pos < spec.size()) {
+        size_t end = spec.find(',', pos);
+        if (end == std::string::npos) end = spec.size();
+        std::string op = spec.substr(pos, end - pos);
+        pos = end + 1;
+        if (op.empty()) continue;
+        std::vector<std::string> f;
+        size_t q = 0;
+        while (q <= op.size()) {
+            size_t e = op.find(':', q);
+            if (e == std::string::npos) e = op.size();
+            f.push_back(op.substr(q, e - q));
+            q = e + 1;
+        }
+        renv::Camera& cam = env.get_camera();
+        auto num = [&](size_t i) { return (float)atof(f[i].c_str()); };
+        if (f[0] == "w") cam.translate(rmath::Vec3<float>{0, 0, MOVE_SPEED});
+        else if (f[0] == "s") cam.translate(rmath::Vec3<float>{0, 0, -MOVE_SPEED});
+        else if (f[0] == "a") cam.translate(rmath::Vec3<float>{-MOVE_SPEED, 0, 0});
+        else if (f[0] == "d") cam.translate(rmath::Vec3<float>{MOVE_SPEED, 0, 0});
+        else if (f[0] == "m" && f.size() == 3) {
+            rmath::Vec<float, 2> rel_mot = rmath::Vec<float, 2>({num(1), num(2)}).normalized();
+            rmath::Quat<float> rot = rmath::Quat<float>(cam.up().direction(), ROT_SPEED * rel_mot[0])
+                                   * rmath::Quat<float>(cam.right().direction(), ROT_SPEED * rel_mot[1]);
+            cam.rotate(rot);
+        } else if ((f[0] == "g" || f[0] == "l") && f.size() == 5) {
+            renv::Transformation& t = env.get_trans()[atoi(f[1].c_str())];
+            rmath::Vec3<float> dp({num(2), num(3), num(4)});
+            if (f[0] == "g") t.translate_global(dp); else t.translate(dp);
+        } else if (f[0] == "r" && f.size() == 6) {
+            renv::Transformation& t = env.get_trans()[atoi(f[1].c_str())];
+            t.rotate(rmath::Quat<float>(rmath::Vec3<float>({num(2), num(3), num(4)}), num(5)));
+        } else {
+            fprintf(stderr, "bad --moves operation '%s'\n", op.c_str());
+            exit(2);
+        }
+    }
+}
+
 int main(int argc, char** argv) {
     if (argc < 2) {
-        fprintf(stderr, "usage: %s world.json [--gpu] [--no-bvh] [--frames N] [--kd D] [--canvas f] [--ids f] [--scene f]\n", argv[0]);
+        fprintf(stderr, "usage: %s world.json [--gpu] [--no-bvh] [--frames N] [--kd D] [--canvas f] [--ids f] [--scene f] [--moves ops]\n", argv[0]);
         return 2;
     }
-    std::string json = argv[1], canvas_out, ids_out, scene_out;
+    std::string json = argv[1], canvas_out, ids_out, scene_out, moves;
     bool gpu = false, optimize = true, ids_bvh_only = false;
     int frames = 1, kd = 16;
     for (int i = 2; i < argc; i++) {
@@ -210,6 +259,7 @@ int main(int argc, char** argv) {
         else if (a == "--canvas" && i + 1 < argc) canvas_out = argv[++i];
         else if (a == "--ids" && i + 1 < argc) ids_out = argv[++i];
         else if (a == "--scene" && i + 1 < argc) scene_out = argv[++i];
+        else if (a == "--moves" && i + 1 < argc) moves = argv[++i];
     }
     std::vector<double> ms;
     int nonzero = 0;
@@ -220,6 +270,7 @@ int main(int argc, char** argv) {
         n_trans = scene->get_environment().n_trans();
         w = scene->get_environment().get_canvas().get_width();
         h = scene->get_environment().get_canvas().get_height();
+        if (!moves.empty()) apply_moves(scene->get_environment(), moves);
         if (!scene_out.empty()) dump_scene(scene, scene_out);
         for (int f = 0; f < frames; f++) {
             auto t0 = std::chrono::high_resolution_clock::now();
@@ -240,6 +291,7 @@ int main(int argc, char** argv) {
         n_trans = scene->get_environment().n_trans();
         w = scene->get_environment().get_canvas().get_width();
         h = scene->get_environment().get_canvas().get_height();
+        if (!moves.empty()) apply_moves(scene->get_environment(), moves);
         for (int f = 0; f < frames; f++) {
             auto t0 = std::chrono::high_resolution_clock::now();
             rtracer::gpu::update_scene(scene, kd, optimize);
