@@ -26,6 +26,7 @@ RT_RENDER_REBUILD_BVH, RT_RENDER_NO_BVH, RT_RENDER_CANVAS_DEVICE = 1, 2, 4
 RT_RENDER_SORT_RAYS, RT_RENDER_TILED_OUTPUT, RT_RENDER_STATS, RT_RENDER_FUSED_SHADE = 8, 16, 32, 64
 RT_RENDER_TRACE_UNLIT = 128
 RT_RENDER_ASYNC = 256
+RT_RENDER_REFIT_BVH = 512
 
 
 class RtMaterial(C.Structure):
@@ -153,6 +154,7 @@ def cuda_lib():
         lib.rt_scene_set_canvas_size.argtypes = [vp, i32, i32]
         lib.rt_bvh_build.argtypes = [vp, C.POINTER(RtBuildStats)]
         lib.rt_bvh_free.argtypes = [vp]
+        lib.rt_bvh_refit.argtypes = [vp, C.POINTER(RtBuildStats)]
         lib.rt_update_scene.argtypes = [vp, i32, i32, vp]
         lib.rt_render.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(RtFrameStats)]
         lib.rt_tiled_slab_pixels.argtypes = [vp, C.POINTER(RtRenderParams), C.POINTER(C.c_int64)]
@@ -311,6 +313,12 @@ class Scene:
     def build_bvh(self):
         st = RtBuildStats()
         _check(cuda_lib().rt_bvh_build(self._h, C.byref(st)), "rt_bvh_build")
+        return st.as_dict()
+
+    def refit_bvh(self):
+        """Keeps the tree, recomputes every box after instances moved (rt_bvh_refit)."""
+        st = RtBuildStats()
+        _check(cuda_lib().rt_bvh_refit(self._h, C.byref(st)), "rt_bvh_refit")
         return st.as_dict()
 
     def free_bvh(self):

@@ -16,6 +16,7 @@
 // -fmad=false), so the result is bit-identical to the sequential host build in oracle/lbvh_host.c
 // that tests/test_bvh_build.py compares it against.
 #include <cooperative_groups.h>
+#include <cstring>
 
 #include "rt_bvh.cuh"
 #include "rt_internal.h"
@@ -357,6 +358,8 @@ struct CollapseArgs {
     int* counts;           // 2 ints per node of the current level: inner children, leaf triangles
     int* block_tot;        // [2 parities][gridDim.x][2]
     int* result;           // [0] = n_nodes8, [1] = n_prims emitted, [2] = levels, [3] = max level width
+    int* node8_root;       // out: BVH2 id each BVH8 node was collapsed from      (kept for k_refit8)
+    int* node8_slot;       // out: BVH2 id in each of its 8 slots, -1 when empty
 };
 
 __device__ __forceinline__ int node_size(const CollapseArgs& a, int id) {
@@ -512,6 +515,8 @@ __device__ int collapse_children_g(const CollapseArgs& a, int root, int j, int& 
 
 // Lane s of the group quantises and emits slot s of one BVH8 node; lanes 0 and 4 store the packed
 // words. `c` = BVH2 id in this lane's slot or -1.
+// BUILD == false (refit): topology, child_base and prim_base are the existing node's; only boxes and triangles change.
+template <bool BUILD>
 __device__ void write_node8_g(const CollapseArgs& a, int root, int node_idx, int c, int j, int child_base, int prim_base,
                               int* next_list, bool valid) {
     const float* nb = a.node_box + 6 * (size_t)root;
@@ -557,7 +562,7 @@ __device__ void write_node8_g(const CollapseArgs& a, int root, int node_idx, int
     if (c >= 0) {
         if (inner) {
             meta = 0x20u | (24u + (unsigned)j);
-            if (valid) next_list[inner_rank] = c;
+            if (BUILD && valid) next_list[inner_rank] = c;
         } else {
             unsigned unary = sz == 1 ? 1u : (sz == 2 ? 3u : 7u);
             meta = (unary << 5) | (unsigned)prim_off;
@@ -566,7 +571,7 @@ __device__ void write_node8_g(const CollapseArgs& a, int root, int node_idx, int
                 int dst = prim_base + prim_off + t;
                 int p = a.sorted_prim[first + t];
                 if (valid) {
-                    a.prim_order8[dst] = first + t;
+                    if (BUILD) a.prim_order8[dst] = first + t;
                     a.prims8[3 * (size_t)dst + 0] = a.prim_world[3 * (size_t)p + 0];
                     a.prims8[3 * (size_t)dst + 1] = a.prim_world[3 * (size_t)p + 1];
                     a.prims8[3 * (size_t)dst + 2] = a.prim_world[3 * (size_t)p + 2];
@@ -585,6 +590,10 @@ __device__ void write_node8_g(const CollapseArgs& a, int root, int node_idx, int
     };
     unsigned wm = pack(meta), w0 = pack(q[0]), w1 = pack(q[1]), w2 = pack(q[2]), w3 = pack(q[3]), w4 = pack(q[4]), w5 = pack(q[5]);
     if (!valid) return;
+    if (BUILD) {
+        a.node8_slot[8 * (size_t)node_idx + j] = c;
+        if (j == 0) a.node8_root[node_idx] = root;
+    }
     unsigned* out = (unsigned*)(a.nodes8 + 5 * (size_t)node_idx);
     if (j == 0) {
         out[0] = __float_as_uint(org[0]); out[1] = __float_as_uint(org[1]); out[2] = __float_as_uint(org[2]);
@@ -728,7 +737,7 @@ __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
             bool valid = t < c1;
             int tt = valid ? t : c0;
             int child_base = a.counts[2 * (size_t)tt];
-            write_node8_g(a, cur[tt], level_base + tt, a.slots[8 * (size_t)tt + j], j, child_base, a.counts[2 * (size_t)tt + 1],
+            write_node8_g<true>(a, cur[tt], level_base + tt, a.slots[8 * (size_t)tt + j], j, child_base, a.counts[2 * (size_t)tt + 1],
                           next + (child_base - next_base), valid);
         }
         level_base = next_base;
@@ -746,6 +755,18 @@ __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
     }
 }
 
+// Refit of the BVH8 (rt_bvh_refit): 8 lanes per node requantise the slots' boxes from the refitted BVH2
+// boxes and re-emit the leaf triangles from the moved world-space triangles. Same code as the build's
+// emit step, so a refit of an unmoved scene reproduces the built tree bit for bit.
+__global__ void __launch_bounds__(kThreads) k_refit8(CollapseArgs a, int n_nodes8) {
+    const int group = (blockIdx.x * blockDim.x + threadIdx.x) >> 3, j = threadIdx.x & 7;
+    const bool valid = group < n_nodes8;
+    const int node = valid ? group : 0;
+    const unsigned* old = (const unsigned*)(a.nodes8 + 5 * (size_t)node);
+    const int child_base = (int)old[4], prim_base = (int)old[5];
+    write_node8_g<false>(a, a.node8_root[node], node, a.node8_slot[8 * (size_t)node + j], j, child_base, prim_base, nullptr, valid);
+}
+
 }  // namespace
 
 namespace rth {
@@ -755,6 +776,7 @@ static inline int grid_for(int n, int per = kThreads) { return n > 0 ? (n + per 
 int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     Bvh& b = sc->bvh;
     b.valid = false;
+    b.topology_valid = false;
     cudaStream_t st = sc->stream;
     int launches0 = sc->kernel_launches;
     // prefix of triangle counts per instance (host; instances change only through rt_scene_set_instances)
@@ -788,7 +810,8 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
         b.left.reserve(4 * (size_t)n) || b.right.reserve(4 * (size_t)n) || b.parent.reserve(4 * 2 * (size_t)n) ||
         b.range_lo.reserve(4 * (size_t)n) || b.range_hi.reserve(4 * (size_t)n) || b.flags.reserve(4 * (size_t)n) ||
         b.node_box.reserve(sizeof(float) * 6 * 2 * (size_t)n) || b.nodes8.reserve(sizeof(uint4) * 5 * (size_t)max_nodes8) ||
-        b.prims8.reserve(sizeof(float4) * 3 * (size_t)n) || b.prim_order8.reserve(4 * (size_t)n))
+        b.prims8.reserve(sizeof(float4) * 3 * (size_t)n) || b.prim_order8.reserve(4 * (size_t)n) ||
+        b.node8_root.reserve(4 * (size_t)max_nodes8) || b.node8_slot.reserve(4 * 8 * (size_t)max_nodes8))
         return RT_ERR_OUT_OF_MEMORY;
     RT_CUDA(cudaMemcpyAsync(b.work.p, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice, st));
     SceneView v = make_view(sc, false);
@@ -859,6 +882,8 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     a.counts = w; w += level_cap * 2;
     a.block_tot = w; w += (size_t)G * 4;
     a.result = w;
+    a.node8_root = b.node8_root.as<int>();
+    a.node8_slot = b.node8_slot.as<int>();
     RT_CUDA(cudaMemsetAsync(a.result, 0, 16 * sizeof(int), st));
     void* args[] = {&a};
     RT_CUDA(cudaLaunchCooperativeKernel((void*)k_collapse, dim3(G), dim3(kThreads), args, 0, st));
@@ -867,7 +892,64 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     RT_CUDA(cudaEventRecord(sc->ev[1], st));
     RT_CUDA(cudaGetLastError());
     b.valid = true;  // provisional until finish_build() has looked at the result
+    b.topology_valid = true;
+    b.topo_meshes.resize((size_t)sc->n_instances);
+    for (int i = 0; i < sc->n_instances; i++) b.topo_meshes[i] = sc->instances[i].mesh;
     b.build_launches = sc->kernel_launches - launches0;
+    if (!sync) return RT_OK;
+    RT_CUDA(cudaStreamSynchronize(st));
+    return finish_build(sc, stats);
+}
+
+bool refit_possible(const RtScene* sc) {
+    const Bvh& b = sc->bvh;
+    if (!b.topology_valid || b.n_prims <= 0 || b.n_nodes8 <= 0 || (int)b.topo_meshes.size() != sc->n_instances) return false;
+    for (int i = 0; i < sc->n_instances; i++)
+        if (b.topo_meshes[i] != sc->instances[i].mesh) return false;
+    return true;
+}
+
+// Replaces nothing in the reference (it rebuilds from scratch every frame, src/raytracer.cu:102-107); the
+// per-frame alternative for scenes whose instances only move. The BVH2 topology, the
+// BVH8 child / slot / triangle layout and the sort order stay; k_flatten recomputes the world-space
+// triangles and their inflated boxes, k_refit the BVH2 boxes, k_refit8 the quantised BVH8 boxes and the
+// leaf-ordered triangles. Traversal stays a conservative filter in front of the exact test, so frames are
+// identical to those of a rebuilt tree; only the number of nodes visited can grow as the scene drifts.
+int refit_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
+    Bvh& b = sc->bvh;
+    if (!refit_possible(sc)) { set_error("no BVH topology to refit (build first; instances must keep their meshes)"); return RT_ERR_NO_BVH; }
+    cudaStream_t st = sc->stream;
+    int launches0 = sc->kernel_launches;
+    const int n = b.n_prims;
+    b.valid = false;
+    RT_CUDA(cudaEventRecord(sc->ev[0], st));
+    if (int rc = update_instance_boxes(sc)) return rc;
+    SceneView v = make_view(sc, false);
+    int* bounds_i = b.scene_bounds.as<int>();
+    k_bounds_init<<<1, 32, 0, st>>>(bounds_i);
+    k_flatten<<<grid_for(n), kThreads, 0, st>>>(v, b.work.as<int>(), n, b.prim_world.as<float4>(), b.prim_box.as<float>(), bounds_i);
+    RT_CUDA(cudaMemsetAsync(b.flags.p, 0, 4 * (size_t)n, st));
+    k_refit<<<grid_for(n), kThreads, 0, st>>>(b.sorted_vals, b.prim_box.as<float>(), n, b.left.as<int>(), b.right.as<int>(),
+                                              b.parent.as<int>(), b.flags.as<unsigned>(), b.node_box.as<float>());
+    CollapseArgs a;
+    memset(&a, 0, sizeof a);
+    a.n = n;
+    a.left = b.left.as<int>(); a.right = b.right.as<int>(); a.range_lo = b.range_lo.as<int>(); a.range_hi = b.range_hi.as<int>();
+    a.node_box = b.node_box.as<float>();
+    a.sorted_prim = b.sorted_vals;
+    a.prim_world = b.prim_world.as<float4>();
+    a.nodes8 = b.nodes8.as<uint4>();
+    a.prims8 = b.prims8.as<float4>();
+    a.prim_order8 = b.prim_order8.as<int>();
+    a.node8_root = b.node8_root.as<int>();
+    a.node8_slot = b.node8_slot.as<int>();
+    k_refit8<<<grid_for(b.n_nodes8 * 8), kThreads, 0, st>>>(a, b.n_nodes8);
+    sc->kernel_launches += 4;
+    RT_CUDA(cudaEventRecord(sc->ev[1], st));
+    RT_CUDA(cudaGetLastError());
+    b.valid = true;
+    b.build_launches = sc->kernel_launches - launches0;
+    // finish_build() re-reads the collapse result of the build this topology came from (still in h_pinned + 32)
     if (!sync) return RT_OK;
     RT_CUDA(cudaStreamSynchronize(st));
     return finish_build(sc, stats);

@@ -58,9 +58,10 @@ void DevBuf::release() {
 void Bvh::release() {
     DevBuf* all[] = {&prim_world, &prim_box, &scene_bounds, &keys_a, &keys_b, &vals_a, &vals_b, &hist, &left, &right,
                      &parent, &range_lo, &range_hi, &flags, &node_box, &nodes8, &prims8, &prim_order8, &work,
-                     &collapse_scratch};
+                     &collapse_scratch, &node8_root, &node8_slot};
     for (DevBuf* b : all) b->release();
     valid = false;
+    topology_valid = false;
 }
 }  // namespace rth
 using rth::set_error;
@@ -1007,6 +1008,12 @@ int rt_bvh_build(RtScene* sc, RtBuildStats* stats) {
     if (!sc) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
     return rth::build_bvh(sc, stats);
 }
+int rt_bvh_refit(RtScene* sc, RtBuildStats* stats) {
+    if (!sc) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
+    if (sc->pending) { if (int rc = rt_frame_finish(sc, nullptr)) return rc; }
+    if (stats) { stats->n_prims = sc->bvh.n_prims; stats->n_bvh2_nodes = sc->bvh.n_bvh2_nodes; stats->n_bvh8_nodes = 0; stats->kernel_launches = 0; stats->ms_build = 0.f; }
+    return rth::refit_bvh(sc, stats);
+}
 int rt_bvh_free(RtScene* sc) {
     if (!sc) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
     sc->bvh.release();
@@ -1164,9 +1171,14 @@ static int run_mega(RtScene* sc, const SceneView& v, const TileMap& tm, uint32_t
 
 // built == nullptr: blocking build. Otherwise the build is only enqueued and *built tells the
 // caller to run rth::finish_build() after its own stream synchronisation.
-static int ensure_bvh(RtScene* sc, bool rebuild, bool* built) {
+static int ensure_bvh(RtScene* sc, bool rebuild, bool* built, bool refit = false) {
     if (built) *built = false;
-    if (sc->bvh.valid && !rebuild) return RT_OK;
+    if (sc->bvh.valid && !rebuild && !refit) return RT_OK;
+    if (!rebuild && rth::refit_possible(sc)) {  // instances moved (or RT_RENDER_REFIT_BVH): keep the tree
+        if (int rc = rth::refit_bvh(sc, nullptr, built == nullptr)) return rc;
+        if (built) *built = true;
+        return RT_OK;
+    }
     if (int rc = rth::build_bvh(sc, nullptr, built == nullptr)) return rc;
     if (built) *built = true;
     return RT_OK;
@@ -1306,7 +1318,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     bool built = false;
     RT_CUDA(cudaEventRecord(sc->ev[2], st));
     if (!no_bvh) {
-        if (int rc = ensure_bvh(sc, (p.flags & RT_RENDER_REBUILD_BVH) != 0, &built)) return rc;
+        if (int rc = ensure_bvh(sc, (p.flags & RT_RENDER_REBUILD_BVH) != 0, &built, (p.flags & RT_RENDER_REFIT_BVH) != 0)) return rc;
     } else {
         if (int rc = rth::update_instance_boxes(sc)) return rc;
     }

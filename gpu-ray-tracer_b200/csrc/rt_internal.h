@@ -52,6 +52,12 @@ struct Bvh {
     const int* sorted_vals = nullptr;
     DevBuf work;         // per-instance triangle prefix
     DevBuf collapse_scratch;  // level lists, slots, counts, block totals
+    // kept for rt_bvh_refit: which BVH2 node every BVH8 node / slot came from, and the instance layout the
+    // topology was built for (refit is only valid while every instance keeps its mesh)
+    DevBuf node8_root;   // int[n_nodes8]
+    DevBuf node8_slot;   // int[8*n_nodes8]
+    bool topology_valid = false;
+    std::vector<int> topo_meshes;  // mesh index per instance at build time
     void release();
 };
 
@@ -91,6 +97,9 @@ namespace rth {
 // sync = false: everything is enqueued, finish_build() must run after the next stream synchronisation
 int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync = true);   // rt_bvh_build.cu
 int finish_build(RtScene* sc, RtBuildStats* stats);
+// keeps the tree, recomputes triangles and every box (instances moved, none added / removed / re-meshed)
+int refit_bvh(RtScene* sc, RtBuildStats* stats, bool sync = true);
+bool refit_possible(const RtScene* sc);
 int update_instance_boxes(RtScene* sc);                    // rt_engine.cu
 rtd::SceneView make_view(const RtScene* sc, bool with_bvh);
 }  // namespace rth

@@ -126,6 +126,8 @@ enum {
     RT_RENDER_FUSED_SHADE = 64,  /* fused shading / bounce kernels instead of the split gen / shadow / resolve pipeline */
     RT_RENDER_ASYNC = 256,       /* rt_render / rt_untile only enqueue on the scene's stream; rt_frame_finish() waits for
                                     the frame and returns its statistics (a host canvas is valid only after that) */
+    RT_RENDER_REFIT_BVH = 512,   /* refit the existing BVH inside the call (rt_bvh_refit) instead of rebuilding it; falls back
+                                    to a build when there is no tree to refit. RT_RENDER_REBUILD_BVH wins when both are set */
     RT_RENDER_TRACE_UNLIT = 128  /* also trace shadow rays whose Phong weight is exactly zero (the reference does; the
                                     split pipeline skips them by default: they cannot change a pixel) */
 };
@@ -199,6 +201,13 @@ int rt_scene_set_canvas_size(RtScene* scene, int32_t width, int32_t height);
  * src/rayopt/bvh.cu:74-91) and BVH::free (src/rayopt/bvh.cu:93-96). */
 int rt_bvh_build(RtScene* scene, RtBuildStats* stats);
 int rt_bvh_free(RtScene* scene);
+/* No counterpart in the reference, which rebuilds its BVH from scratch every frame because the scene is meant
+ * to be interactive (src/raytracer.cu:102-107, src/main.cc:140-179): after rt_scene_set_instances moved
+ * instances (same count, same meshes), keeps the tree built by rt_bvh_build and recomputes the world-space
+ * triangles and every BVH2 / BVH8 box. Frames are identical to those of a rebuilt tree (traversal is a
+ * conservative filter in front of the reference-exact test). RT_ERR_NO_BVH when there is nothing to refit.
+ * rt_render does this on its own, without RT_RENDER_REBUILD_BVH, when instances moved since the last build. */
+int rt_bvh_refit(RtScene* scene, RtBuildStats* stats);
 
 /* Replaces rtracer::gpu::update_scene(scene, kernel_dim, optimize) (src/raytracer.cu:102-120):
  * (re)build the BVH when optimize != 0, trace the frame, synchronise, leave the RGBA8 frame in
