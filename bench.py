@@ -50,6 +50,9 @@ def parse_args():
     ap.add_argument("--tile-h", type=int, default=16)
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: tiles stored into every rank's canvas over NVLink peer memory (p2p) or all-gather + de-interleave (nccl)")
+    ap.add_argument("--band-h", type=int, default=4,
+                    help="N > 1, e2e: rows per full-width band dealt round-robin to the ranks (each rank copies its bands into the one shared host canvas)")
+    ap.add_argument("--host-chunks", type=int, default=0, help="e2e: chunks per frame for copy/render overlap (0 = the library's default)")
     ap.add_argument("--keep-bvh", action="store_true", help="do not rebuild the BVH every frame")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline leg")
@@ -286,21 +289,32 @@ def run_ours(a):
         st = scene.finish()
         return st, st["kernel_launches"] + (1 if world > 1 else 0)
 
+    # N > 1, end to end: ONE host canvas in shared memory, page-locked in every rank's process. The image is dealt in
+    # full-width bands of --band-h rows; each rank renders its bands and copies them straight into the shared canvas
+    # over its own GPU's PCIe link (RT_RENDER_HOST_BANDS) — no device-side gather on this path.
+    shared, shared_handle = None, None
+    band_w = (W + 7) // 8 * 8
+    if world > 1:
+        shm_name = "/rtb200_bench_%s" % os.environ.get("MASTER_PORT", "0")
+        if rank == 0:
+            shared, shared_handle = pkg.host_canvas_open(W * H, shm_name=shm_name, create=True)
+        dist.barrier()
+        if rank != 0:
+            shared, shared_handle = pkg.host_canvas_open(W * H, shm_name=shm_name)
+        dist.barrier()
+    e2e_flags = base | pkg.RT_RENDER_TILED_OUTPUT | pkg.RT_RENDER_HOST_BANDS
+
     def frame_e2e():
         """The call a user of the reference makes per frame, with host buffers on both sides."""
         scene.set_instances(desc.instances, desc.n_instances)
         scene.set_camera(desc.camera)
         if world == 1:
-            _, st = scene.render(flags=base, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=host_canvas.data_ptr())
+            _, st = scene.render(flags=base, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=host_canvas.data_ptr(),
+                                 host_chunks=a.host_chunks)
             return st
-        frame_device()
-        if rank == 0:
-            if gather == "p2p":
-                scene.copy_to_host(own_canvas_ptr, host_canvas.numpy())
-            else:
-                host_canvas.copy_(canvas_dev, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return frame_stats()[0]
+        _, st = scene.render(flags=e2e_flags, rank=rank, world=world, tile_w=band_w, tile_h=a.band_h,
+                             out_ptr=shared.ctypes.data, host_chunks=a.host_chunks)
+        return st
 
     def barrier():
         if world > 1:
@@ -347,6 +361,14 @@ def run_ours(a):
         want = canvas_dev.cpu().numpy().view(np.uint32)
         if not (got == want).all():
             raise SystemExit("rank %d: peer-memory frame differs from the all-gather frame in %d pixels" % (rank, int((got != want).sum())))
+    # untimed check of the end-to-end paths against the device-resident frame
+    scene.render(flags=dev_flags & ~pkg.RT_RENDER_TILED_OUTPUT, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=canvas_dev.data_ptr())
+    want = canvas_dev.cpu().numpy().view(np.uint32)
+    frame_e2e()
+    barrier()
+    got = host_canvas.numpy().view(np.uint32) if world == 1 else shared
+    if rank == 0 and not (got == want).all():
+        raise SystemExit("end-to-end frame differs from the device-resident frame in %d pixels" % int((got != want).sum()))
     sampler = ClockSampler(local_rank) if rank == 0 and not os.environ.get("BENCH_NO_CLOCKS") else None
     if sampler:
         sampler.wait_ready()
@@ -418,8 +440,12 @@ def run_ours(a):
                            "sharding": "screen tiles %dx%d round-robin over %d rank(s)" % (a.tile_w, a.tile_h, world),
                            "exchange": {"p2p": "tiles stored into every rank's canvas over NVLink peer memory (rt_push_tiles) + 1-element all-reduce as barrier",
                                         "nccl": "NCCL all-gather of the tile slabs + de-interleave kernel", "none": "single GPU"}[gather]},
-                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / a.steps, "h2d_bytes_per_step": h2d,
-                        "d2h_bytes_per_step": 4 * W * H},
+                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / a.steps, "h2d_bytes_per_step": h2d * world,
+                        "d2h_bytes_per_step": 4 * W * H,
+                        "path": ("rt_render into a pinned host canvas, frame cut into %d chunks of tile rows (copy of chunk c overlaps chunk c + 1)"
+                                 % outs_e2e[0]["host_chunks"]) if world == 1 else
+                                ("every rank renders full-width bands of %d rows and copies them into one shared pinned host canvas over its own "
+                                 "PCIe link (RT_RENDER_HOST_BANDS), %d chunks per rank" % (a.band_h, outs_e2e[0]["host_chunks"]))},
                 "gpu_launches": launches_all, "clocks": clocks,
                 "breakdown_ms": {"build": avg("ms_build"), "trace": ms_trace, "k_primary": avg("ms_primary"),
                                  "shade": avg("ms_shade"), "k_shadow": avg("ms_shadow"), "bounce_waves": avg("ms_bounce"),
@@ -430,6 +456,9 @@ def run_ours(a):
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
                                     "host_cores": os.cpu_count()}
         print(json.dumps(line), flush=True)
+    if shared_handle:
+        dist.barrier()
+        pkg.host_canvas_close(shared_handle, unlink=(rank == 0))
     if peer_ptrs:
         dist.barrier()
         for r, ptr in enumerate(peer_ptrs):

@@ -27,6 +27,7 @@ RT_RENDER_SORT_RAYS, RT_RENDER_TILED_OUTPUT, RT_RENDER_STATS, RT_RENDER_FUSED_SH
 RT_RENDER_TRACE_UNLIT = 128
 RT_RENDER_ASYNC = 256
 RT_RENDER_REFIT_BVH = 512
+RT_RENDER_HOST_BANDS = 1024
 
 
 class RtMaterial(C.Structure):
@@ -74,7 +75,7 @@ class RtSceneDesc(C.Structure):
 
 class RtRenderParams(C.Structure):
     _fields_ = [("flags", C.c_int32), ("semantics", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("tile_w", C.c_int32), ("tile_h", C.c_int32)]
+                ("tile_w", C.c_int32), ("tile_h", C.c_int32), ("host_chunks", C.c_int32)]
 
 
 class RtFrameStats(C.Structure):
@@ -83,7 +84,7 @@ class RtFrameStats(C.Structure):
                 ("prims_prefiltered", C.c_uint64), ("ms_build", C.c_float), ("ms_trace", C.c_float),
                 ("ms_total", C.c_float), ("waves", C.c_int32), ("kernel_launches", C.c_int32),
                 ("ms_primary", C.c_float), ("ms_shade", C.c_float), ("ms_bounce", C.c_float), ("n_hits", C.c_int32), ("ms_shadow", C.c_float),
-                ("ms_wave_phase", C.c_float * 4), ("rays_culled", C.c_uint64)]
+                ("ms_wave_phase", C.c_float * 4), ("rays_culled", C.c_uint64), ("host_chunks", C.c_int32)]
 
     def as_dict(self):
         return {k: (list(getattr(self, k)) if k == "ms_wave_phase" else getattr(self, k)) for k, _ in self._fields_}
@@ -166,6 +167,8 @@ def cuda_lib():
         lib.rt_peer_canvas_close.argtypes = [vp]
         lib.rt_push_tiles.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(vp), i32]
         lib.rt_copy_to_host.argtypes = [vp, vp, vp, C.c_int64]
+        lib.rt_host_canvas_open.argtypes = [C.c_char_p, C.c_int64, i32, C.POINTER(vp)]
+        lib.rt_host_canvas_close.argtypes = [vp, C.c_int64, C.c_char_p, i32]
         lib.rt_frame_finish.argtypes = [vp, C.POINTER(RtFrameStats)]
         lib.rt_tile_map.argtypes = [i32, i32, i32, i32, i32, i32, vp, C.POINTER(C.c_int64)]
         lib.rt_trace_primary.argtypes = [vp, i32, vp, vp, vp]
@@ -199,6 +202,21 @@ def peer_canvas_open(handle):
     buf = (C.c_ubyte * 64).from_buffer_copy(handle)
     _check(cuda_lib().rt_peer_canvas_open(buf, C.byref(ptr)), "rt_peer_canvas_open")
     return ptr.value
+
+
+def host_canvas_open(pixels, shm_name=None, create=False):
+    """Page-locked host canvas as a uint32 numpy array: private (shm_name None) or POSIX shared memory that every
+    rank of the box maps (RT_RENDER_HOST_BANDS). Keep the returned handle for host_canvas_close()."""
+    ptr = C.c_void_p()
+    name = shm_name.encode() if shm_name else None
+    _check(cuda_lib().rt_host_canvas_open(name, pixels, 1 if create else 0, C.byref(ptr)), "rt_host_canvas_open")
+    arr = np.ctypeslib.as_array(C.cast(ptr.value, C.POINTER(C.c_uint32)), shape=(pixels,))
+    return arr, (ptr.value, pixels, name)
+
+
+def host_canvas_close(handle, unlink=False):
+    ptr, pixels, name = handle
+    _check(cuda_lib().rt_host_canvas_close(ptr, pixels, name, 1 if unlink else 0), "rt_host_canvas_close")
 
 
 def peer_canvas_close(ptr):
@@ -330,17 +348,20 @@ class Scene:
         _check(cuda_lib().rt_update_scene(self._h, kernel_dim, 1 if optimize else 0, canvas.ctypes.data), "rt_update_scene")
         return canvas
 
-    def params(self, flags=0, semantics=RT_SEMANTICS_GPU, rank=0, world=1, tile_w=0, tile_h=0):
-        return RtRenderParams(flags, semantics, rank, world, tile_w, tile_h)
+    def params(self, flags=0, semantics=RT_SEMANTICS_GPU, rank=0, world=1, tile_w=0, tile_h=0, host_chunks=0):
+        return RtRenderParams(flags, semantics, rank, world, tile_w, tile_h, host_chunks)
 
-    def render(self, flags=0, semantics=RT_SEMANTICS_GPU, rank=0, world=1, tile_w=0, tile_h=0, out=None, out_ptr=None):
+    def render(self, flags=0, semantics=RT_SEMANTICS_GPU, rank=0, world=1, tile_w=0, tile_h=0, out=None, out_ptr=None,
+               host_chunks=0):
         """Returns (canvas, stats). out: a host uint32 array to fill; out_ptr: a raw pointer (host, or
         device with RT_RENDER_CANVAS_DEVICE) — then canvas is None."""
-        p = self.params(flags, semantics, rank, world, tile_w, tile_h)
+        p = self.params(flags, semantics, rank, world, tile_w, tile_h, host_chunks)
         st = RtFrameStats()
         canvas = None
         if out_ptr is None:
-            if flags & RT_RENDER_TILED_OUTPUT:
+            if flags & RT_RENDER_HOST_BANDS:
+                canvas = out if out is not None else np.zeros((self.height, self.width), np.uint32)
+            elif flags & RT_RENDER_TILED_OUTPUT:
                 canvas = out if out is not None else np.empty(self.tiled_slab_pixels(p), np.uint32)
             else:
                 canvas = out if out is not None else np.empty((self.height, self.width), np.uint32)

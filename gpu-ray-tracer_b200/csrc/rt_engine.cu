@@ -17,7 +17,12 @@
 //   k_bounce   one wave per launch: cast the top frame's ray of every live path, shade, run the
 //              reference's REFLECT/REFRACT state machine, compact survivors into the next queue.
 // There is no CPU fallback anywhere in this library.
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <unistd.h>
+
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -86,10 +91,12 @@ static int g_sm_count = 148;
 // to `world` ranks; a rank enumerates the warp tiles of the screen tiles it owns.
 struct TileMap {
     int W, H, tile_w, tile_h, tiles_x, n_tiles, rank, world, n_owned, sub_x, sub_per_tile, tiled_out;
-    __host__ __device__ int n_work() const { return n_owned * sub_per_tile; }
+    int k_begin, k_count;  // the owned tiles [k_begin, k_begin + k_count) this launch works on (a chunk of the frame)
+    __host__ __device__ int n_work() const { return k_count * sub_per_tile; }
     // lane -> pixel; returns false for pixels outside the canvas
     __host__ __device__ bool locate(int q, int lane, int& x, int& y, int& out) const {
         int k = q / sub_per_tile, sidx = q - k * sub_per_tile;
+        k += k_begin;
         int T = k * world + rank;
         int tx = T % tiles_x, ty = T / tiles_x;
         int sx = sidx % sub_x, sy = sidx / sub_x;
@@ -121,6 +128,7 @@ static int make_tilemap(const RtScene* sc, const RtRenderParams* p, TileMap& m) 
     m.sub_x = tw / 8;
     m.sub_per_tile = m.sub_x * (th / 4);
     m.tiled_out = tiled;
+    m.k_begin = 0; m.k_count = m.n_owned;
     return RT_OK;
 }
 static long long slab_pixels(const TileMap& m) {
@@ -932,6 +940,14 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
         e = cudaEventCreate(&sc->ev[i]);
         if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaEventCreate", __FILE__, __LINE__));
     }
+    e = cudaStreamCreateWithFlags(&sc->copy_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__));
+    for (int c = 0; c < RtScene::kMaxChunks && e == cudaSuccess; c++) {
+        for (int i = 0; i < 6 && e == cudaSuccess; i++) e = cudaEventCreate(&sc->cev[c][i]);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->chunk_done[c], cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->copies_done, cudaEventDisableTiming);
+    if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaEventCreate", __FILE__, __LINE__));
     sc->n_vertices = d->n_vertices; sc->n_triangles = d->n_triangles; sc->n_meshes = d->n_meshes;
     sc->n_instances = d->n_instances; sc->n_lights = d->n_lights;
     sc->camera = d->camera; sc->env = d->env; sc->width = d->width; sc->height = d->height;
@@ -951,10 +967,11 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
         (rc = upload(sc->d_meshes, hs.meshes, sc->stream)) || (rc = upload(sc->d_mesh_box, hs.mesh_box, sc->stream)) ||
         (rc = upload(sc->d_lights, hs.lights, sc->stream)))
         return fail(rc);
-    if (sc->d_counters.reserve(sizeof(unsigned long long) * C_N)) return fail(RT_ERR_OUT_OF_MEMORY);
-    e = cudaHostAlloc((void**)&sc->h_pinned, 64 * sizeof(unsigned long long), cudaHostAllocDefault);
+    const size_t n_pinned = 64 + (size_t)C_N * RtScene::kMaxChunks;
+    if (sc->d_counters.reserve(sizeof(unsigned long long) * C_N * RtScene::kMaxChunks)) return fail(RT_ERR_OUT_OF_MEMORY);
+    e = cudaHostAlloc((void**)&sc->h_pinned, n_pinned * sizeof(unsigned long long), cudaHostAllocDefault);
     if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaHostAlloc", __FILE__, __LINE__));
-    std::memset(sc->h_pinned, 0, 64 * sizeof(unsigned long long));
+    std::memset(sc->h_pinned, 0, n_pinned * sizeof(unsigned long long));
     if ((rc = upload_instances(sc))) return fail(rc);
     e = cudaStreamSynchronize(sc->stream);
     if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaStreamSynchronize", __FILE__, __LINE__));
@@ -970,7 +987,14 @@ int rt_scene_destroy(RtScene* sc) {
                           &sc->d_queue_b, &sc->d_ids, &sc->d_shadowq, &sc->d_occl, &sc->d_shq_count};
     for (rth::DevBuf* b : all) b->release();
     sc->bvh.release();
+    if (sc->copy_stream) cudaStreamSynchronize(sc->copy_stream);
     for (int i = 0; i < 12; i++) if (sc->ev[i]) cudaEventDestroy(sc->ev[i]);
+    for (int c = 0; c < RtScene::kMaxChunks; c++) {
+        for (int i = 0; i < 6; i++) if (sc->cev[c][i]) cudaEventDestroy(sc->cev[c][i]);
+        if (sc->chunk_done[c]) cudaEventDestroy(sc->chunk_done[c]);
+    }
+    if (sc->copies_done) cudaEventDestroy(sc->copies_done);
+    if (sc->copy_stream) cudaStreamDestroy(sc->copy_stream);
     if (sc->own_stream) cudaStreamDestroy(sc->own_stream);
     if (sc->h_pinned) cudaFreeHost(sc->h_pinned);
     delete sc;
@@ -1033,15 +1057,18 @@ static int persistent_grid(K kernel, int sm_count) {
 }
 
 template <int MODE, bool STATS>
-static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uint32_t* canvas, int* waves) {
+static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uint32_t* canvas, int* waves,
+                         unsigned long long* ctr, cudaEvent_t* cev) {
+    // ctr: this chunk's counter block; cev: its events {start, primary done, shadow rays generated, shadow rays traced,
+    // wave 0 shaded, bounce waves done}
     cudaStream_t st = sc->stream;
-    unsigned long long* ctr = sc->d_counters.as<unsigned long long>();
+    RT_CUDA(cudaEventRecord(cev[0], st));
     long long n_pix = (long long)tm.n_work() * 32;
     if (sc->d_hitq.reserve(sizeof(HitRec) * (size_t)std::max<long long>(n_pix, 1))) return RT_ERR_OUT_OF_MEMORY;
     int g0 = persistent_grid(k_primary<MODE, STATS, false>, sc->sm_count);
     k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr);
     sc->kernel_launches++;
-    RT_CUDA(cudaEventRecord(sc->ev[6], st));
+    RT_CUDA(cudaEventRecord(cev[1], st));
     *waves = 1;
     sc->split_shade_used = false;
     int path_stride = (int)(sizeof(PathHead) + sizeof(Frame) * (size_t)(v.depth + 1));
@@ -1085,9 +1112,9 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     if (!sc->fused_shade) {
         k_shadow_gen<false><<<persistent_grid(k_shadow_gen<false>, sc->sm_count), kThreads, 0, st>>>(v, ctr, C_HITQ, hitq, shq, shq_count, occl, att4, nullptr, 0);
         sc->kernel_launches++;
-        RT_CUDA(cudaEventRecord(sc->ev[8], st));
+        RT_CUDA(cudaEventRecord(cev[2], st));
         trace_shadows(C_HITQ);
-        RT_CUDA(cudaEventRecord(sc->ev[9], st));
+        RT_CUDA(cudaEventRecord(cev[3], st));
         if (secondary)
             k_resolve<true><<<persistent_grid(k_resolve<true>, sc->sm_count), kThreads, 0, st>>>(
                 v, ctr, hitq, occl, att4, canvas, paths, path_stride, sc->d_queue_a.as<int>());
@@ -1103,7 +1130,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         k_shade<MODE, STATS, false><<<g1, kThreads, 0, st>>>(v, ctr, hitq, canvas, paths, path_stride, sc->d_queue_a.as<int>());
     }
     sc->kernel_launches++;
-    RT_CUDA(cudaEventRecord(sc->ev[7], st));
+    RT_CUDA(cudaEventRecord(cev[4], st));
     if (secondary) {
         int in = C_QUEUE_A, outc = C_QUEUE_B;
         int* qin = sc->d_queue_a.as<int>();
@@ -1143,6 +1170,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
             *waves = -1;  // 1 + ctr[C_WAVES], filled in by the caller after the counter read-back
         }
     }
+    RT_CUDA(cudaEventRecord(cev[5], st));
     RT_CUDA(cudaGetLastError());
     return RT_OK;
 }
@@ -1166,6 +1194,42 @@ static int run_mega(RtScene* sc, const SceneView& v, const TileMap& tm, uint32_t
     }
     sc->kernel_launches++;
     RT_CUDA(cudaGetLastError());
+    return RT_OK;
+}
+
+// Device canvas -> host canvas for the owned tiles [k0, k0 + kn), whose pixels are whole rows of the host canvas.
+// bands == false: one rank, row-major device canvas; the tiles are tile rows [k0 / tiles_x, ...), i.e. one contiguous
+// block of rows. bands == true: `dcanvas` is the rank's slab of full-width bands (pitch tile_w) and `host` the row-major
+// W x H canvas every rank scatters its bands into: band k sits at rows (k world + rank) tile_h ..., one strided 3-D copy.
+static int copy_rows_to_host(RtScene* sc, const TileMap& tm, int k0, int kn, const uint32_t* dcanvas, uint32_t* host, bool bands,
+                             cudaStream_t st) {
+    (void)sc;
+    if (kn <= 0) return RT_OK;
+    if (!bands) {
+        const long long y0 = (long long)(k0 / tm.tiles_x) * tm.tile_h;
+        const long long y1 = std::min<long long>((long long)((k0 + kn) / tm.tiles_x) * tm.tile_h, tm.H);
+        if (y1 > y0) RT_CUDA(cudaMemcpyAsync(host + y0 * tm.W, dcanvas + y0 * tm.W, 4 * (size_t)(y1 - y0) * tm.W, cudaMemcpyDeviceToHost, st));
+        return RT_OK;
+    }
+    // the frame's last band may be cut by the canvas edge: copy it on its own
+    int full = kn;
+    const long long last_T = (long long)(k0 + kn - 1) * tm.world + tm.rank;
+    const long long last_rows = std::min<long long>(tm.tile_h, tm.H - last_T * tm.tile_h);
+    if (last_rows < tm.tile_h) full--;
+    if (full > 0) {
+        cudaMemcpy3DParms c;
+        std::memset(&c, 0, sizeof c);
+        c.srcPtr = make_cudaPitchedPtr((void*)(dcanvas + (size_t)k0 * tm.tile_h * tm.tile_w), 4 * (size_t)tm.tile_w, 4 * (size_t)tm.tile_w, tm.tile_h);
+        c.dstPtr = make_cudaPitchedPtr((void*)(host + ((size_t)k0 * tm.world + tm.rank) * tm.tile_h * tm.W), 4 * (size_t)tm.W, 4 * (size_t)tm.W,
+                                       (size_t)tm.world * tm.tile_h);
+        c.extent = make_cudaExtent(4 * (size_t)tm.W, tm.tile_h, full);
+        c.kind = cudaMemcpyDeviceToHost;
+        RT_CUDA(cudaMemcpy3DAsync(&c, st));
+    }
+    if (full < kn && last_rows > 0)
+        RT_CUDA(cudaMemcpy2DAsync(host + (size_t)last_T * tm.tile_h * tm.W, 4 * (size_t)tm.W,
+                                  dcanvas + (size_t)(k0 + kn - 1) * tm.tile_h * tm.tile_w, 4 * (size_t)tm.tile_w, 4 * (size_t)tm.W,
+                                  (size_t)last_rows, cudaMemcpyDeviceToHost, st));
     return RT_OK;
 }
 
@@ -1281,6 +1345,38 @@ int rt_peer_canvas_close(uint32_t* dev_ptr) {
     if (dev_ptr) RT_CUDA(cudaIpcCloseMemHandle(dev_ptr));
     return RT_OK;
 }
+// One host canvas for all ranks of a box (RT_RENDER_HOST_BANDS): POSIX shared memory, page-locked in every process that
+// maps it, so each GPU copies its bands into it over its own PCIe link. shm_name == NULL: private pinned memory.
+int rt_host_canvas_open(const char* shm_name, int64_t pixels, int32_t create, uint32_t** host_ptr) {
+    if (pixels <= 0 || !host_ptr) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    *host_ptr = nullptr;
+    const size_t bytes = 4 * (size_t)pixels;
+    if (!shm_name) {
+        void* p = nullptr;
+        RT_CUDA(cudaHostAlloc(&p, bytes, cudaHostAllocPortable));
+        std::memset(p, 0, bytes);
+        *host_ptr = (uint32_t*)p;
+        return RT_OK;
+    }
+    int fd = shm_open(shm_name, create ? (O_CREAT | O_RDWR) : O_RDWR, 0600);
+    if (fd < 0) { set_error(std::string("shm_open failed for ") + shm_name); return RT_ERR_INVALID_ARG; }
+    if (create && ftruncate(fd, (off_t)bytes) != 0) { close(fd); set_error("ftruncate failed"); return RT_ERR_OUT_OF_MEMORY; }
+    void* p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (p == MAP_FAILED) { set_error("mmap of the shared canvas failed"); return RT_ERR_OUT_OF_MEMORY; }
+    cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e != cudaSuccess) { munmap(p, bytes); return rth::cuda_fail(e, "cudaHostRegister", __FILE__, __LINE__); }
+    *host_ptr = (uint32_t*)p;
+    return RT_OK;
+}
+int rt_host_canvas_close(uint32_t* host_ptr, int64_t pixels, const char* shm_name, int32_t unlink_name) {
+    if (!host_ptr) return RT_OK;
+    if (!shm_name) { RT_CUDA(cudaFreeHost(host_ptr)); return RT_OK; }
+    cudaHostUnregister(host_ptr);
+    munmap(host_ptr, 4 * (size_t)pixels);
+    if (unlink_name) shm_unlink(shm_name);
+    return RT_OK;
+}
 int rt_copy_to_host(RtScene* sc, const uint32_t* dev_ptr, uint32_t* host_ptr, int64_t pixels) {
     if (!sc || !dev_ptr || !host_ptr || pixels < 0) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
     RT_CUDA(cudaMemcpyAsync(host_ptr, dev_ptr, 4 * (size_t)pixels, cudaMemcpyDeviceToHost, sc->stream));
@@ -1324,29 +1420,82 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     }
     long long out_pixels = tm.tiled_out ? slab_pixels(tm) : (long long)tm.W * tm.H;
     uint32_t* dcanvas = canvas;
-    if (!(p.flags & RT_RENDER_CANVAS_DEVICE)) {
+    const bool host_canvas = !(p.flags & RT_RENDER_CANVAS_DEVICE);
+    const bool host_bands = host_canvas && (p.flags & RT_RENDER_HOST_BANDS);
+    if (host_bands && !(tm.tiled_out && tm.tiles_x == 1)) {
+        set_error("RT_RENDER_HOST_BANDS needs RT_RENDER_TILED_OUTPUT and tile_w >= width (full-width bands)");
+        return RT_ERR_INVALID_ARG;
+    }
+    if (host_canvas) {
         if (sc->d_canvas.reserve(4 * (size_t)out_pixels)) return RT_ERR_OUT_OF_MEMORY;
         dcanvas = sc->d_canvas.as<uint32_t>();
     }
+    const bool wavefront = !no_bvh && p.semantics == RT_SEMANTICS_GPU;
+    // Host canvas: cut the frame into chunks of tile rows and copy chunk c while chunk c + 1 renders. Possible when a
+    // chunk's pixels are whole rows of the host canvas: one rank with a row-major canvas, or full-width bands.
+    int n_chunks = 1;
+    const int units = tm.tiles_x > 0 ? tm.n_owned / tm.tiles_x : 0;  // tile rows (world 1) or bands (tiles_x == 1)
+    if (wavefront && host_canvas && ((tm.world == 1 && !tm.tiled_out) || host_bands)) {
+        static const int env_chunks = [] { const char* e = std::getenv("RT_HOST_CHUNKS"); return e ? std::atoi(e) : 0; }();
+        // measured on B200 (world16 at 4K, 33 MB canvas): every extra chunk costs ~0.115 ms of kernel tails, the copy it
+        // hides runs at ~57 GB/s; two chunks win from ~16 MiB of canvas per rank on
+        n_chunks = p.host_chunks > 0 ? p.host_chunks : env_chunks > 0 ? env_chunks : (4 * (size_t)out_pixels >= ((size_t)16 << 20) ? 2 : 1);
+        n_chunks = std::max(1, std::min(std::min(n_chunks, (int)RtScene::kMaxChunks), units));
+    }
     unsigned long long* ctr = sc->d_counters.as<unsigned long long>();
-    RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long) * C_N, st));
+    RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long) * C_N * n_chunks, st));
     // row-major canvas shared with other ranks' tiles: clear them. A tile slab needs no clearing: every
     // in-canvas pixel of an owned tile is written, and the slab padding beyond the canvas edge is never read.
     if (!tm.tiled_out && tm.world > 1) RT_CUDA(cudaMemsetAsync(dcanvas, 0, 4 * (size_t)out_pixels, st));
     RT_CUDA(cudaEventRecord(sc->ev[3], st));
     SceneView v = rth::make_view(sc, !no_bvh);
     int waves = 1, rc = RT_OK;
-    const bool wavefront = !no_bvh && p.semantics == RT_SEMANTICS_GPU;
+    bool canvas_copied = false;
     if (no_bvh) rc = run_mega<TR_BRUTE>(sc, v, tm, dcanvas, p.semantics);
     else if (p.semantics == RT_SEMANTICS_CPU) rc = run_mega<TR_BVH_BOX>(sc, v, tm, dcanvas, p.semantics);
-    else if (want_stats) rc = run_wavefront<TR_BVH_BOX, true>(sc, v, tm, dcanvas, &waves);
-    else rc = run_wavefront<TR_BVH_BOX, false>(sc, v, tm, dcanvas, &waves);
+    else {
+        // chunk sizes fall geometrically (1, 1/2, 1/4, ...): only the last chunk's copy is not hidden behind rendering.
+        // Every chunk gets at least one unit (n_chunks <= units).
+        int bounds[RtScene::kMaxChunks + 1];
+        bounds[0] = 0;
+        const double tot = 2.0 - std::ldexp(1.0, 1 - n_chunks);
+        for (int c = 1; c < n_chunks; c++) {
+            int b = (int)(units * ((2.0 - std::ldexp(1.0, 1 - c)) / tot));
+            bounds[c] = std::min(std::max(b, bounds[c - 1] + 1), units - (n_chunks - c));
+        }
+        bounds[n_chunks] = units;
+        for (int c = 0; c < n_chunks && !rc; c++) {
+            TileMap tc = tm;
+            const int u0 = bounds[c], u1 = bounds[c + 1];
+            if (n_chunks > 1) { tc.k_begin = u0 * tm.tiles_x; tc.k_count = (u1 - u0) * tm.tiles_x; }
+            int w = 1;
+            if (want_stats) rc = run_wavefront<TR_BVH_BOX, true>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c]);
+            else rc = run_wavefront<TR_BVH_BOX, false>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c]);
+            waves = (w < 0 || waves < 0) ? -1 : std::max(waves, w);
+            if (rc || n_chunks == 1) continue;
+            // this chunk's rows go to the host while the next chunk renders
+            RT_CUDA(cudaEventRecord(sc->chunk_done[c], st));
+            RT_CUDA(cudaStreamWaitEvent(sc->copy_stream, sc->chunk_done[c], 0));
+            if (int rc2 = copy_rows_to_host(sc, tm, tc.k_begin, tc.k_count, dcanvas, canvas, host_bands, sc->copy_stream)) return rc2;
+        }
+        if (!rc && n_chunks > 1) {
+            RT_CUDA(cudaEventRecord(sc->copies_done, sc->copy_stream));
+            RT_CUDA(cudaStreamWaitEvent(st, sc->copies_done, 0));
+            canvas_copied = true;
+        }
+    }
     if (rc) return rc;
     RT_CUDA(cudaEventRecord(sc->ev[4], st));
-    unsigned long long* host_ctr = sc->h_pinned;
-    RT_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof(unsigned long long) * C_N, cudaMemcpyDeviceToHost, st));
-    if (!(p.flags & RT_RENDER_CANVAS_DEVICE))
-        RT_CUDA(cudaMemcpyAsync(canvas, dcanvas, 4 * (size_t)out_pixels, cudaMemcpyDeviceToHost, st));
+    unsigned long long* host_ctr = sc->h_pinned + 64;
+    RT_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof(unsigned long long) * C_N * n_chunks, cudaMemcpyDeviceToHost, st));
+    if (host_canvas && !canvas_copied) {
+        if (host_bands) {
+            if (int rc2 = copy_rows_to_host(sc, tm, 0, tm.n_owned, dcanvas, canvas, true, st)) return rc2;
+        } else {
+            RT_CUDA(cudaMemcpyAsync(canvas, dcanvas, 4 * (size_t)out_pixels, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    sc->pend_chunks = n_chunks;
     RT_CUDA(cudaEventRecord(sc->ev[5], st));
     sc->pending = true;
     sc->pend_built = built; sc->pend_wavefront = wavefront; sc->pend_waves = waves; sc->pend_launches0 = launches0;
@@ -1360,10 +1509,19 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
     sc->pending = false;
     const bool built = sc->pend_built, wavefront = sc->pend_wavefront;
     const int waves = sc->pend_waves, launches0 = sc->pend_launches0;
-    unsigned long long* host_ctr = sc->h_pinned;
+    const int n_chunks = sc->pend_chunks;
+    unsigned long long host_ctr[C_N];  // counters summed over the frame's chunks
+    unsigned long long max_waves = 0;
+    for (int i = 0; i < C_N; i++) host_ctr[i] = 0;
     RtFrameStats fs;
     std::memset(&fs, 0, sizeof fs);
     RT_CUDA(cudaEventSynchronize(sc->ev[5]));
+    for (int c = 0; c < n_chunks; c++) {
+        const unsigned long long* hc = sc->h_pinned + 64 + (size_t)C_N * c;
+        for (int i = 0; i < C_N; i++) host_ctr[i] += hc[i];
+        max_waves = std::max(max_waves, hc[C_WAVES]);
+    }
+    host_ctr[C_WAVES] = max_waves;
     if (built) {
         RtBuildStats bs;
         if (int rc2 = rth::finish_build(sc, &bs)) return rc2;
@@ -1380,16 +1538,20 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
     RT_CUDA(cudaEventElapsedTime(&fs.ms_trace, sc->ev[3], sc->ev[4]));
     RT_CUDA(cudaEventElapsedTime(&fs.ms_total, sc->ev[2], sc->ev[5]));
     if (wavefront) {
-        RT_CUDA(cudaEventElapsedTime(&fs.ms_primary, sc->ev[3], sc->ev[6]));
-        RT_CUDA(cudaEventElapsedTime(&fs.ms_shade, sc->ev[6], sc->ev[7]));
-        if (sc->split_shade_used) RT_CUDA(cudaEventElapsedTime(&fs.ms_shadow, sc->ev[8], sc->ev[9]));
-        RT_CUDA(cudaEventElapsedTime(&fs.ms_bounce, sc->ev[7], sc->ev[4]));
+        for (int c = 0; c < n_chunks; c++) {  // per-kernel times: summed over the chunks
+            float ms = 0.0f;
+            RT_CUDA(cudaEventElapsedTime(&ms, sc->cev[c][0], sc->cev[c][1])); fs.ms_primary += ms;
+            RT_CUDA(cudaEventElapsedTime(&ms, sc->cev[c][1], sc->cev[c][4])); fs.ms_shade += ms;
+            if (sc->split_shade_used) { RT_CUDA(cudaEventElapsedTime(&ms, sc->cev[c][2], sc->cev[c][3])); fs.ms_shadow += ms; }
+            RT_CUDA(cudaEventElapsedTime(&ms, sc->cev[c][4], sc->cev[c][5])); fs.ms_bounce += ms;
+        }
         fs.n_hits = (int32_t)host_ctr[C_HITQ];
     }
     for (int k = 0; k < 4; k++) fs.ms_wave_phase[k] = (float)host_ctr[C_PHASE_NS + k] * 1e-6f;
     fs.waves = waves >= 0 ? waves : 1 + (int)host_ctr[C_WAVES];
     if (fs.waves > 4096) { set_error("bounce waves did not terminate"); return RT_ERR_LIMIT; }
     fs.kernel_launches = sc->kernel_launches - launches0;
+    fs.host_chunks = n_chunks;
     if (stats) *stats = fs;
     return RT_OK;
 }

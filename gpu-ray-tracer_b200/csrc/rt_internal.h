@@ -88,7 +88,17 @@ struct RtScene {
     bool pend_built = false, pend_wavefront = false;
     int pend_waves = 0, pend_launches0 = 0;
     cudaEvent_t ev[12] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    unsigned long long* h_pinned = nullptr;  // 64 x u64 of pinned host memory: [0,32) frame counters, [32,36) build result, [40,42) live counts of the bounce waves
+    // A frame rendered into a host canvas is cut into up to RT_MAX_CHUNKS chunks of tile rows; chunk c is copied to the
+    // host on copy_stream while chunk c + 1 renders. Every chunk has its own counter block and events.
+    static constexpr int kMaxChunks = 8;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t cev[kMaxChunks][6] = {};  // per chunk: start, primary done, shadow rays generated, traced, wave 0 shaded, waves done
+    cudaEvent_t chunk_done[kMaxChunks] = {};  // no timing; copy_stream waits on these
+    cudaEvent_t copies_done = nullptr;
+    int pend_chunks = 1;
+    // pinned host memory, u64 units: [32,36) build result, [40,42) live counts of the bounce waves,
+    // [64 + 32 c, 96 + 32 c) counters of chunk c
+    unsigned long long* h_pinned = nullptr;
     int sm_count = 148;
     int kernel_launches = 0;  // running count, sampled around each API call
 };

@@ -128,6 +128,10 @@ enum {
                                     the frame and returns its statistics (a host canvas is valid only after that) */
     RT_RENDER_REFIT_BVH = 512,   /* refit the existing BVH inside the call (rt_bvh_refit) instead of rebuilding it; falls back
                                     to a build when there is no tree to refit. RT_RENDER_REBUILD_BVH wins when both are set */
+    RT_RENDER_HOST_BANDS = 1024, /* multi-GPU frames straight into ONE host canvas: with RT_RENDER_TILED_OUTPUT and
+                                    tile_w >= width (full-width bands of tile_h rows dealt round-robin to the ranks), `canvas` is
+                                    the full W x H row-major HOST canvas (e.g. pinned shared memory mapped by every rank) and
+                                    the call copies only this rank's bands into it, each GPU over its own PCIe link */
     RT_RENDER_TRACE_UNLIT = 128  /* also trace shadow rays whose Phong weight is exactly zero (the reference does; the
                                     split pipeline skips them by default: they cannot change a pixel) */
 };
@@ -138,6 +142,10 @@ typedef struct RtRenderParams {
     /* Multi-GPU screen-space sharding: this process renders tiles t with t % world == rank. */
     int32_t rank, world;
     int32_t tile_w, tile_h;
+    /* Host canvas only: number of chunks of tile rows the frame is cut into so that chunk c is copied to the host while
+     * chunk c + 1 renders (1..8; chunk sizes fall geometrically so that little is left to copy after the last one).
+     * 0 = automatic: 2 from 16 MiB of canvas per rank on, else 1. */
+    int32_t host_chunks;
 } RtRenderParams;
 
 typedef struct RtFrameStats {
@@ -162,6 +170,8 @@ typedef struct RtFrameStats {
                                  generation, shadow traversal, shade + advance), clocked by block 0 of k_bounce_waves */
     uint64_t rays_culled;     /* shadow queries counted in rays_shadow / rays_total that were answered without a
                                  traversal (zero Phong weight, see RT_RENDER_TRACE_UNLIT) */
+    int32_t host_chunks;      /* chunks the frame was cut into for the host copy (RtRenderParams.host_chunks); the per-kernel
+                                 times above are sums over the chunks */
 } RtFrameStats;
 
 typedef struct RtBuildStats {
@@ -248,6 +258,13 @@ int rt_push_tiles(RtScene* scene, const RtRenderParams* params, const uint32_t* 
                   int32_t n_peers);
 /* Blocking device-to-host copy of `pixels` uint32 on the scene's stream. */
 int rt_copy_to_host(RtScene* scene, const uint32_t* dev_ptr, uint32_t* host_ptr, int64_t pixels);
+/* The host canvas of RT_RENDER_HOST_BANDS: page-locked memory every rank of a box can map. The reference keeps its
+ * canvas in managed memory read by the host after each frame (src/rayenv/canvas.cu:7, src/main.cc:181-208); with one
+ * process per GPU the equivalent is one POSIX shared-memory canvas (`shm_name`, e.g. "/rtb200_canvas"; rank 0 passes
+ * create = 1, the others open it after a barrier), registered with CUDA in every process so that each GPU copies its
+ * bands into it over its own PCIe link. shm_name == NULL gives private pinned memory (single process). */
+int rt_host_canvas_open(const char* shm_name, int64_t pixels, int32_t create, uint32_t** host_ptr);
+int rt_host_canvas_close(uint32_t* host_ptr, int64_t pixels, const char* shm_name, int32_t unlink_name);
 
 /* Host-only (no GPU needed): the tile map the kernels use. For every pixel (row-major) writes the
  * index rank `rank` stores it at inside its slab, or -1 if another rank owns the pixel. */

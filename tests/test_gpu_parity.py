@@ -1,6 +1,8 @@
 """-m gpu: the CUDA engine, called through the C ABI, against the oracle and the golden fixtures
 the unmodified reference produced (tests/golden/). Integer ids bit-exact, t bit-exact (tolerance
 stated where looser), canvases bit-exact against the oracle."""
+import os
+
 import numpy as np
 import pytest
 
@@ -285,3 +287,70 @@ def test_async_frame_and_external_stream(pkg, scenes):
         assert (c3 == ref).all()
     finally:
         s.set_stream(None)
+
+
+@pytest.mark.parametrize("name", ["world16", "world8_stress"])
+def test_chunked_host_frame_equals_single_pass(pkg, scenes, name):
+    """A host-canvas frame cut into chunks (chunk c copied to the host while c + 1 renders) is the frame of a
+    single pass, pixel for pixel and ray for ray; odd chunk counts and more chunks than tile rows included."""
+    w, s = scenes(name)
+    oc, ost = ob.OracleScene(w).render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    for chunks, th in ((1, 16), (3, 16), (4, 4), (8, 16), (7, 64)):
+        c, st = s.render(flags=pkg.RT_RENDER_STATS, host_chunks=chunks, tile_h=th, tile_w=32)
+        assert (c == oc).all(), (chunks, th, int((c != oc).sum()))
+        assert st["rays_total"] == ost["rays_total"] and st["rays_secondary"] == ost["rays_secondary"]
+        assert st["ms_primary"] > 0 and st["ms_trace"] >= st["ms_primary"]
+    s.set_canvas_size(333, 101)  # ragged: width not a multiple of 8, height not a multiple of the tile
+    ref, _ = s.render(host_chunks=1)
+    got, _ = s.render(host_chunks=5, tile_w=40, tile_h=12)
+    assert ref.shape == (101, 333) and (got == ref).all()
+    s.set_canvas_size(w.width, w.height)
+
+
+def test_host_bands_scatter_into_one_canvas(pkg, scenes):
+    """RT_RENDER_HOST_BANDS: every rank copies its full-width bands straight into ONE row-major host canvas
+    (emulated on one device: the ranks run one after another into the same pinned canvas)."""
+    w, s = scenes("world8_stress")
+    full, st_full = s.render(host_chunks=1)
+    flags = pkg.RT_RENDER_TILED_OUTPUT | pkg.RT_RENDER_HOST_BANDS
+    for world, th, chunks in ((3, 4, 0), (8, 4, 3), (2, 8, 8), (5, 28, 2)):
+        canvas, handle = pkg.host_canvas_open(w.width * w.height)
+        rays = 0
+        for r in range(world):
+            _, st = s.render(flags=flags, rank=r, world=world, tile_w=w.width, tile_h=th, out_ptr=canvas.ctypes.data,
+                             host_chunks=chunks)
+            rays += st["rays_total"]
+        assert (canvas.reshape(w.height, w.width) == full).all(), (world, th)
+        assert rays == st_full["rays_total"]
+        pkg.host_canvas_close(handle)
+    # ragged canvas: tile_w > width, last band cut by the canvas edge
+    s.set_canvas_size(333, 101)
+    ref, _ = s.render(host_chunks=1)
+    canvas, handle = pkg.host_canvas_open(333 * 101)
+    for r in range(3):
+        s.render(flags=flags, rank=r, world=3, tile_w=336, tile_h=8, out_ptr=canvas.ctypes.data, host_chunks=2)
+    assert (canvas.reshape(101, 333) == ref).all()
+    pkg.host_canvas_close(handle)
+    s.set_canvas_size(w.width, w.height)
+    # bands need the tiled slab and full-width tiles
+    with pytest.raises(RuntimeError):
+        s.render(flags=flags, rank=0, world=2, tile_w=32, tile_h=4)
+
+
+def test_shared_host_canvas_between_processes(pkg, scenes):
+    """The shared-memory canvas: a second process that maps it by name sees what this one rendered into it."""
+    import subprocess, sys as _sys
+    w, s = scenes("world4")
+    name = "/rtb200_test_%d" % os.getpid()
+    canvas, handle = pkg.host_canvas_open(w.width * w.height, shm_name=name, create=True)
+    try:
+        full, _ = s.render(host_chunks=1)
+        s.render(flags=pkg.RT_RENDER_TILED_OUTPUT | pkg.RT_RENDER_HOST_BANDS, rank=0, world=1, tile_w=w.width, tile_h=4,
+                 out_ptr=canvas.ctypes.data)
+        assert (canvas.reshape(w.height, w.width) == full).all()
+        code = ("import numpy as np, sys; a = np.memmap('/dev/shm%s', dtype=np.uint32, mode='r'); "
+                "print(int(a.astype(np.uint64).sum()))" % name)
+        out = subprocess.run([_sys.executable, "-c", code], capture_output=True, text=True, check=True).stdout
+        assert int(out.strip()) == int(full.astype(np.uint64).sum())
+    finally:
+        pkg.host_canvas_close(handle, unlink=True)
