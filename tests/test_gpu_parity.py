@@ -120,10 +120,17 @@ def test_canvas_gpu_semantics_vs_oracle(pkg, scenes, name):
     assert st["rays_culled"] <= st["rays_shadow"]
 
 
-@pytest.mark.parametrize("name", ["world1", "world4", "world16", "world8_stress"])
-def test_bvh_build_bit_exact_vs_host(pkg, scenes, name):
+# (scene, loader overrides): the small worlds sort 32-bit Morton prefixes in 4 passes with the scan fused into the
+# scatter; grid64 (256 k triangles) takes the separate per-digit scan; world16 at grid 150 (1.3 M triangles, more than
+# 2^20) the 63-bit keys in 8 passes
+BVH_CASES = [("world1", {}), ("world4", {}), ("world16", {}), ("world8_stress", {}), ("grid64", {}),
+             ("world16", {"grid_size": 150})]
+
+
+@pytest.mark.parametrize("name,kw", BVH_CASES, ids=lambda v: v if isinstance(v, str) else "-".join("%s%s" % i for i in v.items()))
+def test_bvh_build_bit_exact_vs_host(pkg, scenes, name, kw):
     """GPU LBVH (Morton, radix sort, Karras, refit) and BVH8 collapse == the sequential host build."""
-    w, s = scenes(name)
+    w, s = scenes(name, **kw)
     s.build_bvh()
     d = s.download_bvh()
     hb = ob.OracleBvh(w)
