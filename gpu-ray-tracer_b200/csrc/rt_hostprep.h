@@ -105,13 +105,17 @@ inline void prepare_host_scene(const RtSceneDesc* d, HostScene& hs) {
     }
 }
 
-inline std::vector<rtd::InstRec> prepare_instances(const RtInstance* inst, int n) {
-    std::vector<rtd::InstRec> recs((size_t)n);
+inline void fill_instances(const RtInstance* inst, int n, rtd::InstRec* recs) {
     for (int i = 0; i < n; i++) {
         std::memset(&recs[i], 0, sizeof(rtd::InstRec));
         recs[i].pose = to_pose(inst[i].pose);
         recs[i].mesh = inst[i].mesh;
     }
+}
+
+inline std::vector<rtd::InstRec> prepare_instances(const RtInstance* inst, int n) {
+    std::vector<rtd::InstRec> recs((size_t)n);
+    fill_instances(inst, n, recs.data());
     return recs;
 }
 

@@ -99,6 +99,8 @@ struct RtScene {
     // pinned host memory, u64 units: [32,36) build result, [40,42) live counts of the bounce waves,
     // [64 + 32 c, 96 + 32 c) counters of chunk c
     unsigned long long* h_pinned = nullptr;
+    void* h_inst = nullptr;             // pinned staging of the instance records (rt_scene_set_instances)
+    size_t h_inst_cap = 0;
     int sm_count = 148;
     int kernel_launches = 0;  // running count, sampled around each API call
 };
