@@ -28,6 +28,7 @@ RT_RENDER_TRACE_UNLIT = 128
 RT_RENDER_ASYNC = 256
 RT_RENDER_REFIT_BVH = 512
 RT_RENDER_HOST_BANDS = 1024
+RT_HITABLE_TRIMESH, RT_HITABLE_SPHERE = 0, 1
 
 
 class RtMaterial(C.Structure):
@@ -44,7 +45,7 @@ class RtPose(C.Structure):
 
 
 class RtMesh(C.Structure):
-    _fields_ = [("pose", RtPose), ("tri_begin", C.c_int32), ("tri_end", C.c_int32)]
+    _fields_ = [("pose", RtPose), ("tri_begin", C.c_int32), ("tri_end", C.c_int32), ("kind", C.c_int32), ("radius", C.c_float)]
 
 
 class RtInstance(C.Structure):

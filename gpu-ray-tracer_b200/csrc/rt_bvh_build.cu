@@ -55,22 +55,35 @@ __global__ void k_flatten(SceneView s, const int* __restrict__ prim_offset, int 
         const InstRec& I = s.insts[inst];
         const MeshRec& M = s.meshes[I.mesh];
         int tri = M.tri_begin + (p - prim_offset[inst]);
-        const TriRec T = s.tris[tri];
-        float3 w[3];
-        const int vid[3] = {T.v0, T.v1, T.v2};
+        float L;
+        if (M.kind == RT_HITABLE_SPHERE) {
+            // analytic sphere: world centre, zero edges and L = +inf, which tri_filter passes unconditionally
+            // (the leaf box is the filter; the exact sphere test decides). Tight box = centre +- radius.
+            const float3 c = rtx::point_from_local(I.pose, rtx::point_from_local(M.pose, rtx::mk3(0.f, 0.f, 0.f)));
+            prim_world[3 * (size_t)p + 0] = make_float4(c.x, c.y, c.z, __int_as_float(inst));
+            prim_world[3 * (size_t)p + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(tri));
+            prim_world[3 * (size_t)p + 2] = make_float4(0.f, 0.f, 0.f, INFINITY);
+            lo[0] = c.x - M.radius; lo[1] = c.y - M.radius; lo[2] = c.z - M.radius;
+            hi[0] = c.x + M.radius; hi[1] = c.y + M.radius; hi[2] = c.z + M.radius;
+            L = 6.0f * M.radius;
+        } else {
+            const TriRec T = s.tris[tri];
+            float3 w[3];
+            const int vid[3] = {T.v0, T.v1, T.v2};
 #pragma unroll
-        for (int k = 0; k < 3; k++) {
-            float4 v = s.verts[vid[k]];
-            w[k] = rtx::point_from_local(I.pose, rtx::point_from_local(M.pose, rtx::mk3(v.x, v.y, v.z)));
+            for (int k = 0; k < 3; k++) {
+                float4 v = s.verts[vid[k]];
+                w[k] = rtx::point_from_local(I.pose, rtx::point_from_local(M.pose, rtx::mk3(v.x, v.y, v.z)));
+            }
+            float3 e1 = rtx::sub3(w[1], w[0]), e2 = rtx::sub3(w[2], w[0]);
+            L = ((fabsf(e1.x) + fabsf(e1.y)) + fabsf(e1.z)) + ((fabsf(e2.x) + fabsf(e2.y)) + fabsf(e2.z));
+            prim_world[3 * (size_t)p + 0] = make_float4(w[0].x, w[0].y, w[0].z, __int_as_float(inst));
+            prim_world[3 * (size_t)p + 1] = make_float4(e1.x, e1.y, e1.z, __int_as_float(tri));
+            prim_world[3 * (size_t)p + 2] = make_float4(e2.x, e2.y, e2.z, L);
+            lo[0] = fminf(fminf(w[0].x, w[1].x), w[2].x); hi[0] = fmaxf(fmaxf(w[0].x, w[1].x), w[2].x);
+            lo[1] = fminf(fminf(w[0].y, w[1].y), w[2].y); hi[1] = fmaxf(fmaxf(w[0].y, w[1].y), w[2].y);
+            lo[2] = fminf(fminf(w[0].z, w[1].z), w[2].z); hi[2] = fmaxf(fmaxf(w[0].z, w[1].z), w[2].z);
         }
-        float3 e1 = rtx::sub3(w[1], w[0]), e2 = rtx::sub3(w[2], w[0]);
-        float L = ((fabsf(e1.x) + fabsf(e1.y)) + fabsf(e1.z)) + ((fabsf(e2.x) + fabsf(e2.y)) + fabsf(e2.z));
-        prim_world[3 * (size_t)p + 0] = make_float4(w[0].x, w[0].y, w[0].z, __int_as_float(inst));
-        prim_world[3 * (size_t)p + 1] = make_float4(e1.x, e1.y, e1.z, __int_as_float(tri));
-        prim_world[3 * (size_t)p + 2] = make_float4(e2.x, e2.y, e2.z, L);
-        lo[0] = fminf(fminf(w[0].x, w[1].x), w[2].x); hi[0] = fmaxf(fmaxf(w[0].x, w[1].x), w[2].x);
-        lo[1] = fminf(fminf(w[0].y, w[1].y), w[2].y); hi[1] = fmaxf(fmaxf(w[0].y, w[1].y), w[2].y);
-        lo[2] = fminf(fminf(w[0].z, w[1].z), w[2].z); hi[2] = fmaxf(fmaxf(w[0].z, w[1].z), w[2].z);
         // stored box = tight box inflated by the acceptance margin of tri_filter plus coordinate rounding
         float amax = fmaxf(fmaxf(fmaxf(fabsf(lo[0]), fabsf(hi[0])), fmaxf(fabsf(lo[1]), fabsf(hi[1]))),
                            fmaxf(fabsf(lo[2]), fabsf(hi[2])));

@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
             continue;
         }
         // no secondary rays: acc = 0 + 1 * illuminate, clamp, pack (src/raytracer.cu:36-41)
-        float3 nrm = hit_normal(s, h);
+        float3 nrm = hit_normal(s, h, r);
         float4 c = illuminate<OPAQUE_ONLY>(s, tr, r, h.t, nrm, m, rc);
         canvas[rec.out_index] = rtx::pack_color(c);
     }
@@ -357,7 +357,7 @@ __device__ __forceinline__ void phase_shadow_gen(const SceneView& s, const int n
         if (hit && s.cull_unlit) {
             Hit h;
             h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
-            nrm = hit_normal(s, h);
+            nrm = hit_normal(s, h, r);
             m = &s.mats[s.tris[rec.tri].mat];
         }
         if (!hit) continue;
@@ -498,7 +498,7 @@ __global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_resolve(Sce
             continue;
         }
         // no secondary rays: acc = 0 + 1 * illuminate, clamp, pack (src/raytracer.cu:36-41)
-        float3 nrm = hit_normal(s, h);
+        float3 nrm = hit_normal(s, h, r);
         float4 c = illuminate_resolved(s, r, h.t, nrm, m, att);
         canvas[rec.out_index] = rtx::pack_color(c);
     }
@@ -737,7 +737,7 @@ __global__ void k_debug(SceneView s, int x, int y, RtHit* out) {
     o.instance = hit ? h.inst : -1;
     o.triangle = hit ? h.tri - s.meshes[s.insts[h.inst].mesh].tri_begin : -1;
     o.t = h.t;
-    float3 n = hit ? hit_normal(s, h) : rtx::mk3(0.f, 0.f, 0.f);
+    float3 n = hit ? hit_normal(s, h, r) : rtx::mk3(0.f, 0.f, 0.f);
     o.normal[0] = n.x; o.normal[1] = n.y; o.normal[2] = n.z;
     float4 c;
     if (SEM == RT_SEMANTICS_CPU) {
@@ -931,11 +931,25 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
         set_error("depth must be in 0..9 (the reference's RayFrame[10] stack)");
         return RT_ERR_LIMIT;
     }
-    for (int i = 0; i < d->n_triangles; i++)
-        for (int k = 0; k < 3; k++)
-            if (d->triangles[i].v[k] < 0 || d->triangles[i].v[k] >= d->n_vertices) { set_error("triangle vertex index out of range"); return RT_ERR_INVALID_ARG; }
     for (int i = 0; i < d->n_meshes; i++)
         if (d->meshes[i].tri_begin < 0 || d->meshes[i].tri_end < d->meshes[i].tri_begin || d->meshes[i].tri_end > d->n_triangles) { set_error("mesh triangle range out of range"); return RT_ERR_INVALID_ARG; }
+    {   // vertex indices of every record a triangle mesh can reach (a sphere's material record carries none)
+        std::vector<char> is_sphere_rec((size_t)d->n_triangles, 0);
+        for (int i = 0; i < d->n_meshes; i++)
+            if (d->meshes[i].kind == RT_HITABLE_SPHERE)
+                for (int t = d->meshes[i].tri_begin; t < d->meshes[i].tri_end; t++) is_sphere_rec[t] = 1;
+        for (int i = 0; i < d->n_triangles; i++)
+            for (int k = 0; k < 3 && !is_sphere_rec[i]; k++)
+                if (d->triangles[i].v[k] < 0 || d->triangles[i].v[k] >= d->n_vertices) { set_error("triangle vertex index out of range"); return RT_ERR_INVALID_ARG; }
+    }
+    for (int i = 0; i < d->n_meshes; i++) {
+        const RtMesh& m = d->meshes[i];
+        if (m.kind != RT_HITABLE_TRIMESH && m.kind != RT_HITABLE_SPHERE) { set_error("unknown hitable kind"); return RT_ERR_INVALID_ARG; }
+        if (m.kind == RT_HITABLE_SPHERE && (m.tri_end - m.tri_begin != 1 || !(m.radius > 0.0f) || !std::isfinite(m.radius))) {
+            set_error("a sphere hitable owns exactly one material record and needs a finite radius > 0");
+            return RT_ERR_INVALID_ARG;
+        }
+    }
     for (int i = 0; i < d->n_instances; i++)
         if (d->instances[i].mesh < 0 || d->instances[i].mesh >= d->n_meshes) { set_error("instance mesh index out of range"); return RT_ERR_INVALID_ARG; }
 

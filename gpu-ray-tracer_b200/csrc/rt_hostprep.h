@@ -85,7 +85,14 @@ inline void prepare_host_scene(const RtSceneDesc* d, HostScene& hs) {
         hs.meshes[i].tri_begin = d->meshes[i].tri_begin;
         hs.meshes[i].tri_end = d->meshes[i].tri_end;
         hs.mesh_tri_count[i] = d->meshes[i].tri_end - d->meshes[i].tri_begin;
+        hs.meshes[i].kind = d->meshes[i].kind;
+        hs.meshes[i].radius = d->meshes[i].radius;
         float* b = &hs.mesh_box[8 * (size_t)i];
+        if (d->meshes[i].kind == RT_HITABLE_SPHERE) {  // Sphere::compute_bounding_box: the local cube [-r, r]^3
+            for (int a = 0; a < 3; a++) { b[a] = -d->meshes[i].radius; b[3 + a] = d->meshes[i].radius; }
+            b[6] = 1.f;
+            continue;
+        }
         bool ok = false;
         for (int t = d->meshes[i].tri_begin; t < d->meshes[i].tri_end; t++)
             for (int k = 0; k < 3; k++) {

@@ -4,7 +4,8 @@
 // Layout in HBM (all arrays owned by RtScene, rt_engine.cu):
 //   verts/norms  float4[n_vertices]   mesh-local vertices / generated normals (w unused)
 //   tris         TriRec[n_triangles]  vertex ids + material id          (TriInner, trimesh.cuh:25-53)
-//   meshes       MeshRec[n_meshes]    pose + triangle range             (Trimesh + Entity)
+//   meshes       MeshRec[n_meshes]    pose + triangle range             (Trimesh + Entity); or pose + radius + one
+//                                     material record for an analytic sphere hitable
 //   insts        InstRec[n_instances] pose + mesh + reference leaf box  (Transformation + create_boxes)
 //   mats         MatRec[n_materials]  de-duplicated rprimitives::Material
 //   lights       LightRec[n_lights]
@@ -13,11 +14,12 @@
 #define RTB200_SCENE_CUH
 
 #include "rt_exact.cuh"
+#include "rtb200.h"
 
 namespace rtd {
 
 struct TriRec { int v0, v1, v2, mat; };
-struct MeshRec { rtx::Pose pose; int tri_begin, tri_end; };
+struct MeshRec { rtx::Pose pose; int tri_begin, tri_end; int kind; float radius; };  // kind: RT_HITABLE_TRIMESH / RT_HITABLE_SPHERE
 struct InstRec {
     rtx::Pose pose;
     int mesh;
@@ -80,7 +82,14 @@ RT_HD void instance_box(InstRec& I, const MeshRec* meshes, const float* mesh_box
     const float* mb = mesh_box + 8 * (size_t)I.mesh;
     float b1[6] = {0, 0, 0, 0, 0, 0}, b2[6] = {0, 0, 0, 0, 0, 0};
     int ok1 = 0, ok2 = 0;
-    if (mb[6] != 0.0f) {
+    if (meshes[I.mesh].kind == RT_HITABLE_SPHERE) {
+        // a sphere's box does not depend on the rotations: world centre +- radius (the reference's two-corner refit would
+        // cut a rotated sphere)
+        const float3 c = rtx::point_from_local(I.pose, rtx::point_from_local(meshes[I.mesh].pose, rtx::mk3(0.f, 0.f, 0.f)));
+        const float rad = meshes[I.mesh].radius;
+        b2[0] = c.x - rad; b2[1] = c.y - rad; b2[2] = c.z - rad; b2[3] = c.x + rad; b2[4] = c.y + rad; b2[5] = c.z + rad;
+        ok2 = 1;
+    } else if (mb[6] != 0.0f) {
         const rtx::Pose mp = meshes[I.mesh].pose;
         box_fit(b1, ok1, rtx::point_from_local(mp, rtx::mk3(mb[0], mb[1], mb[2])));
         box_fit(b1, ok1, rtx::point_from_local(mp, rtx::mk3(mb[3], mb[4], mb[5])));
@@ -104,6 +113,7 @@ struct InstCtx {
     float scale;       // |mesh-local direction| (HitHandle::scale)
     float dir_len;     // |instance-local direction| (cast_local)
     int box_pass;      // BoundingBox::intersects on the instance's leaf box
+    float radius;      // >= 0: the instance's hitable is a sphere of this radius; < 0: a triangle mesh
 };
 
 RT_HD_NOINLINE void inst_ctx_load(const SceneView& s, const rtx::Ray& r, int inst, bool use_box, InstCtx& c) {
@@ -118,6 +128,23 @@ RT_HD_NOINLINE void inst_ctx_load(const SceneView& s, const rtx::Ray& r, int ins
     float3 ld2 = rtx::vec_to_local(M.pose, l1.d);
     c.scale = rtx::len3(ld2);
     c.lray = rtx::ray_make(rtx::point_to_local(M.pose, l1.o), ld2);
+    c.radius = M.kind == RT_HITABLE_SPHERE ? M.radius : -1.0f;
+}
+
+// Sphere::hit_local — the analytic sphere hitable (no reference counterpart; written in the reference's style: unit
+// local direction, rmath::dot's summation order, THRESHOLD comparisons). Centre at the local origin.
+//   b = o.d, c = o.o - r^2, disc = b^2 - c; roots -b -+ sqrt(disc); the near root unless it is below THRESHOLD
+//   (origin inside the sphere or on its surface), then the far one.
+RT_HD bool ref_sphere_hit(float radius, const rtx::Ray& lray, float& time) {
+    float b = rtx::dot3(lray.o, lray.d);
+    float c = rtx::dot3(lray.o, lray.o) - radius * radius;
+    float disc = b * b - c;
+    if (!(disc >= 0.0f)) return false;
+    float sq = sqrtf(disc);
+    float t = -b - sq;
+    if (!(t >= RT_THR)) t = -b + sq;
+    time = t;
+    return true;
 }
 
 // One (instance, triangle) candidate through the reference's own arithmetic: TriInner::tri_hit
@@ -129,12 +156,17 @@ RT_HD_NOINLINE bool exact_candidate(const SceneView& s, const rtx::Ray& r, int i
                            Hit& best) {
     if (ctx.inst != inst) inst_ctx_load(s, r, inst, use_box, ctx);
     if (!ctx.box_pass) return false;
-    const TriRec T = s.tris[tri];
-    float4 a4 = s.verts[T.v0], b4 = s.verts[T.v1], c4 = s.verts[T.v2];
     float time, u, v;
-    if (!rtx::ref_triangle_hit(rtx::mk3(a4.x, a4.y, a4.z), rtx::mk3(b4.x, b4.y, b4.z), rtx::mk3(c4.x, c4.y, c4.z),
-                               ctx.lray, time, u, v))
-        return false;
+    if (ctx.radius >= 0.0f) {
+        if (!ref_sphere_hit(ctx.radius, ctx.lray, time)) return false;
+        u = v = 0.0f;
+    } else {
+        const TriRec T = s.tris[tri];
+        float4 a4 = s.verts[T.v0], b4 = s.verts[T.v1], c4 = s.verts[T.v2];
+        if (!rtx::ref_triangle_hit(rtx::mk3(a4.x, a4.y, a4.z), rtx::mk3(b4.x, b4.y, b4.z), rtx::mk3(c4.x, c4.y, c4.z),
+                                   ctx.lray, time, u, v))
+            return false;
+    }
     if (!(time >= RT_THR)) return false;
     float t_world = (time * ctx.scale) * ctx.dir_len;
     bool better;
@@ -149,15 +181,24 @@ RT_HD_NOINLINE bool exact_candidate(const SceneView& s, const rtx::Ray& r, int i
 // back through the mesh pose (HitHandle dtor, hitable.cu:20-26) and the instance pose
 // (cast_local, scene.cu:35-38). The reference recomputes it on every accepted candidate; only
 // the last one survives, so it is evaluated once per closest hit here.
-RT_HD_NOINLINE float3 hit_normal(const SceneView& s, const Hit& h) {
-    const TriRec T = s.tris[h.tri];
-    float4 n0 = s.norms[T.v0], n1 = s.norms[T.v1], n2 = s.norms[T.v2];
-    float bary0 = 1.0f - h.u - h.v;
-    float3 n = rtx::normalized3(rtx::add3(rtx::add3(rtx::scale3(bary0, rtx::mk3(n0.x, n0.y, n0.z)),
-                                                     rtx::scale3(h.u, rtx::mk3(n1.x, n1.y, n1.z))),
-                                           rtx::scale3(h.v, rtx::mk3(n2.x, n2.y, n2.z))));
+// `r` is the ray the hit was found with: a sphere's normal is the local hit point over the radius direction,
+// normalized(lray.at(t_local)), which needs the local ray again.
+RT_HD_NOINLINE float3 hit_normal(const SceneView& s, const Hit& h, const rtx::Ray& r) {
     const InstRec& I = s.insts[h.inst];
     const MeshRec& M = s.meshes[I.mesh];
+    float3 n;
+    if (M.kind == RT_HITABLE_SPHERE) {
+        InstCtx c;
+        inst_ctx_load(s, r, h.inst, false, c);
+        n = rtx::normalized3(rtx::ray_at(c.lray, h.t_local));
+    } else {
+        const TriRec T = s.tris[h.tri];
+        float4 n0 = s.norms[T.v0], n1 = s.norms[T.v1], n2 = s.norms[T.v2];
+        float bary0 = 1.0f - h.u - h.v;
+        n = rtx::normalized3(rtx::add3(rtx::add3(rtx::scale3(bary0, rtx::mk3(n0.x, n0.y, n0.z)),
+                                                  rtx::scale3(h.u, rtx::mk3(n1.x, n1.y, n1.z))),
+                                        rtx::scale3(h.v, rtx::mk3(n2.x, n2.y, n2.z))));
+    }
     n = rtx::normalized3(rtx::vec_from_local(M.pose, n));
     return rtx::vec_from_local(I.pose, n);
 }

@@ -34,7 +34,7 @@ RT_HD float4 light_attenuate_loop(const SceneView& s, const Tracer& tr, const Li
         if (sh.t > max_t) return rv;
         const MatRec& m = s.mats[s.tris[sh.tri].mat];
         if (!m.refractive) return rtx::mk4(0.f, 0.f, 0.f, 0.f);
-        float3 n = hit_normal(s, sh);
+        float3 n = hit_normal(s, sh, cur);
         if (rtx::dot3(n, cur.d) > 0.0f) {  // leaving the solid: calc_shadow_atten = pow(Kt, dist)
             rv = rtx::mul4(rv, rtx::mk4(rtx::ref_powf(m.Kt.x, sh.t), rtx::ref_powf(m.Kt.y, sh.t),
                                         rtx::ref_powf(m.Kt.z, sh.t), rtx::ref_powf(m.Kt.w, sh.t)));
@@ -203,7 +203,7 @@ RT_HD bool path_advance_core(const SceneView& s, Illum illum, Frame* frames, int
         if (!have_top) { top = frames[stack_top]; have_top = true; }
         int mat_id = s.tris[h.tri].mat;
         const MatRec& m = s.mats[mat_id];
-        float3 n = hit_normal(s, h);
+        float3 n = hit_normal(s, h, top.ray);
         rtx::Ray ray = top.ray;
         float4 atten = top.atten;
         if (top.depth > 0) {
@@ -333,7 +333,7 @@ __host__ __device__ float4 propagate_cpu_rec(const SceneView& s, const Tracer& t
     Hit h;
     if (!tr.closest(r, h)) return zero;
     isect.time = h.t;
-    isect.norm = hit_normal(s, h);
+    isect.norm = hit_normal(s, h, r);
     isect.mat = s.tris[h.tri].mat;
     float4 acc = illuminate(s, tr, r, isect.time, isect.norm, s.mats[isect.mat], rc);
     last_time = isect.time;

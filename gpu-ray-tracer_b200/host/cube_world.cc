@@ -71,6 +71,28 @@ rtracer::FlatScene generate_from_text(const std::string& json_text, const WorldO
         }
     }
 
+    // "spheres": schema extension with no reference counterpart: analytic sphere hitables, each
+    // {"radius": r, "pos": [x, y, z], material keys as for cubes}, placed at `pos` after the cubes' transformations.
+    struct SphereAt { int hitable; rtb::Float3 pos; };
+    std::vector<SphereAt> spheres;
+    if (doc.has("spheres")) {
+        const mini_json::Value& sp = doc.at("spheres");
+        for (size_t i = 0; i < sp.size(); i++) {
+            const mini_json::Value& e = sp.at(i);
+            rtracer::Material mat;
+            rtracer::TextureCoords coords;
+            if (e.has("Ke")) mat.set_Ke(inv255 * read_vec4(e.at("Ke")));
+            if (e.has("Ka")) mat.set_Ka(inv255 * read_vec4(e.at("Ka")));
+            if (e.has("Kd")) mat.set_Kd(inv255 * read_vec4(e.at("Kd")));
+            if (e.has("Ks")) mat.set_Ks(inv255 * read_vec4(e.at("Ks")));
+            if (e.has("Kt")) mat.set_Kt(read_vec4(e.at("Kt")));
+            if (e.has("Kr")) mat.set_Kr(read_vec4(e.at("Kr")));
+            if (e.has("alpha")) mat.set_alpha((float)e.at("alpha").as_double());
+            if (e.has("eta")) mat.set_eta((float)e.at("eta").as_double());
+            spheres.push_back({builder.build_sphere((float)e.at("radius").as_double(), coords, mat), read_vec3(e.at("pos"))});
+        }
+    }
+
     // lights (:116-138)
     if (doc.has("lights")) {
         const mini_json::Value& lights = doc.at("lights");
@@ -109,6 +131,11 @@ rtracer::FlatScene generate_from_text(const std::string& json_text, const WorldO
                 max_height = std::max(max_height, last_heights[(size_t)i * grid_size + j]);
             }
         }
+    }
+
+    for (const SphereAt& sa : spheres) {
+        int tid = builder.add_trans(builder.get_mesh_builder(sa.hitable));
+        builder.get_transformation(tid).set_position(sa.pos);
     }
 
     // camera pose (:172-173): note the angle is 45 RADIANS about +x

@@ -75,6 +75,7 @@ int SceneBuilder::build_cube(float scale, const TextureCoords& coords, const Mat
 std::vector<rtb::Float3> SceneBuilder::generate_normals() const {
     std::vector<rtb::Float3> normals(vertices_.size(), rtb::Float3{0.f, 0.f, 0.f});
     for (const MeshBuilder& mesh : meshes_) {
+        if (mesh.kind_ != RT_HITABLE_TRIMESH) continue;  // a sphere's one record is its material, not a triangle
         for (const RtTriangle& tri : mesh.triangles_) {
             rtb::Float3 a = vertices_[tri.v[1]] - vertices_[tri.v[0]];
             rtb::Float3 b = vertices_[tri.v[2]] - vertices_[tri.v[0]];
@@ -109,6 +110,8 @@ FlatScene SceneBuilder::build_flat_scene(int width, int height, const Camera& ca
         m.tri_begin = (int32_t)fs.triangles.size();
         fs.triangles.insert(fs.triangles.end(), mb.triangles_.begin(), mb.triangles_.end());
         m.tri_end = (int32_t)fs.triangles.size();
+        m.kind = mb.kind_;
+        m.radius = mb.radius_;
         fs.meshes.push_back(m);
     }
     for (const Transformation& t : trans_) {

@@ -59,6 +59,8 @@ private:
     friend class SceneBuilder;
     MeshBuilder(int hi, rtb::Float3 pos, rtb::Quat rot) : hitable_idx_(hi), pos_(pos), rot_(rot) {}
     int hitable_idx_;
+    int kind_ = RT_HITABLE_TRIMESH;  // RT_HITABLE_SPHERE: triangles_ holds the one material record, radius_ the radius
+    float radius_ = 0.f;
     std::vector<RtTriangle> triangles_;
     rtb::Float3 pos_;
     rtb::Quat rot_;
@@ -132,6 +134,16 @@ public:
     }
     // 12-triangle, 36-vertex cube (src/scene_builder.cu:181-239)
     int build_cube(float scale, const TextureCoords& coords, const Material& mat);
+    // Analytic sphere hitable centred at its own origin (the reference has no second Hitable
+    // subclass). Returns the hitable index, to be instanced with add_trans(get_mesh_builder(idx)) like a cube.
+    int build_sphere(float radius, const TextureCoords& coords, const Material& mat) {
+        int hi = create_mesh();
+        MeshBuilder& mb = meshes_[hi];
+        mb.kind_ = RT_HITABLE_SPHERE;
+        mb.radius_ = radius;
+        mb.add_triangle(0, 0, 0, coords, mat);  // the material record; its vertex indices are ignored
+        return hi;
+    }
     void add_directional_light(rtb::Float3 dir, rtb::Float4 col) {
         dir_light_dir_.push_back(dir);
         dir_light_col_.push_back(col);

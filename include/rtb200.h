@@ -51,11 +51,18 @@ typedef struct RtPose {
     float pos[3];
 } RtPose;
 
-/* One Trimesh hitable (MeshBuilder, include/scene_builder.h:29-49): its own pose and a
- * [tri_begin, tri_end) range into the triangle array. */
+/* One hitable (rprimitives::gpu::Hitable, include/rayprimitives/gpu/hitable.cuh:27-47): its own Entity pose and
+ *  - RT_HITABLE_TRIMESH: a [tri_begin, tri_end) range into the triangle array (Trimesh, MeshBuilder,
+ *    include/scene_builder.h:29-49) — the reference's only Hitable subclass;
+ *  - RT_HITABLE_SPHERE (no reference counterpart): an analytic sphere of `radius` centred at the
+ *    hitable's local origin. It owns exactly ONE record of the triangle array, [tri_begin, tri_begin + 1), which
+ *    carries its Material (and texture flag); that record's vertex indices are ignored. */
+enum { RT_HITABLE_TRIMESH = 0, RT_HITABLE_SPHERE = 1 };
 typedef struct RtMesh {
     RtPose pose;
     int32_t tri_begin, tri_end;
+    int32_t kind;
+    float radius;
 } RtMesh;
 
 /* renv::Transformation (include/rayenv/transformation.h:13-23): pose + hitable index. */

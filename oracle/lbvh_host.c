@@ -95,6 +95,30 @@ static void flatten(OrBvh* b, const RtSceneDesc* d) {
     for (int inst = 0; inst < d->n_instances; inst++) {
         const RtInstance* I = &d->instances[inst];
         const RtMesh* M = &d->meshes[I->mesh];
+        if (M->kind == RT_HITABLE_SPHERE) { /* world centre, zero edges, L = +inf (the triangle filter passes it) */
+            V3 c = point_from_local(&I->pose, point_from_local(&M->pose, v3(0, 0, 0)));
+            float* o = b->prim_world + 12 * (size_t)p;
+            int32_t ii = inst, tt = M->tri_begin;
+            float cc[3] = {c.x, c.y, c.z}, tl[3], th[3];
+            o[0] = c.x; o[1] = c.y; o[2] = c.z; memcpy(&o[3], &ii, 4);
+            o[4] = 0; o[5] = 0; o[6] = 0; memcpy(&o[7], &tt, 4);
+            o[8] = 0; o[9] = 0; o[10] = 0; o[11] = INFINITY;
+            for (int k = 0; k < 3; k++) {
+                tl[k] = cc[k] - M->radius;
+                th[k] = cc[k] + M->radius;
+                if (tl[k] < lo[k]) lo[k] = tl[k];
+                if (th[k] > hi[k]) hi[k] = th[k];
+            }
+            float amax = fmaxf(fmaxf(fmaxf(fabsf(tl[0]), fabsf(th[0])), fmaxf(fabsf(tl[1]), fabsf(th[1]))),
+                               fmaxf(fabsf(tl[2]), fabsf(th[2])));
+            float m = (2e-4f + 4e-5f * (6.0f * M->radius)) + 1e-6f * amax;
+            for (int k = 0; k < 3; k++) {
+                b->prim_box[6 * (size_t)p + k] = tl[k] - m;
+                b->prim_box[6 * (size_t)p + 3 + k] = th[k] + m;
+            }
+            p++;
+            continue;
+        }
         for (int tri = M->tri_begin; tri < M->tri_end; tri++, p++) {
             V3 w[3];
             for (int k = 0; k < 3; k++) {

@@ -224,6 +224,31 @@ static int tri_hit(const OrScene* s, const RtTriangle* tri, const Ray* local_ray
     return 0;
 }
 
+/* Sphere::hit_local — the analytic sphere hitable. NO reference counterpart: the reference has one
+ * Hitable subclass (include/rayprimitives/gpu/hitable.cuh:27-47). Written in the reference's conventions: unit local
+ * direction (Ray ctor), rmath::dot's summation order, `time >= THRESHOLD && time < isect.time` like TriInner::tri_hit,
+ * normal = normalized(hit point) in the hitable's frame. Centre at the local origin, b = o.d, c = o.o - r^2,
+ * roots -b -+ sqrt(b^2 - c): the near one unless it is below THRESHOLD (origin inside or on the surface). */
+static int sphere_hit(const OrScene* s, const RtMesh* m, const Ray* local_ray, Isect* isect, Ctx* ctx) {
+    float b = v3dot(local_ray->o, local_ray->d);
+    float c = v3dot(local_ray->o, local_ray->o) - m->radius * m->radius;
+    float disc = b * b - c;
+    ctx->st.tri_tests++;
+    if (!(disc >= 0.0f)) return 0;
+    float sq = sqrtf(disc);
+    float time = -b - sq;
+    if (!(time >= THR)) time = -b + sq;
+    if (time >= THR && time < isect->time) {
+        isect->tri = &s->tris[m->tri_begin];
+        isect->u = 0.0f;
+        isect->v = 0.0f;
+        isect->norm = v3normalized(ray_at(local_ray, time));
+        isect->time = time;
+        return 1;
+    }
+    return 0;
+}
+
 /* ref: src/rayprimitives/hitable.cu:7-38 HitHandle + Hitable::hit, trimesh.cu:11-19 hit_local */
 static int hitable_hit(const OrScene* s, int mesh_idx, const Ray* ray, Isect* isect, Ctx* ctx) {
     const RtMesh* m = &s->meshes[mesh_idx];
@@ -231,6 +256,12 @@ static int hitable_hit(const OrScene* s, int mesh_idx, const Ray* ray, Isect* is
     float scale = v3len(vec_to_local(&e, ray->d));
     Ray local_ray = ray_to_local(&e, ray);
     int hit = 0;
+    if (m->kind == RT_HITABLE_SPHERE) {
+        if (sphere_hit(s, m, &local_ray, isect, ctx)) {
+            hit = 1;
+            isect->tri_idx = 0;
+        }
+    } else
     for (int i = m->tri_begin; i < m->tri_end; i++) {
         if (tri_hit(s, &s->tris[i], &local_ray, isect, ctx)) {
             hit = 1;
@@ -559,6 +590,14 @@ static void compute_instance_boxes(OrScene* s) {
         const RtMesh* m = &s->meshes[t->mesh];
         Box local;
         memset(&local, 0, sizeof local);
+        if (m->kind == RT_HITABLE_SPHERE) { /* rotation-independent: world centre +- radius */
+            Entity me = entity_from_pose(&m->pose), te = entity_from_pose(&t->pose);
+            V3 c = point_from_local(&te, point_from_local(&me, v3(0, 0, 0)));
+            s->inst_boxes[i].mn = v3(c.x - m->radius, c.y - m->radius, c.z - m->radius);
+            s->inst_boxes[i].mx = v3(c.x + m->radius, c.y + m->radius, c.z + m->radius);
+            s->inst_boxes[i].nondegenerate = 1;
+            continue;
+        }
         for (int k = m->tri_begin; k < m->tri_end; k++)
             for (int j = 0; j < 3; j++) box_fit(&local, s->vertices[s->tris[k].v[j]]);
         Entity me = entity_from_pose(&m->pose);

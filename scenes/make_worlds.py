@@ -43,6 +43,14 @@ WORLDS = {
     "grid64": world(64, [DIRT, GRASS]),
     "grid64_mixed": world(64, [DIRT, STRESS_GRASS, MIRROR, GLASS], depth=9),
     "grid128": world(128, [DIRT, GRASS]),
+    # analytic sphere hitables (schema extension "spheres"): matte, mirror and glass spheres over world8
+    "spheres8": world(8, [DIRT, GRASS], depth=5, spheres=[
+        dict(radius=1.5, pos=[-2.0, 7.0, 1.0], Ka=[120, 30, 30, 255], Kd=[220, 40, 40, 255], Ks=[255, 255, 255, 255], alpha=20.0),
+        dict(MIRROR, radius=2.0, pos=[2.5, 8.0, 3.0]),
+        dict(radius=1.0, pos=[0.0, 9.0, -1.0], Ka=[20, 20, 40, 255], Kd=[30, 30, 60, 255], Kt=[0.8, 0.8, 0.9, 1.0], eta=0.8),
+        dict(radius=0.75, pos=[-3.25, 4.5, -2.0], Ka=[40, 40, 120, 255], Kd=[60, 60, 230, 255]),
+        dict(radius=0.3, pos=[1.0, 10.5, -3.0], Ke=[255, 220, 120, 255]),
+    ]),
 }
 
 if __name__ == "__main__":
