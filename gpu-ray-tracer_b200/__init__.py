@@ -37,7 +37,8 @@ class RtMaterial(C.Structure):
 
 
 class RtTriangle(C.Structure):
-    _fields_ = [("v", C.c_int32 * 3), ("tex_degenerate", C.c_int32), ("mat", RtMaterial)]
+    _fields_ = [("v", C.c_int32 * 3), ("tex_degenerate", C.c_int32), ("mat", RtMaterial),
+                ("tex_x", C.c_int32), ("tex_y", C.c_int32), ("tex_u", C.c_float * 2), ("tex_v", C.c_float * 2)]
 
 
 class RtPose(C.Structure):
@@ -71,7 +72,8 @@ class RtSceneDesc(C.Structure):
                 ("meshes", C.POINTER(RtMesh)), ("n_meshes", C.c_int32),
                 ("instances", C.POINTER(RtInstance)), ("n_instances", C.c_int32),
                 ("lights", C.POINTER(RtLight)), ("n_lights", C.c_int32),
-                ("camera", RtCamera), ("env", RtEnv), ("width", C.c_int32), ("height", C.c_int32)]
+                ("camera", RtCamera), ("env", RtEnv), ("width", C.c_int32), ("height", C.c_int32),
+                ("atlas", C.POINTER(C.c_float)), ("atlas_width", C.c_int32), ("atlas_height", C.c_int32)]
 
 
 class RtRenderParams(C.Structure):

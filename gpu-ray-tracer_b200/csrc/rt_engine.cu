@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
         }
         // no secondary rays: acc = 0 + 1 * illuminate, clamp, pack (src/raytracer.cu:36-41)
         float3 nrm = hit_normal(s, h, r);
-        float4 c = illuminate<OPAQUE_ONLY>(s, tr, r, h.t, nrm, m, rc);
+        float4 c = illuminate<OPAQUE_ONLY>(s, tr, r, h.t, nrm, m, diffuse_colour(s, m, h.tri, h.u, h.v), rc);
         canvas[rec.out_index] = rtx::pack_color(c);
     }
     flush_counts(ctr, rc, ts, STATS);
@@ -484,7 +484,7 @@ __global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_resolve(Sce
             int stack_top = 0, isect_mat = mat_id;
             float4 acc = rtx::mk4(0.f, 0.f, 0.f, 0.f);
             bool alive = path_advance_core(
-                s, [&](const rtx::Ray& ray, float t, float3 nn, const MatRec& mm) { return illuminate_resolved(s, ray, t, nn, mm, att); },
+                s, [&](const rtx::Ray& ray, float t, float3 nn, const MatRec& mm, float4 kd) { return illuminate_resolved(s, ray, t, nn, mm, kd, att); },
                 frames, stack_top, isect_mat, acc, true, h, top, true);
             if (alive) {
                 PathHead hd;
@@ -499,7 +499,7 @@ __global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_resolve(Sce
         }
         // no secondary rays: acc = 0 + 1 * illuminate, clamp, pack (src/raytracer.cu:36-41)
         float3 nrm = hit_normal(s, h, r);
-        float4 c = illuminate_resolved(s, r, h.t, nrm, m, att);
+        float4 c = illuminate_resolved(s, r, h.t, nrm, m, diffuse_colour(s, m, h.tri, h.u, h.v), att);
         canvas[rec.out_index] = rtx::pack_color(c);
     }
 }
@@ -549,7 +549,7 @@ __device__ __forceinline__ void phase_path_advance(const SceneView& s, const int
         h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
         AttenLookup att = {occl, att4, (size_t)n, (size_t)i};
         bool alive = path_advance_with(
-            s, [&](const rtx::Ray& ray, float t, float3 nn, const MatRec& mm) { return illuminate_resolved(s, ray, t, nn, mm, att); },
+            s, [&](const rtx::Ray& ray, float t, float3 nn, const MatRec& mm, float4 kd) { return illuminate_resolved(s, ray, t, nn, mm, kd, att); },
             frames, stack_top, isect_mat, acc, rec.inst >= 0, h);
         if (alive) {
             head->acc = acc;
@@ -861,6 +861,11 @@ SceneView make_view(const RtScene* sc, bool with_bvh) {
     v.insts = sc->d_insts.as<InstRec>();
     v.mats = sc->d_mats.as<MatRec>();
     v.lights = sc->d_lights.as<LightRec>();
+    if (sc->textured) {
+        v.texc = sc->d_texc.as<TexRec>();
+        v.atlas = sc->d_atlas.as<float4>();
+        v.atlas_w = sc->atlas_w; v.atlas_h = sc->atlas_h;
+    }
     v.n_insts = sc->n_instances;
     v.n_lights = sc->n_lights;
     if (with_bvh && sc->bvh.valid) {
@@ -991,6 +996,11 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
         (rc = upload(sc->d_meshes, hs.meshes, sc->stream)) || (rc = upload(sc->d_mesh_box, hs.mesh_box, sc->stream)) ||
         (rc = upload(sc->d_lights, hs.lights, sc->stream)))
         return fail(rc);
+    sc->textured = !hs.texc.empty();
+    if (sc->textured) {
+        sc->atlas_w = hs.atlas_w; sc->atlas_h = hs.atlas_h;
+        if ((rc = upload(sc->d_texc, hs.texc, sc->stream)) || (rc = upload(sc->d_atlas, hs.atlas, sc->stream))) return fail(rc);
+    }
     const size_t n_pinned = 64 + (size_t)C_N * RtScene::kMaxChunks;
     if (sc->d_counters.reserve(sizeof(unsigned long long) * C_N * RtScene::kMaxChunks)) return fail(RT_ERR_OUT_OF_MEMORY);
     e = cudaHostAlloc((void**)&sc->h_pinned, n_pinned * sizeof(unsigned long long), cudaHostAllocDefault);
@@ -1007,7 +1017,7 @@ int rt_scene_destroy(RtScene* sc) {
     if (!sc) return RT_OK;
     if (sc->stream) cudaStreamSynchronize(sc->stream);
     rth::DevBuf* all[] = {&sc->d_verts, &sc->d_norms, &sc->d_tris, &sc->d_meshes, &sc->d_insts, &sc->d_mats, &sc->d_lights,
-                          &sc->d_mesh_box, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
+                          &sc->d_mesh_box, &sc->d_texc, &sc->d_atlas, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
                           &sc->d_queue_b, &sc->d_ids, &sc->d_shadowq, &sc->d_occl, &sc->d_shq_count};
     for (rth::DevBuf* b : all) b->release();
     sc->bvh.release();

@@ -18,6 +18,9 @@ namespace rth {
 struct HostScene {
     std::vector<float4> verts, norms;
     std::vector<rtd::TriRec> tris;
+    std::vector<rtd::TexRec> texc;   // per triangle record; empty unless the scene has an atlas and a textured triangle
+    std::vector<float4> atlas;
+    int atlas_w = 0, atlas_h = 0;
     std::vector<rtd::MatRec> mats;
     std::vector<rtd::MeshRec> meshes;
     std::vector<float> mesh_box;  // 8 per mesh: lo[3], hi[3], non_degenerate, pad
@@ -74,6 +77,27 @@ inline void prepare_host_scene(const RtSceneDesc* d, HostScene& hs) {
         }
         hs.tris[i].v0 = d->triangles[i].v[0]; hs.tris[i].v1 = d->triangles[i].v[1]; hs.tris[i].v2 = d->triangles[i].v[2];
         hs.tris[i].mat = id;
+    }
+    // texture atlas + TextureCoords, only when something can be sampled
+    bool any_tex = false;
+    if (d->atlas && d->atlas_width > 0 && d->atlas_height > 0)
+        for (int i = 0; i < d->n_triangles && !any_tex; i++) any_tex = d->triangles[i].tex_degenerate == 0;
+    if (any_tex) {
+        hs.atlas_w = d->atlas_width; hs.atlas_h = d->atlas_height;
+        hs.atlas.resize((size_t)hs.atlas_w * hs.atlas_h);
+        for (size_t i = 0; i < hs.atlas.size(); i++) {
+            hs.atlas[i] = make_float4(d->atlas[4 * i], d->atlas[4 * i + 1], d->atlas[4 * i + 2], d->atlas[4 * i + 3]);
+            for (int k = 0; k < 4; k++)
+                if (!std::isfinite(d->atlas[4 * i + k])) hs.cull_ok = 0;
+        }
+        hs.texc.resize(d->n_triangles);
+        for (int i = 0; i < d->n_triangles; i++) {
+            const RtTriangle& t = d->triangles[i];
+            rtd::TexRec r;
+            r.x = t.tex_x; r.y = t.tex_y; r.u0 = t.tex_u[0]; r.u1 = t.tex_u[1]; r.v0 = t.tex_v[0]; r.v1 = t.tex_v[1];
+            r.degenerate = t.tex_degenerate ? 1 : 0; r.pad = 0;
+            hs.texc[i] = r;
+        }
     }
     // meshes: pose + local box over the vertices of their triangles (Trimesh::compute_bounding_box,
     // src/rayprimitives/trimesh.cu:21-32: plain min/max, exact wherever it is evaluated)

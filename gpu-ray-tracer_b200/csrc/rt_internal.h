@@ -76,6 +76,9 @@ struct RtScene {
     std::vector<int> mesh_tri_count;
     // device
     rth::DevBuf d_verts, d_norms, d_tris, d_meshes, d_insts, d_mats, d_lights, d_mesh_box;
+    rth::DevBuf d_texc, d_atlas;    // TextureCoords per triangle record + RGBA atlas; empty when nothing is textured
+    int atlas_w = 0, atlas_h = 0;
+    bool textured = false;
     rth::DevBuf d_canvas, d_counters, d_hitq, d_paths, d_queue_a, d_queue_b, d_ids;
     rth::DevBuf d_shadowq, d_occl, d_shq_count;
     bool fused_shade = false;       // RT_RENDER_FUSED_SHADE: one k_shade kernel instead of gen / traverse / resolve

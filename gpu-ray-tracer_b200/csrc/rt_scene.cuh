@@ -19,6 +19,7 @@
 namespace rtd {
 
 struct TriRec { int v0, v1, v2, mat; };
+struct TexRec { int x, y; float u0, u1, v0, v1; int degenerate, pad; };  // TextureCoords; only present in scenes with an atlas
 struct MeshRec { rtx::Pose pose; int tri_begin, tri_end; int kind; float radius; };  // kind: RT_HITABLE_TRIMESH / RT_HITABLE_SPHERE
 struct InstRec {
     rtx::Pose pose;
@@ -49,6 +50,9 @@ struct SceneView {
     const InstRec* insts;
     const MatRec* mats;
     const LightRec* lights;
+    const TexRec* texc;    // per triangle record, null when the scene has no atlas or no textured triangle
+    const float4* atlas;   // RGBA texels, row-major
+    int atlas_w, atlas_h;
     int n_insts, n_lights, n_prims;
     // BVH8 (null when no BVH is built)
     const uint4* nodes;
@@ -201,6 +205,21 @@ RT_HD_NOINLINE float3 hit_normal(const SceneView& s, const Hit& h, const rtx::Ra
     }
     n = rtx::normalized3(rtx::vec_from_local(M.pose, n));
     return rtx::vec_from_local(I.pose, n);
+}
+
+// The diffuse colour phong() uses for a hit: the material's Kd, or — triangle with non-degenerate TextureCoords in a
+// scene with an atlas — the texel at origin + b1 * u + b2 * v (point sampling, clamped, unnormalised coordinates like
+// the reference's texture descriptor, include/gputils/alloc.h:52-56). No reference counterpart (phong.cu:19-23 is a TODO).
+RT_HD float4 diffuse_colour(const SceneView& s, const MatRec& m, int tri, float u, float v) {
+    if (!s.texc) return m.Kd;
+    const TexRec t = s.texc[tri];
+    if (t.degenerate) return m.Kd;
+    float tx = ((float)t.x + u * t.u0) + v * t.v0;
+    float ty = ((float)t.y + u * t.u1) + v * t.v1;
+    int ix = (int)floorf(tx), iy = (int)floorf(ty);
+    ix = ix < 0 ? 0 : (ix >= s.atlas_w ? s.atlas_w - 1 : ix);
+    iy = iy < 0 ? 0 : (iy >= s.atlas_h ? s.atlas_h - 1 : iy);
+    return s.atlas[(size_t)iy * s.atlas_w + ix];
 }
 
 // cast_ray's `-r/--unoptimize` branch (src/rayenv/scene.cu:48-52): every instance in index order.

@@ -94,10 +94,11 @@ RT_HD float4 light_shine(const SceneView& s, const Tracer& tr, const LightRec& L
     return L.kind == 0 ? rtx::scale4(da, a) : a;
 }
 
-// phong (phong.cu:14-33); the texture branch is empty in the reference.
-RT_HD float4 phong(const MatRec& m, float3 norm, float4 incoming, float3 ray_dir, float3 dir_to_light) {
+// phong (phong.cu:14-33). `kd` is the diffuse colour: the material's Kd, or the atlas texel of a textured triangle
+// (diffuse_colour(); the texture branch is an empty TODO in the reference).
+RT_HD float4 phong(const MatRec& m, float4 kd, float3 norm, float4 incoming, float3 ray_dir, float3 dir_to_light) {
     float norm_dot = fmaxf(rtx::dot3(dir_to_light, norm), 0.0f);
-    float4 diffuse = rtx::scale4(norm_dot, m.Kd);
+    float4 diffuse = rtx::scale4(norm_dot, kd);
     float3 reflected = rtx::ref_reflect(rtx::neg3(dir_to_light), norm);
     float reflect_dot = rtx::dot3(rtx::neg3(reflected), ray_dir);
     float4 specular = rtx::scale4(rtx::ref_powf(fmaxf(reflect_dot, 0.0f), m.alpha), m.Ks);
@@ -107,13 +108,13 @@ RT_HD float4 phong(const MatRec& m, float3 norm, float4 incoming, float3 ray_dir
 // org_light + illuminate (phong.cu:35-53)
 template <bool OPAQUE_ONLY = false, class Tracer>
 RT_HD float4 illuminate(const SceneView& s, const Tracer& tr, const rtx::Ray& ray, float t, float3 norm,
-                        const MatRec& m, RayCounts& rc) {
+                        const MatRec& m, float4 kd, RayCounts& rc) {
     float4 sum = rtx::add4(m.Ke, rtx::mul4(m.Ka, s.ambience));
     float3 hit_pos = rtx::ray_at(ray, t);
     for (int i = 0; i < s.n_lights; i++) {
         float3 dir_to_light;
         float4 incoming = light_shine<OPAQUE_ONLY>(s, tr, s.lights[i], hit_pos, dir_to_light, rc);
-        sum = rtx::add4(sum, phong(m, norm, incoming, ray.d, dir_to_light));
+        sum = rtx::add4(sum, phong(m, kd, norm, incoming, ray.d, dir_to_light));
     }
     return sum;
 }
@@ -133,7 +134,7 @@ RT_HD bool light_unlit(const MatRec& m, float3 norm, float3 dir_to_light) {
 // or the colour filtered by the refractive occluders). Same operations as illuminate().
 template <class Atten>
 RT_HD float4 illuminate_resolved(const SceneView& s, const rtx::Ray& ray, float t, float3 norm, const MatRec& m,
-                                 Atten atten) {
+                                 float4 kd, Atten atten) {
     float4 sum = rtx::add4(m.Ke, rtx::mul4(m.Ka, s.ambience));
     float3 hit_pos = rtx::ray_at(ray, t);
     for (int i = 0; i < s.n_lights; i++) {
@@ -144,7 +145,7 @@ RT_HD float4 illuminate_resolved(const SceneView& s, const rtx::Ray& ray, float 
         if (s.cull_unlit && light_unlit(m, norm, dir_to_light)) continue;  // its shadow ray was not traced
         float4 a = atten(i, L);
         float4 incoming = L.kind == 0 ? rtx::scale4(da, a) : a;
-        sum = rtx::add4(sum, phong(m, norm, incoming, ray.d, dir_to_light));
+        sum = rtx::add4(sum, phong(m, kd, norm, incoming, ray.d, dir_to_light));
     }
     return sum;
 }
@@ -222,7 +223,7 @@ RT_HD bool path_advance_core(const SceneView& s, Illum illum, Frame* frames, int
             have_top = false;
         }
         isect_mat = mat_id;
-        acc = rtx::add4(acc, rtx::mul4(atten, illum(ray, h.t, n, m)));
+        acc = rtx::add4(acc, rtx::mul4(atten, illum(ray, h.t, n, m, diffuse_colour(s, m, h.tri, h.u, h.v))));
     } else {
         stack_top--;
         have_top = false;
@@ -289,7 +290,7 @@ template <class Tracer>
 RT_HD bool path_advance(const SceneView& s, const Tracer& tr, Frame* frames, int& stack_top, int& isect_mat,
                         float4& acc, bool hit, const Hit& h, RayCounts& rc) {
     return path_advance_with(
-        s, [&](const rtx::Ray& ray, float t, float3 n, const MatRec& m) { return illuminate(s, tr, ray, t, n, m, rc); },
+        s, [&](const rtx::Ray& ray, float t, float3 n, const MatRec& m, float4 kd) { return illuminate(s, tr, ray, t, n, m, kd, rc); },
         frames, stack_top, isect_mat, acc, hit, h);
 }
 
@@ -335,7 +336,8 @@ __host__ __device__ float4 propagate_cpu_rec(const SceneView& s, const Tracer& t
     isect.time = h.t;
     isect.norm = hit_normal(s, h, r);
     isect.mat = s.tris[h.tri].mat;
-    float4 acc = illuminate(s, tr, r, isect.time, isect.norm, s.mats[isect.mat], rc);
+    float4 acc = illuminate(s, tr, r, isect.time, isect.norm, s.mats[isect.mat],
+                            diffuse_colour(s, s.mats[isect.mat], h.tri, h.u, h.v), rc);
     last_time = isect.time;
     float next_time = 0.0f;
     if (s.mats[isect.mat].reflective) {

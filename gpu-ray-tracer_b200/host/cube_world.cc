@@ -22,6 +22,26 @@ const float kDefaultFov = M_PI / 4;
 const float kDefaultUnitLen = 200;
 const float kDefaultAmplitude = 1.0f;
 
+std::vector<float> read_ppm(const std::string& path, int& w, int& h) {
+    std::ifstream f(path.c_str(), std::ios::binary);
+    if (!f) throw std::runtime_error("cannot open atlas: " + path);
+    std::string magic;
+    int maxv = 0;
+    f >> magic >> w >> h >> maxv;
+    if (magic != "P6" || w <= 0 || h <= 0 || maxv != 255) throw std::runtime_error("atlas is not a binary PPM with maxval 255: " + path);
+    f.get();  // the single whitespace after the header
+    std::vector<unsigned char> raw((size_t)w * h * 3);
+    f.read((char*)raw.data(), (std::streamsize)raw.size());
+    if ((size_t)f.gcount() != raw.size()) throw std::runtime_error("atlas is truncated: " + path);
+    std::vector<float> rgba((size_t)w * h * 4);
+    const float inv255 = 1.0f / UINT8_MAX;  // Texture::color_to_vec (src/rayprimitives/texture.cu:14-16)
+    for (size_t i = 0; i < (size_t)w * h; i++) {
+        for (int k = 0; k < 3; k++) rgba[4 * i + k] = inv255 * (float)raw[3 * i + k];
+        rgba[4 * i + 3] = inv255 * 255.0f;
+    }
+    return rgba;
+}
+
 rtb::Float3 read_vec3(const mini_json::Value& v) { return {v.at(0).as_float(), v.at(1).as_float(), v.at(2).as_float()}; }
 rtb::Float4 read_vec4(const mini_json::Value& v) {
     return {v.at(0).as_float(), v.at(1).as_float(), v.at(2).as_float(), v.at(3).as_float()};
@@ -67,8 +87,23 @@ rtracer::FlatScene generate_from_text(const std::string& json_text, const WorldO
             if (cube.has("Kr")) mat.set_Kr(read_vec4(cube.at("Kr")));
             if (cube.has("alpha")) mat.set_alpha((float)cube.at("alpha").as_double());
             if (cube.has("eta")) mat.set_eta((float)cube.at("eta").as_double());
-            builder.build_cube(.999f, coords, mat);
+            // "texture": [tile_x, tile_y, tile_size] — schema extension: every face shows that atlas tile
+            if (cube.has("texture")) {
+                const mini_json::Value& t = cube.at("texture");
+                builder.build_textured_cube(.999f, t.at(0).as_int(), t.at(1).as_int(), t.at(2).as_int(), mat);
+            } else {
+                builder.build_cube(.999f, coords, mat);
+            }
         }
+    }
+    // "atlas_ppm": binary PPM (P6, maxval 255) next to the scene file or at an absolute path — the reference reads a PNG
+    // through libpng (src/assets.cc), which this image does not have; texels become RGBA floats c / 255, alpha 1
+    if (doc.has("atlas_ppm")) {
+        std::string path = doc.at("atlas_ppm").as_string();
+        if (!path.empty() && path[0] != '/' && !ov.base_dir.empty()) path = ov.base_dir + "/" + path;
+        int aw = 0, ah = 0;
+        std::vector<float> rgba = read_ppm(path, aw, ah);
+        builder.set_atlas(std::move(rgba), aw, ah);
     }
 
     // "spheres": schema extension with no reference counterpart: analytic sphere hitables, each
@@ -165,7 +200,12 @@ rtracer::FlatScene generate(const std::string& config_path, const WorldOverrides
     if (!ifs) throw std::runtime_error("cannot open scene file: " + config_path);
     std::stringstream ss;
     ss << ifs.rdbuf();
-    return generate_from_text(ss.str(), ov);
+    WorldOverrides o2 = ov;
+    if (o2.base_dir.empty()) {
+        size_t slash = config_path.find_last_of('/');
+        o2.base_dir = slash == std::string::npos ? "." : config_path.substr(0, slash);
+    }
+    return generate_from_text(ss.str(), o2);
 }
 
 }  // namespace procedural

@@ -13,6 +13,7 @@ namespace procedural {
 // Optional key overrides, equivalent to editing the JSON file (<= 0 / < 0 means "keep").
 struct WorldOverrides {
     int width = 0, height = 0, depth = -1, grid_size = 0;
+    std::string base_dir;  // where relative "atlas_ppm" paths are looked up; generate() fills in the scene file's directory
 };
 
 // Throws std::runtime_error on unreadable / malformed input.

@@ -41,6 +41,9 @@ RtSceneDesc FlatScene::desc() const {
     d.env = env;
     d.width = width;
     d.height = height;
+    d.atlas = atlas.empty() ? nullptr : atlas.data();
+    d.atlas_width = atlas_width;
+    d.atlas_height = atlas_height;
     return d;
 }
 
@@ -70,6 +73,33 @@ int SceneBuilder::build_cube(float scale, const TextureCoords& coords, const Mat
         get_mesh_builder(builder_idx).add_triangle(v0, v1, v2, coords, mat);
     }
     return builder_idx;
+}
+
+// build_cube with every face mapped onto one square atlas tile (origin tile_x, tile_y; edge tile_size texels): a
+// corner's tile position comes from its two in-face coordinates, TextureCoords = atlas position of the triangle's first
+// vertex + the atlas-space edges to the second and third (Isect::uv weighs exactly those edges).
+int SceneBuilder::build_textured_cube(float scale, int tile_x, int tile_y, int tile_size, const Material& mat) {
+    int idx = build_cube(scale, TextureCoords(), mat);
+    MeshBuilder& mb = get_mesh_builder(idx);
+    for (RtTriangle& t : mb.triangles_) {
+        rtb::Float3 c[3] = {vertices_[t.v[0]], vertices_[t.v[1]], vertices_[t.v[2]]};
+        // the face's normal axis: the coordinate all three corners share
+        int axis = (c[0].x == c[1].x && c[1].x == c[2].x) ? 0 : ((c[0].y == c[1].y && c[1].y == c[2].y) ? 1 : 2);
+        float a[3][2];
+        for (int k = 0; k < 3; k++) {
+            float p[3] = {c[k].x / scale, c[k].y / scale, c[k].z / scale};  // back to +-0.5
+            float s0 = p[(axis + 1) % 3], s1 = p[(axis + 2) % 3];
+            a[k][0] = (s0 + 0.5f) * (float)tile_size;
+            a[k][1] = (0.5f - s1) * (float)tile_size;
+        }
+        t.tex_degenerate = 0;
+        // integer origin (TextureCoords::texture_x/y are ints): the first vertex sits on a tile corner
+        t.tex_x = tile_x + (int)a[0][0];
+        t.tex_y = tile_y + (int)a[0][1];
+        t.tex_u[0] = a[1][0] - a[0][0]; t.tex_u[1] = a[1][1] - a[0][1];
+        t.tex_v[0] = a[2][0] - a[0][0]; t.tex_v[1] = a[2][1] - a[0][1];
+    }
+    return idx;
 }
 
 std::vector<rtb::Float3> SceneBuilder::generate_normals() const {
@@ -114,6 +144,9 @@ FlatScene SceneBuilder::build_flat_scene(int width, int height, const Camera& ca
         m.radius = mb.radius_;
         fs.meshes.push_back(m);
     }
+    fs.atlas = atlas_;
+    fs.atlas_width = atlas_w_;
+    fs.atlas_height = atlas_h_;
     for (const Transformation& t : trans_) {
         RtInstance inst;
         inst.pose.rot[0] = t.o.i; inst.pose.rot[1] = t.o.j; inst.pose.rot[2] = t.o.k; inst.pose.rot[3] = t.o.r;

@@ -13,12 +13,15 @@
 
 namespace rtracer {
 
-// rprimitives::TextureCoords (include/rayprimitives/texture_coords.h:12-29); only `degenerate`
-// is ever read on the hot path (src/rayprimitives/phong.cu:19-23).
+// rprimitives::TextureCoords (include/rayprimitives/texture_coords.h:12-29): atlas origin + the atlas-space directions
+// of the two barycentric axes. The reference only ever reads `degenerate` (src/rayprimitives/phong.cu:19-23).
 struct TextureCoords {
     int texture_x = 0, texture_y = 0;
     float u[2] = {0, 0}, v[2] = {0, 0};
     bool degenerate = true;
+    TextureCoords() {}
+    TextureCoords(int tx, int ty, float u0, float u1, float v0, float v1)
+        : texture_x(tx), texture_y(ty), u{u0, u1}, v{v0, v1}, degenerate(false) {}
 };
 
 // rprimitives::Material (include/rayprimitives/material.h:14-115) as a POD with the same defaults
@@ -50,6 +53,8 @@ public:
         RtTriangle t;
         t.v[0] = v0; t.v[1] = v1; t.v[2] = v2;
         t.tex_degenerate = coords.degenerate ? 1 : 0;
+        t.tex_x = coords.texture_x; t.tex_y = coords.texture_y;
+        t.tex_u[0] = coords.u[0]; t.tex_u[1] = coords.u[1]; t.tex_v[0] = coords.v[0]; t.tex_v[1] = coords.v[1];
         t.mat = mat.m;
         triangles_.push_back(t);
     }
@@ -99,6 +104,8 @@ struct FlatScene {
     std::vector<RtMesh> meshes;
     std::vector<RtInstance> instances;
     std::vector<RtLight> lights;
+    std::vector<float> atlas;  // RGBA floats (rprimitives::gpu::Texture), empty = none
+    int atlas_width = 0, atlas_height = 0;
     RtCamera camera;
     RtEnv env;
     int width = 0, height = 0;
@@ -134,6 +141,9 @@ public:
     }
     // 12-triangle, 36-vertex cube (src/scene_builder.cu:181-239)
     int build_cube(float scale, const TextureCoords& coords, const Material& mat);
+    // build_cube whose faces each show one square tile of the atlas (texture mapping is a TODO in
+    // the reference, src/procedural/cube_world.cc:79-81)
+    int build_textured_cube(float scale, int tile_x, int tile_y, int tile_size, const Material& mat);
     // Analytic sphere hitable centred at its own origin (the reference has no second Hitable
     // subclass). Returns the hitable index, to be instanced with add_trans(get_mesh_builder(idx)) like a cube.
     int build_sphere(float radius, const TextureCoords& coords, const Material& mat) {
@@ -147,6 +157,11 @@ public:
     void add_directional_light(rtb::Float3 dir, rtb::Float4 col) {
         dir_light_dir_.push_back(dir);
         dir_light_col_.push_back(col);
+    }
+    // The atlas the reference reads with assets::read_png (src/assets.cc, libpng — absent here): RGBA floats in
+    // [0, 1] (Texture::color_to_vec, src/rayprimitives/texture.cu:14-16), row-major.
+    void set_atlas(std::vector<float> rgba, int width, int height) {
+        atlas_ = std::move(rgba); atlas_w_ = width; atlas_h_ = height;
     }
     void add_point_light(rtb::Float3 pos, rtb::Float4 col) {
         point_light_pos_.push_back(pos);
@@ -170,6 +185,8 @@ private:
     std::vector<rtb::Float4> point_light_col_, dir_light_col_;
     std::vector<Transformation> trans_;
     std::string atlas_path_;
+    std::vector<float> atlas_;
+    int atlas_w_ = 0, atlas_h_ = 0;
 };
 
 }  // namespace rtracer

@@ -36,13 +36,21 @@ typedef struct RtMaterial {
     float alpha, eta;
 } RtMaterial;
 
-/* rprimitives::{gpu,cpu}::TriInner (include/rayprimitives/gpu/trimesh.cuh:25-53): vertex index
- * triple, per-triangle material, TextureCoords reduced to its `degenerate` flag (the atlas is
- * never sampled, src/rayprimitives/phong.cu:19-23). */
+/* rprimitives::{gpu,cpu}::TriInner (include/rayprimitives/gpu/trimesh.cuh:25-53): vertex index triple, per-triangle
+ * material and rprimitives::TextureCoords (include/rayprimitives/texture_coords.h:12-29): atlas origin (texels) and the
+ * atlas-space directions of the two barycentric axes. The reference never samples its atlas (`// TODO: implement
+ * texture mapping`, src/rayprimitives/phong.cu:19-23), so with tex_degenerate != 0 — every shipped world — the tex_*
+ * fields are ignored. With tex_degenerate == 0 and an atlas in the scene (no reference counterpart)
+ * the diffuse colour of a hit with Isect::uv = (b1, b2) is the atlas texel at
+ *   (tex_x + b1 * tex_u[0] + b2 * tex_v[0],  tex_y + b1 * tex_u[1] + b2 * tex_v[1]),
+ * point-sampled, clamped, unnormalised coordinates (the reference's texture descriptor, include/gputils/alloc.h:52-56),
+ * and replaces Kd in phong()'s diffuse term. */
 typedef struct RtTriangle {
     int32_t v[3];
     int32_t tex_degenerate;
     RtMaterial mat;
+    int32_t tex_x, tex_y;
+    float tex_u[2], tex_v[2];
 } RtTriangle;
 
 /* rprimitives::Entity pose (include/rayprimitives/entity.h:16-30): quaternion (i,j,k,r) + position. */
@@ -113,6 +121,10 @@ typedef struct RtSceneDesc {
     RtCamera camera;
     RtEnv env;
     int32_t width, height;
+    /* texture atlas (rprimitives::gpu::Texture, a float4 2-D texture in the reference): RGBA floats, row-major,
+     * atlas_width * atlas_height * 4 values; NULL = no atlas, every triangle shades with its Kd */
+    const float* atlas;
+    int32_t atlas_width, atlas_height;
 } RtSceneDesc;
 
 typedef struct RtScene RtScene; /* opaque; owns all device memory */

@@ -174,6 +174,8 @@ struct OrScene {
     RtCamera cam;
     RtEnv env;
     int width, height;
+    float* atlas; /* RGBA floats, NULL = none */
+    int atlas_w, atlas_h;
 };
 
 typedef struct {
@@ -393,11 +395,27 @@ static V4 light_shine(const OrScene* s, const RtLight* l, V3 hit_pos, V3* dir_to
     Ray to_light = ray_make(hit_pos, *dir_to_light);
     return light_attenuate(s, l, &to_light, INFINITY, use_bvh, ctx);
 }
-/* ref: src/rayprimitives/phong.cu:14-33 phong */
-static V4 phong(const Isect* isect, V4 incoming, V3 ray_dir, V3 dir_to_light) {
+/* The texture branch phong.cu:19-23 leaves as `// TODO: implement texture mapping` (NO reference
+ * counterpart): TextureCoords (include/rayprimitives/texture_coords.h:12-29) = atlas origin + the atlas-space directions
+ * of the barycentric axes, Isect::uv = (b1, b2); texel fetch like get_color_from_texture (src/rayprimitives/texture.cu:8-12)
+ * through the reference's descriptor: point filter, clamp, unnormalised coordinates (include/gputils/alloc.h:52-56). */
+static V4 diffuse_colour(const OrScene* s, const Isect* isect) {
+    const RtTriangle* t = isect->tri;
+    if (t->tex_degenerate || !s->atlas) return v4from(t->mat.Kd);
+    float tx = ((float)t->tex_x + isect->u * t->tex_u[0]) + isect->v * t->tex_v[0];
+    float ty = ((float)t->tex_y + isect->u * t->tex_u[1]) + isect->v * t->tex_v[1];
+    int ix = (int)floorf(tx), iy = (int)floorf(ty);
+    ix = ix < 0 ? 0 : (ix >= s->atlas_w ? s->atlas_w - 1 : ix);
+    iy = iy < 0 ? 0 : (iy >= s->atlas_h ? s->atlas_h - 1 : iy);
+    return v4from(s->atlas + 4 * ((size_t)iy * s->atlas_w + ix));
+}
+
+/* ref: src/rayprimitives/phong.cu:14-33 phong. The reference computes diffuse_col and then multiplies Kd regardless; with
+ * a degenerate TextureCoords (every shipped world) both are Kd. */
+static V4 phong(const OrScene* s, const Isect* isect, V4 incoming, V3 ray_dir, V3 dir_to_light) {
     const RtMaterial* m = &isect->tri->mat;
     float norm_dot = fmaxf(v3dot(dir_to_light, isect->norm), 0.0f);
-    V4 diffuse = v4scale(norm_dot, v4from(m->Kd));
+    V4 diffuse = v4scale(norm_dot, diffuse_colour(s, isect));
     V3 reflected = reflect3(v3neg(dir_to_light), isect->norm);
     float reflect_dot = v3dot(v3neg(reflected), ray_dir);
     V4 specular = v4scale(powf(fmaxf(reflect_dot, 0.0f), m->alpha), v4from(m->Ks));
@@ -410,7 +428,7 @@ static V4 illuminate(const OrScene* s, const Ray* org_ray, const Isect* isect, i
     for (int i = 0; i < s->n_lights; i++) {
         V3 dir_to_light;
         V4 incoming = light_shine(s, &s->lights[i], ray_at(org_ray, isect->time), &dir_to_light, use_bvh, ctx);
-        sum = v4add(sum, phong(isect, incoming, org_ray->d, dir_to_light));
+        sum = v4add(sum, phong(s, isect, incoming, org_ray->d, dir_to_light));
     }
     return sum;
 }
@@ -631,6 +649,11 @@ OrScene* or_scene_create(const RtSceneDesc* d) {
     s->env = d->env;
     s->width = d->width;
     s->height = d->height;
+    if (d->atlas && d->atlas_width > 0 && d->atlas_height > 0) {
+        s->atlas = (float*)dup_mem(d->atlas, sizeof(float) * 4 * (size_t)d->atlas_width * (size_t)d->atlas_height);
+        s->atlas_w = d->atlas_width;
+        s->atlas_h = d->atlas_height;
+    }
     compute_instance_boxes(s);
     return s;
 }
@@ -638,7 +661,7 @@ OrScene* or_scene_create(const RtSceneDesc* d) {
 void or_scene_destroy(OrScene* s) {
     if (!s) return;
     free(s->vertices); free(s->normals); free(s->tris); free(s->meshes);
-    free(s->instances); free(s->lights); free(s->inst_boxes); free(s);
+    free(s->instances); free(s->lights); free(s->inst_boxes); free(s->atlas); free(s);
 }
 void or_scene_set_camera(OrScene* s, const RtCamera* cam) { s->cam = *cam; }
 void or_scene_set_env(OrScene* s, const RtEnv* env) { s->env = *env; }

@@ -53,7 +53,33 @@ WORLDS = {
     ]),
 }
 
+def write_atlas(path, tiles=4, tile=16):
+    """Deterministic atlas of tiles x tiles square tiles as a binary PPM: every tile has its own base colour, a darker
+    checker pattern, a bright border and one marked corner, so that orientation and clamping errors show in a frame."""
+    n = tiles * tile
+    rows = bytearray()
+    for y in range(n):
+        for x in range(n):
+            tx, ty, lx, ly = x // tile, y // tile, x % tile, y % tile
+            base = (40 + 60 * tx, 230 - 50 * ty, 60 + 45 * ((tx + 2 * ty) % 4))
+            k = 1.0 if ((lx // 4) + (ly // 4)) % 2 == 0 else 0.55
+            c = [int(v * k) for v in base]
+            if lx in (0, tile - 1) or ly in (0, tile - 1):
+                c = [250, 250, 250]
+            if lx < 4 and ly < 4:
+                c = [255, 0, 0]
+            rows += bytes(c)
+    with open(path, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (n, n))
+        f.write(bytes(rows))
+
+
+WORLDS["textured8"] = dict(world(8, [dict(DIRT, texture=[0, 0, 16]), dict(GRASS, texture=[16, 32, 16])], spheres=[
+    dict(radius=1.5, pos=[-2.0, 7.0, 1.0], Ka=[120, 30, 30, 255], Kd=[220, 40, 40, 255], Ks=[255, 255, 255, 255], alpha=20.0),
+]), atlas_ppm="atlas64.ppm")
+
 if __name__ == "__main__":
+    write_atlas(os.path.join(HERE, "atlas64.ppm"))
     for name, w in WORLDS.items():
         with open(os.path.join(HERE, name + ".json"), "w") as f:
             json.dump(w, f, indent=1)

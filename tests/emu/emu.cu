@@ -30,6 +30,7 @@ static void fill_view(EmuScene* e, const RtSceneDesc* d, const uint32_t* nodes8,
     std::memset(&v, 0, sizeof v);
     v.verts = e->hs.verts.data(); v.norms = e->hs.norms.data(); v.tris = e->hs.tris.data();
     v.meshes = e->hs.meshes.data(); v.insts = e->insts.data(); v.mats = e->hs.mats.data(); v.lights = e->hs.lights.data();
+    if (!e->hs.texc.empty()) { v.texc = e->hs.texc.data(); v.atlas = e->hs.atlas.data(); v.atlas_w = e->hs.atlas_w; v.atlas_h = e->hs.atlas_h; }
     v.n_insts = d->n_instances; v.n_lights = d->n_lights;
     v.n_prims = n_prims; v.nodes = (const uint4*)nodes8; v.prims = (const float4*)prims8;
     const RtCamera& c = d->camera;
