@@ -1474,7 +1474,11 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
         static const int env_chunks = [] { const char* e = std::getenv("RT_HOST_CHUNKS"); return e ? std::atoi(e) : 0; }();
         // measured on B200 (world16 at 4K, 33 MB canvas): every extra chunk costs ~0.115 ms of kernel tails, the copy it
         // hides runs at ~57 GB/s; two chunks win from ~16 MiB of canvas per rank on
-        n_chunks = p.host_chunks > 0 ? p.host_chunks : env_chunks > 0 ? env_chunks : (4 * (size_t)out_pixels >= ((size_t)16 << 20) ? 2 : 1);
+        // (not with secondary rays: every chunk would pay the cooperative bounce-wave launch and its grid barriers again —
+        // world8_stress at 4K: 3.99 ms with two chunks against 2.87 + 0.58 without)
+        const bool bounces = sc->any_secondary && sc->env.depth > 0;
+        n_chunks = p.host_chunks > 0 ? p.host_chunks : env_chunks > 0 ? env_chunks
+                   : (!bounces && 4 * (size_t)out_pixels >= ((size_t)16 << 20) ? 2 : 1);
         n_chunks = std::max(1, std::min(std::min(n_chunks, (int)RtScene::kMaxChunks), units));
     }
     unsigned long long* ctr = sc->d_counters.as<unsigned long long>();

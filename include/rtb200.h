@@ -163,7 +163,7 @@ typedef struct RtRenderParams {
     int32_t tile_w, tile_h;
     /* Host canvas only: number of chunks of tile rows the frame is cut into so that chunk c is copied to the host while
      * chunk c + 1 renders (1..8; chunk sizes fall geometrically so that little is left to copy after the last one).
-     * 0 = automatic: 2 from 16 MiB of canvas per rank on, else 1. */
+     * 0 = automatic: 2 from 16 MiB of canvas per rank on when no material spawns secondary rays, else 1. */
     int32_t host_chunks;
 } RtRenderParams;
 
