@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--band-h", type=int, default=4,
                     help="N > 1, e2e: rows per full-width band dealt round-robin to the ranks (each rank copies its bands into the one shared host canvas)")
     ap.add_argument("--host-chunks", type=int, default=0, help="e2e: chunks per frame for copy/render overlap (0 = the library's default)")
+    ap.add_argument("--host-direct", action="store_true",
+                    help="e2e: let the kernels write the pinned host canvas over PCIe instead of rendering into a device canvas and copying it (measured slower)")
     ap.add_argument("--keep-bvh", action="store_true", help="do not rebuild the BVH every frame")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline leg")
@@ -302,14 +304,15 @@ def run_ours(a):
         if rank != 0:
             shared, shared_handle = pkg.host_canvas_open(W * H, shm_name=shm_name)
         dist.barrier()
-    e2e_flags = base | pkg.RT_RENDER_TILED_OUTPUT | pkg.RT_RENDER_HOST_BANDS
+    staged = pkg.RT_RENDER_HOST_DIRECT if a.host_direct else 0
+    e2e_flags = base | pkg.RT_RENDER_TILED_OUTPUT | pkg.RT_RENDER_HOST_BANDS | staged
 
     def frame_e2e():
         """The call a user of the reference makes per frame, with host buffers on both sides."""
         scene.set_instances(desc.instances, desc.n_instances)
         scene.set_camera(desc.camera)
         if world == 1:
-            _, st = scene.render(flags=base, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=host_canvas.data_ptr(),
+            _, st = scene.render(flags=base | staged, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=host_canvas.data_ptr(),
                                  host_chunks=a.host_chunks)
             return st
         _, st = scene.render(flags=e2e_flags, rank=rank, world=world, tile_w=band_w, tile_h=a.band_h,
@@ -442,10 +445,7 @@ def run_ours(a):
                                         "nccl": "NCCL all-gather of the tile slabs + de-interleave kernel", "none": "single GPU"}[gather]},
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / a.steps, "h2d_bytes_per_step": h2d * world,
                         "d2h_bytes_per_step": 4 * W * H,
-                        "path": ("rt_render into a pinned host canvas, frame cut into %d chunks of tile rows (copy of chunk c overlaps chunk c + 1)"
-                                 % outs_e2e[0]["host_chunks"]) if world == 1 else
-                                ("every rank renders full-width bands of %d rows and copies them into one shared pinned host canvas over its own "
-                                 "PCIe link (RT_RENDER_HOST_BANDS), %d chunks per rank" % (a.band_h, outs_e2e[0]["host_chunks"]))},
+                        "path": e2e_path(world, a, outs_e2e[0]["host_chunks"])},
                 "gpu_launches": launches_all, "clocks": clocks,
                 "breakdown_ms": {"build": avg("ms_build"), "trace": ms_trace, "k_primary": avg("ms_primary"),
                                  "shade": avg("ms_shade"), "k_shadow": avg("ms_shadow"), "bounce_waves": avg("ms_bounce"),
@@ -471,6 +471,14 @@ def run_ours(a):
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def e2e_path(world, a, chunks):
+    where = "a pinned host canvas" if world == 1 else \
+        "ONE pinned host canvas in shared memory (full-width bands of %d rows dealt to the ranks, RT_RENDER_HOST_BANDS)" % a.band_h
+    if chunks == 0:
+        return "rt_render: the kernels write their pixels straight into %s over PCIe while the frame renders; no device-side gather, no copy after the frame" % where
+    return "rt_render into a device canvas, copied into %s in %d chunk(s) of tile rows (copy of chunk c overlaps the rendering of c + 1)" % (where, chunks)
 
 
 def sst_prims(scene):

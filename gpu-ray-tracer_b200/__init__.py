@@ -28,6 +28,7 @@ RT_RENDER_TRACE_UNLIT = 128
 RT_RENDER_ASYNC = 256
 RT_RENDER_REFIT_BVH = 512
 RT_RENDER_HOST_BANDS = 1024
+RT_RENDER_HOST_DIRECT = 2048
 RT_HITABLE_TRIMESH, RT_HITABLE_SPHERE = 0, 1
 
 

@@ -99,6 +99,7 @@ struct RtScene {
     cudaEvent_t chunk_done[kMaxChunks] = {};  // no timing; copy_stream waits on these
     cudaEvent_t copies_done = nullptr;
     int pend_chunks = 1;
+    bool pend_direct = false;
     // pinned host memory, u64 units: [32,36) build result, [40,42) live counts of the bounce waves,
     // [64 + 32 c, 96 + 32 c) counters of chunk c
     unsigned long long* h_pinned = nullptr;

@@ -151,6 +151,10 @@ enum {
                                     tile_w >= width (full-width bands of tile_h rows dealt round-robin to the ranks), `canvas` is
                                     the full W x H row-major HOST canvas (e.g. pinned shared memory mapped by every rank) and
                                     the call copies only this rank's bands into it, each GPU over its own PCIe link */
+    RT_RENDER_HOST_DIRECT = 2048, /* host canvas in page-locked, device-addressable memory (rt_host_canvas_open, cudaHostAlloc,
+                                    cudaHostRegister): the kernels write it directly over PCIe while the frame renders instead
+                                    of rendering into a device canvas that is copied afterwards. Falls back to the staged copy
+                                    for pageable memory. Opt-in: slower than the staged, chunked copy on B200 */
     RT_RENDER_TRACE_UNLIT = 128  /* also trace shadow rays whose Phong weight is exactly zero (the reference does; the
                                     split pipeline skips them by default: they cannot change a pixel) */
 };
@@ -190,7 +194,7 @@ typedef struct RtFrameStats {
     uint64_t rays_culled;     /* shadow queries counted in rays_shadow / rays_total that were answered without a
                                  traversal (zero Phong weight, see RT_RENDER_TRACE_UNLIT) */
     int32_t host_chunks;      /* chunks the frame was cut into for the host copy (RtRenderParams.host_chunks); the per-kernel
-                                 times above are sums over the chunks */
+                                 times above are sums over the chunks. 0 = no copy: the kernels wrote the host canvas directly */
 } RtFrameStats;
 
 typedef struct RtBuildStats {

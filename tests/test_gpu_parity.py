@@ -361,3 +361,30 @@ def test_shared_host_canvas_between_processes(pkg, scenes):
         assert int(out.strip()) == int(full.astype(np.uint64).sum())
     finally:
         pkg.host_canvas_close(handle, unlink=True)
+
+
+def test_kernels_write_a_pinned_host_canvas_directly(pkg, scenes):
+    """RT_RENDER_HOST_DIRECT with a page-locked host canvas: no staging canvas and no copy (host_chunks == 0 in the
+    statistics), the kernels store the pixels over PCIe; same frame as the staged path and as the oracle. Pageable
+    memory falls back to the staged copy."""
+    w, s = scenes("world8_stress")
+    oc, ost = ob.OracleScene(w).render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    canvas, handle = pkg.host_canvas_open(w.width * w.height)
+    D = pkg.RT_RENDER_HOST_DIRECT
+    for flags, want_chunks in ((D, 0), (D | pkg.RT_RENDER_FUSED_SHADE, 0), (0, 1), (D | pkg.RT_RENDER_NO_BVH, 0)):
+        canvas[:] = 0xdeadbeef
+        _, st = s.render(flags=flags, out_ptr=canvas.ctypes.data)
+        assert st["host_chunks"] == want_chunks
+        if not flags & pkg.RT_RENDER_NO_BVH:
+            assert (canvas.reshape(w.height, w.width) == oc).all(), flags
+            assert st["rays_total"] == ost["rays_total"]
+    # bands of several ranks, written directly into the one canvas
+    canvas[:] = 0xdeadbeef
+    for r in range(3):
+        s.render(flags=D | pkg.RT_RENDER_TILED_OUTPUT | pkg.RT_RENDER_HOST_BANDS, rank=r, world=3, tile_w=w.width, tile_h=4,
+                 out_ptr=canvas.ctypes.data)
+    assert (canvas.reshape(w.height, w.width) == oc).all()
+    pkg.host_canvas_close(handle)
+    pageable = np.empty((w.height, w.width), np.uint32)
+    _, st = s.render(flags=D, out=pageable)
+    assert st["host_chunks"] == 1 and (pageable == oc).all()
