@@ -48,8 +48,10 @@ def parse_args():
     ap.add_argument("--grid-size", type=int, default=0)
     ap.add_argument("--tile-w", type=int, default=32)
     ap.add_argument("--tile-h", type=int, default=16)
-    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"],
-                    help="N > 1: tiles stored into every rank's canvas over NVLink peer memory (p2p) or all-gather + de-interleave (nccl)")
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "p2p-nccl", "nccl"],
+                    help="N > 1, device-resident frame: p2p = tiles stored into every rank's canvas over NVLink peer memory and a "
+                         "mailbox barrier over the same peer memory (no collective call); p2p-nccl = the same stores with a "
+                         "1-element NCCL all-reduce as barrier; nccl = all-gather of the slabs + de-interleave kernel")
     ap.add_argument("--band-h", type=int, default=4,
                     help="N > 1, e2e: rows per full-width band dealt round-robin to the ranks (each rank copies its bands into the one shared host canvas)")
     ap.add_argument("--host-chunks", type=int, default=0, help="e2e: chunks per frame for copy/render overlap (0 = the library's default)")
@@ -254,8 +256,9 @@ def run_ours(a):
     # CUDA IPC and rt_push_tiles stores the rank's tiles into all of them; a one-element all-reduce on
     # the same stream is the barrier that tells every rank its canvas is complete.
     peer_ptrs, own_canvas_ptr, token = None, None, None
+    epoch = [0]
     gather = a.gather if world > 1 else "none"
-    if gather == "p2p":
+    if gather in ("p2p", "p2p-nccl"):
         try:
             own_canvas_ptr, handle = pkg.peer_canvas_alloc(W * H)
             mine = torch.tensor(list(handle), dtype=torch.uint8, device="cuda")
@@ -281,6 +284,9 @@ def run_ours(a):
             return
         scene.render(flags=flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=slab_t.data_ptr())
         if gather == "p2p":
+            epoch[0] += 1
+            scene.push_tiles_signal(params_async, slab_t.data_ptr(), peer_ptrs, W * H, epoch[0])
+        elif gather == "p2p-nccl":
             scene.push_tiles(params_async, slab_t.data_ptr(), peer_ptrs)
             dist.all_reduce(token)
         else:
@@ -349,7 +355,7 @@ def run_ours(a):
             total_ms = float(t.item())
         return total_ms, out, clocks
 
-    if gather == "p2p":
+    if gather in ("p2p", "p2p-nccl"):
         # untimed check: the peer-memory exchange leaves the frame the all-gather path leaves
         frame_device()
         torch.cuda.current_stream().synchronize()
@@ -441,7 +447,8 @@ def run_ours(a):
                            "triangles": sst_prims(scene), "step": "BVH rebuild + trace" if not a.keep_bvh else "trace (BVH kept)",
                            "l2": "flushed between timed iterations (256 MiB write)",
                            "sharding": "screen tiles %dx%d round-robin over %d rank(s)" % (a.tile_w, a.tile_h, world),
-                           "exchange": {"p2p": "tiles stored into every rank's canvas over NVLink peer memory (rt_push_tiles) + 1-element all-reduce as barrier",
+                           "exchange": {"p2p": "tiles stored into every rank's canvas over NVLink peer memory, completion signalled through mailboxes in the same peer memory (rt_push_tiles_signal: no collective call on the frame's path)",
+                                        "p2p-nccl": "tiles stored into every rank's canvas over NVLink peer memory (rt_push_tiles) + 1-element all-reduce as barrier",
                                         "nccl": "NCCL all-gather of the tile slabs + de-interleave kernel", "none": "single GPU"}[gather]},
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / a.steps, "h2d_bytes_per_step": h2d * world,
                         "d2h_bytes_per_step": 4 * W * H,

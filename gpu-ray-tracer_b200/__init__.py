@@ -170,6 +170,7 @@ def cuda_lib():
         lib.rt_peer_canvas_open.argtypes = [vp, C.POINTER(vp)]
         lib.rt_peer_canvas_close.argtypes = [vp]
         lib.rt_push_tiles.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(vp), i32]
+        lib.rt_push_tiles_signal.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(vp), i32, C.c_int64, C.c_uint32]
         lib.rt_copy_to_host.argtypes = [vp, vp, vp, C.c_int64]
         lib.rt_host_canvas_open.argtypes = [C.c_char_p, C.c_int64, i32, C.POINTER(vp)]
         lib.rt_host_canvas_close.argtypes = [vp, C.c_int64, C.c_char_p, i32]
@@ -396,6 +397,12 @@ class Scene:
         """Stores this rank's tiles into every rank's row-major canvas (NVLink peer memory)."""
         arr = (C.c_void_p * len(peer_ptrs))(*peer_ptrs)
         _check(cuda_lib().rt_push_tiles(self._h, C.byref(params), slab_dev_ptr, arr, len(peer_ptrs)), "rt_push_tiles")
+
+    def push_tiles_signal(self, params, slab_dev_ptr, peer_ptrs, canvas_pixels, epoch):
+        """push_tiles + the exchange barrier over the canvases' mailboxes (no collective call)."""
+        arr = (C.c_void_p * len(peer_ptrs))(*peer_ptrs)
+        _check(cuda_lib().rt_push_tiles_signal(self._h, C.byref(params), slab_dev_ptr, arr, len(peer_ptrs), canvas_pixels, epoch),
+               "rt_push_tiles_signal")
 
     def copy_to_host(self, dev_ptr, out):
         _check(cuda_lib().rt_copy_to_host(self._h, dev_ptr, out.ctypes.data, out.size), "rt_copy_to_host")

@@ -16,6 +16,7 @@
 // -fmad=false), so the result is bit-identical to the sequential host build in oracle/lbvh_host.c
 // that tests/test_bvh_build.py compares it against.
 #include <cooperative_groups.h>
+#include <cstdlib>
 #include <cstring>
 
 #include "rt_bvh.cuh"
@@ -889,6 +890,10 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     int want = (n / 4 * 8 + kThreads - 1) / kThreads;  // 8 lanes per BVH8 node, about n/4 nodes on the widest level
     if (want < 1) want = 1;
     if (G > want) G = want;
+    {   // experiment knob: grid barriers get cheaper with fewer blocks, the per-level work slower
+        static const int env_blocks = [] { const char* e = std::getenv("RT_COLLAPSE_BLOCKS"); return e ? std::atoi(e) : 0; }();
+        if (env_blocks > 0 && env_blocks < G) G = env_blocks;
+    }
     size_t level_cap = (size_t)n + 8;
     size_t wbytes = sizeof(int) * (level_cap * 2 + level_cap * 8 + level_cap * 2 + (size_t)G * 4 + 16);
     static_assert(sizeof(int) == 4, "int");

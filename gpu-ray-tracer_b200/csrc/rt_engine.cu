@@ -770,10 +770,44 @@ __global__ void k_untile(TileMap tm, long long slab, const uint32_t* gathered, u
 // in the canvas, so a warp writes whole 128-byte segments. Replaces all-gather + k_untile.
 struct PeerCanvases { uint32_t* p[RT_MAX_PEERS]; int n; };
 
-__global__ void k_push_tiles(TileMap tm, const uint32_t* slab, PeerCanvases pc) {
+// Exchange barrier over peer memory (no collective library on the frame's data path). Behind the pixels of every
+// peer canvas sits a mailbox of RT_MAX_PEERS words; after its last tile store a rank writes the frame's epoch into
+// slot [rank] of every rank's mailbox, and k_wait_mailbox on the receiving side spins until all slots carry the epoch.
+struct PushSignal { long long mailbox_offset; unsigned epoch; unsigned* done_blocks; };
+
+__device__ __forceinline__ void push_signal_tail(const TileMap& tm, const PeerCanvases& pc, const PushSignal& sg) {
+    // every block: make its peer stores visible system-wide, then count itself; the last block signals
+    __shared__ bool s_last;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned prev = atomicAdd(sg.done_blocks, 1u);
+        s_last = prev + 1u == gridDim.x;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence_system();
+    if (threadIdx.x < pc.n) {
+        volatile unsigned* box = (volatile unsigned*)(pc.p[threadIdx.x] + sg.mailbox_offset);
+        box[tm.rank] = sg.epoch;
+    }
+    if (threadIdx.x == 0) *sg.done_blocks = 0u;  // ready for the next frame
+}
+
+__global__ void k_wait_mailbox(const uint32_t* own_canvas, long long mailbox_offset, int n, unsigned epoch, long long timeout_cycles) {
+    if ((int)threadIdx.x >= n) return;
+    volatile const unsigned* box = (volatile const unsigned*)(own_canvas + mailbox_offset);
+    long long t0 = clock64();
+    // epochs only grow; a peer that died would hang the GPU, so the wait gives up after timeout_cycles (the frame is then
+    // incomplete, which the caller's own checks see)
+    while ((int)(box[threadIdx.x] - epoch) < 0) {
+        if (clock64() - t0 > timeout_cycles) break;
+    }
+    __threadfence_system();
+}
+
+__device__ __forceinline__ void push_tile_quad(const TileMap& tm, const uint32_t* slab, const PeerCanvases& pc, long long q, long long n_quads) {
     const int quads_per_row = tm.tile_w >> 2;
-    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    long long n_quads = (long long)tm.n_owned * tm.tile_h * quads_per_row;
     if (q >= n_quads) return;
     int lq = (int)(q % quads_per_row);
     long long row = q / quads_per_row;
@@ -795,6 +829,14 @@ __global__ void k_push_tiles(TileMap tm, const uint32_t* slab, PeerCanvases pc) 
     }
 }
 
+template <bool SIGNAL>
+__global__ void k_push_tiles(TileMap tm, const uint32_t* slab, PeerCanvases pc, PushSignal sg) {
+    const int quads_per_row = tm.tile_w >> 2;
+    long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long n_quads = (long long)tm.n_owned * tm.tile_h * quads_per_row;
+    push_tile_quad(tm, slab, pc, q, n_quads);
+    if (SIGNAL) push_signal_tail(tm, pc, sg);
+}
 // Resident-working-set read bandwidth (the L2 roofline denominator).
 __global__ void k_l2_read(const uint4* buf, long long n16, int iters, unsigned* sink) {
     unsigned acc = 0;
@@ -1017,7 +1059,7 @@ int rt_scene_destroy(RtScene* sc) {
     if (!sc) return RT_OK;
     if (sc->stream) cudaStreamSynchronize(sc->stream);
     rth::DevBuf* all[] = {&sc->d_verts, &sc->d_norms, &sc->d_tris, &sc->d_meshes, &sc->d_insts, &sc->d_mats, &sc->d_lights,
-                          &sc->d_mesh_box, &sc->d_texc, &sc->d_atlas, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
+                          &sc->d_mesh_box, &sc->d_texc, &sc->d_atlas, &sc->d_push_ctr, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
                           &sc->d_queue_b, &sc->d_ids, &sc->d_shadowq, &sc->d_occl, &sc->d_shq_count};
     for (rth::DevBuf* b : all) b->release();
     sc->bvh.release();
@@ -1327,25 +1369,52 @@ int rt_untile(RtScene* sc, const RtRenderParams* p, const uint32_t* gathered, ui
     return RT_OK;
 }
 
-int rt_push_tiles(RtScene* sc, const RtRenderParams* p, const uint32_t* slab, uint32_t* const* peer_canvases, int32_t n_peers) {
+static int push_tiles_impl(RtScene* sc, const RtRenderParams* p, const uint32_t* slab, uint32_t* const* peer_canvases, int32_t n_peers,
+                           int64_t canvas_pixels, uint32_t epoch, bool signal) {
     if (!sc || !slab || !peer_canvases || n_peers < 1 || n_peers > RT_MAX_PEERS) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
     TileMap tm;
     if (int rc = make_tilemap(sc, p, tm)) return rc;
     if (tm.tile_w % 4) { set_error("tile_w must be a multiple of 4"); return RT_ERR_INVALID_ARG; }
+    if (signal && (n_peers != tm.world || canvas_pixels < (int64_t)tm.W * tm.H)) {
+        set_error("signalled push needs one canvas per rank and the canvas size the mailbox sits behind");
+        return RT_ERR_INVALID_ARG;
+    }
     PeerCanvases pc;
     pc.n = n_peers;
     for (int r = 0; r < n_peers; r++) {
         if (!peer_canvases[r]) { set_error("null peer canvas"); return RT_ERR_INVALID_ARG; }
         pc.p[r] = peer_canvases[r];
     }
+    PushSignal sg;
+    sg.mailbox_offset = canvas_pixels; sg.epoch = epoch; sg.done_blocks = nullptr;
     long long n_quads = (long long)tm.n_owned * tm.tile_h * (tm.tile_w / 4);
-    if (n_quads > 0) {
-        k_push_tiles<<<(unsigned)((n_quads + kThreads - 1) / kThreads), kThreads, 0, sc->stream>>>(tm, slab, pc);
+    if (signal) {
+        if (!sc->d_push_ctr.p) {
+            if (sc->d_push_ctr.reserve(16)) return RT_ERR_OUT_OF_MEMORY;
+            RT_CUDA(cudaMemsetAsync(sc->d_push_ctr.p, 0, 16, sc->stream));
+        }
+        sg.done_blocks = sc->d_push_ctr.as<unsigned>();
+        // a rank that owns no tile still has to signal: one block, no quads
+        unsigned grid = (unsigned)std::max<long long>((n_quads + kThreads - 1) / kThreads, 1);
+        k_push_tiles<true><<<grid, kThreads, 0, sc->stream>>>(tm, slab, pc, sg);
+        k_wait_mailbox<<<1, 32, 0, sc->stream>>>(peer_canvases[tm.rank], canvas_pixels, n_peers, epoch, 4000000000LL);
+        sc->kernel_launches += 2;
+    } else if (n_quads > 0) {
+        k_push_tiles<false><<<(unsigned)((n_quads + kThreads - 1) / kThreads), kThreads, 0, sc->stream>>>(tm, slab, pc, sg);
         sc->kernel_launches++;
     }
     RT_CUDA(cudaGetLastError());
     if (!(p && (p->flags & RT_RENDER_ASYNC))) RT_CUDA(cudaStreamSynchronize(sc->stream));
     return RT_OK;
+}
+
+int rt_push_tiles(RtScene* sc, const RtRenderParams* p, const uint32_t* slab, uint32_t* const* peer_canvases, int32_t n_peers) {
+    return push_tiles_impl(sc, p, slab, peer_canvases, n_peers, 0, 0, false);
+}
+
+int rt_push_tiles_signal(RtScene* sc, const RtRenderParams* p, const uint32_t* slab, uint32_t* const* peer_canvases, int32_t n_peers,
+                         int64_t canvas_pixels, uint32_t epoch) {
+    return push_tiles_impl(sc, p, slab, peer_canvases, n_peers, canvas_pixels, epoch, true);
 }
 
 // Canvas memory other processes can map: plain cudaMalloc (torch's caching allocator hands out
@@ -1354,8 +1423,9 @@ int rt_peer_canvas_alloc(int64_t pixels, uint32_t** dev_ptr, unsigned char handl
     if (pixels <= 0 || !dev_ptr || !handle) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
     void* p = nullptr;
-    RT_CUDA(cudaMalloc(&p, 4 * (size_t)pixels));
-    RT_CUDA(cudaMemset(p, 0, 4 * (size_t)pixels));
+    const size_t bytes = 4 * ((size_t)pixels + RT_MAX_PEERS);  // + the mailbox of rt_push_tiles_signal
+    RT_CUDA(cudaMalloc(&p, bytes));
+    RT_CUDA(cudaMemset(p, 0, bytes));
     cudaIpcMemHandle_t h;
     cudaError_t e = cudaIpcGetMemHandle(&h, p);
     if (e != cudaSuccess) { cudaFree(p); return rth::cuda_fail(e, "cudaIpcGetMemHandle", __FILE__, __LINE__); }

@@ -81,6 +81,7 @@ struct RtScene {
     bool textured = false;
     rth::DevBuf d_canvas, d_counters, d_hitq, d_paths, d_queue_a, d_queue_b, d_ids;
     rth::DevBuf d_shadowq, d_occl, d_shq_count;
+    rth::DevBuf d_push_ctr;         // block counter of the signalled tile push
     bool fused_shade = false;       // RT_RENDER_FUSED_SHADE: one k_shade kernel instead of gen / traverse / resolve
     bool split_shade_used = false;
     rth::Bvh bvh;

@@ -279,6 +279,14 @@ int rt_peer_canvas_open(const unsigned char ipc_handle[64], uint32_t** dev_ptr);
 int rt_peer_canvas_close(uint32_t* dev_ptr);
 int rt_push_tiles(RtScene* scene, const RtRenderParams* params, const uint32_t* slab_dev, uint32_t* const* peer_canvases,
                   int32_t n_peers);
+/* rt_push_tiles followed by the exchange barrier, both over peer memory (no collective call on the frame's path):
+ * every canvas from rt_peer_canvas_alloc carries a mailbox of RT_MAX_PEERS words behind its `canvas_pixels` pixels.
+ * After its last tile store the rank writes `epoch` (grow it by one per frame, start at 1) into its slot of every
+ * rank's mailbox; a second kernel on the same stream then waits until all `n_peers` slots of the rank's OWN mailbox
+ * carry the epoch, i.e. until every rank's tiles have landed in this rank's canvas. peer_canvases[rank] must be the
+ * rank's own canvas and n_peers == world. The consumers of frame i must be done before any rank pushes frame i + 1. */
+int rt_push_tiles_signal(RtScene* scene, const RtRenderParams* params, const uint32_t* slab_dev, uint32_t* const* peer_canvases,
+                         int32_t n_peers, int64_t canvas_pixels, uint32_t epoch);
 /* Blocking device-to-host copy of `pixels` uint32 on the scene's stream. */
 int rt_copy_to_host(RtScene* scene, const uint32_t* dev_ptr, uint32_t* host_ptr, int64_t pixels);
 /* The host canvas of RT_RENDER_HOST_BANDS: page-locked memory every rank of a box can map. The reference keeps its

@@ -388,3 +388,28 @@ def test_kernels_write_a_pinned_host_canvas_directly(pkg, scenes):
     pageable = np.empty((w.height, w.width), np.uint32)
     _, st = s.render(flags=D, out=pageable)
     assert st["host_chunks"] == 1 and (pageable == oc).all()
+
+
+def test_signalled_tile_push(pkg, scenes):
+    """rt_push_tiles_signal on one rank: tiles land in the peer canvas, the rank's mailbox slot carries the epoch and
+    the wait kernel returns (a missing signal would run into its timeout and leave the epoch unset)."""
+    import time
+    import torch
+    w, s = scenes("world4")
+    full, _ = s.render()
+    n = w.width * w.height
+    ptr, _handle = pkg.peer_canvas_alloc(n)
+    flags = pkg.RT_RENDER_TILED_OUTPUT | pkg.RT_RENDER_CANVAS_DEVICE
+    p = s.params(flags=flags, world=1, tile_w=32, tile_h=16)
+    slab = torch.zeros(s.tiled_slab_pixels(p), dtype=torch.int32, device="cuda")
+    s.render(flags=flags, tile_w=32, tile_h=16, out_ptr=slab.data_ptr())
+    t0 = time.time()
+    for epoch in (1, 2, 3):
+        s.push_tiles_signal(p, slab.data_ptr(), [ptr], n, epoch)
+    assert time.time() - t0 < 1.0
+    got = s.copy_to_host(ptr, np.empty(n + 16, np.uint32))
+    assert (got[:n].reshape(w.height, w.width) == full).all()
+    assert got[n] == 3 and (got[n + 1:] == 0).all()
+    with pytest.raises(RuntimeError):
+        s.push_tiles_signal(p, slab.data_ptr(), [ptr, ptr], n, 4)  # one canvas per rank
+    pkg.peer_canvas_free(ptr)
