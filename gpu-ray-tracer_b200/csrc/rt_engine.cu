@@ -212,7 +212,7 @@ template <> struct TracerOf<TR_BRUTE_BOX> {
 // IDS == true: parity hook (rt_trace_primary) — writes (instance, triangle-in-mesh, t) per pixel.
 template <int MODE, bool STATS, bool IDS>
 __global__ void __launch_bounds__(kThreads) k_primary(SceneView s, TileMap tm, unsigned long long* ctr, HitRec* hitq,
-                                                     uint32_t* canvas, int* id_inst, int* id_tri, float* id_t) {
+                                                     uint32_t* canvas, int* id_inst, int* id_tri, float* id_t, int aligned) {
     TravStats ts = {0, 0, 0};
     RayCounts rc = {0, 0, 0};
     typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
@@ -243,17 +243,22 @@ __global__ void __launch_bounds__(kThreads) k_primary(SceneView s, TileMap tm, u
             continue;
         }
         if (valid && !hit) canvas[out] = 0u;  // pack_color(0,0,0,0)
-        // warp-aggregated append of the hits
+        // Warp-aggregated append of the hits. ctr[C_HITQ]: low word = queue slots, high word = hits.
+        // aligned: a tile with any hit takes 32 slots, lane l writes slot base + l (inst = -1 for its misses), so that
+        // every warp of the shading kernels works on the 8x4 pixels of ONE tile. Packed (popc(m) slots per tile), a
+        // warp of k_shadow held the hits of two or three tiles from unrelated parts of the screen — whichever warps
+        // of k_primary appended one after the other — and walked the union of their traversals.
         unsigned m = __ballot_sync(0xffffffffu, hit);
         if (m) {
             unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(&ctr[C_HITQ], (unsigned long long)__popc(m));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (hit) {
+            const unsigned long long slots = aligned ? 32ull : (unsigned long long)__popc(m);
+            if (lane == 0) base = atomicAdd(&ctr[C_HITQ], slots | ((unsigned long long)__popc(m) << 32));
+            base = __shfl_sync(0xffffffffu, base, 0) & 0xffffffffull;
+            if (hit || aligned) {
                 HitRec rec;
-                rec.out_index = out; rec.xy = x | (y << 16); rec.inst = h.inst; rec.tri = h.tri;
+                rec.out_index = out; rec.xy = x | (y << 16); rec.inst = hit ? h.inst : -1; rec.tri = h.tri;
                 rec.t = h.t; rec.u = h.u; rec.v = h.v; rec.t_local = h.t_local;
-                hitq[base + __popc(m & ((1u << lane) - 1u))] = rec;
+                hitq[base + (aligned ? (unsigned)lane : (unsigned)__popc(m & ((1u << lane) - 1u)))] = rec;
             }
         }
     }
@@ -270,6 +275,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
     const int n = (int)ctr[C_HITQ];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         HitRec rec = hitq[i];
+        if (rec.inst < 0) continue;  // a missed pixel inside a tile-aligned group
         Hit h;
         h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
         rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
@@ -342,14 +348,19 @@ __device__ __forceinline__ void phase_shadow_gen(const SceneView& s, const int n
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         HitRec rec = hitq[i];
         rtx::Ray r;
-        bool hit = true;
+        const bool hit = rec.inst >= 0;  // wave 0: a missed pixel inside a tile-aligned group; waves: a path ray that missed
         if (PATHS) {
-            hit = rec.inst >= 0;
             PathHead* head;
             Frame* frames = path_frames(paths, path_stride, rec.out_index, &head);
             if (hit) r = frames[head->stack_top].ray;
-        } else {
+        } else if (hit) {
             r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
+        } else {
+            // wave 0 queues are slot-indexed: k_shadow must find a hole, not stale data
+            ShadowRec hole;
+            hole.o_maxt = make_float4(0.f, 0.f, 0.f, -1.f);
+            hole.d = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int l = 0; l < s.n_lights; l++) shq[(size_t)l * n + i] = hole;
         }
         float3 hit_pos = hit ? rtx::ray_at(r, rec.t) : rtx::mk3(0.f, 0.f, 0.f);
         float3 nrm = rtx::mk3(0.f, 0.f, 0.f);
@@ -405,7 +416,7 @@ __global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned l
                                                         unsigned char* occl, float4* att4, unsigned char* paths,
                                                         int path_stride) {
     unsigned culled = 0;
-    phase_shadow_gen<PATHS>(s, (int)ctr[ctr_n], hitq, shq, shq_count, occl, att4, paths, path_stride, culled);
+    phase_shadow_gen<PATHS>(s, (int)(unsigned)ctr[ctr_n], hitq, shq, shq_count, occl, att4, paths, path_stride, culled);
     flush_culled(s, ctr, culled);
 }
 
@@ -444,7 +455,7 @@ __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(Scene
     TravStats ts = {0, 0, 0};
     RayCounts rc = {0, 0, 0};
     typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
-    phase_shadow<LOOP>(s, tr, rc, (long long)ctr[ctr_n], shq, shq_count, occl, att4);
+    phase_shadow<LOOP>(s, tr, rc, (long long)(unsigned)ctr[ctr_n], shq, shq_count, occl, att4);
     flush_counts(ctr, rc, ts, STATS);
 }
 
@@ -469,6 +480,7 @@ __global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_resolve(Sce
     const int n = (int)ctr[C_HITQ];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         HitRec rec = hitq[i];
+        if (rec.inst < 0) continue;  // a missed pixel inside a tile-aligned group (k_primary wrote its black)
         Hit h;
         h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
         rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
@@ -1143,7 +1155,8 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     long long n_pix = (long long)tm.n_work() * 32;
     if (sc->d_hitq.reserve(sizeof(HitRec) * (size_t)std::max<long long>(n_pix, 1))) return RT_ERR_OUT_OF_MEMORY;
     int g0 = persistent_grid(k_primary<MODE, STATS, false>, sc->sm_count);
-    k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr);
+    static const int aligned_hitq = [] { const char* e = std::getenv("RT_PACKED_HITQ"); return (e && std::atoi(e)) ? 0 : 1; }();
+    k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr, aligned_hitq);
     sc->kernel_launches++;
     RT_CUDA(cudaEventRecord(cev[1], st));
     *waves = 1;
@@ -1159,7 +1172,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         if (hit_cap * (size_t)path_stride > ((size_t)4 << 30)) {
             RT_CUDA(cudaMemcpyAsync(&n_hits, ctr + C_HITQ, 8, cudaMemcpyDeviceToHost, st));
             RT_CUDA(cudaStreamSynchronize(st));
-            hit_cap = (size_t)std::max<unsigned long long>(n_hits, 1);
+            hit_cap = (size_t)std::max<unsigned long long>(n_hits & 0xffffffffull, 1);  // queue slots (>= hits)
         }
         if (sc->d_paths.reserve(hit_cap * path_stride) || sc->d_queue_a.reserve(4 * hit_cap) || sc->d_queue_b.reserve(4 * hit_cap))
             return RT_ERR_OUT_OF_MEMORY;
@@ -1674,7 +1687,7 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
             if (sc->split_shade_used) { RT_CUDA(cudaEventElapsedTime(&ms, sc->cev[c][2], sc->cev[c][3])); fs.ms_shadow += ms; }
             RT_CUDA(cudaEventElapsedTime(&ms, sc->cev[c][4], sc->cev[c][5])); fs.ms_bounce += ms;
         }
-        fs.n_hits = (int32_t)host_ctr[C_HITQ];
+        fs.n_hits = (int32_t)(host_ctr[C_HITQ] >> 32);  // high word = hits, low word = queue slots
     }
     for (int k = 0; k < 4; k++) fs.ms_wave_phase[k] = (float)host_ctr[C_PHASE_NS + k] * 1e-6f;
     fs.waves = waves >= 0 ? waves : 1 + (int)host_ctr[C_WAVES];
@@ -1723,10 +1736,10 @@ int rt_trace_primary(RtScene* sc, int32_t use_bvh, int32_t* instance, int32_t* t
     SceneView v = rth::make_view(sc, true);
     int g = sc->sm_count * 4;
     switch (mode) {
-        case TR_BVH_BOX: k_primary<TR_BVH_BOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt); break;
-        case TR_BVH_NOBOX: k_primary<TR_BVH_NOBOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt); break;
-        case TR_BRUTE: k_primary<TR_BRUTE, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt); break;
-        default: k_primary<TR_BRUTE_BOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt); break;
+        case TR_BVH_BOX: k_primary<TR_BVH_BOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0); break;
+        case TR_BVH_NOBOX: k_primary<TR_BVH_NOBOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0); break;
+        case TR_BRUTE: k_primary<TR_BRUTE, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0); break;
+        default: k_primary<TR_BRUTE_BOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0); break;
     }
     sc->kernel_launches++;
     RT_CUDA(cudaGetLastError());
