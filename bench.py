@@ -427,8 +427,15 @@ def run_ours(a):
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
         l2_bytes = 80.0 * sst["nodes_visited"] + 48.0 * sst["prims_prefiltered"]
         ms_trace = avg("ms_trace")
+        traffic, traffic_src = None, None
+        try:  # dram__bytes_read.sum + dram__bytes_write.sum of that kernel, one launch, from the committed ncu capture
+            cap = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")))
+            if cap["workload"] == workload_name(a) and world == 1:
+                traffic, traffic_src = cap["kernels"][dom]["traffic"], cap["source"]
+        except Exception:
+            pass
         roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": dom_ms,
                     "note": "scene + BVH8 (< 2 MB) are L1/L2-resident; the kernel is issue/latency-bound, not HBM-bound",
                     "l2": {"bytes_per_frame": l2_bytes, "achieved": l2_bytes / (ms_trace * 1e-3) / 1e9,

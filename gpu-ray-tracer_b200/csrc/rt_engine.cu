@@ -422,15 +422,31 @@ __global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned l
 
 // LOOP == false: occl[j] = 1 when anything blocks the ray within max_t (any-hit).
 // LOOP == true : att4[j] = Light::attenuate's result (closest-hit walk through refractive occluders).
+// work: null = static assignment (entry f to thread f mod T, or sparse lanes for small waves); otherwise a counter
+// from which every warp pulls the next 32 entries — shadow rays cost between one node test and a full traversal, and
+// with a static split the warps that drew cheap rays left a quarter of k_shadow's warp slots idle (ncu: achieved
+// occupancy 29 % of a theoretical 37.5 %).
 template <bool LOOP, class Tracer>
 __device__ __forceinline__ void phase_shadow(const SceneView& s, const Tracer& tr, RayCounts& rc, const long long n_hits,
                                              const ShadowRec* shq, const unsigned* shq_count, unsigned char* occl,
-                                             float4* att4) {
+                                             float4* att4, unsigned long long* work = nullptr) {
     long long total = 0;
     for (int l = 0; l < s.n_lights; l++) total += shq_count[l];
-    long long f0, fstep;
-    if (!sparse_lanes(total, f0, fstep)) return;
-    for (long long f = f0; f < total; f += fstep) {
+    long long f0 = 0, fstep = 0;
+    const bool dynamic = work != nullptr && total >= (long long)gridDim.x * blockDim.x;
+    if (!dynamic && !sparse_lanes(total, f0, fstep)) return;
+    const int lane = threadIdx.x & 31;
+    for (long long f = f0;; f += fstep) {
+        if (dynamic) {
+            unsigned long long b = 0;
+            if (lane == 0) b = atomicAdd(work, 32ull);
+            b = __shfl_sync(0xffffffffu, b, 0);
+            if ((long long)b >= total) break;
+            f = (long long)b + lane;
+            if (f >= total) continue;
+        } else if (f >= total) {
+            break;
+        }
         int l = 0;
         long long k = f;
         for (unsigned c; k >= (long long)(c = shq_count[l]); l++) k -= c;  // light whose queue holds entry f
@@ -451,11 +467,12 @@ __device__ __forceinline__ void phase_shadow(const SceneView& s, const Tracer& t
 
 template <int MODE, bool STATS, bool LOOP>
 __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(SceneView s, unsigned long long* ctr, int ctr_n, const ShadowRec* shq,
-                                                       const unsigned* shq_count, unsigned char* occl, float4* att4) {
+                                                       const unsigned* shq_count, unsigned char* occl, float4* att4,
+                                                       unsigned long long* work) {
     TravStats ts = {0, 0, 0};
     RayCounts rc = {0, 0, 0};
     typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
-    phase_shadow<LOOP>(s, tr, rc, (long long)(unsigned)ctr[ctr_n], shq, shq_count, occl, att4);
+    phase_shadow<LOOP>(s, tr, rc, (long long)(unsigned)ctr[ctr_n], shq, shq_count, occl, att4, work);
     flush_counts(ctr, rc, ts, STATS);
 }
 
@@ -1191,10 +1208,12 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     unsigned* shq_count = sc->d_shq_count.as<unsigned>();
     // one any-hit / closest-loop traversal of the shadow rays queued in shq
     auto trace_shadows = [&](int ctr_n) {
+        static const int static_split = [] { const char* e = std::getenv("RT_SHADOW_STATIC"); return (e && std::atoi(e)) ? 1 : 0; }();
+        unsigned long long* work = static_split ? nullptr : ctr + C_WORK1;  // zeroed with the frame's counters
         if (loop) k_shadow<MODE, STATS, true><<<persistent_grid(k_shadow<MODE, STATS, true>, sc->sm_count), kThreads, 0, st>>>(
-            v, ctr, ctr_n, shq, shq_count, occl, att4);
+            v, ctr, ctr_n, shq, shq_count, occl, att4, work);
         else k_shadow<MODE, STATS, false><<<persistent_grid(k_shadow<MODE, STATS, false>, sc->sm_count), kThreads, 0, st>>>(
-            v, ctr, ctr_n, shq, shq_count, occl, att4);
+            v, ctr, ctr_n, shq, shq_count, occl, att4, work);
         sc->kernel_launches++;
     };
     HitRec* hitq = sc->d_hitq.as<HitRec>();
