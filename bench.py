@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--host-chunks", type=int, default=0, help="e2e: chunks per frame for copy/render overlap (0 = the library's default)")
     ap.add_argument("--host-direct", action="store_true",
                     help="e2e: let the kernels write the pinned host canvas over PCIe instead of rendering into a device canvas and copying it (measured slower)")
+    ap.add_argument("--sort-rays", action="store_true", help="RT_RENDER_SORT_RAYS: sort the live paths between bounce waves")
     ap.add_argument("--keep-bvh", action="store_true", help="do not rebuild the BVH every frame")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline leg")
@@ -233,7 +234,7 @@ def run_ours(a):
                       grid_size=a.grid_size)
     scene = pkg.Scene(wfile, device=local_rank)
     W, H = wfile.width, wfile.height
-    base = 0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH
+    base = (0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH) | (pkg.RT_RENDER_SORT_RAYS if a.sort_rays else 0)
     dev_flags = base | pkg.RT_RENDER_CANVAS_DEVICE | (pkg.RT_RENDER_TILED_OUTPUT if world > 1 else 0)
     params = scene.params(flags=dev_flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h)
     canvas_dev = torch.zeros(H * W, dtype=torch.int32, device="cuda")

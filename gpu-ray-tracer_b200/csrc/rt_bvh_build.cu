@@ -794,6 +794,32 @@ namespace rth {
 
 static inline int grid_for(int n, int per = kThreads) { return n > 0 ? (n + per - 1) / per : 1; }
 
+// Stable LSD radix sort of (key, value) pairs, 8 bits per pass over the low 8 * n_passes key bits, ping-ponging
+// between the a and b buffers (swapped in place: after the call `keys_a` / `vals_a` point at the sorted data).
+// hist: kBins * (tiles + 1) counters. Returns the number of kernels launched.
+size_t radix_hist_bytes(int n) { return sizeof(unsigned) * kBins * ((size_t)((n + kRadixTile - 1) / kRadixTile) + 1); }
+int radix_sort_pairs(cudaStream_t st, unsigned long long*& keys_a, unsigned long long*& keys_b, int*& vals_a, int*& vals_b,
+                     unsigned* hist, int n, int n_passes) {
+    const int nb = (n + kRadixTile - 1) / kRadixTile;
+    const bool fused_scan = nb <= 64;
+    int launches = 0;
+    for (int pass = 0; pass < n_passes; pass++) {
+        int shift = pass * 8;
+        k_radix_hist<<<nb, kThreads, 0, st>>>(keys_a, n, shift, hist, nb);
+        if (fused_scan) {
+            k_radix_scatter<true><<<nb, kThreads, 0, st>>>(keys_a, vals_a, n, shift, hist, nb, keys_b, vals_b);
+            launches += 2;
+        } else {
+            k_radix_scan<<<kBins, kThreads, 0, st>>>(hist, nb);
+            k_radix_scatter<false><<<nb, kThreads, 0, st>>>(keys_a, vals_a, n, shift, hist, nb, keys_b, vals_b);
+            launches += 3;
+        }
+        std::swap(keys_a, keys_b);
+        std::swap(vals_a, vals_b);
+    }
+    return launches;
+}
+
 int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     Bvh& b = sc->bvh;
     b.valid = false;
@@ -856,21 +882,7 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     unsigned long long* kout = b.keys_b.as<unsigned long long>();
     int* vin = b.vals_a.as<int>();
     int* vout = b.vals_b.as<int>();
-    const bool fused_scan = nb <= 64;
-    for (int pass = 0; pass < n_passes; pass++) {
-        int shift = pass * 8;
-        k_radix_hist<<<nb, kThreads, 0, st>>>(kin, n, shift, b.hist.as<unsigned>(), nb);
-        if (fused_scan) {
-            k_radix_scatter<true><<<nb, kThreads, 0, st>>>(kin, vin, n, shift, b.hist.as<unsigned>(), nb, kout, vout);
-            sc->kernel_launches += 2;
-        } else {
-            k_radix_scan<<<kBins, kThreads, 0, st>>>(b.hist.as<unsigned>(), nb);
-            k_radix_scatter<false><<<nb, kThreads, 0, st>>>(kin, vin, n, shift, b.hist.as<unsigned>(), nb, kout, vout);
-            sc->kernel_launches += 3;
-        }
-        std::swap(kin, kout);
-        std::swap(vin, vout);
-    }
+    sc->kernel_launches += radix_sort_pairs(st, kin, kout, vin, vout, b.hist.as<unsigned>(), n, n_passes);
     b.sorted_keys = kin;  // even number of passes: back in keys_a / vals_a
     b.sorted_vals = vin;
     if (n > 1) {

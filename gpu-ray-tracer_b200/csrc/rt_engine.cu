@@ -670,6 +670,53 @@ __global__ void __launch_bounds__(kThreads, RT_WAVES_MIN_BLOCKS) k_bounce_waves(
     flush_culled(s, a.ctr, culled);
 }
 
+// ---------------------------------------------------------------- waves >= 1 with ray sorting (RT_RENDER_SORT_RAYS)
+// One launch per phase and wave, and between the waves the live queue is sorted by a coherence key: 21-bit Morton code
+// of the pending ray's origin inside the scene bounds (7 bits per axis), then the direction octant (24 bits, three radix
+// passes). Neighbouring lanes then trace rays that start in the same cell and head the same way. The order of the queue
+// does not enter any result (whit / occl are indexed by queue position within a wave).
+__device__ __forceinline__ unsigned spread7(unsigned v) {  // 7 bits -> every third bit
+    v &= 0x7fu;
+    v = (v | (v << 8)) & 0x0000700fu;
+    v = (v | (v << 4)) & 0x000430c3u;
+    v = (v | (v << 2)) & 0x00049249u;
+    return v;
+}
+__global__ void k_path_keys(const int* __restrict__ queue, int n, const unsigned char* paths, int path_stride,
+                            const float* __restrict__ bounds6, unsigned long long* __restrict__ keys, int* __restrict__ vals) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int slot = queue[i];
+    PathHead* head;
+    Frame* frames = path_frames((unsigned char*)paths, path_stride, slot, &head);
+    rtx::Ray r = frames[head->stack_top].ray;
+    float o[3] = {r.o.x, r.o.y, r.o.z}, d[3] = {r.d.x, r.d.y, r.d.z};
+    unsigned q[3], oct = 0;
+    for (int k = 0; k < 3; k++) {
+        float ext = bounds6[3 + k] - bounds6[k];
+        float t = ext > 0.0f ? (o[k] - bounds6[k]) / ext : 0.0f;
+        q[k] = (unsigned)fminf(fmaxf(t * 128.0f, 0.0f), 127.0f);
+        oct |= (d[k] < 0.0f ? 1u : 0u) << k;
+    }
+    unsigned morton = (spread7(q[0]) << 2) | (spread7(q[1]) << 1) | spread7(q[2]);
+    keys[i] = ((unsigned long long)morton << 3) | oct;
+    vals[i] = slot;
+}
+template <int MODE, bool STATS>
+__global__ void __launch_bounds__(kThreads, RT_WAVES_MIN_BLOCKS) k_wave_trace(SceneView s, unsigned long long* ctr, int ctr_in, const int* queue_in,
+                                                         unsigned char* paths, int path_stride, HitRec* whit) {
+    TravStats ts = {0, 0, 0};
+    RayCounts rc = {0, 0, 0};
+    typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
+    phase_path_trace(s, tr, rc, (int)ctr[ctr_in], queue_in, paths, path_stride, whit);
+    flush_counts(ctr, rc, ts, STATS);
+}
+__global__ void __launch_bounds__(kThreads, RT_WAVES_MIN_BLOCKS) k_wave_advance(SceneView s, unsigned long long* ctr, int ctr_in, int ctr_out,
+                                                           const HitRec* whit, const unsigned char* occl, const float4* att4,
+                                                           int* queue_out, uint32_t* canvas, unsigned char* paths, int path_stride) {
+    phase_path_advance(s, (int)ctr[ctr_in], &ctr[ctr_out], whit, occl, att4, queue_out, canvas, paths, path_stride);
+}
+
 // ---------------------------------------------------------------- waves >= 1, fused variant (RT_RENDER_FUSED_SHADE)
 template <int MODE, bool STATS>
 __global__ void __launch_bounds__(kThreads) k_bounce(SceneView s, unsigned long long* ctr, int ctr_in, int ctr_out,
@@ -1088,7 +1135,8 @@ int rt_scene_destroy(RtScene* sc) {
     if (!sc) return RT_OK;
     if (sc->stream) cudaStreamSynchronize(sc->stream);
     rth::DevBuf* all[] = {&sc->d_verts, &sc->d_norms, &sc->d_tris, &sc->d_meshes, &sc->d_insts, &sc->d_mats, &sc->d_lights,
-                          &sc->d_mesh_box, &sc->d_texc, &sc->d_atlas, &sc->d_push_ctr, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
+                          &sc->d_mesh_box, &sc->d_texc, &sc->d_atlas, &sc->d_push_ctr, &sc->d_sort_keys_a, &sc->d_sort_keys_b,
+                          &sc->d_sort_vals_b, &sc->d_sort_hist, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
                           &sc->d_queue_b, &sc->d_ids, &sc->d_shadowq, &sc->d_occl, &sc->d_shq_count};
     for (rth::DevBuf* b : all) b->release();
     sc->bvh.release();
@@ -1254,6 +1302,46 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
                 k_bounce<MODE, STATS><<<persistent_grid(k_bounce<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, outc, qin, qout, canvas, paths, path_stride);
                 sc->kernel_launches++;
+                (*waves)++;
+                std::swap(in, outc);
+                std::swap(qin, qout);
+                if (*waves > 4096) { set_error("bounce waves did not terminate"); return RT_ERR_LIMIT; }
+            }
+        } else if (sc->sort_rays) {
+            // RT_RENDER_SORT_RAYS: one launch per phase and wave, the live queue sorted by origin cell + direction octant
+            // before each trace phase (one 8-byte read-back per wave tells the host how many paths are alive)
+            if (!sc->bvh.scene_bounds.p) { set_error("no scene bounds to sort rays by"); return RT_ERR_NO_BVH; }
+            const float* bounds6 = (const float*)((const char*)sc->bvh.scene_bounds.p + 32);
+            for (;;) {
+                unsigned long long live = 0;
+                RT_CUDA(cudaMemcpyAsync(&live, ctr + in, 8, cudaMemcpyDeviceToHost, st));
+                RT_CUDA(cudaStreamSynchronize(st));
+                if (live == 0) break;
+                const int n = (int)live;
+                if (sc->d_sort_keys_a.reserve(8 * (size_t)n) || sc->d_sort_keys_b.reserve(8 * (size_t)n) ||
+                    sc->d_sort_vals_b.reserve(4 * (size_t)n) || sc->d_sort_hist.reserve(rth::radix_hist_bytes(n)))
+                    return RT_ERR_OUT_OF_MEMORY;
+                unsigned long long* ka = sc->d_sort_keys_a.as<unsigned long long>();
+                unsigned long long* kb = sc->d_sort_keys_b.as<unsigned long long>();
+                int* va = qout;  // the other queue is free until this wave's advance phase: sort into it
+                int* vb = sc->d_sort_vals_b.as<int>();
+                k_path_keys<<<(n + kThreads - 1) / kThreads, kThreads, 0, st>>>(qin, n, paths, path_stride, bounds6, ka, va);
+                sc->kernel_launches += 1 + rth::radix_sort_pairs(st, ka, kb, va, vb, sc->d_sort_hist.as<unsigned>(), n, 3);
+                // three passes: the sorted slots are in what `vb` pointed at first, i.e. d_sort_vals_b; copy them into the queue
+                RT_CUDA(cudaMemcpyAsync(qin, va, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st));
+                RT_CUDA(cudaMemsetAsync(ctr + outc, 0, 8, st));
+                RT_CUDA(cudaMemsetAsync(shq_count, 0, sizeof(unsigned) * (size_t)std::max(v.n_lights, 1), st));
+                k_wave_trace<MODE, STATS><<<persistent_grid(k_wave_trace<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
+                    v, ctr, in, qin, paths, path_stride, hitq);
+                k_shadow_gen<true><<<persistent_grid(k_shadow_gen<true>, sc->sm_count), kThreads, 0, st>>>(
+                    v, ctr, in, hitq, shq, shq_count, occl, att4, paths, path_stride);
+                if (loop) k_shadow<MODE, STATS, true><<<persistent_grid(k_shadow<MODE, STATS, true>, sc->sm_count), kThreads, 0, st>>>(
+                    v, ctr, in, shq, shq_count, occl, att4, nullptr);
+                else k_shadow<MODE, STATS, false><<<persistent_grid(k_shadow<MODE, STATS, false>, sc->sm_count), kThreads, 0, st>>>(
+                    v, ctr, in, shq, shq_count, occl, att4, nullptr);
+                k_wave_advance<<<persistent_grid(k_wave_advance, sc->sm_count), kThreads, 0, st>>>(
+                    v, ctr, in, outc, hitq, occl, att4, qout, canvas, paths, path_stride);
+                sc->kernel_launches += 4;
                 (*waves)++;
                 std::swap(in, outc);
                 std::swap(qin, qout);
@@ -1548,6 +1636,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     const bool want_stats = (p.flags & RT_RENDER_STATS) != 0;
     sc->fused_shade = (p.flags & RT_RENDER_FUSED_SHADE) != 0;
     sc->trace_unlit = (p.flags & RT_RENDER_TRACE_UNLIT) != 0;
+    sc->sort_rays = (p.flags & RT_RENDER_SORT_RAYS) != 0;
     bool built = false;
     RT_CUDA(cudaEventRecord(sc->ev[2], st));
     if (!no_bvh) {

@@ -82,6 +82,8 @@ struct RtScene {
     rth::DevBuf d_canvas, d_counters, d_hitq, d_paths, d_queue_a, d_queue_b, d_ids;
     rth::DevBuf d_shadowq, d_occl, d_shq_count;
     rth::DevBuf d_push_ctr;         // block counter of the signalled tile push
+    rth::DevBuf d_sort_keys_a, d_sort_keys_b, d_sort_vals_b, d_sort_hist;  // RT_RENDER_SORT_RAYS
+    bool sort_rays = false;
     bool fused_shade = false;       // RT_RENDER_FUSED_SHADE: one k_shade kernel instead of gen / traverse / resolve
     bool split_shade_used = false;
     rth::Bvh bvh;
@@ -117,6 +119,10 @@ int finish_build(RtScene* sc, RtBuildStats* stats);
 // keeps the tree, recomputes triangles and every box (instances moved, none added / removed / re-meshed)
 int refit_bvh(RtScene* sc, RtBuildStats* stats, bool sync = true);
 bool refit_possible(const RtScene* sc);
+// stable LSD radix sort of (u64 key, int value) pairs on the low 8 * n_passes key bits; the a pointers end up at the result
+size_t radix_hist_bytes(int n);
+int radix_sort_pairs(cudaStream_t st, unsigned long long*& keys_a, unsigned long long*& keys_b, int*& vals_a, int*& vals_b,
+                     unsigned* hist, int n, int n_passes);
 int update_instance_boxes(RtScene* sc);                    // rt_engine.cu
 rtd::SceneView make_view(const RtScene* sc, bool with_bvh);
 }  // namespace rth

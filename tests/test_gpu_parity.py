@@ -413,3 +413,16 @@ def test_signalled_tile_push(pkg, scenes):
     with pytest.raises(RuntimeError):
         s.push_tiles_signal(p, slab.data_ptr(), [ptr, ptr], n, 4)  # one canvas per rank
     pkg.peer_canvas_free(ptr)
+
+
+@pytest.mark.parametrize("name,kw", [("world8_stress", {}), ("grid64_mixed", MIXED), ("spheres8", {}), ("world4", {})])
+def test_sorted_bounce_waves(pkg, scenes, name, kw):
+    """RT_RENDER_SORT_RAYS: per-wave launches with the live paths sorted by origin cell and direction octant between
+    the waves; the order of a wave's queue enters no result, so frame and query counts are the oracle's."""
+    w, s = scenes(name, **kw)
+    oc, ost = ob.OracleScene(w).render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    c, st = s.render(flags=pkg.RT_RENDER_SORT_RAYS | pkg.RT_RENDER_REBUILD_BVH | pkg.RT_RENDER_STATS)
+    assert (c == oc).all(), int((c != oc).sum())
+    assert st["rays_total"] == ost["rays_total"] and st["rays_secondary"] == ost["rays_secondary"]
+    c2, st2 = s.render()
+    assert (c2 == c).all() and st2["waves"] == st["waves"]
