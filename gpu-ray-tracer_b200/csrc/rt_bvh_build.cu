@@ -396,7 +396,6 @@ __device__ __forceinline__ float half_area(const float* b) {
 // with uniform trip counts; `width = 8` keeps the exchange inside one node's lane group. ----
 #define FULL 0xffffffffu
 __device__ __forceinline__ int g_shfl(int v, int src) { return __shfl_sync(FULL, v, src, 8); }
-__device__ __forceinline__ float g_shflf(float v, int src) { return __shfl_sync(FULL, v, src, 8); }
 __device__ __forceinline__ int g_sum(int v) {
     v += __shfl_xor_sync(FULL, v, 1, 8);
     v += __shfl_xor_sync(FULL, v, 2, 8);

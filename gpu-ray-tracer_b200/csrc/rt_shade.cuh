@@ -99,9 +99,17 @@ RT_HD float4 light_shine(const SceneView& s, const Tracer& tr, const LightRec& L
 RT_HD float4 phong(const MatRec& m, float4 kd, float3 norm, float4 incoming, float3 ray_dir, float3 dir_to_light) {
     float norm_dot = fmaxf(rtx::dot3(dir_to_light, norm), 0.0f);
     float4 diffuse = rtx::scale4(norm_dot, kd);
-    float3 reflected = rtx::ref_reflect(rtx::neg3(dir_to_light), norm);
-    float reflect_dot = rtx::dot3(rtx::neg3(reflected), ray_dir);
-    float4 specular = rtx::scale4(rtx::ref_powf(fmaxf(reflect_dot, 0.0f), m.alpha), m.Ks);
+    float4 specular;
+    if (m.Ks.x == 0.0f && m.Ks.y == 0.0f && m.Ks.z == 0.0f && m.Ks.w == 0.0f && m.alpha >= 0.0f) {
+        // Ks = +-0 in every channel (all shipped worlds): pow(max(.,0), alpha >= 0) is finite and carries a plus sign, so
+        // pow * Ks is Ks itself, bit for bit, and the reflection vector and the double-precision pow (half of k_resolve's
+        // instructions) need not be evaluated.
+        specular = m.Ks;
+    } else {
+        float3 reflected = rtx::ref_reflect(rtx::neg3(dir_to_light), norm);
+        float reflect_dot = rtx::dot3(rtx::neg3(reflected), ray_dir);
+        specular = rtx::scale4(rtx::ref_powf(fmaxf(reflect_dot, 0.0f), m.alpha), m.Ks);
+    }
     return rtx::mul4(rtx::add4(diffuse, specular), incoming);
 }
 

@@ -29,7 +29,9 @@ def test_bvh8_traversal_primary_bit_exact(pkg, name):
     assert st["nodes"] > 0 and st["exact"] <= st["prims"]
 
 
-@pytest.mark.parametrize("name,sem", [("world1", 0), ("world1", 1), ("world4", 0), ("world8_stress", 0), ("world16", 0)])
+# config: Ks = 0 with alpha = 0.8 (phong's specular shortcut: pow * (+-0) is +-0 bit for bit); world8_stress: Ks != 0
+@pytest.mark.parametrize("name,sem", [("world1", 0), ("world1", 1), ("world4", 0), ("world8_stress", 0), ("world16", 0),
+                                      ("config", 0), ("config", 1)])
 def test_render_bit_exact(pkg, name, sem):
     w = pkg.World(scene_path(name), width=320, height=240)
     bvh = ob.OracleBvh(w)
