@@ -30,6 +30,7 @@ RT_RENDER_REFIT_BVH = 512
 RT_RENDER_HOST_BANDS = 1024
 RT_RENDER_HOST_DIRECT = 2048
 RT_HITABLE_TRIMESH, RT_HITABLE_SPHERE = 0, 1
+RT_DEBUG_PREFIX_UPLOADS, RT_DEBUG_BVH8_LEVELS, RT_DEBUG_BUILD_PATH, RT_DEBUG_BUILD_LAUNCHES = 0, 1, 2, 3
 
 
 class RtMaterial(C.Structure):
@@ -96,7 +97,7 @@ class RtFrameStats(C.Structure):
 
 class RtBuildStats(C.Structure):
     _fields_ = [("n_prims", C.c_int32), ("n_bvh2_nodes", C.c_int32), ("n_bvh8_nodes", C.c_int32),
-                ("kernel_launches", C.c_int32), ("ms_build", C.c_float)]
+                ("kernel_launches", C.c_int32), ("ms_build", C.c_float), ("n_levels8", C.c_int32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -181,6 +182,7 @@ def cuda_lib():
         lib.rt_debug_cast.argtypes = [vp, i32, i32, i32, C.POINTER(RtHit)]
         lib.rt_bvh_download.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
         lib.rt_bvh8_download.argtypes = [vp, vp, i32, i32p, vp, vp, i32, i32p]
+        lib.rt_debug_get.argtypes = [vp, i32, C.POINTER(C.c_int64)]
         lib.rt_measure_l2_bandwidth.argtypes = [C.c_int64, i32, f32p]
         lib.rt_last_error_string.restype = C.c_char_p
         lib.rt_version.restype = C.c_char_p
@@ -447,6 +449,11 @@ class Scene:
         _check(lib.rt_bvh8_download(self._h, out["nodes8"].ctypes.data, n8, C.byref(nn), out["prims8"].ctypes.data,
                                     out["prim_order8"].ctypes.data, n, C.byref(npr)), "rt_bvh8_download")
         return out
+
+    def debug_get(self, what):
+        v = C.c_int64()
+        _check(cuda_lib().rt_debug_get(self._h, what, C.byref(v)), "rt_debug_get")
+        return v.value
 
     def close(self):
         if getattr(self, "_h", None):

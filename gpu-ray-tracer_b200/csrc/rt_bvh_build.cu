@@ -14,10 +14,11 @@
 //
 // Every step is deterministic (stable sort, exact min/max, fixed float evaluation order with
 // -fmad=false), so the result is bit-identical to the sequential host build in oracle/lbvh_host.c
-// that tests/test_bvh_build.py compares it against.
+// that tests/test_gpu_parity.py::test_bvh_build_bit_exact_vs_host compares it against.
 #include <cooperative_groups.h>
 #include <cstdlib>
 #include <cstring>
+#include <string>
 
 #include "rt_bvh.cuh"
 #include "rt_internal.h"
@@ -821,13 +822,13 @@ int radix_sort_pairs(cudaStream_t st, unsigned long long*& keys_a, unsigned long
 
 int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     Bvh& b = sc->bvh;
+    // prefix of triangle counts per instance (host). It only depends on which mesh every instance uses: when that is
+    // what the previous build saw, the prefix already on the device (b.work) is reused.
+    bool same_layout = b.topology_valid && (int)b.topo_meshes.size() == sc->n_instances && b.work.p != nullptr;
     b.valid = false;
     b.topology_valid = false;
     cudaStream_t st = sc->stream;
     int launches0 = sc->kernel_launches;
-    // prefix of triangle counts per instance (host). It only depends on which mesh every instance uses: when that is
-    // what the previous build saw, the prefix already on the device (b.work) is reused.
-    bool same_layout = b.topology_valid && (int)b.topo_meshes.size() == sc->n_instances && b.work.p != nullptr;
     for (int i = 0; same_layout && i < sc->n_instances; i++) same_layout = b.topo_meshes[i] == sc->instances[i].mesh;
     std::vector<int> off;
     int n = b.n_prims;
@@ -866,7 +867,22 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
         b.prims8.reserve(sizeof(float4) * 3 * (size_t)n) || b.prim_order8.reserve(4 * (size_t)n) ||
         b.node8_root.reserve(4 * (size_t)max_nodes8) || b.node8_slot.reserve(4 * 8 * (size_t)max_nodes8))
         return RT_ERR_OUT_OF_MEMORY;
-    if (!same_layout) RT_CUDA(cudaMemcpyAsync(b.work.p, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice, st));
+    if (!same_layout) {
+        // staged through pinned memory (a pageable source makes the copy synchronous with the host: 1.2 MB at 314 k instances)
+        const size_t bytes = sizeof(int) * off.size();
+        if (b.h_off_cap < bytes) {
+            if (b.h_off) { RT_CUDA(cudaStreamSynchronize(st)); RT_CUDA(cudaFreeHost(b.h_off)); b.h_off = nullptr; b.h_off_cap = 0; }
+            RT_CUDA(cudaHostAlloc((void**)&b.h_off, bytes + bytes / 2, cudaHostAllocDefault));
+            b.h_off_cap = bytes + bytes / 2;
+        } else if (b.off_in_flight) {
+            RT_CUDA(cudaEventSynchronize(sc->ev[11]));
+        }
+        std::memcpy(b.h_off, off.data(), bytes);
+        RT_CUDA(cudaMemcpyAsync(b.work.p, b.h_off, bytes, cudaMemcpyHostToDevice, st));
+        RT_CUDA(cudaEventRecord(sc->ev[11], st));
+        b.off_in_flight = true;
+        b.prefix_uploads++;
+    }
     SceneView v = make_view(sc, false);
     int* bounds_i = b.scene_bounds.as<int>();
     float* bounds_f = (float*)(bounds_i + 8);
@@ -941,6 +957,7 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
         for (int i = 0; i < sc->n_instances; i++) b.topo_meshes[i] = sc->instances[i].mesh;
     }
     b.build_launches = sc->kernel_launches - launches0;
+    b.build_path = 1;
     if (!sync) return RT_OK;
     RT_CUDA(cudaStreamSynchronize(st));
     return finish_build(sc, stats);
@@ -1006,8 +1023,22 @@ int finish_build(RtScene* sc, RtBuildStats* stats) {
     const int* result = (const int*)(sc->h_pinned + 32);
     b.n_nodes8 = result[0];
     if (result[1] != b.n_prims) { b.valid = false; set_error("BVH8 collapse emitted a wrong number of triangles"); return RT_ERR_CUDA; }
-    if (result[2] > RT_STACK_SIZE) { b.valid = false; set_error("BVH8 deeper than the traversal stack"); return RT_ERR_LIMIT; }
+    // Traversal (rt_bvh.cuh bvh_query) pushes at most ONE stack entry per node it descends through — the remaining hit
+    // children of that node's group — so the stack never holds more entries than the tree has levels. A tree deeper than
+    // the stack is refused here instead of dropping groups (= missing hits) at run time. An LBVH over duplicate Morton
+    // codes splits on the triangle index, so its depth is bounded by key bits + log2(duplicates), not by the scene size.
+    // RT_TEST_STACK_LIMIT lowers the limit so that tests can reach this path with a real tree.
+    int stack_limit = RT_STACK_SIZE;
+    if (const char* e = std::getenv("RT_TEST_STACK_LIMIT")) { int v = std::atoi(e); if (v > 0 && v < stack_limit) stack_limit = v; }
+    b.n_levels8 = result[2];
+    if (result[2] > stack_limit) {
+        b.valid = false;
+        b.topology_valid = false;
+        set_error("BVH8 has " + std::to_string(result[2]) + " levels, more than the traversal stack holds (" + std::to_string(stack_limit) + ")");
+        return RT_ERR_LIMIT;
+    }
     if (stats) {
+        stats->n_levels8 = result[2];
         stats->n_bvh8_nodes = b.n_nodes8;
         stats->kernel_launches = b.build_launches;
         float ms = 0.f;

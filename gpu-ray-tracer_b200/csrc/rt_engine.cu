@@ -65,6 +65,8 @@ void Bvh::release() {
                      &parent, &range_lo, &range_hi, &flags, &node_box, &nodes8, &prims8, &prim_order8, &work,
                      &collapse_scratch, &node8_root, &node8_slot};
     for (DevBuf* b : all) b->release();
+    if (h_off) { cudaFreeHost(h_off); h_off = nullptr; h_off_cap = 0; }
+    off_in_flight = false;
     valid = false;
     topology_valid = false;
 }
@@ -278,7 +280,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_shade(SceneView s, unsigned lon
         if (rec.inst < 0) continue;  // a missed pixel inside a tile-aligned group
         Hit h;
         h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
-        rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
+        rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)((unsigned)rec.xy >> 16));
         int mat_id = s.tris[h.tri].mat;
         const MatRec& m = s.mats[mat_id];
         if (!OPAQUE_ONLY && s.depth > 0 && (m.reflective || m.refractive)) {
@@ -354,7 +356,7 @@ __device__ __forceinline__ void phase_shadow_gen(const SceneView& s, const int n
             Frame* frames = path_frames(paths, path_stride, rec.out_index, &head);
             if (hit) r = frames[head->stack_top].ray;
         } else if (hit) {
-            r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
+            r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)((unsigned)rec.xy >> 16));
         } else {
             // wave 0 queues are slot-indexed: k_shadow must find a hole, not stale data
             ShadowRec hole;
@@ -500,7 +502,7 @@ __global__ void __launch_bounds__(kThreads, RT_RESOLVE_MIN_BLOCKS) k_resolve(Sce
         if (rec.inst < 0) continue;  // a missed pixel inside a tile-aligned group (k_primary wrote its black)
         Hit h;
         h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
-        rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)(rec.xy >> 16));
+        rtx::Ray r = rtx::camera_ray(s.cam, (float)(rec.xy & 0xffff), (float)((unsigned)rec.xy >> 16));
         int mat_id = s.tris[h.tri].mat;
         const MatRec& m = s.mats[mat_id];
         AttenLookup att = {occl, att4, (size_t)n, (size_t)i};
@@ -870,14 +872,17 @@ __device__ __forceinline__ void push_signal_tail(const TileMap& tm, const PeerCa
     if (threadIdx.x == 0) *sg.done_blocks = 0u;  // ready for the next frame
 }
 
-__global__ void k_wait_mailbox(const uint32_t* own_canvas, long long mailbox_offset, int n, unsigned epoch, long long timeout_cycles) {
+__global__ void k_wait_mailbox(const uint32_t* own_canvas, long long mailbox_offset, int n, unsigned epoch, long long timeout_cycles,
+                               unsigned* status) {
     if ((int)threadIdx.x >= n) return;
     volatile const unsigned* box = (volatile const unsigned*)(own_canvas + mailbox_offset);
     long long t0 = clock64();
-    // epochs only grow; a peer that died would hang the GPU, so the wait gives up after timeout_cycles (the frame is then
-    // incomplete, which the caller's own checks see)
+    // epochs only grow; a peer that died would hang the GPU, so the wait gives up after timeout_cycles. The frame is then
+    // incomplete: the slot that timed out is recorded in *status (pinned host memory, bit r = rank r never signalled) and
+    // the host turns it into RT_ERR_CUDA at the next synchronisation point of this scene (rt_frame_finish / the
+    // blocking rt_push_tiles_signal).
     while ((int)(box[threadIdx.x] - epoch) < 0) {
-        if (clock64() - t0 > timeout_cycles) break;
+        if (clock64() - t0 > timeout_cycles) { atomicOr(status, 1u << threadIdx.x); break; }
     }
     __threadfence_system();
 }
@@ -1050,6 +1055,10 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
         set_error("null array with non-zero count");
         return RT_ERR_INVALID_ARG;
     }
+    if ((long long)d->width * d->height > (1ll << 30)) {  // pixel indices are 32-bit ints in the kernels (y * W + x)
+        set_error("canvas larger than 2^30 pixels");
+        return RT_ERR_LIMIT;
+    }
     if (d->env.depth < 0 || d->env.depth >= RT_MAX_FRAMES) {  // RayFrame frames[MAX_DEPTH], scene.cu:25,96
         set_error("depth must be in 0..9 (the reference's RayFrame[10] stack)");
         return RT_ERR_LIMIT;
@@ -1094,6 +1103,7 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->chunk_done[c], cudaEventDisableTiming);
     }
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->copies_done, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&sc->ev_exchange, cudaEventDisableTiming);
     if (e != cudaSuccess) return fail(rth::cuda_fail(e, "cudaEventCreate", __FILE__, __LINE__));
     sc->n_vertices = d->n_vertices; sc->n_triangles = d->n_triangles; sc->n_meshes = d->n_meshes;
     sc->n_instances = d->n_instances; sc->n_lights = d->n_lights;
@@ -1147,6 +1157,7 @@ int rt_scene_destroy(RtScene* sc) {
         if (sc->chunk_done[c]) cudaEventDestroy(sc->chunk_done[c]);
     }
     if (sc->copies_done) cudaEventDestroy(sc->copies_done);
+    if (sc->ev_exchange) cudaEventDestroy(sc->ev_exchange);
     if (sc->copy_stream) cudaStreamDestroy(sc->copy_stream);
     if (sc->own_stream) cudaStreamDestroy(sc->own_stream);
     if (sc->h_pinned) cudaFreeHost(sc->h_pinned);
@@ -1176,6 +1187,7 @@ int rt_scene_set_instances(RtScene* sc, const RtInstance* inst, int32_t n) {
 }
 int rt_scene_set_canvas_size(RtScene* sc, int32_t w, int32_t h) {
     if (!sc || w <= 0 || h <= 0 || w > 65535 || h > 65535) { set_error("invalid canvas size"); return RT_ERR_INVALID_ARG; }
+    if ((long long)w * h > (1ll << 30)) { set_error("canvas larger than 2^30 pixels"); return RT_ERR_LIMIT; }
     sc->width = w; sc->height = h;
     sc->camera.canvas_width = (float)w;
     sc->camera.canvas_height = (float)h;
@@ -1489,6 +1501,30 @@ int rt_untile(RtScene* sc, const RtRenderParams* p, const uint32_t* gathered, ui
     return RT_OK;
 }
 
+// Time-out of the mailbox wait: 2 s by default (RT_MAILBOX_TIMEOUT_MS overrides it), in SM cycles at ~2 GHz.
+static long long mailbox_timeout_cycles() {
+    static const long long cyc = [] {
+        const char* e = std::getenv("RT_MAILBOX_TIMEOUT_MS");
+        double ms = e ? std::atof(e) : 2000.0;
+        if (!(ms > 0.0)) ms = 2000.0;
+        return (long long)(ms * 2.0e6);
+    }();
+    return cyc;
+}
+// The word k_wait_mailbox / the fused exchange report a time-out in: h_pinned[48] (page-locked, device-addressable under UVA).
+static unsigned* exchange_status(RtScene* sc) { return (unsigned*)(sc->h_pinned + 48); }
+// After a stream synchronisation: a mailbox wait of this scene that gave up makes the frame an error, not a silent hole.
+static int check_exchange(RtScene* sc) {
+    unsigned* st = exchange_status(sc);
+    const unsigned missing = *(volatile unsigned*)st;
+    if (!missing) return RT_OK;
+    *st = 0u;
+    char buf[160];
+    std::snprintf(buf, sizeof buf, "peer exchange timed out: ranks with mask 0x%x never signalled this frame (canvas incomplete)", missing);
+    set_error(buf);
+    return RT_ERR_CUDA;
+}
+
 static int push_tiles_impl(RtScene* sc, const RtRenderParams* p, const uint32_t* slab, uint32_t* const* peer_canvases, int32_t n_peers,
                            int64_t canvas_pixels, uint32_t epoch, bool signal) {
     if (!sc || !slab || !peer_canvases || n_peers < 1 || n_peers > RT_MAX_PEERS) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
@@ -1517,14 +1553,21 @@ static int push_tiles_impl(RtScene* sc, const RtRenderParams* p, const uint32_t*
         // a rank that owns no tile still has to signal: one block, no quads
         unsigned grid = (unsigned)std::max<long long>((n_quads + kThreads - 1) / kThreads, 1);
         k_push_tiles<true><<<grid, kThreads, 0, sc->stream>>>(tm, slab, pc, sg);
-        k_wait_mailbox<<<1, 32, 0, sc->stream>>>(peer_canvases[tm.rank], canvas_pixels, n_peers, epoch, 4000000000LL);
+        k_wait_mailbox<<<1, 32, 0, sc->stream>>>(peer_canvases[tm.rank], canvas_pixels, n_peers, epoch, mailbox_timeout_cycles(),
+                                                 exchange_status(sc));
+        RT_CUDA(cudaEventRecord(sc->ev_exchange, sc->stream));
+        sc->exchange_pending = true;
         sc->kernel_launches += 2;
     } else if (n_quads > 0) {
         k_push_tiles<false><<<(unsigned)((n_quads + kThreads - 1) / kThreads), kThreads, 0, sc->stream>>>(tm, slab, pc, sg);
         sc->kernel_launches++;
     }
     RT_CUDA(cudaGetLastError());
-    if (!(p && (p->flags & RT_RENDER_ASYNC))) RT_CUDA(cudaStreamSynchronize(sc->stream));
+    if (!(p && (p->flags & RT_RENDER_ASYNC))) {
+        RT_CUDA(cudaStreamSynchronize(sc->stream));
+        sc->exchange_pending = false;
+        return check_exchange(sc);
+    }
     return RT_OK;
 }
 
@@ -1769,6 +1812,13 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
     RtFrameStats fs;
     std::memset(&fs, 0, sizeof fs);
     RT_CUDA(cudaEventSynchronize(sc->ev[5]));
+    // an exchange enqueued behind the frame on the same stream (rt_push_tiles_signal with RT_RENDER_ASYNC) reports its
+    // time-out here once the stream has drained
+    if (sc->exchange_pending) {
+        sc->exchange_pending = false;
+        RT_CUDA(cudaEventSynchronize(sc->ev_exchange));
+        if (int rc_x = check_exchange(sc)) return rc_x;
+    }
     for (int c = 0; c < n_chunks; c++) {
         const unsigned long long* hc = sc->h_pinned + 64 + (size_t)C_N * c;
         for (int i = 0; i < C_N; i++) host_ctr[i] += hc[i];
@@ -1913,6 +1963,18 @@ int rt_debug_cast(RtScene* sc, int32_t x, int32_t y, int32_t semantics, RtHit* o
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaMemcpyAsync(out, sc->d_ids.p, sizeof(RtHit), cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaStreamSynchronize(st));
+    return RT_OK;
+}
+
+int rt_debug_get(RtScene* sc, int32_t what, int64_t* out) {
+    if (!sc || !out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    switch (what) {
+        case RT_DEBUG_PREFIX_UPLOADS: *out = sc->bvh.prefix_uploads; break;
+        case RT_DEBUG_BVH8_LEVELS: *out = sc->bvh.n_levels8; break;
+        case RT_DEBUG_BUILD_PATH: *out = sc->bvh.build_path; break;
+        case RT_DEBUG_BUILD_LAUNCHES: *out = sc->bvh.build_launches; break;
+        default: set_error("unknown debug counter"); return RT_ERR_INVALID_ARG;
+    }
     return RT_OK;
 }
 

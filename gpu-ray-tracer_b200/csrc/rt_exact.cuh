@@ -6,7 +6,7 @@
 // path. The translation unit MUST be compiled with -fmad=false (no FMA contraction), default
 // -prec-div/-prec-sqrt/-ftz=false. Citations are /root/reference paths.
 //
-// Used only on CANDIDATES that survived the conservative BVH8 traversal (rt_traverse.cuh), on
+// Used only on CANDIDATES that survived the conservative BVH8 traversal (rt_bvh.cuh), on
 // the final hit (normal) and in shading; everything is __host__ __device__ so the host-side unit
 // harness (tests/emu) can exercise the same code without a GPU.
 #ifndef RTB200_EXACT_CUH

@@ -38,6 +38,7 @@ struct Bvh {
     int n_bvh2_nodes = 0;
     int n_nodes8 = 0;
     int build_launches = 0;
+    int build_path = 0;  // which builder produced the tree: 1 = multi-kernel pipeline, 2 = one-launch cluster kernel
     DevBuf prim_world;   // float4[3*n_prims]  world-space triangles in input (instance-major) order
     DevBuf prim_box;     // float[6*n_prims]   inflated prim AABBs
     DevBuf scene_bounds; // float[6] (+ atomics scratch)
@@ -57,7 +58,12 @@ struct Bvh {
     DevBuf node8_root;   // int[n_nodes8]
     DevBuf node8_slot;   // int[8*n_nodes8]
     bool topology_valid = false;
+    int n_levels8 = 0;   // depth of the BVH8 (finish_build)
     std::vector<int> topo_meshes;  // mesh index per instance at build time
+    int* h_off = nullptr;          // pinned staging of the per-instance triangle prefix
+    size_t h_off_cap = 0;
+    bool off_in_flight = false;
+    int prefix_uploads = 0;        // how many builds had to upload the prefix (tests: unchanged meshes upload once)
     void release();
 };
 
@@ -101,9 +107,11 @@ struct RtScene {
     cudaEvent_t cev[kMaxChunks][6] = {};  // per chunk: start, primary done, shadow rays generated, traced, wave 0 shaded, waves done
     cudaEvent_t chunk_done[kMaxChunks] = {};  // no timing; copy_stream waits on these
     cudaEvent_t copies_done = nullptr;
+    cudaEvent_t ev_exchange = nullptr;  // recorded behind the mailbox wait of a signalled exchange
+    bool exchange_pending = false;      // ... whose outcome (h_pinned[48]) rt_frame_finish still has to look at
     int pend_chunks = 1;
     bool pend_direct = false;
-    // pinned host memory, u64 units: [32,36) build result, [40,42) live counts of the bounce waves,
+    // pinned host memory, u64 units: [32,36) build result, [48] exchange time-out mask, [40,42) live counts of the bounce waves,
     // [64 + 32 c, 96 + 32 c) counters of chunk c
     unsigned long long* h_pinned = nullptr;
     void* h_inst = nullptr;             // pinned staging of the instance records (rt_scene_set_instances)

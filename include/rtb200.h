@@ -206,6 +206,8 @@ typedef struct RtBuildStats {
     int32_t n_bvh8_nodes;
     int32_t kernel_launches;
     float ms_build;
+    int32_t n_levels8;        /* depth of the BVH8 (levels of the breadth-first layout). The traversal stack holds one entry
+                                 per level; a tree deeper than the stack (32) is refused with RT_ERR_LIMIT at build time */
 } RtBuildStats;
 
 typedef struct RtHit {
@@ -326,6 +328,15 @@ int rt_bvh_download(RtScene* scene, uint64_t* morton, int32_t* perm, int32_t* le
  * sorted (Morton) position of each leaf-order triangle. */
 int rt_bvh8_download(RtScene* scene, void* nodes80, int32_t max_nodes, int32_t* n_nodes, void* prims48,
                      int32_t* prim_order, int32_t max_prims, int32_t* n_prims);
+
+/* Introspection for the tests (no reference counterpart): counters of the scene's BVH builder. */
+enum {
+    RT_DEBUG_PREFIX_UPLOADS = 0, /* builds that had to upload the per-instance triangle prefix (unchanged meshes: once) */
+    RT_DEBUG_BVH8_LEVELS = 1,    /* depth of the BVH8 of the last build */
+    RT_DEBUG_BUILD_PATH = 2,     /* 1 = multi-kernel pipeline, 2 = one-launch thread-block-cluster build */
+    RT_DEBUG_BUILD_LAUNCHES = 3  /* kernels the last build / refit launched */
+};
+int rt_debug_get(RtScene* scene, int32_t what, int64_t* out);
 
 /* Measured memory peaks used by bench.py for the L2 roofline (resident-working-set read). */
 int rt_measure_l2_bandwidth(int64_t bytes, int32_t iters, float* gbps);

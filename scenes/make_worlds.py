@@ -43,6 +43,9 @@ WORLDS = {
     "grid64": world(64, [DIRT, GRASS]),
     "grid64_mixed": world(64, [DIRT, STRESS_GRASS, MIRROR, GLASS], depth=9),
     "grid128": world(128, [DIRT, GRASS]),
+    # a large world with real secondary rays that stays benchable and checkable at depth 9: the mirror layer of
+    # world8_stress on top of a 64 x 64 terrain (no stacked glass, so none of grid64_mixed's Light::attenuate restarts)
+    "grid64_mirror": world(64, [DIRT, STRESS_GRASS, MIRROR], depth=9),
     # analytic sphere hitables (schema extension "spheres"): matte, mirror and glass spheres over world8
     "spheres8": world(8, [DIRT, GRASS], depth=5, spheres=[
         dict(radius=1.5, pos=[-2.0, 7.0, 1.0], Ka=[120, 30, 30, 255], Kd=[220, 40, 40, 255], Ks=[255, 255, 255, 255], alpha=20.0),

@@ -138,3 +138,22 @@ def test_c5_world8_stress_4k(pkg, big):
     assert (c2 == c).all() and st2["rays_total"] == st["rays_total"] and st2["rays_secondary"] == st["rays_secondary"]
     c3, st3 = s.render(flags=pkg.RT_RENDER_REFIT_BVH, host_chunks=3)
     assert (c3 == c).all() and st3["rays_total"] == st["rays_total"]
+
+
+@pytest.mark.parametrize("name,bands", [("grid64", 4), ("grid64_mirror", 4), ("grid128", 3)])
+def test_f3_large_world_frame_parity(pkg, big, name, bands):
+    """rendered pixels of the large procedural worlds (256 k, 384 k and 937 k triangles; the mirror world
+    at depth 9 with real secondary rays), not only their BVH builds: oracle row bands bit for bit, closest-hit ids / t on
+    those bands, BVH kept == rebuilt == refitted. (The reference's own CUDA build renders grid64 and grid64_mirror in
+    tests/test_gpu_vs_ref_cuda.py.) Generator: /root/reference/src/procedural/cube_world.cc:145-170."""
+    w, s = big(name)
+    c, st = s.render(flags=pkg.RT_RENDER_REBUILD_BVH)
+    assert st["rays_primary"] == w.width * w.height and st["n_hits"] > 50000
+    if name == "grid64_mirror":
+        assert st["rays_secondary"] > 10000 and st["waves"] > 2
+    inst, tri, t = s.trace_primary(use_bvh=1)
+    oracle_bands(pkg, w, c, inst, tri, t, bands=bands, rows=2, scene=s)
+    c2, st2 = s.render(flags=pkg.RT_RENDER_REFIT_BVH)
+    assert (c2 == c).all() and st2["rays_total"] == st["rays_total"]
+    c3, st3 = s.render()
+    assert (c3 == c).all()

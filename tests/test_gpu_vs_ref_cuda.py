@@ -20,26 +20,52 @@ def channels(a):
     return np.stack([(a >> s) & 255 for s in (24, 16, 8, 0)], -1).astype(np.float64) / 255.0
 
 
-@pytest.mark.skipif(not os.path.exists(REF_GPU), reason="oracle/_ref/ref_gpu not built (needs /root/reference at build time)")
-@pytest.mark.parametrize("name,max_diff", [("world1", 0.0001), ("world4", 0.0), ("world8", 0.0), ("world16", 0.0002),
-                                           ("world8_stress", 0.0001)])
-def test_frame_equals_reference_cuda_build(pkg, gpu_ok, tmp_path, name, max_diff):
+def run_ref_gpu(path, tmp_path):
     dump = str(tmp_path / "canvas.bin")
-    out = subprocess.run([REF_GPU, scene_path(name), "--gpu", "--frames", "1", "--kd", "16", "--canvas", dump],
-                         capture_output=True, text=True, timeout=300)
+    out = subprocess.run([REF_GPU, path, "--gpu", "--frames", "1", "--kd", "16", "--canvas", dump],
+                         capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr
     info = json.loads(out.stdout.strip().splitlines()[-1])
     raw = np.fromfile(dump, dtype=np.uint32)
     w, h = int(raw[0]), int(raw[1])
-    ref = raw[2:].reshape(h, w)
-    world = pkg.World(scene_path(name))
+    return raw[2:].reshape(h, w), info
+
+
+# (scene, JSON overrides, pixel budget = largest fraction of pixels allowed to differ). The budgets are statements about
+# the reference's CUDA build, not about this engine: nvcc contracts the reference's multiply-adds, so agreement with it is
+# statistical (bit-exact agreement is with the reference's serial build, tests/test_oracle_golden.py + test_gpu_parity.py).
+# Shipped files first; then the RayFrame[MAX_DEPTH] state machine (src/rayenv/scene.cu:25,96-188) at depth 0, 1 (BASELINE
+# config C1: "1 bounce") and 9 (the deepest the reference's stack allows) on the refractive and the reflective scene; then
+# a 256 k-triangle procedural world (src/procedural/cube_world.cc:145-170).
+CASES = [("world1", {}, 1e-4), ("world4", {}, 0.0), ("world8", {}, 0.0), ("world16", {}, 2e-4), ("world8_stress", {}, 1e-4),
+         ("world1", {"depth": 0}, 1e-4), ("world1", {"depth": 1}, 1e-4), ("world1", {"depth": 9}, 1e-4),
+         ("world8_stress", {"depth": 1}, 1e-4), ("world8_stress", {"depth": 9}, 2e-4),
+         ("grid64", {}, 2e-4), ("grid64_mirror", {}, 5e-4)]
+
+
+@pytest.mark.skipif(not os.path.exists(REF_GPU), reason="oracle/_ref/ref_gpu not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("name,override,max_diff", CASES,
+                         ids=lambda v: v if isinstance(v, str) else ("-".join("%s%s" % i for i in v.items()) or "shipped") if isinstance(v, dict) else None)
+def test_frame_equals_reference_cuda_build(pkg, gpu_ok, tmp_path, name, override, max_diff):
+    path = scene_path(name)
+    if override:
+        cfg = json.load(open(path))
+        cfg.update(override)
+        path = str(tmp_path / (name + "_override.json"))
+        json.dump(cfg, open(path, "w"))
+    ref, info = run_ref_gpu(path, tmp_path)
+    h, w = ref.shape
+    world = pkg.World(path)
     assert (world.width, world.height, world.n_instances) == (w, h, info["n_trans"])
     scene = pkg.Scene(world)
     canvas, st = scene.render(flags=pkg.RT_RENDER_REBUILD_BVH)
     scene.close()
     differ = float((canvas != ref).mean())
     rmse = float(np.sqrt(np.mean((channels(canvas) - channels(ref)) ** 2)))
-    print(name, "pixels differing: %.5f %%, RMSE %.2e" % (100 * differ, rmse))
+    print(name, override, "pixels differing: %d of %d (%.5f %%), RMSE %.2e, waves %d, secondary rays %d" %
+          (int((canvas != ref).sum()), canvas.size, 100 * differ, rmse, st["waves"], st["rays_secondary"]))
     assert rmse <= 1e-3
     assert differ <= max_diff, differ
     assert (ref != 0).sum() > 1000
+    if override.get("depth") == 9 and name == "world8_stress":
+        assert st["waves"] == 10 and st["rays_secondary"] > 0

@@ -1,0 +1,58 @@
+#!/bin/bash
+# One parameterised GPU-box script (replaces the per-session tools/gpu_*.sh of round 1). Run under gpurun from the repo
+# root:   gpurun --timeout 1500 -- 'bash tools/gpu_run.sh <tag> <step> [<step> ...]'
+# Every step writes into gpurun_out/<tag>_*; copy what should be judged into profiles/ afterwards.
+#   tests           python -m pytest tests -m gpu -x -q
+#   tests:<expr>    ... -k <expr>
+#   bench           python bench.py --steps 20 --warmup 5                 (world16 4K depth 9, N = 1)
+#   bench:<args>    python bench.py <args>   (commas become spaces, e.g. bench:--scene,world8_stress)
+#   multi:<N>       torchrun --nproc-per-node N bench.py --gpus N
+#   launches        ncu launch list (gpu__time_duration.sum) of tools/profile_frame.py world16 3840 2160 9 3
+#   ncu:<regex>     ncu --set full of the kernels matching <regex> in the same command (summary csv + .ncu-rep)
+#   sanitizer       compute-sanitizer memcheck over the smoke frame and a small cluster build
+#   refcmp          tools/ref_gpu_compare.py (the reference's own CUDA build beside the engine)
+#   cmd:<shell>     anything else (commas become spaces)
+set -u
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+TAG=$1; shift
+export PYTHONUNBUFFERED=1
+for STEP in "$@"; do
+  NAME=${STEP%%:*}; ARG=""; [[ "$STEP" == *:* ]] && ARG=${STEP#*:}
+  ARGS=${ARG//,/ }
+  echo "=== $TAG $STEP"
+  case $NAME in
+    tests)
+      if [ -n "$ARG" ]; then timeout 1200 python -m pytest tests -m gpu -x -q -k "$ARGS" 2>&1 | tail -40 | tee gpurun_out/${TAG}_tests.log
+      else timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -40 | tee gpurun_out/${TAG}_tests.log; fi ;;
+    bench)
+      SUF=$(echo "$ARG" | tr -c 'A-Za-z0-9' '_' | cut -c1-40)
+      timeout 600 python bench.py ${ARGS:---steps 20 --warmup 5} > gpurun_out/${TAG}_bench_${SUF}.json 2> gpurun_out/${TAG}_bench_${SUF}.err
+      tail -c 1500 gpurun_out/${TAG}_bench_${SUF}.json; tail -5 gpurun_out/${TAG}_bench_${SUF}.err ;;
+    multi)
+      N=${ARG%%,*}; EXTRA=""; [[ "$ARG" == *,* ]] && EXTRA=${ARG#*,}; EXTRA=${EXTRA//,/ }
+      SUF=$(echo "$EXTRA" | tr -c 'A-Za-z0-9' '_' | cut -c1-30)
+      timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 \
+        bench.py --gpus $N --steps 20 --warmup 5 $EXTRA > gpurun_out/${TAG}_bench_n${N}_${SUF}.json 2> gpurun_out/${TAG}_bench_n${N}_${SUF}.err
+      tail -c 1200 gpurun_out/${TAG}_bench_n${N}_${SUF}.json; tail -5 gpurun_out/${TAG}_bench_n${N}_${SUF}.err ;;
+    launches)
+      timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${TAG}_launches.csv \
+        python tools/profile_frame.py ${ARGS:-world16 3840 2160 9 3 1} > gpurun_out/${TAG}_launches.log 2>&1
+      python tools/launch_summary.py gpurun_out/${TAG}_launches.csv | tee gpurun_out/${TAG}_launches.txt ;;
+    ncu)
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:"$ARG" -s 6 -c 6 -f -o gpurun_out/${TAG}_full \
+        python tools/profile_frame.py world16 3840 2160 9 3 1 > gpurun_out/${TAG}_ncu.log 2>&1
+      ncu -i gpurun_out/${TAG}_full.ncu-rep --page details --csv > gpurun_out/${TAG}_ncu_details.csv 2>/dev/null
+      ncu -i gpurun_out/${TAG}_full.ncu-rep --page raw --csv > gpurun_out/${TAG}_ncu_raw.csv 2>/dev/null
+      ls -la gpurun_out/${TAG}_full.ncu-rep ;;
+    sanitizer)
+      timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -25 | tee gpurun_out/${TAG}_sanitizer.log ;;
+    refcmp)
+      timeout 900 python tools/ref_gpu_compare.py ${ARGS:-20} > gpurun_out/${TAG}_ref_gpu_compare.jsonl 2> gpurun_out/${TAG}_ref_gpu_compare.err
+      cat gpurun_out/${TAG}_ref_gpu_compare.jsonl | cut -c1-600 ;;
+    cmd)
+      timeout 1200 bash -c "$ARGS" 2>&1 | tail -60 | tee gpurun_out/${TAG}_cmd.log ;;
+    *) echo "unknown step $STEP" ;;
+  esac
+done
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,temperature.gpu --format=csv,noheader | head -8
