@@ -42,12 +42,10 @@ __global__ void k_bounds_init(int* bounds) {
     else if (threadIdx.x < 6) bounds[threadIdx.x] = (int)0x80000000;
 }
 
-// One thread per world-space triangle p = prim_offset[inst] + k.
-__global__ void k_flatten(SceneView s, const int* __restrict__ prim_offset, int n_prims, float4* __restrict__ prim_world,
-                          float* __restrict__ prim_box, int* __restrict__ bounds) {
-    int p = blockIdx.x * blockDim.x + threadIdx.x;
-    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    if (p < n_prims) {
+// World-space triangle p = prim_offset[inst] + k: record, inflated box, tight bounds (lo / hi).
+__device__ __forceinline__ void flatten_prim(const SceneView& s, const int* prim_offset, int p, float4* prim_world, float* prim_box,
+                                             float lo[3], float hi[3]) {
+    {
         int a = 0, b = s.n_insts;  // last instance with prim_offset[inst] <= p
         while (b - a > 1) {
             int m = (a + b) >> 1;
@@ -96,6 +94,14 @@ __global__ void k_flatten(SceneView s, const int* __restrict__ prim_offset, int 
             prim_box[6 * (size_t)p + 3 + k] = hi[k] + m;
         }
     }
+}
+
+// One thread per world-space triangle.
+__global__ void k_flatten(SceneView s, const int* __restrict__ prim_offset, int n_prims, float4* __restrict__ prim_world,
+                          float* __restrict__ prim_box, int* __restrict__ bounds) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (p < n_prims) flatten_prim(s, prim_offset, p, prim_world, prim_box, lo, hi);
     // block reduce of the TIGHT bounds, then one atomic per block and component
     __shared__ int s_lo[3][kThreads / 32], s_hi[3][kThreads / 32];
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -129,20 +135,11 @@ __device__ __forceinline__ unsigned long long expand21(unsigned long long v) {
     return v;
 }
 
+// 63-bit Morton code of triangle p's centroid inside the scene bounds.
 // key_shift: 0 keeps the 63-bit code; 31 keeps its top 32 bits (scenes up to 2^20 triangles: four
 // radix passes instead of eight; equal prefixes fall back to the triangle index like equal codes do).
-__global__ void k_morton(const float* __restrict__ prim_box, const float4* __restrict__ prim_world, int n_prims,
-                         const int* __restrict__ bounds, unsigned long long* __restrict__ keys, int* __restrict__ vals,
-                         float* __restrict__ bounds_f, int key_shift) {
-    int p = blockIdx.x * blockDim.x + threadIdx.x;
-    float blo[3], bhi[3];
-#pragma unroll
-    for (int k = 0; k < 3; k++) { blo[k] = float_unflip(bounds[k]); bhi[k] = float_unflip(bounds[3 + k]); }
-    if (p == 0) {
-#pragma unroll
-        for (int k = 0; k < 3; k++) { bounds_f[k] = blo[k]; bounds_f[3 + k] = bhi[k]; }
-    }
-    if (p >= n_prims) return;
+__device__ __forceinline__ unsigned long long morton_key(const float4* prim_world, int p, const float blo[3], const float bhi[3],
+                                                         int key_shift) {
     // centroid of the tight box, recomputed from the triangle so it does not depend on the margin
     float4 p0 = prim_world[3 * (size_t)p], p1 = prim_world[3 * (size_t)p + 1], p2 = prim_world[3 * (size_t)p + 2];
     float v0[3] = {p0.x, p0.y, p0.z}, e1[3] = {p1.x, p1.y, p1.z}, e2[3] = {p2.x, p2.y, p2.z};
@@ -158,7 +155,22 @@ __global__ void k_morton(const float* __restrict__ prim_box, const float4* __res
         sc = fminf(fmaxf(sc, 0.0f), 2097151.0f);
         q[k] = (unsigned long long)(unsigned)sc;
     }
-    keys[p] = ((expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2])) >> key_shift;
+    return ((expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2])) >> key_shift;
+}
+
+__global__ void k_morton(const float* __restrict__ prim_box, const float4* __restrict__ prim_world, int n_prims,
+                         const int* __restrict__ bounds, unsigned long long* __restrict__ keys, int* __restrict__ vals,
+                         float* __restrict__ bounds_f, int key_shift) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    float blo[3], bhi[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) { blo[k] = float_unflip(bounds[k]); bhi[k] = float_unflip(bounds[3 + k]); }
+    if (p == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) { bounds_f[k] = blo[k]; bounds_f[3 + k] = bhi[k]; }
+    }
+    if (p >= n_prims) return;
+    keys[p] = morton_key(prim_world, p, blo, bhi, key_shift);
     vals[p] = p;
     (void)prim_box;
 }
@@ -298,17 +310,15 @@ __global__ void k_radix_scatter(const unsigned long long* __restrict__ keys_in, 
 
 // ---------------------------------------------------------------- Karras 2012 hierarchy
 // Node ids: internal 0..n-2 (root 0), leaf of sorted position j = n-1+j.
-__device__ __forceinline__ int delta(const unsigned long long* __restrict__ keys, int n, int i, int j) {
+__device__ __forceinline__ int delta(const unsigned long long* keys, int n, int i, int j) {
     if (j < 0 || j >= n) return -1;
     unsigned long long a = keys[i], b = keys[j];
     if (a == b) return 64 + __clz(i ^ j);
     return __clzll((long long)(a ^ b));
 }
 
-__global__ void k_karras(const unsigned long long* __restrict__ keys, int n, int* __restrict__ left, int* __restrict__ right,
-                         int* __restrict__ parent, int* __restrict__ range_lo, int* __restrict__ range_hi) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n - 1) return;
+__device__ __forceinline__ void karras_node(const unsigned long long* keys, int n, int i, int* left, int* right, int* parent,
+                                            int* range_lo, int* range_hi) {
     int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) > 0 ? 1 : -1;
     int dmin = delta(keys, n, i, i - d);
     int lmax = 2;
@@ -334,6 +344,13 @@ __global__ void k_karras(const unsigned long long* __restrict__ keys, int n, int
     range_lo[i] = lo;
     range_hi[i] = hi;
     if (i == 0) parent[0] = -1;
+}
+
+__global__ void k_karras(const unsigned long long* __restrict__ keys, int n, int* __restrict__ left, int* __restrict__ right,
+                         int* __restrict__ parent, int* __restrict__ range_lo, int* __restrict__ range_hi) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    karras_node(keys, n, i, left, right, parent, range_lo, range_hi);
 }
 
 // One thread per leaf climbs; the second arrival at a node unions its children.
@@ -647,24 +664,31 @@ __device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned n_block
 // Cooperative kernel: all levels in one launch, two grid barriers per level. Blocks own
 // contiguous chunks of the level so that the per-level exclusive scan (which fixes child_base
 // and prim_base, i.e. the memory order of the whole tree) follows node order deterministically.
-__global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
-    unsigned epoch = 0;
-    unsigned* bar = (unsigned*)(a.result + 8);  // zeroed by the host before the launch
-    __shared__ int s_warp[2][kThreads / 32];
+// Runs on G co-resident blocks (block index bid) that `sync` can synchronise: the whole grid of the cooperative
+// k_collapse (global-atomic barrier) or the CTAs of one thread-block cluster inside k_build_cluster (hardware barrier).
+struct GridSync {
+    unsigned* bar;
+    unsigned n_blocks, epoch;
+    __device__ __forceinline__ void operator()() { grid_barrier(bar, n_blocks, epoch); }
+};
+
+template <class Sync>
+__device__ __forceinline__ void collapse_levels(const CollapseArgs& a, Sync& sync, const int G, const int bid) {
+    __shared__ int s_warp[2][32];
     __shared__ int s_carry[2];
     __shared__ int s_base[2];
-    const int G = gridDim.x, B = blockDim.x;
+    const int B = blockDim.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int level_n = 1, level_base = 0, prim_total = 0, levels = 0, max_width = 1;
-    if (blockIdx.x == 0 && threadIdx.x == 0) a.level_a[0] = 0;
-    grid_barrier(bar, gridDim.x, epoch);
+    if (bid == 0 && threadIdx.x == 0) a.level_a[0] = 0;
+    sync();
     while (level_n > 0) {
         int parity = levels & 1;
         int* cur = parity ? a.level_b : a.level_a;
         int* next = parity ? a.level_a : a.level_b;
         int* btot = a.block_tot + (size_t)parity * G * 2;
         int per_block = (level_n + G - 1) / G;
-        int c0 = min(level_n, blockIdx.x * per_block), c1 = min(level_n, c0 + per_block);
+        int c0 = min(level_n, bid * per_block), c1 = min(level_n, c0 + per_block);
         // phase A: children + counts, 8 lanes per node
         const int group = threadIdx.x >> 3, j = threadIdx.x & 7, groups = B >> 3;
         int my_inner = 0, my_prims = 0;
@@ -692,16 +716,16 @@ __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
         if (threadIdx.x == 0) {
             int ti = 0, tp = 0;
             for (int w = 0; w < B / 32; w++) { ti += s_warp[0][w]; tp += s_warp[1][w]; }
-            btot[2 * blockIdx.x] = ti;
-            btot[2 * blockIdx.x + 1] = tp;
+            btot[2 * bid] = ti;
+            btot[2 * bid + 1] = tp;
         }
-        grid_barrier(bar, gridDim.x, epoch);
+        sync();
         // phase B: block offsets (every block sums the totals of the blocks before it), ordered scan, emit
         int pre_i = 0, pre_p = 0, tot_i = 0, tot_p = 0;
         for (int b = threadIdx.x; b < G; b += B) {
             int vi = btot[2 * b], vp = btot[2 * b + 1];
             tot_i += vi; tot_p += vp;
-            if (b < (int)blockIdx.x) { pre_i += vi; pre_p += vp; }
+            if (b < bid) { pre_i += vi; pre_p += vp; }
         }
         for (int o = 16; o; o >>= 1) {
             pre_i += __shfl_xor_sync(0xffffffffu, pre_i, o);
@@ -766,14 +790,22 @@ __global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
         level_n = level_inner;
         levels++;
         if (level_n > max_width) max_width = level_n;
-        grid_barrier(bar, gridDim.x, epoch);
+        sync();
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (bid == 0 && threadIdx.x == 0) {
         a.result[0] = level_base;
         a.result[1] = prim_total;
         a.result[2] = levels;
         a.result[3] = max_width;
     }
+}
+
+__global__ void __launch_bounds__(kThreads) k_collapse(CollapseArgs a) {
+    GridSync sync;
+    sync.bar = (unsigned*)(a.result + 8);  // zeroed by the host before the launch
+    sync.n_blocks = gridDim.x;
+    sync.epoch = 0;
+    collapse_levels(a, sync, (int)gridDim.x, (int)blockIdx.x);
 }
 
 // Refit of the BVH8 (rt_bvh_refit): 8 lanes per node requantise the slots' boxes from the refitted BVH2
@@ -786,6 +818,340 @@ __global__ void __launch_bounds__(kThreads) k_refit8(CollapseArgs a, int n_nodes
     const unsigned* old = (const unsigned*)(a.nodes8 + 5 * (size_t)node);
     const int child_base = (int)old[4], prim_base = (int)old[5];
     write_node8_g<false>(a, a.node8_root[node], node, a.node8_slot[8 * (size_t)node + j], j, child_base, prim_base, nullptr, valid);
+}
+
+
+// ================================================================ one-launch build on one thread-block cluster
+// Small scenes (n <= G * 4096 triangles; world16 has 17 424): every step of the pipeline above in ONE kernel on ONE
+// cluster of G = 8 or 16 CTAs x 512 threads. The steps are separated by the hardware cluster barrier
+// (barrier.cluster, ~0.2 us, release / acquire at cluster scope) instead of 14 kernel boundaries, three software grid
+// barriers per collapse level through a global atomic and the chained global arrival counters of k_refit:
+//   * scene bounds and the radix histograms are exchanged through distributed shared memory (map_shared_rank);
+//   * the radix sort keeps k_radix_scatter's stable match_any ranking, one contiguous run of keys per warp;
+//   * the BVH2 boxes of nodes whose leaves lie inside one CTA's chunk are united with arrival counters in SHARED
+//     memory; the few nodes that span chunks take the union of a suffix of the first chunk, the whole chunks between and
+//     a prefix of the last one (min / max are exact, so any association gives the same bits) — no dependency chain;
+//   * the BVH8 collapse is collapse_levels() with the cluster barrier.
+// Arrays stay in global memory (L2-resident, ~250 cycles) so that rt_bvh_download, rt_bvh_refit and the traversal see
+// exactly what the multi-kernel path leaves; results are bit-identical to it and to oracle/lbvh_host.c.
+constexpr int kCT = 512;                        // threads per CTA (128 registers each)
+constexpr int kCW = kCT / 32;                   // warps per CTA
+constexpr int kMaxIpw = 8;                      // 32-key runs per warp and radix pass
+constexpr int kChunkCap = kCW * 32 * kMaxIpw;   // keys / leaves per CTA: 4096
+
+struct ClusterBuildArgs {
+    SceneView s;
+    InstRec* insts;            // instance boxes are written here (create_boxes)
+    const float* mesh_box;
+    int n_insts, do_inst_boxes;
+    const int* prim_offset;
+    int n;
+    float4* prim_world;
+    float* prim_box;
+    int* bounds_i;
+    float* bounds_f;
+    unsigned long long* keys_a; unsigned long long* keys_b;
+    int* vals_a; int* vals_b;
+    int key_shift, n_passes;
+    int* left; int* right; int* parent; int* range_lo; int* range_hi;
+    float* node_box;
+    float* edge_box;           // 6 floats x (n prefix unions, n suffix unions, G chunk totals)
+    CollapseArgs c;
+    unsigned long long* phase_ns;  // 12 time stamps of CTA 0 (RT_BUILD_TIMERS), else null
+};
+
+struct ClusterSync {
+    __device__ __forceinline__ void operator()() { cg::this_cluster().sync(); }
+};
+
+__device__ __forceinline__ unsigned long long build_global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void box_unite(float* acc, const float* b) {
+#pragma unroll
+    for (int k = 0; k < 3; k++) { acc[k] = fminf(acc[k], b[k]); acc[3 + k] = fmaxf(acc[3 + k], b[3 + k]); }
+}
+
+__global__ void __launch_bounds__(kCT, 1) k_build_cluster(ClusterBuildArgs a) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const int crank = (int)cluster.block_rank(), G = (int)cluster.num_blocks();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int T = G * kCT, gt = crank * kCT + tid;
+    const int n = a.n;
+    __shared__ unsigned s_big[kChunkCap];  // radix: digit counts per warp [kCW][kBins]; refit: arrival counters of the chunk
+    __shared__ unsigned s_hist[kBins];     // this CTA's digit totals, read by every CTA of the cluster
+    __shared__ int s_bounds[6];            // this CTA's scene bounds, read by every CTA of the cluster
+    __shared__ int s_red[6][kCW];
+    __shared__ unsigned s_wtot[kCW];
+    __shared__ float s_scan[2][kCW][6];
+    __shared__ float s_gb[6];
+    const bool clock = a.phase_ns != nullptr && crank == 0 && tid == 0;
+    if (clock) a.phase_ns[0] = build_global_ns();
+
+    // ---- create_boxes, world-space triangles, scene bounds
+    if (a.do_inst_boxes)
+        for (int i = gt; i < a.n_insts; i += T) {
+            InstRec I = a.insts[i];
+            instance_box(I, a.s.meshes, a.mesh_box);
+#pragma unroll
+            for (int k = 0; k < 6; k++) a.insts[i].box[k] = I.box[k];
+            a.insts[i].box_ok = I.box_ok;
+        }
+    {
+        int bl[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff}, bh[3] = {(int)0x80000000, (int)0x80000000, (int)0x80000000};
+        for (int p = gt; p < n; p += T) {
+            float lo[3], hi[3];
+            flatten_prim(a.s, a.prim_offset, p, a.prim_world, a.prim_box, lo, hi);
+#pragma unroll
+            for (int k = 0; k < 3; k++) { bl[k] = min(bl[k], float_flip(lo[k])); bh[k] = max(bh[k], float_flip(hi[k])); }
+        }
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            int l = bl[k], h = bh[k];
+            for (int o = 16; o; o >>= 1) {
+                l = min(l, __shfl_xor_sync(0xffffffffu, l, o));
+                h = max(h, __shfl_xor_sync(0xffffffffu, h, o));
+            }
+            if (lane == 0) { s_red[k][warp] = l; s_red[3 + k][warp] = h; }
+        }
+        __syncthreads();
+        if (tid < 6) {
+            int v = s_red[tid][0];
+            for (int w = 1; w < kCW; w++) v = tid < 3 ? min(v, s_red[tid][w]) : max(v, s_red[tid][w]);
+            s_bounds[tid] = v;
+        }
+    }
+    cluster.sync();
+    if (tid < 6) {
+        int v = s_bounds[tid];
+        for (int r = 0; r < G; r++) {
+            const int* rb = cluster.map_shared_rank(s_bounds, r);
+            v = tid < 3 ? min(v, rb[tid]) : max(v, rb[tid]);
+        }
+        s_gb[tid] = float_unflip(v);
+        if (crank == 0) { a.bounds_i[tid] = v; a.bounds_f[tid] = float_unflip(v); }
+    }
+    __syncthreads();
+    if (clock) a.phase_ns[1] = build_global_ns();
+
+    // ---- Morton keys
+    {
+        const float blo[3] = {s_gb[0], s_gb[1], s_gb[2]}, bhi[3] = {s_gb[3], s_gb[4], s_gb[5]};
+        for (int p = gt; p < n; p += T) {
+            a.keys_a[p] = morton_key(a.prim_world, p, blo, bhi, a.key_shift);
+            a.vals_a[p] = p;
+        }
+    }
+    cluster.sync();
+    if (clock) a.phase_ns[2] = build_global_ns();
+
+    // ---- stable LSD radix sort. Warp gw owns the ipw consecutive 32-key runs [gw * ipw, (gw + 1) * ipw): element order =
+    // (CTA, warp, run, lane), which is index order.
+    unsigned long long* kin = a.keys_a;
+    unsigned long long* kout = a.keys_b;
+    int* vin = a.vals_a;
+    int* vout = a.vals_b;
+    {
+        const int nruns = (n + 31) >> 5, nwarps = G * kCW;
+        const int ipw = (nruns + nwarps - 1) / nwarps;  // <= kMaxIpw (host-checked)
+        const int gw = crank * kCW + warp;
+        for (int pass = 0; pass < a.n_passes; pass++) {
+            const int shift = pass * 8;
+            for (int i = tid; i < kCW * kBins; i += kCT) s_big[i] = 0u;
+            __syncthreads();
+            unsigned long long k[kMaxIpw];
+            int v[kMaxIpw];
+#pragma unroll
+            for (int it = 0; it < kMaxIpw; it++) {
+                k[it] = ~0ull; v[it] = 0;
+                if (it < ipw) {
+                    const int idx = ((gw * ipw + it) << 5) + lane;
+                    const bool ok = idx < n;
+                    if (ok) { k[it] = kin[idx]; v[it] = vin[idx]; }
+                    const unsigned d = (unsigned)(k[it] >> shift) & 0xffu;
+                    const unsigned act = __ballot_sync(0xffffffffu, ok);
+                    if (ok) {
+                        const unsigned peers = __match_any_sync(act, d);
+                        if (lane == (31 - __clz((int)peers))) s_big[warp * kBins + d] += (unsigned)__popc(peers);
+                    }
+                    __syncwarp();
+                }
+            }
+            __syncthreads();
+            if (tid < kBins) {
+                unsigned t = 0;
+                for (int w = 0; w < kCW; w++) t += s_big[w * kBins + tid];
+                s_hist[tid] = t;
+            }
+            cluster.sync();  // every CTA's digit totals are in its s_hist
+            unsigned tot = 0, before = 0;
+            if (tid < kBins)
+                for (int r = 0; r < G; r++) {
+                    const unsigned* rh = cluster.map_shared_rank(s_hist, r);
+                    const unsigned c = rh[tid];
+                    tot += c;
+                    if (r < crank) before += c;
+                }
+            unsigned x = tot;  // exclusive scan over the digits (threads 0..255)
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += y;
+            }
+            if (lane == 31) s_wtot[warp] = x;
+            __syncthreads();
+            if (tid < kBins) {
+                unsigned run = x - tot + before;
+                for (int w = 0; w < warp; w++) run += s_wtot[w];
+                for (int w = 0; w < kCW; w++) {  // counts -> running offsets, warp by warp
+                    const unsigned c = s_big[w * kBins + tid];
+                    s_big[w * kBins + tid] = run;
+                    run += c;
+                }
+            }
+            __syncthreads();
+#pragma unroll
+            for (int it = 0; it < kMaxIpw; it++) {
+                if (it < ipw) {
+                    const int idx = ((gw * ipw + it) << 5) + lane;
+                    const bool ok = idx < n;
+                    const unsigned d = (unsigned)(k[it] >> shift) & 0xffu;
+                    const unsigned act = __ballot_sync(0xffffffffu, ok);
+                    if (ok) {
+                        const unsigned peers = __match_any_sync(act, d);
+                        const unsigned rank = (unsigned)__popc(peers & ((1u << lane) - 1u));
+                        const unsigned pos = s_big[warp * kBins + d] + rank;
+                        kout[pos] = k[it];
+                        vout[pos] = v[it];
+                        __syncwarp(act);
+                        if (lane == (31 - __clz((int)peers))) s_big[warp * kBins + d] += (unsigned)__popc(peers);
+                    }
+                    __syncwarp();
+                }
+            }
+            cluster.sync();  // the pass is in global memory; s_hist may be rewritten
+            unsigned long long* tk = kin; kin = kout; kout = tk;
+            int* tv = vin; vin = vout; vout = tv;
+        }
+    }
+    if (clock) a.phase_ns[3] = build_global_ns();
+
+    // ---- Karras topology
+    for (int i = gt; i < n - 1; i += T) karras_node(kin, n, i, a.left, a.right, a.parent, a.range_lo, a.range_hi);
+    cluster.sync();
+    if (clock) a.phase_ns[4] = build_global_ns();
+
+    // ---- BVH2 boxes
+    const int per = (n + G - 1) / G;  // leaves per CTA, <= kChunkCap
+    const int L0 = min(n, crank * per), L1 = min(n, L0 + per);
+    float* pre = a.edge_box;
+    float* suf = a.edge_box + 6 * (size_t)n;
+    float* ctot = a.edge_box + 12 * (size_t)n;
+    for (int i = tid; i < per; i += kCT) s_big[i] = 0u;
+    __syncthreads();
+    for (int j = L0 + tid; j < L1; j += kCT) {
+        const int p = vin[j];
+        float box[6];
+#pragma unroll
+        for (int k = 0; k < 6; k++) box[k] = a.prim_box[6 * (size_t)p + k];
+        int child = n - 1 + j;
+#pragma unroll
+        for (int k = 0; k < 6; k++) a.node_box[6 * (size_t)child + k] = box[k];
+        if (n == 1) continue;
+        int cur = a.parent[child];
+        while (cur >= 0) {
+            const int lo = a.range_lo[cur], hi = a.range_hi[cur];
+            if (lo < L0 || hi >= L1) break;  // spans chunks: united from prefix / suffix unions below
+            __threadfence_block();           // this thread's box of `child` is visible to the CTA before it arrives
+            if (atomicAdd(&s_big[cur - L0], 1u) == 0u) break;  // first arrival leaves; the second unites
+            __threadfence_block();
+            const int l = a.left[cur], r = a.right[cur];
+            const volatile float* sb = a.node_box + 6 * (size_t)(l == child ? r : l);
+            float o[6];
+#pragma unroll
+            for (int k = 0; k < 6; k++) o[k] = sb[k];
+            box_unite(box, o);
+#pragma unroll
+            for (int k = 0; k < 6; k++) a.node_box[6 * (size_t)cur + k] = box[k];
+            child = cur;
+            cur = a.parent[cur];
+        }
+    }
+    __syncthreads();
+    {   // prefix and suffix unions of the chunk's leaf boxes: thread t owns the R consecutive leaves [j0, j1)
+        const int R = (per + kCT - 1) / kCT;
+        const int j0 = min(L1, L0 + tid * R), j1 = min(L1, j0 + R);
+        float run[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        for (int j = j0; j < j1; j++) box_unite(run, a.node_box + 6 * (size_t)(n - 1 + j));
+        float inc[6], dec[6];
+#pragma unroll
+        for (int k = 0; k < 6; k++) { inc[k] = run[k]; dec[k] = run[k]; }
+        for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) {
+                const float yu = __shfl_up_sync(0xffffffffu, inc[k], o), yd = __shfl_down_sync(0xffffffffu, dec[k], o);
+                if (lane >= o) inc[k] = k < 3 ? fminf(inc[k], yu) : fmaxf(inc[k], yu);
+                if (lane + o < 32) dec[k] = k < 3 ? fminf(dec[k], yd) : fmaxf(dec[k], yd);
+            }
+        }
+        if (lane == 31) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) s_scan[0][warp][k] = inc[k];
+        }
+        if (lane == 0) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) s_scan[1][warp][k] = dec[k];
+        }
+        __syncthreads();
+        float ex[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        float sx[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        for (int w = 0; w < warp; w++) box_unite(ex, s_scan[0][w]);
+        for (int w = warp + 1; w < kCW; w++) box_unite(sx, s_scan[1][w]);
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+            const float yu = __shfl_up_sync(0xffffffffu, inc[k], 1), yd = __shfl_down_sync(0xffffffffu, dec[k], 1);
+            if (lane > 0) ex[k] = k < 3 ? fminf(ex[k], yu) : fmaxf(ex[k], yu);
+            if (lane < 31) sx[k] = k < 3 ? fminf(sx[k], yd) : fmaxf(sx[k], yd);
+        }
+        for (int j = j0; j < j1; j++) {
+            box_unite(ex, a.node_box + 6 * (size_t)(n - 1 + j));
+#pragma unroll
+            for (int k = 0; k < 6; k++) pre[6 * (size_t)j + k] = ex[k];
+        }
+        for (int j = j1 - 1; j >= j0; j--) {
+            box_unite(sx, a.node_box + 6 * (size_t)(n - 1 + j));
+#pragma unroll
+            for (int k = 0; k < 6; k++) suf[6 * (size_t)j + k] = sx[k];
+        }
+        if (tid == 0) {
+            float t6[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+            for (int w = 0; w < kCW; w++) box_unite(t6, s_scan[0][w]);
+#pragma unroll
+            for (int k = 0; k < 6; k++) ctot[6 * (size_t)crank + k] = t6[k];
+        }
+    }
+    cluster.sync();
+    if (clock) a.phase_ns[5] = build_global_ns();
+    for (int i = gt; i < n - 1; i += T) {  // nodes whose leaves span chunks
+        const int lo = a.range_lo[i], hi = a.range_hi[i];
+        const int cl = lo / per, ch = hi / per;
+        if (cl == ch) continue;
+        float box[6];
+#pragma unroll
+        for (int k = 0; k < 6; k++) box[k] = suf[6 * (size_t)lo + k];
+        box_unite(box, pre + 6 * (size_t)hi);
+        for (int c = cl + 1; c < ch; c++) box_unite(box, ctot + 6 * (size_t)c);
+#pragma unroll
+        for (int k = 0; k < 6; k++) a.node_box[6 * (size_t)i + k] = box[k];
+    }
+    cluster.sync();
+    if (clock) a.phase_ns[6] = build_global_ns();
+
+    // ---- BVH8
+    ClusterSync csync;
+    collapse_levels(a.c, csync, G, crank);
+    if (clock) a.phase_ns[7] = build_global_ns();
 }
 
 }  // namespace
@@ -820,6 +1186,117 @@ int radix_sort_pairs(cudaStream_t st, unsigned long long*& keys_a, unsigned long
     return launches;
 }
 
+// Cluster size of the one-launch build for a scene of n triangles, or 0 to use the multi-kernel pipeline.
+static int cluster_build_size(int n) {
+    if (n < 1) return 0;
+    int want = 16;
+    if (const char* e = std::getenv("RT_BUILD_PATH")) { if (std::atoi(e) == 1) return 0; }
+    if (const char* e = std::getenv("RT_BUILD_CLUSTER")) { int v = std::atoi(e); if (v == 8 || v == 16 || v == 4 || v == 2 || v == 1) want = v; }
+    static int max_cluster = -1;  // largest cluster of k_build_cluster this device can co-schedule
+    if (max_cluster < 0) {
+        max_cluster = 0;
+        cudaFuncSetAttribute(k_build_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        for (int g = 16; g >= 1; g >>= 1) {
+            cudaLaunchConfig_t cfg;
+            std::memset(&cfg, 0, sizeof cfg);
+            cfg.gridDim = dim3(g); cfg.blockDim = dim3(kCT);
+            cudaLaunchAttribute at;
+            at.id = cudaLaunchAttributeClusterDimension;
+            at.val.clusterDim.x = g; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+            cfg.attrs = &at; cfg.numAttrs = 1;
+            int nc = 0;
+            if (cudaOccupancyMaxActiveClusters(&nc, k_build_cluster, &cfg) == cudaSuccess && nc >= 1) { max_cluster = g; break; }
+            (void)cudaGetLastError();
+        }
+    }
+    int G = want < max_cluster ? want : max_cluster;
+    if (G < 1) return 0;
+    if ((long long)n > (long long)G * kChunkCap) return 0;
+    return G;
+}
+
+static int launch_cluster_build(RtScene* sc, const SceneView& v, int n, int key_shift, int n_passes, int G) {
+    Bvh& b = sc->bvh;
+    cudaStream_t st = sc->stream;
+    const size_t level_cap = (size_t)n + 8;
+    if (b.edge_box.reserve(sizeof(float) * 6 * (2 * (size_t)n + 16)) ||
+        b.collapse_scratch.reserve(sizeof(int) * (level_cap * 2 + level_cap * 8 + level_cap * 2 + (size_t)G * 4 + 16)))
+        return RT_ERR_OUT_OF_MEMORY;
+    int* bounds_i = b.scene_bounds.as<int>();
+    ClusterBuildArgs a;
+    std::memset(&a, 0, sizeof a);
+    a.s = v;
+    a.insts = sc->d_insts.as<InstRec>();
+    a.mesh_box = sc->d_mesh_box.as<float>();
+    a.n_insts = sc->n_instances;
+    a.do_inst_boxes = sc->boxes_valid ? 0 : 1;
+    a.prim_offset = b.work.as<int>();
+    a.n = n;
+    a.prim_world = b.prim_world.as<float4>();
+    a.prim_box = b.prim_box.as<float>();
+    a.bounds_i = bounds_i;
+    a.bounds_f = (float*)(bounds_i + 8);
+    a.keys_a = b.keys_a.as<unsigned long long>(); a.keys_b = b.keys_b.as<unsigned long long>();
+    a.vals_a = b.vals_a.as<int>(); a.vals_b = b.vals_b.as<int>();
+    a.key_shift = key_shift; a.n_passes = n_passes;
+    a.left = b.left.as<int>(); a.right = b.right.as<int>(); a.parent = b.parent.as<int>();
+    a.range_lo = b.range_lo.as<int>(); a.range_hi = b.range_hi.as<int>();
+    a.node_box = b.node_box.as<float>();
+    a.edge_box = b.edge_box.as<float>();
+    static const bool timers = [] { const char* e = std::getenv("RT_BUILD_TIMERS"); return e && std::atoi(e); }();
+    a.phase_ns = timers ? (unsigned long long*)(bounds_i + 16) : nullptr;
+    int* w = b.collapse_scratch.as<int>();
+    CollapseArgs& c = a.c;
+    c.n = n;
+    c.left = a.left; c.right = a.right; c.range_lo = a.range_lo; c.range_hi = a.range_hi;
+    c.node_box = a.node_box;
+    c.sorted_prim = a.vals_a;  // even number of passes
+    c.prim_world = a.prim_world;
+    c.nodes8 = b.nodes8.as<uint4>();
+    c.prims8 = b.prims8.as<float4>();
+    c.prim_order8 = b.prim_order8.as<int>();
+    c.level_a = w; w += level_cap;
+    c.level_b = w; w += level_cap;
+    c.slots = w; w += level_cap * 8;
+    c.counts = w; w += level_cap * 2;
+    c.block_tot = w; w += (size_t)G * 4;
+    c.result = w;
+    c.node8_root = b.node8_root.as<int>();
+    c.node8_slot = b.node8_slot.as<int>();
+    cudaLaunchConfig_t cfg;
+    std::memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(G); cfg.blockDim = dim3(kCT); cfg.stream = st;
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeClusterDimension;
+    at.val.clusterDim.x = G; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+    cfg.attrs = &at; cfg.numAttrs = 1;
+    RT_CUDA(cudaLaunchKernelEx(&cfg, k_build_cluster, a));
+    sc->kernel_launches++;
+    sc->boxes_valid = true;
+    b.cluster_size = G;
+    RT_CUDA(cudaMemcpyAsync(sc->h_pinned + 32, c.result, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (a.phase_ns) RT_CUDA(cudaMemcpyAsync(sc->h_pinned + 50, a.phase_ns, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    return RT_OK;
+}
+
+// Common tail of both builders: the collapse result is on its way to h_pinned[32..36).
+static int finish_enqueue(RtScene* sc, RtBuildStats* stats, bool same_layout, int launches0, bool sync) {
+    Bvh& b = sc->bvh;
+    cudaStream_t st = sc->stream;
+    RT_CUDA(cudaEventRecord(sc->ev[1], st));
+    RT_CUDA(cudaGetLastError());
+    b.valid = true;  // provisional until finish_build() has looked at the result
+    b.topology_valid = true;
+    if (!same_layout) {
+        b.topo_meshes.resize((size_t)sc->n_instances);
+        for (int i = 0; i < sc->n_instances; i++) b.topo_meshes[i] = sc->instances[i].mesh;
+    }
+    b.build_launches = sc->kernel_launches - launches0;
+    if (!sync) return RT_OK;
+    RT_CUDA(cudaStreamSynchronize(st));
+    return finish_build(sc, stats);
+}
+
 int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     Bvh& b = sc->bvh;
     // prefix of triangle counts per instance (host). It only depends on which mesh every instance uses: when that is
@@ -848,7 +1325,8 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     b.n_nodes8 = 0;
     if (stats) { stats->n_prims = n; stats->n_bvh2_nodes = b.n_bvh2_nodes; stats->n_bvh8_nodes = 0; stats->kernel_launches = 0; stats->ms_build = 0.f; }
     RT_CUDA(cudaEventRecord(sc->ev[0], st));
-    if (int rc = update_instance_boxes(sc)) return rc;
+    const int cluster_G = cluster_build_size(n);  // > 0: the one-launch build, which also computes the instance boxes
+    if (!cluster_G) { if (int rc = update_instance_boxes(sc)) return rc; }
     if (n == 0) {
         b.valid = true;
         RT_CUDA(cudaEventRecord(sc->ev[1], st));
@@ -858,7 +1336,7 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     int nb = (n + kRadixTile - 1) / kRadixTile;
     int max_nodes8 = n;  // every BVH8 node owns >= 1 BVH2 internal node with > 3 triangles (or is the root)
     if (b.work.reserve(sizeof(int) * ((size_t)sc->n_instances + 1)) || b.prim_world.reserve(sizeof(float4) * 3 * (size_t)n) ||
-        b.prim_box.reserve(sizeof(float) * 6 * (size_t)n) || b.scene_bounds.reserve(64) ||
+        b.prim_box.reserve(sizeof(float) * 6 * (size_t)n) || b.scene_bounds.reserve(256) ||
         b.keys_a.reserve(8 * (size_t)n) || b.keys_b.reserve(8 * (size_t)n) || b.vals_a.reserve(4 * (size_t)n) ||
         b.vals_b.reserve(4 * (size_t)n) || b.hist.reserve(sizeof(unsigned) * kBins * ((size_t)nb + 1)) ||
         b.left.reserve(4 * (size_t)n) || b.right.reserve(4 * (size_t)n) || b.parent.reserve(4 * 2 * (size_t)n) ||
@@ -886,10 +1364,19 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     SceneView v = make_view(sc, false);
     int* bounds_i = b.scene_bounds.as<int>();
     float* bounds_f = (float*)(bounds_i + 8);
-    k_bounds_init<<<1, 32, 0, st>>>(bounds_i);
-    k_flatten<<<grid_for(n), kThreads, 0, st>>>(v, b.work.as<int>(), n, b.prim_world.as<float4>(), b.prim_box.as<float>(), bounds_i);
     const int key_shift = n <= (1 << 20) ? 31 : 0;
     const int n_passes = key_shift ? 4 : 8;
+    // One launch on one thread-block cluster when the scene fits (n <= G * 4096); RT_BUILD_PATH=1 forces the multi-kernel
+    // pipeline, RT_BUILD_CLUSTER=8|16 the cluster size (read per build so that tests can switch).
+    if (cluster_G) {
+        if (int rc = launch_cluster_build(sc, v, n, key_shift, n_passes, cluster_G)) return rc;
+        b.sorted_keys = b.keys_a.as<unsigned long long>();  // even number of passes: back in keys_a / vals_a
+        b.sorted_vals = b.vals_a.as<int>();
+        b.build_path = 2;
+        return finish_enqueue(sc, stats, same_layout, launches0, sync);
+    }
+    k_bounds_init<<<1, 32, 0, st>>>(bounds_i);
+    k_flatten<<<grid_for(n), kThreads, 0, st>>>(v, b.work.as<int>(), n, b.prim_world.as<float4>(), b.prim_box.as<float>(), bounds_i);
     k_morton<<<grid_for(n), kThreads, 0, st>>>(b.prim_box.as<float>(), b.prim_world.as<float4>(), n, bounds_i,
                                                b.keys_a.as<unsigned long long>(), b.vals_a.as<int>(), bounds_f, key_shift);
     sc->kernel_launches += 3;
@@ -948,19 +1435,8 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     RT_CUDA(cudaLaunchCooperativeKernel((void*)k_collapse, dim3(G), dim3(kThreads), args, 0, st));
     sc->kernel_launches++;
     RT_CUDA(cudaMemcpyAsync(sc->h_pinned + 32, a.result, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    RT_CUDA(cudaEventRecord(sc->ev[1], st));
-    RT_CUDA(cudaGetLastError());
-    b.valid = true;  // provisional until finish_build() has looked at the result
-    b.topology_valid = true;
-    if (!same_layout) {
-        b.topo_meshes.resize((size_t)sc->n_instances);
-        for (int i = 0; i < sc->n_instances; i++) b.topo_meshes[i] = sc->instances[i].mesh;
-    }
-    b.build_launches = sc->kernel_launches - launches0;
     b.build_path = 1;
-    if (!sync) return RT_OK;
-    RT_CUDA(cudaStreamSynchronize(st));
-    return finish_build(sc, stats);
+    return finish_enqueue(sc, stats, same_layout, launches0, sync);
 }
 
 bool refit_possible(const RtScene* sc) {

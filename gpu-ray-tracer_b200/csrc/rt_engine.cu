@@ -63,7 +63,7 @@ void DevBuf::release() {
 void Bvh::release() {
     DevBuf* all[] = {&prim_world, &prim_box, &scene_bounds, &keys_a, &keys_b, &vals_a, &vals_b, &hist, &left, &right,
                      &parent, &range_lo, &range_hi, &flags, &node_box, &nodes8, &prims8, &prim_order8, &work,
-                     &collapse_scratch, &node8_root, &node8_slot};
+                     &collapse_scratch, &edge_box, &node8_root, &node8_slot};
     for (DevBuf* b : all) b->release();
     if (h_off) { cudaFreeHost(h_off); h_off = nullptr; h_off_cap = 0; }
     off_in_flight = false;
@@ -1973,7 +1973,16 @@ int rt_debug_get(RtScene* sc, int32_t what, int64_t* out) {
         case RT_DEBUG_BVH8_LEVELS: *out = sc->bvh.n_levels8; break;
         case RT_DEBUG_BUILD_PATH: *out = sc->bvh.build_path; break;
         case RT_DEBUG_BUILD_LAUNCHES: *out = sc->bvh.build_launches; break;
-        default: set_error("unknown debug counter"); return RT_ERR_INVALID_ARG;
+        case RT_DEBUG_BUILD_CLUSTER: *out = sc->bvh.build_path == 2 ? sc->bvh.cluster_size : 0; break;
+        default:
+            // RT_DEBUG_BUILD_PHASE_NS + i, i in 0..6: nanoseconds CTA 0 of the last cluster build spent in phase i (flatten +
+            // bounds, Morton, sort, Karras, chunk-local boxes, spanning boxes, BVH8 collapse); needs RT_BUILD_TIMERS=1
+            if (what >= RT_DEBUG_BUILD_PHASE_NS && what < RT_DEBUG_BUILD_PHASE_NS + 7) {
+                const unsigned long long* t = sc->h_pinned + 50;
+                *out = (int64_t)(t[what - RT_DEBUG_BUILD_PHASE_NS + 1] - t[what - RT_DEBUG_BUILD_PHASE_NS]);
+                break;
+            }
+            set_error("unknown debug counter"); return RT_ERR_INVALID_ARG;
     }
     return RT_OK;
 }

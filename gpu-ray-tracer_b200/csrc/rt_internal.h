@@ -53,6 +53,8 @@ struct Bvh {
     const int* sorted_vals = nullptr;
     DevBuf work;         // per-instance triangle prefix
     DevBuf collapse_scratch;  // level lists, slots, counts, block totals
+    DevBuf edge_box;          // cluster build: prefix / suffix unions of each CTA's leaf chunk
+    int cluster_size = 0;     // CTAs of the last one-launch build
     // kept for rt_bvh_refit: which BVH2 node every BVH8 node / slot came from, and the instance layout the
     // topology was built for (refit is only valid while every instance keeps its mesh)
     DevBuf node8_root;   // int[n_nodes8]
@@ -111,7 +113,7 @@ struct RtScene {
     bool exchange_pending = false;      // ... whose outcome (h_pinned[48]) rt_frame_finish still has to look at
     int pend_chunks = 1;
     bool pend_direct = false;
-    // pinned host memory, u64 units: [32,36) build result, [48] exchange time-out mask, [40,42) live counts of the bounce waves,
+    // pinned host memory, u64 units: [32,36) build result, [48] exchange time-out mask, [50,58) phase time stamps of the cluster build (RT_BUILD_TIMERS), [40,42) live counts of the bounce waves,
     // [64 + 32 c, 96 + 32 c) counters of chunk c
     unsigned long long* h_pinned = nullptr;
     void* h_inst = nullptr;             // pinned staging of the instance records (rt_scene_set_instances)

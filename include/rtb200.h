@@ -334,7 +334,9 @@ enum {
     RT_DEBUG_PREFIX_UPLOADS = 0, /* builds that had to upload the per-instance triangle prefix (unchanged meshes: once) */
     RT_DEBUG_BVH8_LEVELS = 1,    /* depth of the BVH8 of the last build */
     RT_DEBUG_BUILD_PATH = 2,     /* 1 = multi-kernel pipeline, 2 = one-launch thread-block-cluster build */
-    RT_DEBUG_BUILD_LAUNCHES = 3  /* kernels the last build / refit launched */
+    RT_DEBUG_BUILD_LAUNCHES = 3, /* kernels the last build / refit launched */
+    RT_DEBUG_BUILD_CLUSTER = 4,  /* CTAs in the cluster of the last one-launch build (0: multi-kernel pipeline) */
+    RT_DEBUG_BUILD_PHASE_NS = 16 /* + i (0..6): ns per phase of the last cluster build, with RT_BUILD_TIMERS=1 in the environment */
 };
 int rt_debug_get(RtScene* scene, int32_t what, int64_t* out);
 

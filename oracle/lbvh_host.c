@@ -12,7 +12,7 @@
  *   - boxes by a post-order union (the kernels use atomics-ordered bottom-up refit),
  *   - BVH8 collapse, slot assignment and quantisation by a breadth-first queue (the kernels use a
  *     cooperative level-synchronous pass with scans).
- * tests/test_bvh_build.py compares every array of both builds for equality.
+ * tests/test_gpu_parity.py::test_bvh_build_bit_exact_vs_host compares every array of both builds for equality.
  *
  * Floating-point rules shared with the kernels (both sides compile without FMA contraction):
  * every expression below is written operation by operation in the order documented in

@@ -127,13 +127,32 @@ BVH_CASES = [("world1", {}), ("world4", {}), ("world16", {}), ("world8_stress", 
              ("world16", {"grid_size": 150})]
 
 
-@pytest.mark.parametrize("name,kw", BVH_CASES, ids=lambda v: v if isinstance(v, str) else "-".join("%s%s" % i for i in v.items()))
-def test_bvh_build_bit_exact_vs_host(pkg, scenes, name, kw):
-    """GPU LBVH (Morton, radix sort, Karras, refit) and BVH8 collapse == the sequential host build."""
+# builder: auto = the one-launch cluster build when the scene fits a cluster (n <= 16 x 4096 triangles), else the
+# multi-kernel pipeline; multi = the pipeline forced; cluster8 = an 8-CTA cluster forced
+BVH_BUILDS = [(n, kw, b) for n, kw in BVH_CASES for b in (("auto", "multi", "cluster8") if not kw and n != "grid64" else ("auto",))]
+
+
+@pytest.mark.parametrize("name,kw,builder", BVH_BUILDS, ids=lambda v: v if isinstance(v, str) else "-".join("%s%s" % i for i in v.items()))
+def test_bvh_build_bit_exact_vs_host(pkg, scenes, monkeypatch, name, kw, builder):
+    """GPU LBVH (Morton, radix sort, Karras, refit) and BVH8 collapse == the sequential host build, for both builders."""
     w, s = scenes(name, **kw)
-    s.build_bvh()
+    monkeypatch.delenv("RT_BUILD_PATH", raising=False)
+    monkeypatch.delenv("RT_BUILD_CLUSTER", raising=False)
+    if builder == "multi":
+        monkeypatch.setenv("RT_BUILD_PATH", "1")
+    elif builder == "cluster8":
+        monkeypatch.setenv("RT_BUILD_CLUSTER", "8")
+    bs = s.build_bvh()
+    path, csize = s.debug_get(pkg.RT_DEBUG_BUILD_PATH), s.debug_get(pkg.RT_DEBUG_BUILD_CLUSTER)
+    if builder == "multi" or bs["n_prims"] > 16 * 4096:
+        assert path == 1 and bs["kernel_launches"] >= 10
+    elif builder == "cluster8":
+        assert (path, csize, bs["kernel_launches"]) == (2, 8, 1) if bs["n_prims"] <= 8 * 4096 else path == 1
+    else:
+        assert path == 2 and csize in (8, 16) and bs["kernel_launches"] == 1
     d = s.download_bvh()
     hb = ob.OracleBvh(w)
+    assert bs["n_levels8"] == hb.levels
     assert d["n_prims"] == hb.n_prims and d["n_nodes8"] == hb.n_nodes8
     assert (d["bounds"] == hb.bounds).all()
     assert (d["morton"] == hb.morton).all()
@@ -144,6 +163,13 @@ def test_bvh_build_bit_exact_vs_host(pkg, scenes, name, kw):
     assert (d["prim_order8"] == hb.prim_order8).all()
     assert (d["nodes8"] == hb.nodes8).all()
     assert (d["prims8"].view(np.uint32) == hb.prims8.view(np.uint32)).all()
+    # the tree the builder left is the one the frame is traced through, and a refit of it reproduces it
+    if name in ("world4", "world16"):
+        c, _ = s.render()
+        c2, _ = s.render(flags=pkg.RT_RENDER_REFIT_BVH)
+        assert (c == c2).all()
+        d2 = s.download_bvh()
+        assert (d2["nodes8"] == hb.nodes8).all() and (d2["node_boxes"].view(np.uint32) == hb.node_boxes.view(np.uint32)).all()
 
 
 def test_random_rays_vs_oracle(pkg, scenes):

@@ -40,7 +40,7 @@ def run_ref_gpu(path, tmp_path):
 CASES = [("world1", {}, 1e-4), ("world4", {}, 0.0), ("world8", {}, 0.0), ("world16", {}, 2e-4), ("world8_stress", {}, 1e-4),
          ("world1", {"depth": 0}, 1e-4), ("world1", {"depth": 1}, 1e-4), ("world1", {"depth": 9}, 1e-4),
          ("world8_stress", {"depth": 1}, 1e-4), ("world8_stress", {"depth": 9}, 2e-4),
-         ("grid64", {}, 2e-4), ("grid64_mirror", {}, 5e-4)]
+         ("grid64", {}, 2e-3), ("grid64_mirror", {}, 5e-3)]
 
 
 @pytest.mark.skipif(not os.path.exists(REF_GPU), reason="oracle/_ref/ref_gpu not built (needs /root/reference at build time)")
