@@ -10,8 +10,13 @@ Default workload: world16.json at 3840x2160, depth 9 (BASELINE.json configs[3], 
   value : frame with everything resident in HBM (canvas stays on the device)
   e2e   : the same frame through the C ABI with HOST buffers — instances and camera uploaded,
           canvas copied back into pinned host memory — inside the timed region
-  N > 1 : screen tiles dealt round-robin to the ranks, scene + BVH replicated, one NCCL
-          all-gather of the RGBA8 slabs per frame and a de-interleave kernel ("strong" scaling)
+  N > 1 : screen tiles dealt round-robin to the ranks, scene + BVH replicated; the frame's kernels
+          store their pixels straight into the gathering rank's canvas over NVLink peer memory and
+          signal through a mailbox (RT_RENDER_PEER_STORE, --gather fused-root; fused-all = every
+          rank receives the frame). p2p / nccl: the round-1 exchanges (slab + push kernel, NCCL
+          all-gather + de-interleave), kept as checked alternatives ("strong" scaling)
+  ref_cuda / stress : N = 1 — the reference's own CUDA build (oracle/_ref/ref_gpu, bench() scope)
+          timed on the same GPU in the same run, and the same measurement on world8_stress
 
 `--impl reference` times the reference's own serial CPU path (oracle/_ref/ref_cpu, built from the
 unmodified sources; falls back to the oracle port) on a bounded sample of the same workload.
@@ -48,10 +53,15 @@ def parse_args():
     ap.add_argument("--grid-size", type=int, default=0)
     ap.add_argument("--tile-w", type=int, default=32)
     ap.add_argument("--tile-h", type=int, default=16)
-    ap.add_argument("--gather", default="p2p", choices=["p2p", "p2p-nccl", "nccl"],
-                    help="N > 1, device-resident frame: p2p = tiles stored into every rank's canvas over NVLink peer memory and a "
-                         "mailbox barrier over the same peer memory (no collective call); p2p-nccl = the same stores with a "
-                         "1-element NCCL all-reduce as barrier; nccl = all-gather of the slabs + de-interleave kernel")
+    ap.add_argument("--gather", default="fused-root", choices=["fused-root", "fused-all", "p2p", "p2p-nccl", "nccl"],
+                    help="N > 1, device-resident frame: fused-root = the kernels that produce the pixels store them into rank 0's "
+                         "canvas over NVLink peer memory and signal its mailbox (the framebuffer gathered, no extra kernel, no "
+                         "collective); fused-all = the same into every rank's canvas; p2p = slab + rt_push_tiles_signal into every "
+                         "rank's canvas; p2p-nccl = rt_push_tiles + 1-element all-reduce; nccl = all-gather of the slabs + "
+                         "de-interleave kernel")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA-build leg (N = 1)")
+    ap.add_argument("--no-stress", action="store_true", help="skip the world8_stress block (N = 1)")
+    ap.add_argument("--split-shade", action="store_true", help="RT_RENDER_SPLIT_SHADE: the round-1 split pipeline instead of k_tile")
     ap.add_argument("--band-h", type=int, default=4,
                     help="N > 1, e2e: rows per full-width band dealt round-robin to the ranks (each rank copies its bands into the one shared host canvas)")
     ap.add_argument("--host-chunks", type=int, default=0, help="e2e: chunks per frame for copy/render overlap (0 = the library's default)")
@@ -208,6 +218,108 @@ def run_reference_arm(a):
     return 0
 
 
+
+# ------------------------------------------------------------------ the reference's own CUDA build, same GPU, same run
+def ref_cuda_run(a, scene_name, frames=7):
+    """oracle/_ref/ref_gpu (the unmodified reference compiled by oracle/ref_build, nvcc -arch=sm_100) on the bench
+    workload: median ms of rtracer::gpu::update_scene(scene, 16, true) = BVH build + trace, the scope of its bench()
+    (/root/reference/src/main.cc:65-68,210-216, -d 16). Its canvas lives in managed memory and is not read by the host
+    inside the timed scope. Returns None when the binary is not there."""
+    ref_gpu = os.path.join(ROOT, "oracle", "_ref", "ref_gpu")
+    if not os.path.exists(ref_gpu):
+        return None
+    cfg = json.load(open(os.path.join(ROOT, "scenes", scene_name + ".json")))
+    cfg.update(width=a.width, height=a.height, depth=a.depth)
+    if a.grid_size:
+        cfg["grid_size"] = a.grid_size
+    with tempfile.NamedTemporaryFile("w", suffix=".json", delete=False) as f:
+        json.dump(cfg, f)
+        tmp = f.name
+    try:
+        out = subprocess.run([ref_gpu, tmp, "--gpu", "--frames", str(frames), "--kd", "16"], capture_output=True, text=True, timeout=600)
+        if out.returncode != 0:
+            return {"error": (out.stderr or out.stdout)[-200:]}
+        return json.loads(out.stdout.strip().splitlines()[-1])
+    except Exception as e:  # noqa: BLE001
+        return {"error": str(e)[-200:]}
+    finally:
+        os.unlink(tmp)
+
+
+def ref_cuda_block(a, scene_name, rays_per_frame, ms_dev, ms_e2e):
+    info = ref_cuda_run(a, scene_name)
+    if info is None:
+        return {"unavailable": "oracle/_ref/ref_gpu not built (needs /root/reference at build time)"}
+    if "error" in info:
+        return {"unavailable": info["error"]}
+    ms = info["ms_median"]
+    return {"ms": ms, "ms_min": info.get("ms_min"), "mrays_s": rays_per_frame / ms / 1e3,
+            "scope": "rtracer::gpu::update_scene = BVH build + trace per frame, -d 16, canvas left in managed memory (the reference's bench() scope)",
+            "binary": "oracle/_ref/ref_gpu (unmodified reference sources, nvcc -arch=sm_100), run on the same GPU after the timed region",
+            "rays": "counted by this engine's frame of the same scene (both answer the same closest-hit queries)",
+            "ratio_device_resident": ms / ms_dev, "ratio_e2e_pinned_host_canvas": ms / ms_e2e,
+            "note": "ratio_device_resident compares like scopes (neither side reads the frame on the host); ratio_e2e charges this "
+                    "engine the copy of the frame into pinned host memory, which the reference's scope does not contain"}
+
+
+def single_gpu_block(pkg, torch, a, scene_name, steps, flush):
+    """The N = 1 measurement of the main line (device-resident `value`, `e2e` with host buffers, reference CUDA build) for a
+    second scene: world8_stress, the other scene north_star's >= 10x target names."""
+    wfile = pkg.World(os.path.join(ROOT, "scenes", scene_name + ".json"), width=a.width, height=a.height, depth=a.depth)
+    scene = pkg.Scene(wfile, device=int(os.environ.get("LOCAL_RANK", "0")))
+    scene.set_stream(torch.cuda.current_stream().cuda_stream)
+    W, H = wfile.width, wfile.height
+    desc = wfile.desc
+    canvas_dev = torch.zeros(H * W, dtype=torch.int32, device="cuda")
+    host_canvas = torch.zeros(H * W, dtype=torch.int32).pin_memory()
+    base = (0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH) | (pkg.RT_RENDER_SPLIT_SHADE if a.split_shade else 0)
+
+    def dev():
+        scene.render(flags=base | pkg.RT_RENDER_CANVAS_DEVICE | pkg.RT_RENDER_ASYNC, out_ptr=canvas_dev.data_ptr())
+        return None
+
+    def e2e():
+        scene.set_instances(desc.instances, desc.n_instances)
+        scene.set_camera(desc.camera)
+        _, st = scene.render(flags=base, out_ptr=host_canvas.data_ptr())
+        return st
+
+    def timed(fn, finish):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        total, outs = 0.0, []
+        for _ in range(steps):
+            flush.zero_()
+            torch.cuda.synchronize()
+            ev0.record()
+            r = fn()
+            ev1.record()
+            ev1.synchronize()
+            outs.append(r if r is not None else finish())
+            total += ev0.elapsed_time(ev1)
+        return total / steps, outs
+
+    for _ in range(3):
+        dev(); torch.cuda.synchronize(); scene.finish(); e2e()
+    want = None
+    ms_dev, outs = timed(dev, scene.finish)
+    want = canvas_dev.cpu().numpy().view(np.uint32)
+    ms_e2e, outs_e = timed(e2e, None)
+    if not (host_canvas.numpy().view(np.uint32) == want).all():
+        raise SystemExit("%s: end-to-end frame differs from the device-resident frame" % scene_name)
+    rays = outs[0]["rays_total"]
+    st = outs[0]
+    block = {"workload": "%s.json %dx%d depth %d" % (scene_name, a.width, a.height, a.depth), "value": rays / ms_dev / 1e3, "unit": UNIT,
+             "ms_per_step": ms_dev, "steps": steps, "rays_per_frame": rays, "rays_secondary": st["rays_secondary"], "waves": st["waves"],
+             "e2e": {"value": rays / ms_e2e / 1e3, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": C.sizeof(pkg.RtInstance) * desc.n_instances + C.sizeof(pkg.RtCamera),
+                     "d2h_bytes_per_step": 4 * W * H},
+             "breakdown_ms": {k: sum(o[k] for o in outs) / len(outs) for k in ("ms_build", "ms_primary", "ms_shade", "ms_bounce")},
+             "gpu_launches": sum(o["kernel_launches"] for o in outs)}
+    if not a.no_ref_cuda:
+        block["ref_cuda"] = ref_cuda_block(a, scene_name, rays, ms_dev, ms_e2e)
+    scene.close()
+    return block
+
+
 # ------------------------------------------------------------------ our arm
 def hbm_peak():
     try:
@@ -234,7 +346,8 @@ def run_ours(a):
                       grid_size=a.grid_size)
     scene = pkg.Scene(wfile, device=local_rank)
     W, H = wfile.width, wfile.height
-    base = (0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH) | (pkg.RT_RENDER_SORT_RAYS if a.sort_rays else 0)
+    base = (0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH) | (pkg.RT_RENDER_SORT_RAYS if a.sort_rays else 0) | \
+        (pkg.RT_RENDER_SPLIT_SHADE if a.split_shade else 0)
     dev_flags = base | pkg.RT_RENDER_CANVAS_DEVICE | (pkg.RT_RENDER_TILED_OUTPUT if world > 1 else 0)
     params = scene.params(flags=dev_flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h)
     canvas_dev = torch.zeros(H * W, dtype=torch.int32, device="cuda")
@@ -259,22 +372,32 @@ def run_ours(a):
     peer_ptrs, own_canvas_ptr, token = None, None, None
     epoch = [0]
     gather = a.gather if world > 1 else "none"
-    if gather in ("p2p", "p2p-nccl"):
+    fused = gather in ("fused-root", "fused-all")
+    fused_sets = None  # [parity][rank] canvases of RT_RENDER_PEER_STORE
+    if gather in ("p2p", "p2p-nccl") or fused:
         try:
-            own_canvas_ptr, handle = pkg.peer_canvas_alloc(W * H)
-            mine = torch.tensor(list(handle), dtype=torch.uint8, device="cuda")
-            allh = torch.empty(world * 64, dtype=torch.uint8, device="cuda")
+            n_own = 2 if fused else 1
+            own = [pkg.peer_canvas_alloc(W * H) for _ in range(n_own)]
+            mine = torch.tensor([b for _, hnd in own for b in hnd], dtype=torch.uint8, device="cuda")
+            allh = torch.empty(world * 64 * n_own, dtype=torch.uint8, device="cuda")
             dist.all_gather_into_tensor(allh, mine)
             allh = bytes(allh.cpu().numpy().tobytes())
-            peer_ptrs = [own_canvas_ptr if r == rank else pkg.peer_canvas_open(allh[64 * r:64 * r + 64]) for r in range(world)]
+            sets = [[own[k][0] if r == rank else pkg.peer_canvas_open(allh[64 * (r * n_own + k):64 * (r * n_own + k) + 64])
+                     for r in range(world)] for k in range(n_own)]
+            own_canvas_ptr = own[0][0]
+            peer_ptrs = sets[0]
+            if fused:
+                fused_sets = sets
+                scene.set_peers(sets[0] + sets[1], world, W * H, 0 if gather == "fused-root" else -1)
             ok = torch.ones(1, device="cuda")
         except RuntimeError as e:
             sys.stderr.write("peer canvases unavailable (%s); using the all-gather path\n" % e)
             ok = torch.zeros(1, device="cuda")
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if float(ok.item()) == 0.0:
-            gather, peer_ptrs = "nccl", None
+            gather, peer_ptrs, fused, fused_sets = "nccl", None, False, None
         token = torch.zeros(1, device="cuda")
+    fused_flags = (dev_flags & ~pkg.RT_RENDER_TILED_OUTPUT) | pkg.RT_RENDER_PEER_STORE
 
     def frame_device(flags=dev_flags):
         """One frame, canvas left in HBM (rank-local tiles gathered and de-interleaved when N > 1).
@@ -282,6 +405,11 @@ def run_ours(a):
         flags |= pkg.RT_RENDER_ASYNC
         if world == 1:
             scene.render(flags=flags, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=canvas_dev.data_ptr())
+            return
+        if fused:
+            # the gather is part of the frame: k_tile stores into the peer canvases and signals; rank 0 (or every rank) waits
+            scene.render(flags=(flags & ~pkg.RT_RENDER_TILED_OUTPUT) | pkg.RT_RENDER_PEER_STORE, rank=rank, world=world,
+                         tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=0)
             return
         scene.render(flags=flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=slab_t.data_ptr())
         if gather == "p2p":
@@ -296,7 +424,7 @@ def run_ours(a):
 
     def frame_stats():
         st = scene.finish()
-        return st, st["kernel_launches"] + (1 if world > 1 else 0)
+        return st, st["kernel_launches"] + (1 if world > 1 and not fused else 0)
 
     # N > 1, end to end: ONE host canvas in shared memory, page-locked in every rank's process. The image is dealt in
     # full-width bands of --band-h rows; each rank renders its bands and copies them straight into the shared canvas
@@ -356,12 +484,14 @@ def run_ours(a):
             total_ms = float(t.item())
         return total_ms, out, clocks
 
-    if gather in ("p2p", "p2p-nccl"):
+    if gather in ("p2p", "p2p-nccl") or fused:
         # untimed check: the peer-memory exchange leaves the frame the all-gather path leaves
         frame_device()
         torch.cuda.current_stream().synchronize()
         frame_stats()
-        got = scene.copy_to_host(own_canvas_ptr, np.empty(H * W, np.uint32))
+        receives = not fused or gather == "fused-all" or rank == 0
+        src_ptr = scene.peer_frame_canvas(rank)[0] if fused else own_canvas_ptr
+        got = scene.copy_to_host(src_ptr, np.empty(H * W, np.uint32))
         scene.render(flags=dev_flags | pkg.RT_RENDER_ASYNC, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h,
                      out_ptr=slab_t.data_ptr())
         dist.all_gather_into_tensor(gathered, slab_t)
@@ -369,7 +499,7 @@ def run_ours(a):
         torch.cuda.current_stream().synchronize()
         frame_stats()
         want = canvas_dev.cpu().numpy().view(np.uint32)
-        if not (got == want).all():
+        if receives and not (got == want).all():
             raise SystemExit("rank %d: peer-memory frame differs from the all-gather frame in %d pixels" % (rank, int((got != want).sum())))
     # untimed check of the end-to-end paths against the device-resident frame
     scene.render(flags=dev_flags & ~pkg.RT_RENDER_TILED_OUTPUT, tile_w=a.tile_w, tile_h=a.tile_h, out_ptr=canvas_dev.data_ptr())
@@ -421,8 +551,12 @@ def run_ours(a):
         hits = sst["n_hits"]
         #   k_shadow : 32 B per traced shadow ray (queue read) + 1 B (occlusion flag)
         shadow_traced = sst["rays_shadow"] - sst["rays_culled"]
-        kernels = {"k_primary": (avg("ms_primary"), 4.0 * (pix_local - hits) + 32.0 * hits),
-                   "k_shadow": (avg("ms_shadow"), 33.0 * shadow_traced)}
+        if sst["tile_kernel"]:
+            # k_tile keeps rays, hits and shadow rays in registers: what it must move through HBM is the pixel it stores
+            kernels = {"k_tile": (avg("ms_primary"), 4.0 * pix_local)}
+        else:
+            kernels = {"k_primary": (avg("ms_primary"), 4.0 * (pix_local - hits) + 32.0 * hits),
+                       "k_shadow": (avg("ms_shadow"), 33.0 * shadow_traced)}
         dom = max(kernels, key=lambda k: kernels[k][0])
         dom_ms, dom_bytes = kernels[dom]
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
@@ -430,7 +564,7 @@ def run_ours(a):
         ms_trace = avg("ms_trace")
         traffic, traffic_src = None, None
         try:  # dram__bytes_read.sum + dram__bytes_write.sum of that kernel, one launch, from the committed ncu capture
-            cap = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")))
+            cap = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json" if sst["tile_kernel"] else "r1_ncu_traffic.json")))
             if cap["workload"] == workload_name(a) and world == 1:
                 traffic, traffic_src = cap["kernels"][dom]["traffic"], cap["source"]
         except Exception:
@@ -444,7 +578,11 @@ def run_ours(a):
                            "peak_source": "rt_measure_l2_bandwidth (32 MiB resident read, measured in this run)",
                            "nodes_per_ray": sst["nodes_visited"] / max(sst["rays_total"], 1),
                            "tri_filters_per_ray": sst["prims_prefiltered"] / max(sst["rays_total"], 1),
-                           "exact_tests_per_ray": sst["tris_tested"] / max(sst["rays_total"], 1)}}
+                           "exact_tests_per_ray": sst["tris_tested"] / max(sst["rays_total"], 1),
+                           "node_fetches_per_ray_after_warp_broadcast": sst["node_fetches"] / max(sst["rays_total"], 1),
+                           "bytes": "80 B x node visits counted per active ray + 48 B x triangle filters (SURVEY 8d). With k_tile a node is "
+                                    "fetched once per warp and tested against 4 ray-group beams, so the bytes a per-ray traversal would "
+                                    "request are no longer requested: node_fetches_per_ray is what is actually loaded"}}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
                 "ms_per_step": ms_dev / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic (procedural world, seed 42)",
@@ -455,7 +593,9 @@ def run_ours(a):
                            "triangles": sst_prims(scene), "step": "BVH rebuild + trace" if not a.keep_bvh else "trace (BVH kept)",
                            "l2": "flushed between timed iterations (256 MiB write)",
                            "sharding": "screen tiles %dx%d round-robin over %d rank(s)" % (a.tile_w, a.tile_h, world),
-                           "exchange": {"p2p": "tiles stored into every rank's canvas over NVLink peer memory, completion signalled through mailboxes in the same peer memory (rt_push_tiles_signal: no collective call on the frame's path)",
+                           "exchange": {"fused-root": "RT_RENDER_PEER_STORE: the frame's kernels store every pixel into rank 0's row-major canvas over NVLink peer memory (double-buffered by frame parity) and signal its mailbox; rank 0 waits for all ranks (the framebuffer gathered: no slab, no push kernel, no collective call)",
+                                        "fused-all": "RT_RENDER_PEER_STORE into every rank's canvas (all ranks receive the frame)",
+                                        "p2p": "tiles stored into every rank's canvas over NVLink peer memory, completion signalled through mailboxes in the same peer memory (rt_push_tiles_signal: no collective call on the frame's path)",
                                         "p2p-nccl": "tiles stored into every rank's canvas over NVLink peer memory (rt_push_tiles) + 1-element all-reduce as barrier",
                                         "nccl": "NCCL all-gather of the tile slabs + de-interleave kernel", "none": "single GPU"}[gather]},
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / a.steps, "h2d_bytes_per_step": h2d * world,
@@ -466,6 +606,11 @@ def run_ours(a):
                                  "shade": avg("ms_shade"), "k_shadow": avg("ms_shadow"), "bounce_waves": avg("ms_bounce"),
                                  "waves": st[0]["waves"]},
                 "roofline": roofline}
+        line["frame_kernels"] = "k_tile (wave 0 in one kernel, warp-coherent traversal)" if sst["tile_kernel"] else "k_primary + k_shadow_gen + k_shadow + k_resolve (split pipeline)"
+        if world == 1 and not a.no_ref_cuda:
+            line["ref_cuda"] = ref_cuda_block(a, a.scene, rays_per_frame, ms_dev / a.steps, ms_e2e / a.steps)
+        if world == 1 and not a.no_stress and a.scene != "world8_stress":
+            line["stress"] = single_gpu_block(pkg, torch, a, "world8_stress", max(5, a.steps // 2), flush)
         if world == 1 and not a.no_cpu_baseline:
             v, kind, cores, sample, _ = cpu_reference_run(a, a.cpu_seconds)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
@@ -476,11 +621,16 @@ def run_ours(a):
         pkg.host_canvas_close(shared_handle, unlink=(rank == 0))
     if peer_ptrs:
         dist.barrier()
-        for r, ptr in enumerate(peer_ptrs):
-            if r != rank:
-                pkg.peer_canvas_close(ptr)
+        sets = fused_sets if fused_sets else [peer_ptrs]
+        if fused_sets:
+            scene.set_peers([], 0, 0)
+        for st_ in sets:
+            for r, ptr in enumerate(st_):
+                if r != rank:
+                    pkg.peer_canvas_close(ptr)
         dist.barrier()
-        pkg.peer_canvas_free(own_canvas_ptr)
+        for st_ in sets:
+            pkg.peer_canvas_free(st_[rank])
     scene.close()
     if world > 1:
         dist.barrier()

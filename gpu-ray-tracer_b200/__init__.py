@@ -29,6 +29,8 @@ RT_RENDER_ASYNC = 256
 RT_RENDER_REFIT_BVH = 512
 RT_RENDER_HOST_BANDS = 1024
 RT_RENDER_HOST_DIRECT = 2048
+RT_RENDER_SPLIT_SHADE = 4096
+RT_RENDER_PEER_STORE = 8192
 RT_HITABLE_TRIMESH, RT_HITABLE_SPHERE = 0, 1
 RT_DEBUG_PREFIX_UPLOADS, RT_DEBUG_BVH8_LEVELS, RT_DEBUG_BUILD_PATH, RT_DEBUG_BUILD_LAUNCHES, RT_DEBUG_BUILD_CLUSTER = 0, 1, 2, 3, 4
 RT_DEBUG_BUILD_PHASE_NS = 16
@@ -90,7 +92,8 @@ class RtFrameStats(C.Structure):
                 ("prims_prefiltered", C.c_uint64), ("ms_build", C.c_float), ("ms_trace", C.c_float),
                 ("ms_total", C.c_float), ("waves", C.c_int32), ("kernel_launches", C.c_int32),
                 ("ms_primary", C.c_float), ("ms_shade", C.c_float), ("ms_bounce", C.c_float), ("n_hits", C.c_int32), ("ms_shadow", C.c_float),
-                ("ms_wave_phase", C.c_float * 4), ("rays_culled", C.c_uint64), ("host_chunks", C.c_int32)]
+                ("ms_wave_phase", C.c_float * 4), ("rays_culled", C.c_uint64), ("host_chunks", C.c_int32),
+                ("tile_kernel", C.c_int32), ("node_fetches", C.c_uint64)]
 
     def as_dict(self):
         return {k: (list(getattr(self, k)) if k == "ms_wave_phase" else getattr(self, k)) for k, _ in self._fields_}
@@ -174,6 +177,8 @@ def cuda_lib():
         lib.rt_push_tiles.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(vp), i32]
         lib.rt_push_tiles_signal.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(vp), i32, C.c_int64, C.c_uint32]
         lib.rt_copy_to_host.argtypes = [vp, vp, vp, C.c_int64]
+        lib.rt_scene_set_peers.argtypes = [vp, C.POINTER(vp), i32, C.c_int64, i32]
+        lib.rt_peer_frame_canvas.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(C.c_uint32)]
         lib.rt_host_canvas_open.argtypes = [C.c_char_p, C.c_int64, i32, C.POINTER(vp)]
         lib.rt_host_canvas_close.argtypes = [vp, C.c_int64, C.c_char_p, i32]
         lib.rt_frame_finish.argtypes = [vp, C.POINTER(RtFrameStats)]
@@ -406,6 +411,18 @@ class Scene:
         arr = (C.c_void_p * len(peer_ptrs))(*peer_ptrs)
         _check(cuda_lib().rt_push_tiles_signal(self._h, C.byref(params), slab_dev_ptr, arr, len(peer_ptrs), canvas_pixels, epoch),
                "rt_push_tiles_signal")
+
+    def set_peers(self, canvases, n_ranks, canvas_pixels, gather_root=-1):
+        """canvases: 2 * n_ranks device pointers, [parity][rank] (rt_scene_set_peers); frames rendered with
+        RT_RENDER_PEER_STORE are stored into them by the kernels that produce the pixels."""
+        arr = (C.c_void_p * len(canvases))(*canvases)
+        _check(cuda_lib().rt_scene_set_peers(self._h, arr, n_ranks, canvas_pixels, gather_root), "rt_scene_set_peers")
+
+    def peer_frame_canvas(self, rank):
+        """(device pointer, epoch) of the canvas of `rank` that holds the last RT_RENDER_PEER_STORE frame."""
+        ptr, ep = C.c_void_p(), C.c_uint32()
+        _check(cuda_lib().rt_peer_frame_canvas(self._h, rank, C.byref(ptr), C.byref(ep)), "rt_peer_frame_canvas")
+        return ptr.value, ep.value
 
     def copy_to_host(self, dev_ptr, out):
         _check(cuda_lib().rt_copy_to_host(self._h, dev_ptr, out.ctypes.data, out.size), "rt_copy_to_host")

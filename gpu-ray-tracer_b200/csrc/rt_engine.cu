@@ -28,6 +28,7 @@
 #include <cstring>
 #include <new>
 
+#include "rt_beam.cuh"
 #include "rt_bvh.cuh"
 #include "rt_hostprep.h"
 #include "rt_internal.h"
@@ -141,7 +142,7 @@ static long long slab_pixels(const TileMap& m) {
 // ---------------------------------------------------------------- device counters
 // d_counters layout (unsigned long long[32]):
 enum { C_WORK0 = 0, C_HITQ = 1, C_WORK1 = 2, C_PATHS = 3, C_QUEUE_A = 4, C_QUEUE_B = 5, C_WORK2 = 6,
-       C_RAYS_PRIMARY = 8, C_RAYS_SHADOW = 9, C_RAYS_SECONDARY = 10, C_NODES = 11, C_PRIMS = 12, C_EXACT = 13, C_RAYS_CULLED = 14, C_WAVES = 15, C_BARRIER = 16, C_PHASE_NS = 20, C_N = 32 };
+       C_RAYS_PRIMARY = 8, C_RAYS_SHADOW = 9, C_RAYS_SECONDARY = 10, C_NODES = 11, C_PRIMS = 12, C_EXACT = 13, C_RAYS_CULLED = 14, C_WAVES = 15, C_BARRIER = 16, C_PHASE_NS = 20, C_FETCHES = 24, C_N = 32 };
 
 __device__ __forceinline__ void flush_counts(unsigned long long* ctr, const RayCounts& rc, const TravStats& ts, bool stats) {
     unsigned v[6] = {rc.primary, rc.shadow, rc.secondary, ts.nodes, ts.prims, ts.exact};
@@ -672,6 +673,157 @@ __global__ void __launch_bounds__(kThreads, RT_WAVES_MIN_BLOCKS) k_bounce_waves(
     flush_culled(s, a.ctr, culled);
 }
 
+// ---------------------------------------------------------------- wave 0 in ONE kernel: k_tile
+// Camera rays, closest hit, shadow rays, Phong and the pixel store for one 8x4 tile per warp, with the warp-coherent
+// traversal of rt_beam.cuh for the camera rays and for the shadow rays of each light. Replaces, for scenes whose shadow
+// rays are plain occlusion queries (no material refracts), the chain k_primary -> hit queue -> k_shadow_gen -> shadow
+// queues -> k_shadow -> occlusion flags -> k_resolve: the 32-byte hit records, the 32-byte shadow records and the flags
+// (0.7 GB of the 1.07 GB of HBM traffic of a 4K world16 frame) are never written, three kernel launches and their tails
+// disappear, and what reaches HBM is 4 bytes per pixel. The warp keeps the tile from ray generation to the pixel: the
+// tile-aligned queues of the split pipeline already gave every warp of the shading kernels the hits of ONE tile, so the
+// lanes idle here (missed pixels of a partly covered tile) idled there as well.
+// Arithmetic: the same rt_shade.cuh / rt_scene.cuh functions in the same order as k_shadow_gen + k_resolve, so frames are
+// bit-identical to the split pipeline's. SECONDARY: hits on reflective materials start a path (RayFrame stack) exactly as
+// k_resolve<true> does and the bounce waves continue from there.
+// PEERS > 0: multi-GPU — the pixel goes straight into the row-major canvases of `PEERS` ranks over NVLink peer
+// mappings (the gathering rank's, or every rank's) instead of a local slab that a second kernel pushes; the last block
+// to finish signals the frame's epoch to their mailboxes (rt_render with RtRenderParams.peers).
+struct PeerCanvases { uint32_t* p[RT_MAX_PEERS]; int n; };
+struct PushSignal { long long mailbox_offset; unsigned epoch; unsigned* done_blocks; };
+struct PeerOut { PeerCanvases pc; PushSignal sg; int rank; };
+
+struct AttenMask {  // what Light::attenuate returned for light l: its colour, or black when the shadow ray was blocked
+    unsigned long long occl;
+    __device__ __forceinline__ float4 operator()(int l, const LightRec& L) const {
+        return ((occl >> l) & 1ull) ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : L.color;
+    }
+};
+
+#ifndef RT_TILE_MIN_BLOCKS
+#define RT_TILE_MIN_BLOCKS 2
+#endif
+template <bool STATS, bool SECONDARY, bool PEERS>
+__global__ void __launch_bounds__(kThreads, RT_TILE_MIN_BLOCKS) k_tile(SceneView s, TileMap tm, unsigned long long* ctr, uint32_t* canvas,
+                                                                      PeerOut po, unsigned char* paths, int path_stride, int* queue) {
+    TravStats ts = {0, 0, 0};
+    BeamStats bs = {0};
+    RayCounts rc = {0, 0, 0};
+    unsigned culled = 0, n_hit = 0;
+    const int lane = threadIdx.x & 31;
+    const int n_work = tm.n_work();
+    auto store = [&](int out, uint32_t v) {
+        if (PEERS) {
+            for (int k = 0; k < po.pc.n; k++) po.pc.p[k][out] = v;
+        } else {
+            canvas[out] = v;
+        }
+    };
+    for (;;) {
+        int q = 0;
+        if (lane == 0) q = (int)atomicAdd(&ctr[C_WORK0], 1ull);
+        q = __shfl_sync(0xffffffffu, q, 0);
+        if (q >= n_work) break;
+        int x, y, out;
+        const bool valid = tm.locate(q, lane, x, y, out);
+        rtx::Ray r;
+        r.o = s.cam.pos; r.d = s.cam.f;
+        if (valid) {
+            r = rtx::camera_ray(s.cam, (float)x, (float)y);
+            rc.primary++;
+        }
+        Hit h;
+        const bool hit = beam_query<false, STATS>(s, r, valid, true, INFINITY, h, ts, bs);
+        if (valid && !hit) store(out, 0u);  // pack_color(0,0,0,0)
+        if (!__any_sync(0xffffffffu, hit)) continue;
+        if (hit) n_hit++;
+        // ---- shading of the tile's hits: k_shadow_gen + k_shadow + k_resolve
+        float3 nrm = rtx::mk3(0.f, 0.f, 0.f), hit_pos = rtx::mk3(0.f, 0.f, 0.f);
+        int mat_id = 0;
+        if (hit) {
+            mat_id = s.tris[h.tri].mat;
+            nrm = hit_normal(s, h, r);
+            hit_pos = rtx::ray_at(r, h.t);
+        }
+        const MatRec& m = s.mats[mat_id];
+        unsigned long long occl = 0ull;  // bit l: light l's shadow ray is blocked
+        for (int l = 0; l < s.n_lights; l++) {
+            bool trace = false;
+            rtx::Ray sr;
+            sr.o = hit_pos; sr.d = r.d;
+            float max_t = 0.0f;
+            if (hit) {
+                float3 dir;
+                float da;
+                light_setup(s, s.lights[l], hit_pos, dir, max_t, da);
+                if (s.cull_unlit && light_unlit(m, nrm, dir)) {
+                    culled++;  // never read by illuminate_resolved (same predicate there)
+                } else {
+                    trace = true;
+                    sr = shadow_ray(hit_pos, dir);
+                    rc.shadow++;
+                }
+            }
+            Hit sh;
+            if (beam_query<true, STATS>(s, sr, trace, true, max_t, sh, ts, bs)) occl |= 1ull << l;
+        }
+        if (!hit) continue;
+        const AttenMask att = {occl};
+        if (SECONDARY && (m.reflective || m.refractive)) {
+            // the pixel continues: first RayFrame transitions here (k_resolve<true>), then the bounce waves
+            int slot = warp_alloc(&ctr[C_PATHS]);
+            PathHead* head;
+            Frame* frames = path_frames(paths, path_stride, slot, &head);
+            Frame top;
+            frame_init_root(top, r, s.depth);
+            int stack_top = 0, isect_mat = mat_id;
+            float4 acc = rtx::mk4(0.f, 0.f, 0.f, 0.f);
+            bool alive = path_advance_core(
+                s, [&](const rtx::Ray& ray, float t, float3 nn, const MatRec& mm, float4 kd) { return illuminate_resolved(s, ray, t, nn, mm, kd, att); },
+                frames, stack_top, isect_mat, acc, true, h, top, true);
+            if (alive) {
+                PathHead hd;
+                hd.acc = acc; hd.out_index = out; hd.stack_top = stack_top; hd.isect_mat = isect_mat;
+                hd.pending = 0; hd.hit = h; hd.pad0 = hd.pad1 = 0;
+                *head = hd;
+                queue[warp_alloc(&ctr[C_QUEUE_A])] = slot;
+            } else {
+                store(out, rtx::pack_color(acc));
+            }
+            continue;
+        }
+        // no secondary rays: acc = 0 + 1 * illuminate, clamp, pack (src/raytracer.cu:36-41)
+        float4 c = illuminate_resolved(s, r, h.t, nrm, m, diffuse_colour(s, m, h.tri, h.u, h.v), att);
+        store(out, rtx::pack_color(c));
+    }
+    flush_counts(ctr, rc, ts, STATS);
+    flush_culled(s, ctr, culled);
+    {
+        unsigned v = n_hit, f = bs.node_fetches;
+        for (int o = 16; o; o >>= 1) { v += __shfl_xor_sync(0xffffffffu, v, o); f += __shfl_xor_sync(0xffffffffu, f, o); }
+        if (lane == 0 && v) atomicAdd(&ctr[C_HITQ], (unsigned long long)v << 32);  // high word = hits (n_hits)
+        if (STATS && lane == 0 && f) atomicAdd(&ctr[C_FETCHES], (unsigned long long)f);
+    }
+    if (PEERS) {
+        // every block: make its peer stores visible system-wide, then count itself; the last block signals
+        __shared__ bool s_last;
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned prev = atomicAdd(po.sg.done_blocks, 1u);
+            s_last = prev + 1u == gridDim.x;
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence_system();
+            if ((int)threadIdx.x < po.pc.n) {
+                volatile unsigned* box = (volatile unsigned*)(po.pc.p[threadIdx.x] + po.sg.mailbox_offset);
+                box[po.rank] = po.sg.epoch;
+            }
+            if (threadIdx.x == 0) *po.sg.done_blocks = 0u;  // ready for the next frame
+        }
+    }
+}
+
 // ---------------------------------------------------------------- waves >= 1 with ray sorting (RT_RENDER_SORT_RAYS)
 // One launch per phase and wave, and between the waves the live queue is sorted by a coherence key: 21-bit Morton code
 // of the pending ray's origin inside the scene bounds (7 bits per axis), then the direction octant (24 bits, three radix
@@ -846,12 +998,9 @@ __global__ void k_untile(TileMap tm, long long slab, const uint32_t* gathered, u
 // it owns straight into the row-major canvas of every peer (its own included) through NVLink peer
 // mappings. One thread moves 4 pixels (16 bytes); a tile row is a contiguous run in the slab and
 // in the canvas, so a warp writes whole 128-byte segments. Replaces all-gather + k_untile.
-struct PeerCanvases { uint32_t* p[RT_MAX_PEERS]; int n; };
-
 // Exchange barrier over peer memory (no collective library on the frame's data path). Behind the pixels of every
 // peer canvas sits a mailbox of RT_MAX_PEERS words; after its last tile store a rank writes the frame's epoch into
 // slot [rank] of every rank's mailbox, and k_wait_mailbox on the receiving side spins until all slots carry the epoch.
-struct PushSignal { long long mailbox_offset; unsigned epoch; unsigned* done_blocks; };
 
 __device__ __forceinline__ void push_signal_tail(const TileMap& tm, const PeerCanvases& pc, const PushSignal& sg) {
     // every block: make its peer stores visible system-wide, then count itself; the last block signals
@@ -918,6 +1067,36 @@ __global__ void k_push_tiles(TileMap tm, const uint32_t* slab, PeerCanvases pc, 
     push_tile_quad(tm, slab, pc, q, n_quads);
     if (SIGNAL) push_signal_tail(tm, pc, sg);
 }
+// RT_RENDER_PEER_STORE when the frame could not store its pixels into the peers itself (secondary rays, refractive
+// scenes, -r / serial semantics): the rank rendered its tiles into its own row-major canvas; this kernel forwards them
+// to the other target canvases and signals all targets.
+__global__ void k_forward_tiles(TileMap tm, const uint32_t* own, PeerCanvases pc, PushSignal sg) {
+    const int quads_per_row = tm.tile_w >> 2;
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long n_quads = (long long)tm.n_owned * tm.tile_h * quads_per_row;
+    if (q < n_quads) {
+        const int lq = (int)(q % quads_per_row);
+        const long long row = q / quads_per_row;
+        const int ly = (int)(row % tm.tile_h), k = (int)(row / tm.tile_h);
+        const int T = k * tm.world + tm.rank;
+        const int tx = T % tm.tiles_x, ty = T / tm.tiles_x;
+        const int x = tx * tm.tile_w + lq * 4, y = ty * tm.tile_h + ly;
+        if (y < tm.H && x < tm.W) {
+            const long long dst = (long long)y * tm.W + x;
+            if (x + 4 <= tm.W && (tm.W & 3) == 0) {
+                const uint4 v = *(const uint4*)(own + dst);
+                for (int r = 0; r < pc.n; r++) if (pc.p[r] != own) *(uint4*)(pc.p[r] + dst) = v;
+            } else {
+                for (int i = 0; i < 4 && x + i < tm.W; i++) {
+                    const uint32_t v = own[dst + i];
+                    for (int r = 0; r < pc.n; r++) if (pc.p[r] != own) pc.p[r][dst + i] = v;
+                }
+            }
+        }
+    }
+    push_signal_tail(tm, pc, sg);
+}
+
 // Resident-working-set read bandwidth (the L2 roofline denominator).
 __global__ void k_l2_read(const uint4* buf, long long n16, int iters, unsigned* sink) {
     unsigned acc = 0;
@@ -1222,31 +1401,48 @@ static int persistent_grid(K kernel, int sm_count) {
     return sm_count * per_sm;
 }
 
+// Is wave 0 of this frame one k_tile launch? Scenes whose shadow rays are occlusion queries (no refractive material),
+// at most 64 lights (the occlusion mask of a hit), BVH traversal with the reference's leaf-box rule.
+static bool tile_kernel_eligible(const RtScene* sc, const SceneView& v, int mode) {
+    static const int env_off = [] { const char* e = std::getenv("RT_TILE_KERNEL"); return (e && !std::atoi(e)) ? 1 : 0; }();
+    return mode == TR_BVH_BOX && !env_off && !sc->fused_shade && !sc->split_shade && !v.any_refractive && v.n_lights <= 64;
+}
+
 template <int MODE, bool STATS>
 static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uint32_t* canvas, int* waves,
-                         unsigned long long* ctr, cudaEvent_t* cev) {
+                         unsigned long long* ctr, cudaEvent_t* cev, const PeerOut* peers) {
     // ctr: this chunk's counter block; cev: its events {start, primary done, shadow rays generated, shadow rays traced,
-    // wave 0 shaded, bounce waves done}
+    // wave 0 shaded, bounce waves done}. peers: k_tile stores the pixels into these peer canvases and signals them
+    // (only passed when the tile kernel is eligible and the frame has no secondary rays).
     cudaStream_t st = sc->stream;
     RT_CUDA(cudaEventRecord(cev[0], st));
     long long n_pix = (long long)tm.n_work() * 32;
-    if (sc->d_hitq.reserve(sizeof(HitRec) * (size_t)std::max<long long>(n_pix, 1))) return RT_ERR_OUT_OF_MEMORY;
-    int g0 = persistent_grid(k_primary<MODE, STATS, false>, sc->sm_count);
-    static const int aligned_hitq = [] { const char* e = std::getenv("RT_PACKED_HITQ"); return (e && std::atoi(e)) ? 0 : 1; }();
-    k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr, aligned_hitq);
-    sc->kernel_launches++;
-    RT_CUDA(cudaEventRecord(cev[1], st));
     *waves = 1;
     sc->split_shade_used = false;
+    sc->tile_kernel_used = false;
     int path_stride = (int)(sizeof(PathHead) + sizeof(Frame) * (size_t)(v.depth + 1));
     const bool secondary = v.any_secondary && v.depth > 0;
     const bool loop = v.any_refractive != 0;  // shadow rays walk through refractive occluders
     unsigned long long n_hits = 0;
     size_t hit_cap = (size_t)std::max<long long>(n_pix, 1);
+    // k_tile starts the paths of reflective hits itself, so their stacks are allocated for every pixel of the chunk (only
+    // the slots of real paths are ever touched); beyond 32 GB the split pipeline, which can size them after k_primary, runs
+    bool use_tile = tile_kernel_eligible(sc, v, MODE) && !(secondary && hit_cap * (size_t)path_stride > ((size_t)32 << 30));
+    if (peers && !(use_tile && !secondary)) { set_error("internal: peer stores need the tile kernel"); return RT_ERR_INVALID_ARG; }
+    if (!use_tile || secondary) {
+        if (sc->d_hitq.reserve(sizeof(HitRec) * (size_t)std::max<long long>(n_pix, 1))) return RT_ERR_OUT_OF_MEMORY;
+    }
+    if (!use_tile) {
+        int g0 = persistent_grid(k_primary<MODE, STATS, false>, sc->sm_count);
+        static const int aligned_hitq = [] { const char* e = std::getenv("RT_PACKED_HITQ"); return (e && std::atoi(e)) ? 0 : 1; }();
+        k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr, aligned_hitq);
+        sc->kernel_launches++;
+        RT_CUDA(cudaEventRecord(cev[1], st));
+    }
     if (secondary) {
         // Path stacks for every pixel when that is affordable (no host round trip after k_primary);
         // otherwise they are allocated for the hits actually found (one 8-byte read-back).
-        if (hit_cap * (size_t)path_stride > ((size_t)4 << 30)) {
+        if (!use_tile && hit_cap * (size_t)path_stride > ((size_t)4 << 30)) {
             RT_CUDA(cudaMemcpyAsync(&n_hits, ctr + C_HITQ, 8, cudaMemcpyDeviceToHost, st));
             RT_CUDA(cudaStreamSynchronize(st));
             hit_cap = (size_t)std::max<unsigned long long>(n_hits & 0xffffffffull, 1);  // queue slots (>= hits)
@@ -1257,7 +1453,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     unsigned char* occl = nullptr;
     float4* att4 = nullptr;
     ShadowRec* shq = nullptr;
-    if (!sc->fused_shade) {
+    if (!sc->fused_shade && (!use_tile || secondary)) {
         size_t cap = hit_cap * (size_t)std::max(v.n_lights, 1);
         if (sc->d_shadowq.reserve(sizeof(ShadowRec) * cap) || sc->d_occl.reserve((loop ? sizeof(float4) : 1) * cap) ||
             sc->d_shq_count.reserve(sizeof(unsigned) * (size_t)std::max(v.n_lights, 1)))
@@ -1278,7 +1474,26 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     };
     HitRec* hitq = sc->d_hitq.as<HitRec>();
     unsigned char* paths = sc->d_paths.as<unsigned char>();
-    if (!sc->fused_shade) {
+    if (use_tile) {
+        PeerOut po;
+        std::memset(&po, 0, sizeof po);
+        if (peers) po = *peers;
+        int* qa = secondary ? sc->d_queue_a.as<int>() : nullptr;
+        if (peers) {
+            static const int g = persistent_grid(k_tile<STATS, false, true>, sc->sm_count);
+            k_tile<STATS, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, canvas, po, nullptr, 0, nullptr);
+        } else if (secondary) {
+            static const int g = persistent_grid(k_tile<STATS, true, false>, sc->sm_count);
+            k_tile<STATS, true, false><<<g, kThreads, 0, st>>>(v, tm, ctr, canvas, po, paths, path_stride, qa);
+        } else {
+            static const int g = persistent_grid(k_tile<STATS, false, false>, sc->sm_count);
+            k_tile<STATS, false, false><<<g, kThreads, 0, st>>>(v, tm, ctr, canvas, po, nullptr, 0, nullptr);
+        }
+        sc->tile_kernel_used = true;
+        RT_CUDA(cudaEventRecord(cev[1], st));
+        RT_CUDA(cudaEventRecord(cev[2], st));
+        RT_CUDA(cudaEventRecord(cev[3], st));
+    } else if (!sc->fused_shade) {
         k_shadow_gen<false><<<persistent_grid(k_shadow_gen<false>, sc->sm_count), kThreads, 0, st>>>(v, ctr, C_HITQ, hitq, shq, shq_count, occl, att4, nullptr, 0);
         sc->kernel_launches++;
         RT_CUDA(cudaEventRecord(cev[2], st));
@@ -1652,6 +1867,28 @@ int rt_copy_to_host(RtScene* sc, const uint32_t* dev_ptr, uint32_t* host_ptr, in
     return RT_OK;
 }
 
+int rt_scene_set_peers(RtScene* sc, uint32_t* const* canvases, int32_t n_ranks, int64_t canvas_pixels, int32_t gather_root) {
+    if (!sc) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    if (sc->pending) { if (int rc = rt_frame_finish(sc, nullptr)) return rc; }
+    if (n_ranks == 0) { sc->peer_canv.clear(); sc->peer_n = 0; return RT_OK; }
+    if (!canvases || n_ranks < 1 || n_ranks > RT_MAX_PEERS || canvas_pixels < (int64_t)sc->width * sc->height || gather_root >= n_ranks) {
+        set_error("rt_scene_set_peers: 1..16 ranks, 2 * n_ranks canvases of at least width * height pixels, gather_root < n_ranks");
+        return RT_ERR_INVALID_ARG;
+    }
+    for (int i = 0; i < 2 * n_ranks; i++) if (!canvases[i]) { set_error("null peer canvas"); return RT_ERR_INVALID_ARG; }
+    sc->peer_canv.assign(canvases, canvases + 2 * n_ranks);
+    sc->peer_n = n_ranks;
+    sc->peer_pixels = canvas_pixels;
+    sc->peer_root = gather_root < 0 ? -1 : gather_root;
+    return RT_OK;
+}
+int rt_peer_frame_canvas(RtScene* sc, int32_t rank, uint32_t** canvas, uint32_t* epoch) {
+    if (!sc || !canvas || sc->peer_n < 1 || rank < 0 || rank >= sc->peer_n) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    *canvas = sc->peer_canv[(size_t)(sc->peer_epoch & 1u) * sc->peer_n + rank];
+    if (epoch) *epoch = sc->peer_epoch;
+    return RT_OK;
+}
+
 int rt_scene_set_stream(RtScene* sc, void* stream, int32_t external) {
     if (!sc) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
     if (sc->pending) {
@@ -1663,10 +1900,12 @@ int rt_scene_set_stream(RtScene* sc, void* stream, int32_t external) {
 }
 
 int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFrameStats* stats) {
-    if (!sc || !canvas) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    if (!sc) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
     RtRenderParams p;
     std::memset(&p, 0, sizeof p);
     if (params) p = *params;
+    const bool peer_store = (p.flags & RT_RENDER_PEER_STORE) != 0;
+    if (!canvas && !peer_store) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
     if (p.semantics != RT_SEMANTICS_GPU && p.semantics != RT_SEMANTICS_CPU) { set_error("unknown semantics"); return RT_ERR_INVALID_ARG; }
     if (sc->pending) {  // an asynchronous frame was never finished: its counters are about to be reused
         if (int rc = rt_frame_finish(sc, nullptr)) return rc;
@@ -1680,6 +1919,31 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     sc->fused_shade = (p.flags & RT_RENDER_FUSED_SHADE) != 0;
     sc->trace_unlit = (p.flags & RT_RENDER_TRACE_UNLIT) != 0;
     sc->sort_rays = (p.flags & RT_RENDER_SORT_RAYS) != 0;
+    sc->split_shade = (p.flags & RT_RENDER_SPLIT_SHADE) != 0;
+    // RT_RENDER_PEER_STORE: this frame's epoch and canvases (double-buffered by the parity of the epoch)
+    uint32_t* peer_own = nullptr;
+    PeerOut po;
+    std::memset(&po, 0, sizeof po);
+    if (peer_store) {
+        const int n = sc->peer_n;
+        if (n < 1 || p.world != n || (n > 1 && (p.rank < 0 || p.rank >= n)) || (p.flags & RT_RENDER_TILED_OUTPUT)) {
+            set_error("RT_RENDER_PEER_STORE needs rt_scene_set_peers, world == its n_ranks and a row-major canvas (no RT_RENDER_TILED_OUTPUT)");
+            return RT_ERR_INVALID_ARG;
+        }
+        p.flags |= RT_RENDER_CANVAS_DEVICE;
+        const unsigned epoch = ++sc->peer_epoch;
+        uint32_t* const* set = sc->peer_canv.data() + (size_t)(epoch & 1u) * n;
+        peer_own = set[tm.rank];
+        if (sc->peer_root >= 0) { po.pc.n = 1; po.pc.p[0] = set[sc->peer_root]; }
+        else { po.pc.n = n; for (int r = 0; r < n; r++) po.pc.p[r] = set[r]; }
+        if (!sc->d_push_ctr.p) {
+            if (sc->d_push_ctr.reserve(16)) return RT_ERR_OUT_OF_MEMORY;
+            RT_CUDA(cudaMemsetAsync(sc->d_push_ctr.p, 0, 16, st));
+        }
+        po.sg.mailbox_offset = sc->peer_pixels; po.sg.epoch = epoch; po.sg.done_blocks = sc->d_push_ctr.as<unsigned>();
+        po.rank = tm.rank;
+        canvas = peer_own;
+    }
     bool built = false;
     RT_CUDA(cudaEventRecord(sc->ev[2], st));
     if (!no_bvh) {
@@ -1738,11 +2002,12 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long) * C_N * n_chunks, st));
     // row-major canvas shared with other ranks' tiles: clear them. A tile slab needs no clearing: every
     // in-canvas pixel of an owned tile is written, and the slab padding beyond the canvas edge is never read.
-    if (!tm.tiled_out && tm.world > 1 && !(direct && host_bands)) RT_CUDA(cudaMemsetAsync(dcanvas, 0, 4 * (size_t)out_pixels, st));
+    // (not a peer canvas either: the other ranks are storing their tiles into it)
+    if (!tm.tiled_out && tm.world > 1 && !(direct && host_bands) && !peer_store) RT_CUDA(cudaMemsetAsync(dcanvas, 0, 4 * (size_t)out_pixels, st));
     RT_CUDA(cudaEventRecord(sc->ev[3], st));
     SceneView v = rth::make_view(sc, !no_bvh);
     int waves = 1, rc = RT_OK;
-    bool canvas_copied = false;
+    bool canvas_copied = false, peer_direct = false;
     if (no_bvh) rc = run_mega<TR_BRUTE>(sc, v, tm, dcanvas, p.semantics);
     else if (p.semantics == RT_SEMANTICS_CPU) rc = run_mega<TR_BVH_BOX>(sc, v, tm, dcanvas, p.semantics);
     else {
@@ -1764,8 +2029,12 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
             const int u0 = bounds[c], u1 = bounds[c + 1];
             if (n_chunks > 1) { tc.k_begin = u0 * tm.tiles_x; tc.k_count = (u1 - u0) * tm.tiles_x; }
             int w = 1;
-            if (want_stats) rc = run_wavefront<TR_BVH_BOX, true>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c]);
-            else rc = run_wavefront<TR_BVH_BOX, false>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c]);
+            // peer frames without secondary rays: k_tile stores into the peers and signals them itself
+            const bool secondary = v.any_secondary && v.depth > 0;
+            peer_direct = peer_store && !secondary && tile_kernel_eligible(sc, v, TR_BVH_BOX);
+            const PeerOut* pp = peer_direct ? &po : nullptr;
+            if (want_stats) rc = run_wavefront<TR_BVH_BOX, true>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], pp);
+            else rc = run_wavefront<TR_BVH_BOX, false>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], pp);
             waves = (w < 0 || waves < 0) ? -1 : std::max(waves, w);
             if (rc || n_chunks == 1) continue;
             // this chunk's rows go to the host while the next chunk renders
@@ -1780,6 +2049,22 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
         }
     }
     if (rc) return rc;
+    if (peer_store) {
+        if (!peer_direct) {  // the frame is in this rank's own canvas: forward the owned tiles and signal
+            if (tm.tile_w % 4) { set_error("tile_w must be a multiple of 4"); return RT_ERR_INVALID_ARG; }
+            const long long n_quads = (long long)tm.n_owned * tm.tile_h * (tm.tile_w / 4);
+            const unsigned grid = (unsigned)std::max<long long>((n_quads + kThreads - 1) / kThreads, 1);
+            k_forward_tiles<<<grid, kThreads, 0, st>>>(tm, peer_own, po.pc, po.sg);
+            sc->kernel_launches++;
+        }
+        if (sc->peer_root < 0 || sc->peer_root == tm.rank) {  // this rank receives the frame: wait until every rank has signalled
+            k_wait_mailbox<<<1, 32, 0, st>>>(peer_own, sc->peer_pixels, sc->peer_n, po.sg.epoch, mailbox_timeout_cycles(), exchange_status(sc));
+            sc->kernel_launches++;
+            RT_CUDA(cudaEventRecord(sc->ev_exchange, st));
+            sc->exchange_pending = true;
+        }
+        RT_CUDA(cudaGetLastError());
+    }
     RT_CUDA(cudaEventRecord(sc->ev[4], st));
     unsigned long long* host_ctr = sc->h_pinned + 64;
     RT_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof(unsigned long long) * C_N * n_chunks, cudaMemcpyDeviceToHost, st));
@@ -1855,6 +2140,8 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
     if (fs.waves > 4096) { set_error("bounce waves did not terminate"); return RT_ERR_LIMIT; }
     fs.kernel_launches = sc->kernel_launches - launches0;
     fs.host_chunks = sc->pend_direct ? 0 : n_chunks;
+    fs.tile_kernel = sc->tile_kernel_used ? 1 : 0;
+    fs.node_fetches = host_ctr[C_FETCHES];
     if (stats) *stats = fs;
     return RT_OK;
 }

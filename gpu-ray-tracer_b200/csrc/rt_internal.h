@@ -90,10 +90,17 @@ struct RtScene {
     rth::DevBuf d_canvas, d_counters, d_hitq, d_paths, d_queue_a, d_queue_b, d_ids;
     rth::DevBuf d_shadowq, d_occl, d_shq_count;
     rth::DevBuf d_push_ctr;         // block counter of the signalled tile push
+    // RT_RENDER_PEER_STORE (rt_scene_set_peers): [parity][rank] canvases, frame epoch, gathering rank (-1: every rank)
+    std::vector<uint32_t*> peer_canv;
+    int peer_n = 0, peer_root = -1;
+    long long peer_pixels = 0;
+    unsigned peer_epoch = 0;
     rth::DevBuf d_sort_keys_a, d_sort_keys_b, d_sort_vals_b, d_sort_hist;  // RT_RENDER_SORT_RAYS
     bool sort_rays = false;
     bool fused_shade = false;       // RT_RENDER_FUSED_SHADE: one k_shade kernel instead of gen / traverse / resolve
     bool split_shade_used = false;
+    bool split_shade = false;       // RT_RENDER_SPLIT_SHADE: never use the one-kernel wave 0 (k_tile)
+    bool tile_kernel_used = false;
     rth::Bvh bvh;
     bool boxes_valid = false;
     cudaStream_t stream = nullptr;      // the stream all work of this scene goes to: own_stream or the caller's (rt_scene_set_stream)

@@ -158,6 +158,14 @@ enum {
                                     cudaHostRegister): the kernels write it directly over PCIe while the frame renders instead
                                     of rendering into a device canvas that is copied afterwards. Falls back to the staged copy
                                     for pageable memory. Opt-in: slower than the staged, chunked copy on B200 */
+    RT_RENDER_SPLIT_SHADE = 4096, /* wave 0 as the split pipeline k_primary -> k_shadow_gen -> k_shadow -> k_resolve through hit and
+                                    shadow-ray queues in HBM instead of the one-kernel k_tile (warp-coherent traversal, no queues);
+                                    same frame. Scenes with a refractive material or more than 64 lights always take the split
+                                    pipeline (their shadow rays are closest-hit walks, src/rayprimitives/light.cu:34-60) */
+    RT_RENDER_PEER_STORE = 8192, /* multi-GPU frame gathered by the kernels that produce the pixels: this rank's tiles (rank / world
+                                    of RtRenderParams) are stored straight into the row-major peer canvases registered with
+                                    rt_scene_set_peers over NVLink, and the frame's completion is signalled through their
+                                    mailboxes; `canvas` is ignored (may be NULL) */
     RT_RENDER_TRACE_UNLIT = 128  /* also trace shadow rays whose Phong weight is exactly zero (the reference does; the
                                     split pipeline skips them by default: they cannot change a pixel) */
 };
@@ -198,6 +206,9 @@ typedef struct RtFrameStats {
                                  traversal (zero Phong weight, see RT_RENDER_TRACE_UNLIT) */
     int32_t host_chunks;      /* chunks the frame was cut into for the host copy (RtRenderParams.host_chunks); the per-kernel
                                  times above are sums over the chunks. 0 = no copy: the kernels wrote the host canvas directly */
+    int32_t tile_kernel;      /* 1: wave 0 ran as the one-kernel k_tile (ms_primary is its time, ms_shade / ms_shadow are 0) */
+    uint64_t node_fetches;    /* RT_RENDER_STATS, k_tile: 80-byte node fetches after the warp broadcast (one per warp-level
+                                 visit); nodes_visited counts the same visits once per active ray */
 } RtFrameStats;
 
 typedef struct RtBuildStats {
@@ -292,6 +303,22 @@ int rt_push_tiles(RtScene* scene, const RtRenderParams* params, const uint32_t* 
  * rank's own canvas and n_peers == world. The consumers of frame i must be done before any rank pushes frame i + 1. */
 int rt_push_tiles_signal(RtScene* scene, const RtRenderParams* params, const uint32_t* slab_dev, uint32_t* const* peer_canvases,
                          int32_t n_peers, int64_t canvas_pixels, uint32_t epoch);
+/* The gather fused into the frame (RT_RENDER_PEER_STORE): instead of rendering into a slab that rt_push_tiles then copies,
+ * the frame's kernels store every finished pixel into the peer canvases themselves and the last block of the frame signals.
+ *   canvases     2 * n_ranks device pointers from rt_peer_canvas_alloc / rt_peer_canvas_open: [parity][rank]. Frame e
+ *                (e = 1, 2, ... counted per scene, the same on every rank) uses the set e & 1, so a rank that is still
+ *                reading frame e (display, copy — enqueued on the scene's stream after the frame) is never overwritten by
+ *                ranks already rendering frame e + 1: they cannot start frame e + 2 before every rank has produced e + 1,
+ *                which in stream order is after its consumers of frame e.
+ *   gather_root  r >= 0: only rank r receives the frame (north_star's "framebuffer gathered": 4 bytes per pixel cross
+ *                NVLink once); -1: every rank receives it (all-gather: every pixel is stored n_ranks times).
+ * A receiving rank's rt_render ends with a one-warp wait on its own mailbox (all ranks' epochs), so when the call — or
+ * rt_frame_finish after RT_RENDER_ASYNC — returns RT_OK the frame in rt_peer_frame_canvas() is complete; a peer that never
+ * signals makes it RT_ERR_CUDA after the time-out instead. Frames with secondary rays or refractive materials render into
+ * the rank's own canvas and forward their tiles with one extra kernel. n_ranks == 0 clears the registration. */
+int rt_scene_set_peers(RtScene* scene, uint32_t* const* canvases, int32_t n_ranks, int64_t canvas_pixels, int32_t gather_root);
+/* The canvas of `rank` that holds (or will hold) the frame of the last rt_render with RT_RENDER_PEER_STORE, and its epoch. */
+int rt_peer_frame_canvas(RtScene* scene, int32_t rank, uint32_t** canvas, uint32_t* epoch);
 /* Blocking device-to-host copy of `pixels` uint32 on the scene's stream. */
 int rt_copy_to_host(RtScene* scene, const uint32_t* dev_ptr, uint32_t* host_ptr, int64_t pixels);
 /* The host canvas of RT_RENDER_HOST_BANDS: page-locked memory every rank of a box can map. The reference keeps its

@@ -244,3 +244,65 @@ def _oracle_rows(pkg, w, width, height, rows):
     cam.canvas_width, cam.canvas_height = float(width), float(height)
     o.set_camera(cam)
     return o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1, rows=rows)
+
+
+# ------------------------------------------------------------------ wave 0 in one kernel (k_tile) and the fused gather
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,kw", [("world4", {}), ("world16", {}), ("world8_stress", {"depth": 9}), ("world16", {"width": 1000, "height": 333}),
+                                     ("grid64_mirror", {}), ("textured8", {})])
+def test_tile_kernel_equals_split_pipeline(pkg, gpu_ok, name, kw):
+    """k_tile (warp-coherent traversal, no queues) and the split pipeline give the same frame and the same query
+    counts; the frame equals the oracle's on row bands."""
+    w = pkg.World(scene_path(name), **kw)
+    s = pkg.Scene(w)
+    c, st = s.render(flags=pkg.RT_RENDER_REBUILD_BVH | pkg.RT_RENDER_STATS)
+    c2, st2 = s.render(flags=pkg.RT_RENDER_SPLIT_SHADE | pkg.RT_RENDER_STATS)
+    assert st["tile_kernel"] == 1 and st2["tile_kernel"] == 0
+    assert (c == c2).all(), int((c != c2).sum())
+    for k in ("rays_total", "rays_primary", "rays_shadow", "rays_secondary", "rays_culled", "n_hits", "waves"):
+        assert st[k] == st2[k], (k, st[k], st2[k])
+    assert 0 < st["node_fetches"] < st["nodes_visited"] <= st2["nodes_visited"] * 4
+    o = ob.OracleScene(w)
+    H = w.height
+    for y0 in (H // 3, H // 2, (3 * H) // 4):
+        oc, _ = o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1, rows=(y0, y0 + 2))
+        assert (c[y0:y0 + 2] == oc[y0:y0 + 2]).all()
+    s.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,n,root", [("world16", 2, -1), ("world16", 4, 0), ("world16", 8, 3), ("world8_stress", 2, -1),
+                                         ("world8_stress", 4, 1), ("world1", 2, 0)])
+def test_peer_store_frames(pkg, gpu_ok, name, n, root):
+    """RT_RENDER_PEER_STORE with n ranks emulated on one device (one Scene per rank, each on its own stream): the tiles
+    every rank's kernels store into the shared row-major canvases reassemble the single-rank frame — on every rank
+    (root = -1) or on the gathering rank only — for two consecutive frames (both parities). world16: k_tile stores and
+    signals itself; world8_stress (secondary rays) and world1 (refractive: split pipeline) forward their own canvas."""
+    w = pkg.World(scene_path(name), width=512, height=272)
+    W, H = w.width, w.height
+    ref = pkg.Scene(w)
+    full, st_full = ref.render()
+    ref.close()
+    canv = [pkg.peer_canvas_alloc(W * H)[0] for _ in range(2 * n)]
+    ranks = [pkg.Scene(w) for _ in range(n)]
+    for s in ranks:
+        s.set_peers(canv, n, W * H, root)
+    for frame in (1, 2, 3):
+        for r, s in enumerate(ranks):
+            s.render(flags=pkg.RT_RENDER_PEER_STORE | pkg.RT_RENDER_ASYNC | pkg.RT_RENDER_REBUILD_BVH, rank=r, world=n, tile_w=32, tile_h=16,
+                     out_ptr=0)
+        rays = 0
+        for r, s in enumerate(ranks):
+            st = s.finish()
+            rays += st["rays_total"]
+        assert rays == st_full["rays_total"]
+        for r, s in enumerate(ranks):
+            ptr, epoch = s.peer_frame_canvas(r)
+            assert epoch == frame and ptr == canv[(frame & 1) * n + r]
+            if root < 0 or root == r:
+                got = s.copy_to_host(ptr, np.empty(W * H, np.uint32)).reshape(H, W)
+                assert (got == full).all(), (frame, r, int((got != full).sum()))
+    for s in ranks:
+        s.close()
+    for p in canv:
+        pkg.peer_canvas_free(p)
