@@ -19,7 +19,8 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 HOST_LIB_PATH = os.path.join(_HERE, "librtb200_host.so")
-CUDA_LIB_PATH = os.path.join(_HERE, "librtb200.so")
+# RTB200_CUDA_LIB: an experiment build of the engine (tools/build_variant.sh) instead of the shipped library
+CUDA_LIB_PATH = os.environ.get("RTB200_CUDA_LIB") or os.path.join(_HERE, "librtb200.so")
 
 RT_SEMANTICS_GPU, RT_SEMANTICS_CPU = 0, 1
 RT_RENDER_REBUILD_BVH, RT_RENDER_NO_BVH, RT_RENDER_CANVAS_DEVICE = 1, 2, 4

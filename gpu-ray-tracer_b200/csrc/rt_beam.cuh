@@ -48,12 +48,22 @@ __device__ __forceinline__ float beam_gmax(float v) {
     return fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 4));
 }
 
-// Closest-hit (ANY == false) or occlusion (ANY == true) query for the rays of one warp. Every lane of the warp must
+// The per-lane walk for warps whose rays do not share a direction octant: out of line, it is cold.
+template <bool STATS>
+__device__ __noinline__ bool beam_fallback(const SceneView& s, const rtx::Ray& r, bool any, bool use_box, float max_t, Hit& best, TravStats& st) {
+    TravStats* stp = STATS ? &st : nullptr;
+    return any ? bvh_query<true>(s, r, use_box, max_t, best, stp) : bvh_query<false>(s, r, use_box, max_t, best, stp);
+}
+
+// Closest-hit (any == false) or occlusion (any == true) query for the rays of one warp. Every lane of the warp must
 // call it (full-mask shuffles); `active` says whether the lane carries a ray. Closest hit: returns whether the lane's
 // ray hit, `best` holds the hit. Occlusion: returns whether anything blocks the lane's ray within max_t.
-template <bool ANY, bool STATS>
-__device__ __forceinline__ bool beam_query(const SceneView& s, const rtx::Ray& r, bool active, bool use_box, float max_t, Hit& best,
-                                           TravStats& st, BeamStats& bst) {
+// One out-of-line copy serves the camera rays and every light's shadow rays of k_tile (`any` is a run-time flag): the
+// kernel's hot loop has to fit the instruction cache (the first version inlined a closest-hit and an occlusion copy, each
+// with its per-lane fallback — 96 KB of SASS, 3.2 warps stalled on instruction fetch per issued instruction).
+template <bool STATS>
+__device__ __noinline__ bool beam_query(const SceneView& s, const rtx::Ray& r, bool active, const bool ANY, bool use_box, float max_t,
+                                        Hit& best, TravStats& st, BeamStats& bst) {
     const unsigned FULLM = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     hit_reset(best);
@@ -65,8 +75,7 @@ __device__ __forceinline__ bool beam_query(const SceneView& s, const rtx::Ray& r
     const unsigned oct_first = __shfl_sync(FULLM, rp.octinv, __ffs((int)act0) - 1);
     if (__any_sync(FULLM, active && rp.octinv != oct_first)) {
         if (!active) return false;
-        TravStats* stp = STATS ? &st : nullptr;
-        return bvh_query<ANY>(s, r, use_box, max_t, best, stp);
+        return beam_fallback<STATS>(s, r, ANY, use_box, max_t, best, st);
     }
     const unsigned octinv = oct_first;
     // mirrored coordinates: axis k negated when the rays travel in its negative direction, so that 1 / d > 0

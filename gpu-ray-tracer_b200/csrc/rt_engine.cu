@@ -692,19 +692,23 @@ struct PeerCanvases { uint32_t* p[RT_MAX_PEERS]; int n; };
 struct PushSignal { long long mailbox_offset; unsigned epoch; unsigned* done_blocks; };
 struct PeerOut { PeerCanvases pc; PushSignal sg; int rank; };
 
-struct AttenMask {  // what Light::attenuate returned for light l: its colour, or black when the shadow ray was blocked
-    unsigned long long occl;
-    __device__ __forceinline__ float4 operator()(int l, const LightRec& L) const {
-        return ((occl >> l) & 1ull) ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : L.color;
-    }
-};
-
+// PHASE 0: the whole tile in one kernel. PHASE 1 + PHASE 2: the same code cut at the hit — k_tile<1> finds the closest
+// hits and appends them tile-aligned (32 slots per tile with a hit, lane l -> slot l) to the hit queue, k_tile<2> pulls
+// those groups and shades them. Two launches and 64 B of queue traffic per hit slot, but each kernel's hot loop fits
+// the instruction cache and runs with fewer registers (measured: profiles/r2_summary.md).
 #ifndef RT_TILE_MIN_BLOCKS
 #define RT_TILE_MIN_BLOCKS 2
 #endif
-template <bool STATS, bool SECONDARY, bool PEERS>
-__global__ void __launch_bounds__(kThreads, RT_TILE_MIN_BLOCKS) k_tile(SceneView s, TileMap tm, unsigned long long* ctr, uint32_t* canvas,
-                                                                      PeerOut po, unsigned char* paths, int path_stride, int* queue) {
+#ifndef RT_TILE1_MIN_BLOCKS
+#define RT_TILE1_MIN_BLOCKS 3
+#endif
+#ifndef RT_TILE2_MIN_BLOCKS
+#define RT_TILE2_MIN_BLOCKS 2   /* 128 registers: at 3 blocks (80) the shading phase spills 324 B and runs 6 % slower */
+#endif
+template <bool STATS, bool SECONDARY, bool PEERS, int PHASE>
+__global__ void __launch_bounds__(kThreads, PHASE == 0 ? RT_TILE_MIN_BLOCKS : PHASE == 1 ? RT_TILE1_MIN_BLOCKS : RT_TILE2_MIN_BLOCKS)
+k_tile(SceneView s, TileMap tm, unsigned long long* ctr, uint32_t* canvas, PeerOut po, unsigned char* paths, int path_stride, int* queue,
+       HitRec* hitq) {
     TravStats ts = {0, 0, 0};
     BeamStats bs = {0};
     RayCounts rc = {0, 0, 0};
@@ -718,25 +722,50 @@ __global__ void __launch_bounds__(kThreads, RT_TILE_MIN_BLOCKS) k_tile(SceneView
             canvas[out] = v;
         }
     };
+    const unsigned n_groups = PHASE == 2 ? (unsigned)ctr[C_HITQ] >> 5 : 0u;  // 32-slot hit groups left by k_tile<1>
     for (;;) {
         int q = 0;
-        if (lane == 0) q = (int)atomicAdd(&ctr[C_WORK0], 1ull);
+        if (lane == 0) q = (int)atomicAdd(&ctr[PHASE == 2 ? C_WORK1 : C_WORK0], 1ull);
         q = __shfl_sync(0xffffffffu, q, 0);
-        if (q >= n_work) break;
         int x, y, out;
-        const bool valid = tm.locate(q, lane, x, y, out);
         rtx::Ray r;
         r.o = s.cam.pos; r.d = s.cam.f;
-        if (valid) {
-            r = rtx::camera_ray(s.cam, (float)x, (float)y);
-            rc.primary++;
-        }
         Hit h;
-        const bool hit = beam_query<false, STATS>(s, r, valid, true, INFINITY, h, ts, bs);
-        if (valid && !hit) store(out, 0u);  // pack_color(0,0,0,0)
-        if (!__any_sync(0xffffffffu, hit)) continue;
-        if (hit) n_hit++;
-        // ---- shading of the tile's hits: k_shadow_gen + k_shadow + k_resolve
+        bool hit;
+        if (PHASE != 2) {
+            if (q >= n_work) break;
+            const bool valid = tm.locate(q, lane, x, y, out);
+            if (valid) {
+                r = rtx::camera_ray(s.cam, (float)x, (float)y);
+                rc.primary++;
+            }
+            hit = beam_query<STATS>(s, r, valid, false, true, INFINITY, h, ts, bs);
+            if (valid && !hit) store(out, 0u);  // pack_color(0,0,0,0)
+            const unsigned hm = __ballot_sync(0xffffffffu, hit);
+            if (!hm) continue;
+            if (PHASE == 1) {
+                // tile-aligned append (k_primary's): ctr[C_HITQ] low word = queue slots, high word = hits
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(&ctr[C_HITQ], 32ull | ((unsigned long long)__popc(hm) << 32));
+                base = __shfl_sync(0xffffffffu, base, 0) & 0xffffffffull;
+                HitRec rec;
+                rec.out_index = out; rec.xy = x | (y << 16); rec.inst = hit ? h.inst : -1; rec.tri = h.tri;
+                rec.t = h.t; rec.u = h.u; rec.v = h.v; rec.t_local = h.t_local;
+                hitq[base + (unsigned)lane] = rec;
+                continue;
+            }
+            if (hit) n_hit++;
+        } else {
+            if (PHASE == 2 && (unsigned)q >= n_groups) break;
+            const HitRec rec = hitq[(size_t)q * 32 + lane];
+            hit = rec.inst >= 0;
+            out = rec.out_index; x = rec.xy & 0xffff; y = (int)((unsigned)rec.xy >> 16);
+            h.t = rec.t; h.t_local = rec.t_local; h.u = rec.u; h.v = rec.v; h.inst = rec.inst; h.tri = rec.tri;
+            if (hit) r = rtx::camera_ray(s.cam, (float)x, (float)y);
+        }
+        // ---- shading of the tile's hits: k_shadow_gen + k_shadow + k_resolve in place. illuminate() (phong.cu:35-53):
+        // Ke + Ka * ambience, then one Phong term per light in light order — accumulated as the lights' shadow rays are
+        // answered, in the order and with the operations of illuminate_resolved().
         float3 nrm = rtx::mk3(0.f, 0.f, 0.f), hit_pos = rtx::mk3(0.f, 0.f, 0.f);
         int mat_id = 0;
         if (hit) {
@@ -745,18 +774,21 @@ __global__ void __launch_bounds__(kThreads, RT_TILE_MIN_BLOCKS) k_tile(SceneView
             hit_pos = rtx::ray_at(r, h.t);
         }
         const MatRec& m = s.mats[mat_id];
-        unsigned long long occl = 0ull;  // bit l: light l's shadow ray is blocked
+        float4 kd = rtx::mk4(0.f, 0.f, 0.f, 0.f), sum = kd;
+        if (hit) {
+            kd = diffuse_colour(s, m, h.tri, h.u, h.v);
+            sum = rtx::add4(m.Ke, rtx::mul4(m.Ka, s.ambience));
+        }
         for (int l = 0; l < s.n_lights; l++) {
             bool trace = false;
             rtx::Ray sr;
             sr.o = hit_pos; sr.d = r.d;
-            float max_t = 0.0f;
+            float3 dir = r.d;
+            float max_t = 0.0f, da = 1.0f;
             if (hit) {
-                float3 dir;
-                float da;
                 light_setup(s, s.lights[l], hit_pos, dir, max_t, da);
                 if (s.cull_unlit && light_unlit(m, nrm, dir)) {
-                    culled++;  // never read by illuminate_resolved (same predicate there)
+                    culled++;  // zero Phong weight: the term is +0 whatever the shadow ray says (rt_shade.cuh light_unlit)
                 } else {
                     trace = true;
                     sr = shadow_ray(hit_pos, dir);
@@ -764,10 +796,15 @@ __global__ void __launch_bounds__(kThreads, RT_TILE_MIN_BLOCKS) k_tile(SceneView
                 }
             }
             Hit sh;
-            if (beam_query<true, STATS>(s, sr, trace, true, max_t, sh, ts, bs)) occl |= 1ull << l;
+            const bool blocked = beam_query<STATS>(s, sr, trace, true, true, max_t, sh, ts, bs);
+            if (trace) {
+                const LightRec& L = s.lights[l];
+                const float4 a = blocked ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : L.color;
+                const float4 incoming = L.kind == 0 ? rtx::scale4(da, a) : a;
+                sum = rtx::add4(sum, phong(m, kd, nrm, incoming, r.d, dir));
+            }
         }
         if (!hit) continue;
-        const AttenMask att = {occl};
         if (SECONDARY && (m.reflective || m.refractive)) {
             // the pixel continues: first RayFrame transitions here (k_resolve<true>), then the bounce waves
             int slot = warp_alloc(&ctr[C_PATHS]);
@@ -778,7 +815,7 @@ __global__ void __launch_bounds__(kThreads, RT_TILE_MIN_BLOCKS) k_tile(SceneView
             int stack_top = 0, isect_mat = mat_id;
             float4 acc = rtx::mk4(0.f, 0.f, 0.f, 0.f);
             bool alive = path_advance_core(
-                s, [&](const rtx::Ray& ray, float t, float3 nn, const MatRec& mm, float4 kd) { return illuminate_resolved(s, ray, t, nn, mm, kd, att); },
+                s, [&](const rtx::Ray&, float, float3, const MatRec&, float4) { return sum; },  // illuminate() of this hit
                 frames, stack_top, isect_mat, acc, true, h, top, true);
             if (alive) {
                 PathHead hd;
@@ -792,18 +829,17 @@ __global__ void __launch_bounds__(kThreads, RT_TILE_MIN_BLOCKS) k_tile(SceneView
             continue;
         }
         // no secondary rays: acc = 0 + 1 * illuminate, clamp, pack (src/raytracer.cu:36-41)
-        float4 c = illuminate_resolved(s, r, h.t, nrm, m, diffuse_colour(s, m, h.tri, h.u, h.v), att);
-        store(out, rtx::pack_color(c));
+        store(out, rtx::pack_color(sum));
     }
     flush_counts(ctr, rc, ts, STATS);
     flush_culled(s, ctr, culled);
     {
         unsigned v = n_hit, f = bs.node_fetches;
         for (int o = 16; o; o >>= 1) { v += __shfl_xor_sync(0xffffffffu, v, o); f += __shfl_xor_sync(0xffffffffu, f, o); }
-        if (lane == 0 && v) atomicAdd(&ctr[C_HITQ], (unsigned long long)v << 32);  // high word = hits (n_hits)
+        if (PHASE == 0 && lane == 0 && v) atomicAdd(&ctr[C_HITQ], (unsigned long long)v << 32);  // high word = hits (n_hits)
         if (STATS && lane == 0 && f) atomicAdd(&ctr[C_FETCHES], (unsigned long long)f);
     }
-    if (PEERS) {
+    if (PEERS && PHASE != 1) {
         // every block: make its peer stores visible system-wide, then count itself; the last block signals
         __shared__ bool s_last;
         __threadfence_system();
@@ -1402,10 +1438,10 @@ static int persistent_grid(K kernel, int sm_count) {
 }
 
 // Is wave 0 of this frame one k_tile launch? Scenes whose shadow rays are occlusion queries (no refractive material),
-// at most 64 lights (the occlusion mask of a hit), BVH traversal with the reference's leaf-box rule.
+// BVH traversal with the reference's leaf-box rule.
 static bool tile_kernel_eligible(const RtScene* sc, const SceneView& v, int mode) {
     static const int env_off = [] { const char* e = std::getenv("RT_TILE_KERNEL"); return (e && !std::atoi(e)) ? 1 : 0; }();
-    return mode == TR_BVH_BOX && !env_off && !sc->fused_shade && !sc->split_shade && !v.any_refractive && v.n_lights <= 64;
+    return mode == TR_BVH_BOX && !env_off && !sc->fused_shade && !sc->split_shade && !v.any_refractive;
 }
 
 template <int MODE, bool STATS>
@@ -1479,16 +1515,30 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         std::memset(&po, 0, sizeof po);
         if (peers) po = *peers;
         int* qa = secondary ? sc->d_queue_a.as<int>() : nullptr;
-        if (peers) {
-            static const int g = persistent_grid(k_tile<STATS, false, true>, sc->sm_count);
-            k_tile<STATS, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, canvas, po, nullptr, 0, nullptr);
-        } else if (secondary) {
-            static const int g = persistent_grid(k_tile<STATS, true, false>, sc->sm_count);
-            k_tile<STATS, true, false><<<g, kThreads, 0, st>>>(v, tm, ctr, canvas, po, paths, path_stride, qa);
-        } else {
-            static const int g = persistent_grid(k_tile<STATS, false, false>, sc->sm_count);
-            k_tile<STATS, false, false><<<g, kThreads, 0, st>>>(v, tm, ctr, canvas, po, nullptr, 0, nullptr);
+        // RT_TILE_PHASES=1: the whole tile in one kernel; 2 (default): closest hits, then shading, through the hit queue
+        static const int phases = [] { const char* e = std::getenv("RT_TILE_PHASES"); int v = e ? std::atoi(e) : 2; return v == 1 ? 1 : 2; }();
+        HitRec* hq = nullptr;
+        if (phases == 2) {
+            if (sc->d_hitq.reserve(sizeof(HitRec) * (size_t)std::max<long long>(n_pix, 1))) return RT_ERR_OUT_OF_MEMORY;
+            hq = sc->d_hitq.as<HitRec>();
         }
+#define RT_LAUNCH_TILE(SEC, PEER, PH)                                                                              \
+        {                                                                                                          \
+            static const int g = persistent_grid(k_tile<STATS, SEC, PEER, PH>, sc->sm_count);                      \
+            k_tile<STATS, SEC, PEER, PH><<<g, kThreads, 0, st>>>(v, tm, ctr, canvas, po, paths, path_stride, qa, hq); \
+            sc->kernel_launches++;                                                                                 \
+        }
+        if (phases == 2) {
+            if (peers) { RT_LAUNCH_TILE(false, true, 1) RT_LAUNCH_TILE(false, true, 2) }
+            else if (secondary) { RT_LAUNCH_TILE(true, false, 1) RT_LAUNCH_TILE(true, false, 2) }
+            else { RT_LAUNCH_TILE(false, false, 1) RT_LAUNCH_TILE(false, false, 2) }
+        } else {
+            if (peers) RT_LAUNCH_TILE(false, true, 0)
+            else if (secondary) RT_LAUNCH_TILE(true, false, 0)
+            else RT_LAUNCH_TILE(false, false, 0)
+        }
+#undef RT_LAUNCH_TILE
+        sc->kernel_launches--;  // the common tail below counts wave 0's last kernel
         sc->tile_kernel_used = true;
         RT_CUDA(cudaEventRecord(cev[1], st));
         RT_CUDA(cudaEventRecord(cev[2], st));

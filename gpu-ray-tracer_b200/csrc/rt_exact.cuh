@@ -153,6 +153,11 @@ RT_HD bool ref_box_intersects(const float* box, bool nondegenerate, const Ray& r
 
 // ---- rmath::Plane::hit + rmath::Triangle::hit (include/raymath/geometry.h:253-261, 275-290) ----
 // Unsigned-area barycentric test: accept iff |b0+b1+b2-1| <= THRESHOLD. uv = (b1, b2).
+// One unsigned sub-area over the triangle's area (geometry.h:283-285). Out of line on the device: three calls instead
+// of three inlined copies of cross + sqrt + divide keep the exact-test code small (instruction cache, rt_engine.cu k_tile).
+RT_HD_NOINLINE float ref_bary_term(float3 x, float3 y, float3 p, float tri_area) {
+    return len3(cross3(sub3(x, p), sub3(y, p))) / tri_area;
+}
 RT_HD bool ref_triangle_hit(float3 a, float3 b, float3 c, const Ray& r, float& time, float& u, float& v) {
     float3 plane_norm = cross3(sub3(b, a), sub3(c, a));
     float3 n = normalized3(plane_norm);
@@ -161,9 +166,9 @@ RT_HD bool ref_triangle_hit(float3 a, float3 b, float3 c, const Ray& r, float& t
     time = (1.0f / denom) * dot3(sub3(a, r.o), n);
     float3 p = ray_at(r, time);
     float tri_area = len3(plane_norm);
-    float bary0 = len3(cross3(sub3(c, p), sub3(b, p))) / tri_area;
-    float bary1 = len3(cross3(sub3(c, p), sub3(a, p))) / tri_area;
-    float bary2 = len3(cross3(sub3(a, p), sub3(b, p))) / tri_area;
+    float bary0 = ref_bary_term(c, b, p, tri_area);
+    float bary1 = ref_bary_term(c, a, p, tri_area);
+    float bary2 = ref_bary_term(a, b, p, tri_area);
     if (fabsf(bary0 + bary1 + bary2 - 1.0f) <= RT_THR) {
         u = bary1;
         v = bary2;

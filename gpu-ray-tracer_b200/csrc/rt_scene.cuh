@@ -120,18 +120,24 @@ struct InstCtx {
     float radius;      // >= 0: the instance's hitable is a sphere of this radius; < 0: a triangle mesh
 };
 
+// A ray into the frame of one Entity: the direction through vec_to_local (its length is what cast_local / HitHandle
+// rescale the hit time by), the origin through point_to_local, the Ray constructor's normalisation. One out-of-line copy
+// serves both levels (instance, then mesh).
+RT_HD_NOINLINE float ray_into_pose(const rtx::Pose& pose, const rtx::Ray& in, rtx::Ray& out) {
+    float3 local_dir = rtx::vec_to_local(pose, in.d);
+    float len = rtx::len3(local_dir);
+    out = rtx::ray_make(rtx::point_to_local(pose, in.o), local_dir);
+    return len;
+}
 RT_HD_NOINLINE void inst_ctx_load(const SceneView& s, const rtx::Ray& r, int inst, bool use_box, InstCtx& c) {
     const InstRec& I = s.insts[inst];
     c.inst = inst;
     c.box_pass = use_box ? (rtx::ref_box_intersects(I.box, I.box_ok != 0, r) ? 1 : 0) : 1;
     if (!c.box_pass) return;
-    float3 local_dir = rtx::vec_to_local(I.pose, r.d);
-    c.dir_len = rtx::len3(local_dir);
-    rtx::Ray l1 = rtx::ray_make(rtx::point_to_local(I.pose, r.o), local_dir);
+    rtx::Ray l1;
+    c.dir_len = ray_into_pose(I.pose, r, l1);
     const MeshRec& M = s.meshes[I.mesh];
-    float3 ld2 = rtx::vec_to_local(M.pose, l1.d);
-    c.scale = rtx::len3(ld2);
-    c.lray = rtx::ray_make(rtx::point_to_local(M.pose, l1.o), ld2);
+    c.scale = ray_into_pose(M.pose, l1, c.lray);
     c.radius = M.kind == RT_HITABLE_SPHERE ? M.radius : -1.0f;
 }
 

@@ -160,7 +160,7 @@ enum {
                                     for pageable memory. Opt-in: slower than the staged, chunked copy on B200 */
     RT_RENDER_SPLIT_SHADE = 4096, /* wave 0 as the split pipeline k_primary -> k_shadow_gen -> k_shadow -> k_resolve through hit and
                                     shadow-ray queues in HBM instead of the one-kernel k_tile (warp-coherent traversal, no queues);
-                                    same frame. Scenes with a refractive material or more than 64 lights always take the split
+                                    same frame. Scenes with a refractive material always take the split
                                     pipeline (their shadow rays are closest-hit walks, src/rayprimitives/light.cu:34-60) */
     RT_RENDER_PEER_STORE = 8192, /* multi-GPU frame gathered by the kernels that produce the pixels: this rank's tiles (rank / world
                                     of RtRenderParams) are stored straight into the row-major peer canvases registered with

@@ -3,6 +3,10 @@ import sys
 
 import pytest
 
+# the multi-rank emulation tests run up to 8 scenes (16 streams) with spinning mailbox waits on ONE device: enough hardware
+# queues that no stream is serialised behind another scene's wait kernel (must be set before the CUDA context exists)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))

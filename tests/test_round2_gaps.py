@@ -288,9 +288,12 @@ def test_peer_store_frames(pkg, gpu_ok, name, n, root):
     for s in ranks:
         s.set_peers(canv, n, W * H, root)
     for frame in (1, 2, 3):
-        for r, s in enumerate(ranks):
-            s.render(flags=pkg.RT_RENDER_PEER_STORE | pkg.RT_RENDER_ASYNC | pkg.RT_RENDER_REBUILD_BVH, rank=r, world=n, tile_w=32, tile_h=16,
-                     out_ptr=0)
+        # on real hardware every rank has its own GPU; here the ranks share one, so the gathering rank's frame (whose last
+        # kernel spins on its mailbox) is enqueued last
+        order = [r for r in range(n) if r != root] + ([root] if root >= 0 else [])
+        for r in order:
+            ranks[r].render(flags=pkg.RT_RENDER_PEER_STORE | pkg.RT_RENDER_ASYNC | pkg.RT_RENDER_REBUILD_BVH, rank=r, world=n, tile_w=32,
+                            tile_h=16, out_ptr=0)
         rays = 0
         for r, s in enumerate(ranks):
             st = s.finish()

@@ -35,13 +35,38 @@ for STEP in "$@"; do
       timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 \
         bench.py --gpus $N --steps 20 --warmup 5 $EXTRA > gpurun_out/${TAG}_bench_n${N}_${SUF}.json 2> gpurun_out/${TAG}_bench_n${N}_${SUF}.err
       tail -c 1200 gpurun_out/${TAG}_bench_n${N}_${SUF}.json; tail -5 gpurun_out/${TAG}_bench_n${N}_${SUF}.err ;;
+    multiab)
+      # multiab:<N>;<label>=<env and bench args, comma separated>;...   several N-GPU bench runs in one call, e.g.
+      #   multiab:8;tile=--gather,fused-root;split=--split-shade,--gather,p2p
+      N=${ARG%%;*}; REST=${ARG#*;}
+      IFS=';' read -ra RUNS <<< "$REST"
+      for RUN in "${RUNS[@]}"; do
+        LBL=${RUN%%=*}; RA=${RUN#*=}; RA=${RA//,/ }
+        ENVS=""; BA=""
+        for TOK in $RA; do if [[ "$TOK" == [A-Z_]*=* && "$TOK" != --* ]]; then ENVS="$ENVS $TOK"; else BA="$BA $TOK"; fi; done
+        env $ENVS timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 \
+          bench.py --gpus $N --steps 20 --warmup 5 $BA > gpurun_out/${TAG}_n${N}_${LBL}.json 2> gpurun_out/${TAG}_n${N}_${LBL}.err
+        python - "$LBL" gpurun_out/${TAG}_n${N}_${LBL}.json <<'PY'
+import json, sys
+try:
+    l = json.loads(open(sys.argv[2]).read().strip().splitlines()[-1])
+    print("%-14s N=%d %.3f ms/step  %.0f Mrays/s  e2e %.3f ms  launches %d  %s" % (sys.argv[1], l["n_gpus"], l["ms_per_step"], l["value"], l["e2e"]["ms_per_step"], l["gpu_launches"], {k: round(v, 3) for k, v in l["breakdown_ms"].items()}))
+except Exception as e:
+    print(sys.argv[1], "FAILED", e)
+PY
+        grep -v "^W\|^\*\*\*\|OMP_NUM" gpurun_out/${TAG}_n${N}_${LBL}.err | tail -4
+      done ;;
     launches)
       timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${TAG}_launches.csv \
         python tools/profile_frame.py ${ARGS:-world16 3840 2160 9 3 1} > gpurun_out/${TAG}_launches.log 2>&1
       python tools/launch_summary.py gpurun_out/${TAG}_launches.csv | tee gpurun_out/${TAG}_launches.txt ;;
     ncu)
-      timeout 900 ncu --set full --clock-control none --import-source on -k regex:"$ARG" -s 6 -c 6 -f -o gpurun_out/${TAG}_full \
-        python tools/profile_frame.py world16 3840 2160 9 3 1 > gpurun_out/${TAG}_ncu.log 2>&1
+      # ncu:<regex>[,<skip>,<count>[,<profile_frame args...>]]   (skip / count are launches MATCHING the regex)
+      RX=${ARG%%,*}; REST=""; [[ "$ARG" == *,* ]] && REST=${ARG#*,}
+      SKIP=1; CNT=2; PF="world16 3840 2160 9 3 1"
+      if [ -n "$REST" ]; then SKIP=${REST%%,*}; REST2=${REST#*,}; CNT=${REST2%%,*}; [[ "$REST2" == *,* ]] && PF=${REST2#*,} && PF=${PF//,/ }; fi
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:"$RX" -s $SKIP -c $CNT -f -o gpurun_out/${TAG}_full \
+        python tools/profile_frame.py $PF > gpurun_out/${TAG}_ncu.log 2>&1
       ncu -i gpurun_out/${TAG}_full.ncu-rep --page details --csv > gpurun_out/${TAG}_ncu_details.csv 2>/dev/null
       ncu -i gpurun_out/${TAG}_full.ncu-rep --page raw --csv > gpurun_out/${TAG}_ncu_raw.csv 2>/dev/null
       ls -la gpurun_out/${TAG}_full.ncu-rep ;;
@@ -50,6 +75,23 @@ for STEP in "$@"; do
     refcmp)
       timeout 900 python tools/ref_gpu_compare.py ${ARGS:-20} > gpurun_out/${TAG}_ref_gpu_compare.jsonl 2> gpurun_out/${TAG}_ref_gpu_compare.err
       cat gpurun_out/${TAG}_ref_gpu_compare.jsonl | cut -c1-600 ;;
+    ab)
+      # ab:<variant>[,<variant>...][;bench args]  — A/B of engine builds from tools/build_variant.sh ("main" = the shipped library)
+      VARS=${ARG%%;*}; BARGS=""; [[ "$ARG" == *";"* ]] && BARGS=${ARG#*;}; BARGS=${BARGS//,/ }
+      for V in ${VARS//,/ }; do
+        LIB=""; [ "$V" != "main" ] && LIB=gpu-ray-tracer_b200/variants/librtb200_${V}.so
+        RTB200_CUDA_LIB=$LIB timeout 600 python bench.py --steps 20 --warmup 5 --no-stress --no-ref-cuda --no-cpu-baseline $BARGS \
+          > gpurun_out/${TAG}_ab_${V}.json 2> gpurun_out/${TAG}_ab_${V}.err
+        python - "$V" gpurun_out/${TAG}_ab_${V}.json <<'PY'
+import json, sys
+try:
+    l = json.loads(open(sys.argv[2]).read().strip().splitlines()[-1])
+    print("%-12s %.3f ms/step  %.0f Mrays/s  e2e %.3f ms  %s" % (sys.argv[1], l["ms_per_step"], l["value"], l["e2e"]["ms_per_step"], {k: round(v, 3) for k, v in l["breakdown_ms"].items()}))
+except Exception as e:
+    print(sys.argv[1], "FAILED", e)
+PY
+        tail -3 gpurun_out/${TAG}_ab_${V}.err
+      done ;;
     cmd)
       timeout 1200 bash -c "$ARGS" 2>&1 | tail -60 | tee gpurun_out/${TAG}_cmd.log ;;
     *) echo "unknown step $STEP" ;;
