@@ -61,7 +61,8 @@ def parse_args():
                          "de-interleave kernel")
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA-build leg (N = 1)")
     ap.add_argument("--no-stress", action="store_true", help="skip the world8_stress block (N = 1)")
-    ap.add_argument("--split-shade", action="store_true", help="RT_RENDER_SPLIT_SHADE: the round-1 split pipeline instead of k_tile")
+    ap.add_argument("--split-shade", action="store_true", help="RT_RENDER_SPLIT_SHADE: round 1's split pipeline (per-lane k_primary)")
+    ap.add_argument("--tile-kernel", action="store_true", help="RT_RENDER_TILE_KERNEL: wave 0 entirely in the tile kernels")
     ap.add_argument("--band-h", type=int, default=4,
                     help="N > 1, e2e: rows per full-width band dealt round-robin to the ranks (each rank copies its bands into the one shared host canvas)")
     ap.add_argument("--host-chunks", type=int, default=0, help="e2e: chunks per frame for copy/render overlap (0 = the library's default)")
@@ -272,7 +273,8 @@ def single_gpu_block(pkg, torch, a, scene_name, steps, flush):
     desc = wfile.desc
     canvas_dev = torch.zeros(H * W, dtype=torch.int32, device="cuda")
     host_canvas = torch.zeros(H * W, dtype=torch.int32).pin_memory()
-    base = (0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH) | (pkg.RT_RENDER_SPLIT_SHADE if a.split_shade else 0)
+    base = (0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH) | (pkg.RT_RENDER_SPLIT_SHADE if a.split_shade else 0) | \
+        (pkg.RT_RENDER_TILE_KERNEL if a.tile_kernel else 0)
 
     def dev():
         scene.render(flags=base | pkg.RT_RENDER_CANVAS_DEVICE | pkg.RT_RENDER_ASYNC, out_ptr=canvas_dev.data_ptr())
@@ -347,7 +349,7 @@ def run_ours(a):
     scene = pkg.Scene(wfile, device=local_rank)
     W, H = wfile.width, wfile.height
     base = (0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH) | (pkg.RT_RENDER_SORT_RAYS if a.sort_rays else 0) | \
-        (pkg.RT_RENDER_SPLIT_SHADE if a.split_shade else 0)
+        (pkg.RT_RENDER_SPLIT_SHADE if a.split_shade else 0) | (pkg.RT_RENDER_TILE_KERNEL if a.tile_kernel else 0)
     dev_flags = base | pkg.RT_RENDER_CANVAS_DEVICE | (pkg.RT_RENDER_TILED_OUTPUT if world > 1 else 0)
     params = scene.params(flags=dev_flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h)
     canvas_dev = torch.zeros(H * W, dtype=torch.int32, device="cuda")
@@ -551,11 +553,11 @@ def run_ours(a):
         hits = sst["n_hits"]
         #   k_shadow : 32 B per traced shadow ray (queue read) + 1 B (occlusion flag)
         shadow_traced = sst["rays_shadow"] - sst["rays_culled"]
-        if sst["tile_kernel"]:
+        if sst["tile_kernel"] == 1:
             # k_tile keeps rays, hits and shadow rays in registers: what it must move through HBM is the pixel it stores
             kernels = {"k_tile": (avg("ms_primary"), 4.0 * pix_local)}
         else:
-            kernels = {"k_primary": (avg("ms_primary"), 4.0 * (pix_local - hits) + 32.0 * hits),
+            kernels = {("k_tile<1>" if sst["tile_kernel"] == 2 else "k_primary"): (avg("ms_primary"), 4.0 * (pix_local - hits) + 32.0 * hits),
                        "k_shadow": (avg("ms_shadow"), 33.0 * shadow_traced)}
         dom = max(kernels, key=lambda k: kernels[k][0])
         dom_ms, dom_bytes = kernels[dom]
@@ -564,7 +566,7 @@ def run_ours(a):
         ms_trace = avg("ms_trace")
         traffic, traffic_src = None, None
         try:  # dram__bytes_read.sum + dram__bytes_write.sum of that kernel, one launch, from the committed ncu capture
-            cap = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json" if sst["tile_kernel"] else "r1_ncu_traffic.json")))
+            cap = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")))
             if cap["workload"] == workload_name(a) and world == 1:
                 traffic, traffic_src = cap["kernels"][dom]["traffic"], cap["source"]
         except Exception:
@@ -606,7 +608,9 @@ def run_ours(a):
                                  "shade": avg("ms_shade"), "k_shadow": avg("ms_shadow"), "bounce_waves": avg("ms_bounce"),
                                  "waves": st[0]["waves"]},
                 "roofline": roofline}
-        line["frame_kernels"] = "k_tile (wave 0 in one kernel, warp-coherent traversal)" if sst["tile_kernel"] else "k_primary + k_shadow_gen + k_shadow + k_resolve (split pipeline)"
+        line["frame_kernels"] = {0: "k_primary (per-lane walk) + k_shadow_gen + k_shadow + k_resolve (round 1's split pipeline)",
+                                 1: "k_tile<1> + k_tile<2> (tile kernels, warp-coherent traversal, no shadow queues)",
+                                 2: "k_tile<1> (warp-coherent closest hits) + k_shadow_gen + k_shadow + k_resolve"}[sst["tile_kernel"]]
         if world == 1 and not a.no_ref_cuda:
             line["ref_cuda"] = ref_cuda_block(a, a.scene, rays_per_frame, ms_dev / a.steps, ms_e2e / a.steps)
         if world == 1 and not a.no_stress and a.scene != "world8_stress":

@@ -1437,11 +1437,20 @@ static int persistent_grid(K kernel, int sm_count) {
     return sm_count * per_sm;
 }
 
-// Is wave 0 of this frame one k_tile launch? Scenes whose shadow rays are occlusion queries (no refractive material),
-// BVH traversal with the reference's leaf-box rule.
+// Wave 0 has three forms (all give the same frame; measured in profiles/r2_summary.md):
+//   split          k_primary (per-lane traversal) -> k_shadow_gen -> k_shadow -> k_resolve       RT_RENDER_SPLIT_SHADE
+//   beam primary   k_tile<1> (warp-coherent closest hits, rt_beam.cuh) -> the same split shading  the default
+//   tile kernels   k_tile<1> -> k_tile<2> (or the one-kernel k_tile<0>): no shadow queues         RT_RENDER_TILE_KERNEL
+// Is wave 0 of this frame run by the tile kernels? Opt-in (flag, or RT_TILE_KERNEL=1 in the environment), for scenes whose
+// shadow rays are occlusion queries (no refractive material), BVH traversal with the reference's leaf-box rule.
 static bool tile_kernel_eligible(const RtScene* sc, const SceneView& v, int mode) {
-    static const int env_off = [] { const char* e = std::getenv("RT_TILE_KERNEL"); return (e && !std::atoi(e)) ? 1 : 0; }();
-    return mode == TR_BVH_BOX && !env_off && !sc->fused_shade && !sc->split_shade && !v.any_refractive;
+    static const int env_on = [] { const char* e = std::getenv("RT_TILE_KERNEL"); return (e && std::atoi(e)) ? 1 : 0; }();
+    return mode == TR_BVH_BOX && (env_on || sc->tile_kernel) && !sc->fused_shade && !sc->split_shade && !v.any_refractive;
+}
+// The closest hits of the camera rays by the warp-coherent k_tile<1> in front of the split shading kernels (default).
+static bool beam_primary_eligible(const RtScene* sc, int mode) {
+    static const int env_off = [] { const char* e = std::getenv("RT_BEAM_PRIMARY"); return (e && !std::atoi(e)) ? 1 : 0; }();
+    return mode == TR_BVH_BOX && !env_off && !sc->fused_shade && !sc->split_shade;
 }
 
 template <int MODE, bool STATS>
@@ -1468,7 +1477,16 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     if (!use_tile || secondary) {
         if (sc->d_hitq.reserve(sizeof(HitRec) * (size_t)std::max<long long>(n_pix, 1))) return RT_ERR_OUT_OF_MEMORY;
     }
-    if (!use_tile) {
+    sc->wave0_form = use_tile ? 1 : 0;
+    if (!use_tile && beam_primary_eligible(sc, MODE)) {
+        PeerOut po0;
+        std::memset(&po0, 0, sizeof po0);
+        static const int g0 = persistent_grid(k_tile<STATS, false, false, 1>, sc->sm_count);
+        k_tile<STATS, false, false, 1><<<g0, kThreads, 0, st>>>(v, tm, ctr, canvas, po0, nullptr, 0, nullptr, sc->d_hitq.as<HitRec>());
+        sc->kernel_launches++;
+        sc->wave0_form = 2;
+        RT_CUDA(cudaEventRecord(cev[1], st));
+    } else if (!use_tile) {
         int g0 = persistent_grid(k_primary<MODE, STATS, false>, sc->sm_count);
         static const int aligned_hitq = [] { const char* e = std::getenv("RT_PACKED_HITQ"); return (e && std::atoi(e)) ? 0 : 1; }();
         k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr, aligned_hitq);
@@ -1970,6 +1988,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     sc->trace_unlit = (p.flags & RT_RENDER_TRACE_UNLIT) != 0;
     sc->sort_rays = (p.flags & RT_RENDER_SORT_RAYS) != 0;
     sc->split_shade = (p.flags & RT_RENDER_SPLIT_SHADE) != 0;
+    sc->tile_kernel = (p.flags & RT_RENDER_TILE_KERNEL) != 0;
     // RT_RENDER_PEER_STORE: this frame's epoch and canvases (double-buffered by the parity of the epoch)
     uint32_t* peer_own = nullptr;
     PeerOut po;
@@ -2081,7 +2100,11 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
             int w = 1;
             // peer frames without secondary rays: k_tile stores into the peers and signals them itself
             const bool secondary = v.any_secondary && v.depth > 0;
-            peer_direct = peer_store && !secondary && tile_kernel_eligible(sc, v, TR_BVH_BOX);
+            // Opt-in (RT_PEER_DIRECT=1): measured on 8 B200 the 4-byte pixel stores of a warp tile (four 32-byte runs) over
+            // NVLink stall the tile kernels — 0.333 ms for 1/8 of a world16 4K frame against 0.26 ms with local stores plus
+            // the 16-byte-vector forward kernel below (profiles/r2_summary.md) — the same finding as RT_RENDER_HOST_DIRECT.
+            static const bool env_direct = [] { const char* e = std::getenv("RT_PEER_DIRECT"); return e && std::atoi(e); }();
+            peer_direct = env_direct && peer_store && !secondary && tile_kernel_eligible(sc, v, TR_BVH_BOX);
             const PeerOut* pp = peer_direct ? &po : nullptr;
             if (want_stats) rc = run_wavefront<TR_BVH_BOX, true>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], pp);
             else rc = run_wavefront<TR_BVH_BOX, false>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], pp);
@@ -2190,7 +2213,7 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
     if (fs.waves > 4096) { set_error("bounce waves did not terminate"); return RT_ERR_LIMIT; }
     fs.kernel_launches = sc->kernel_launches - launches0;
     fs.host_chunks = sc->pend_direct ? 0 : n_chunks;
-    fs.tile_kernel = sc->tile_kernel_used ? 1 : 0;
+    fs.tile_kernel = sc->wave0_form;
     fs.node_fetches = host_ctr[C_FETCHES];
     if (stats) *stats = fs;
     return RT_OK;

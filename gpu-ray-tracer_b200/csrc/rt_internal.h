@@ -101,6 +101,8 @@ struct RtScene {
     bool split_shade_used = false;
     bool split_shade = false;       // RT_RENDER_SPLIT_SHADE: never use the one-kernel wave 0 (k_tile)
     bool tile_kernel_used = false;
+    bool tile_kernel = false;       // RT_RENDER_TILE_KERNEL
+    int wave0_form = 0;             // 0 split, 1 tile kernels, 2 beam primary + split shading (RtFrameStats.tile_kernel)
     rth::Bvh bvh;
     bool boxes_valid = false;
     cudaStream_t stream = nullptr;      // the stream all work of this scene goes to: own_stream or the caller's (rt_scene_set_stream)

@@ -158,10 +158,14 @@ enum {
                                     cudaHostRegister): the kernels write it directly over PCIe while the frame renders instead
                                     of rendering into a device canvas that is copied afterwards. Falls back to the staged copy
                                     for pageable memory. Opt-in: slower than the staged, chunked copy on B200 */
-    RT_RENDER_SPLIT_SHADE = 4096, /* wave 0 as the split pipeline k_primary -> k_shadow_gen -> k_shadow -> k_resolve through hit and
-                                    shadow-ray queues in HBM instead of the one-kernel k_tile (warp-coherent traversal, no queues);
-                                    same frame. Scenes with a refractive material always take the split
-                                    pipeline (their shadow rays are closest-hit walks, src/rayprimitives/light.cu:34-60) */
+    RT_RENDER_SPLIT_SHADE = 4096, /* wave 0 as round 1's split pipeline: k_primary with the per-lane BVH8 walk, then k_shadow_gen ->
+                                    k_shadow -> k_resolve. Default: the camera rays' closest hits come from the warp-coherent
+                                    k_tile<1> (rt_beam.cuh: one walk per 8x4 tile) in front of the same shading kernels. Same frame */
+    RT_RENDER_TILE_KERNEL = 16384, /* wave 0 entirely in the tile kernels: closest hits, then shadow rays + Phong + pixel per tile with the
+                                    warp-coherent traversal — no shadow-ray queues, 2 launches (1 with RT_TILE_PHASES=1). Same
+                                    frame; 26 % fewer instructions but lower issue rate (instruction cache, 128 registers), so it
+                                    is opt-in: equal to the default on 1 GPU, slower on 8. Scenes with a refractive
+                                    material always shade through the split kernels (closest-hit shadow walks, light.cu:34-60) */
     RT_RENDER_PEER_STORE = 8192, /* multi-GPU frame gathered by the kernels that produce the pixels: this rank's tiles (rank / world
                                     of RtRenderParams) are stored straight into the row-major peer canvases registered with
                                     rt_scene_set_peers over NVLink, and the frame's completion is signalled through their
@@ -206,7 +210,9 @@ typedef struct RtFrameStats {
                                  traversal (zero Phong weight, see RT_RENDER_TRACE_UNLIT) */
     int32_t host_chunks;      /* chunks the frame was cut into for the host copy (RtRenderParams.host_chunks); the per-kernel
                                  times above are sums over the chunks. 0 = no copy: the kernels wrote the host canvas directly */
-    int32_t tile_kernel;      /* 1: wave 0 ran as the one-kernel k_tile (ms_primary is its time, ms_shade / ms_shadow are 0) */
+    int32_t tile_kernel;      /* form of wave 0: 0 = split pipeline with the per-lane k_primary, 2 = warp-coherent closest hits
+                                 (k_tile<1>) + split shading (default), 1 = tile kernels only (ms_primary is their time,
+                                 ms_shade / ms_shadow are 0) */
     uint64_t node_fetches;    /* RT_RENDER_STATS, k_tile: 80-byte node fetches after the warp broadcast (one per warp-level
                                  visit); nodes_visited counts the same visits once per active ray */
 } RtFrameStats;

@@ -106,7 +106,7 @@ def test_c4_world16_4k_depth9(pkg, big):
     assert (inst >= 0).sum() == st["n_hits"]
     assert oracle_bands(pkg, w, c, inst, tri, t, scene=s) >= 6 * 2 * W4K
     # every pipeline variant: same canvas, same query count
-    for flags in (pkg.RT_RENDER_FUSED_SHADE, pkg.RT_RENDER_TRACE_UNLIT, pkg.RT_RENDER_REFIT_BVH, pkg.RT_RENDER_SPLIT_SHADE, 0):
+    for flags in (pkg.RT_RENDER_FUSED_SHADE, pkg.RT_RENDER_TRACE_UNLIT, pkg.RT_RENDER_REFIT_BVH, pkg.RT_RENDER_SPLIT_SHADE, pkg.RT_RENDER_TILE_KERNEL, 0):
         c2, st2 = s.render(flags=flags)
         assert (c2 == c).all() and st2["rays_total"] == st["rays_total"], flags
     for chunks in (1, 2, 5):
@@ -139,7 +139,9 @@ def test_c5_world8_stress_4k(pkg, big):
     c3, st3 = s.render(flags=pkg.RT_RENDER_REFIT_BVH, host_chunks=3)
     assert (c3 == c).all() and st3["rays_total"] == st["rays_total"]
     c4, st4 = s.render(flags=pkg.RT_RENDER_SPLIT_SHADE)
-    assert (c4 == c).all() and st4["rays_total"] == st["rays_total"] and st4["tile_kernel"] == 0 and st["tile_kernel"] == 1
+    assert (c4 == c).all() and st4["rays_total"] == st["rays_total"] and st4["tile_kernel"] == 0 and st["tile_kernel"] == 2
+    c5, st5 = s.render(flags=pkg.RT_RENDER_TILE_KERNEL)
+    assert (c5 == c).all() and st5["rays_total"] == st["rays_total"] and st5["tile_kernel"] == 1 and st5["waves"] == st["waves"]
 
 
 @pytest.mark.parametrize("name,bands", [("grid64", 4), ("grid64_mirror", 4), ("grid128", 3)])

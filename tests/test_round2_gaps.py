@@ -250,23 +250,42 @@ def _oracle_rows(pkg, w, width, height, rows):
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,kw", [("world4", {}), ("world16", {}), ("world8_stress", {"depth": 9}), ("world16", {"width": 1000, "height": 333}),
                                      ("grid64_mirror", {}), ("textured8", {})])
-def test_tile_kernel_equals_split_pipeline(pkg, gpu_ok, name, kw):
-    """k_tile (warp-coherent traversal, no queues) and the split pipeline give the same frame and the same query
-    counts; the frame equals the oracle's on row bands."""
+def test_tile_kernel_equals_split_pipeline(pkg, gpu_ok, monkeypatch, name, kw):
+    """The three forms of wave 0 — round 1's split pipeline, warp-coherent closest hits (k_tile<1>) in front of the
+    split shading (default), tile kernels only (RT_RENDER_TILE_KERNEL, in two phases and as one kernel) — give the
+    same frame and the same query counts; the frame equals the oracle's on row bands."""
     w = pkg.World(scene_path(name), **kw)
     s = pkg.Scene(w)
     c, st = s.render(flags=pkg.RT_RENDER_REBUILD_BVH | pkg.RT_RENDER_STATS)
     c2, st2 = s.render(flags=pkg.RT_RENDER_SPLIT_SHADE | pkg.RT_RENDER_STATS)
-    assert st["tile_kernel"] == 1 and st2["tile_kernel"] == 0
+    c3, st3 = s.render(flags=pkg.RT_RENDER_TILE_KERNEL | pkg.RT_RENDER_STATS)
+    assert (st["tile_kernel"], st2["tile_kernel"], st3["tile_kernel"]) == (2, 0, 1)
     assert (c == c2).all(), int((c != c2).sum())
+    assert (c == c3).all(), int((c != c3).sum())
     for k in ("rays_total", "rays_primary", "rays_shadow", "rays_secondary", "rays_culled", "n_hits", "waves"):
-        assert st[k] == st2[k], (k, st[k], st2[k])
-    assert 0 < st["node_fetches"] < st["nodes_visited"] <= st2["nodes_visited"] * 4
+        assert st[k] == st2[k] == st3[k], (k, st[k], st2[k], st3[k])
+    assert 0 < st3["node_fetches"] < st3["nodes_visited"] <= st2["nodes_visited"] * 4
+    assert 0 < st["node_fetches"] < st3["node_fetches"] and st2["node_fetches"] == 0
     o = ob.OracleScene(w)
     H = w.height
     for y0 in (H // 3, H // 2, (3 * H) // 4):
         oc, _ = o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1, rows=(y0, y0 + 2))
         assert (c[y0:y0 + 2] == oc[y0:y0 + 2]).all()
+    s.close()
+
+
+@pytest.mark.gpu
+def test_refractive_scene_beam_primary(pkg, gpu_ok):
+    """world1 (refractive cube): the tile kernels are not eligible (closest-hit shadow walks), the warp-coherent closest
+    hits are; RT_RENDER_TILE_KERNEL is ignored, the frame equals the split pipeline's and the oracle's."""
+    w = pkg.World(scene_path("world1"), depth=5)
+    s = pkg.Scene(w)
+    c, st = s.render(flags=pkg.RT_RENDER_TILE_KERNEL)
+    c2, st2 = s.render(flags=pkg.RT_RENDER_SPLIT_SHADE)
+    assert (st["tile_kernel"], st2["tile_kernel"]) == (2, 0)
+    assert (c == c2).all() and st["rays_total"] == st2["rays_total"]
+    oc, ost = ob.OracleScene(w).render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    assert (c == oc).all() and st["rays_total"] == ost["rays_total"]
     s.close()
 
 

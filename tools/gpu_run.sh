@@ -92,6 +92,25 @@ except Exception as e:
 PY
         tail -3 gpurun_out/${TAG}_ab_${V}.err
       done ;;
+    abf)
+      # abf:<label>=<env / bench args, comma separated>;...   A/B of bench flags on one GPU with the shipped library
+      IFS=';' read -ra RUNS <<< "$ARG"
+      for RUN in "${RUNS[@]}"; do
+        LBL=${RUN%%=*}; RA=${RUN#*=}; [ "$RA" == "$RUN" ] && RA=""; RA=${RA//,/ }
+        ENVS=""; BA=""
+        for TOK in $RA; do if [[ "$TOK" == [A-Z_]*=* && "$TOK" != --* ]]; then ENVS="$ENVS $TOK"; else BA="$BA $TOK"; fi; done
+        env $ENVS timeout 600 python bench.py --steps 20 --warmup 5 --no-stress --no-ref-cuda --no-cpu-baseline $BA \
+          > gpurun_out/${TAG}_abf_${LBL}.json 2> gpurun_out/${TAG}_abf_${LBL}.err
+        python - "$LBL" gpurun_out/${TAG}_abf_${LBL}.json <<'PY'
+import json, sys
+try:
+    l = json.loads(open(sys.argv[2]).read().strip().splitlines()[-1])
+    print("%-14s %.3f ms/step  %.0f Mrays/s  e2e %.3f ms  launches %d  %s" % (sys.argv[1], l["ms_per_step"], l["value"], l["e2e"]["ms_per_step"], l["gpu_launches"], {k: round(v, 3) for k, v in l["breakdown_ms"].items()}))
+except Exception as e:
+    print(sys.argv[1], "FAILED", e)
+PY
+        tail -2 gpurun_out/${TAG}_abf_${LBL}.err
+      done ;;
     cmd)
       timeout 1200 bash -c "$ARGS" 2>&1 | tail -60 | tee gpurun_out/${TAG}_cmd.log ;;
     *) echo "unknown step $STEP" ;;
