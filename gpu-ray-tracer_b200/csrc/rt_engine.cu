@@ -479,6 +479,46 @@ __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(Scene
     flush_counts(ctr, rc, ts, STATS);
 }
 
+// Wave 0, opaque scenes: the shadow-ray queue of a light is slot-indexed like the tile-aligned hit queue, so 32 consecutive
+// entries are the shadow rays of ONE 8x4 tile towards ONE light (holes: misses and culled lights). Walked together by the
+// warp-coherent traversal of rt_beam.cuh instead of 32 per-lane occlusion queries; same flags out.
+template <bool STATS>
+__global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow_beam(SceneView s, unsigned long long* ctr, int ctr_n,
+                                                                               const ShadowRec* shq, unsigned char* occl,
+                                                                               unsigned long long* work) {
+    TravStats ts = {0, 0, 0};
+    BeamStats bs = {0};
+    RayCounts rc = {0, 0, 0};
+    const long long n_hits = (long long)(unsigned)ctr[ctr_n];  // queue slots: a multiple of 32
+    const long long total = n_hits * s.n_lights;
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        unsigned long long b = 0;
+        if (lane == 0) b = atomicAdd(work, 32ull);
+        b = __shfl_sync(0xffffffffu, b, 0);
+        if ((long long)b >= total) break;
+        const long long f = (long long)b + lane;
+        const long long l = (long long)b / n_hits;  // warp-uniform: n_hits is a multiple of 32
+        const ShadowRec q = shq[f];
+        const bool trace = q.o_maxt.w >= 0.f;       // not a hole
+        rtx::Ray r;
+        r.o = rtx::mk3(q.o_maxt.x, q.o_maxt.y, q.o_maxt.z);
+        r.d = rtx::mk3(q.d.x, q.d.y, q.d.z);
+        Hit h;
+        const bool blocked = beam_query<STATS>(s, r, trace, true, true, q.o_maxt.w, h, ts, bs);
+        if (trace) {
+            rc.shadow++;
+            occl[(size_t)l * n_hits + (size_t)__float_as_int(q.d.w)] = blocked ? 1 : 0;
+        }
+    }
+    flush_counts(ctr, rc, ts, STATS);
+    if (STATS) {
+        unsigned f = bs.node_fetches;
+        for (int o = 16; o; o >>= 1) f += __shfl_xor_sync(0xffffffffu, f, o);
+        if (lane == 0 && f) atomicAdd(&ctr[C_FETCHES], (unsigned long long)f);
+    }
+}
+
 // What Light::attenuate returned for (light l, hit i of n), from whichever k_shadow variant ran.
 struct AttenLookup {
     const unsigned char* occl;
@@ -1404,6 +1444,7 @@ int rt_scene_set_canvas_size(RtScene* sc, int32_t w, int32_t h) {
     if (!sc || w <= 0 || h <= 0 || w > 65535 || h > 65535) { set_error("invalid canvas size"); return RT_ERR_INVALID_ARG; }
     if ((long long)w * h > (1ll << 30)) { set_error("canvas larger than 2^30 pixels"); return RT_ERR_LIMIT; }
     sc->width = w; sc->height = h;
+    sc->sb_choice = -1; sc->sb_frames = 0; sc->sb_ms[0] = sc->sb_ms[1] = 0.0f;
     sc->camera.canvas_width = (float)w;
     sc->camera.canvas_height = (float)h;
     return RT_OK;
@@ -1520,6 +1561,21 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     auto trace_shadows = [&](int ctr_n) {
         static const int static_split = [] { const char* e = std::getenv("RT_SHADOW_STATIC"); return (e && std::atoi(e)) ? 1 : 0; }();
         unsigned long long* work = static_split ? nullptr : ctr + C_WORK1;  // zeroed with the frame's counters
+        // Wave 0 of an opaque scene behind k_tile<1>: the queues are tile-aligned, so one warp-coherent occlusion walk per
+        // tile and light is possible (k_shadow_beam). Which kernel wins depends on the scene (world16 at 4K: 0.61 ms against
+        // 0.70 per lane; world8_stress: 0.40 against 0.31, where most shadow rays are blocked at once and a lane-wise walk
+        // stops early), so a scene times both on its first four frames (same flags either way) and keeps the faster;
+        // RT_BEAM_SHADOW=0|1 forces one.
+        static const int beam_env = [] { const char* e = std::getenv("RT_BEAM_SHADOW"); return e ? (std::atoi(e) ? 1 : 0) : -1; }();
+        const bool beam_possible = !loop && sc->wave0_form == 2 && ctr_n == C_HITQ && v.n_lights > 0;
+        const int beam_pick = beam_env >= 0 ? beam_env : sc->sb_choice >= 0 ? sc->sb_choice : ((sc->sb_frames & 1) ? 0 : 1);
+        sc->sb_used = beam_possible ? beam_pick : -1;
+        if (beam_possible && beam_pick) {
+            static const int g = persistent_grid(k_shadow_beam<STATS>, sc->sm_count);
+            k_shadow_beam<STATS><<<g, kThreads, 0, st>>>(v, ctr, ctr_n, shq, occl, ctr + C_WORK1);
+            sc->kernel_launches++;
+            return;
+        }
         if (loop) k_shadow<MODE, STATS, true><<<persistent_grid(k_shadow<MODE, STATS, true>, sc->sm_count), kThreads, 0, st>>>(
             v, ctr, ctr_n, shq, shq_count, occl, att4, work);
         else k_shadow<MODE, STATS, false><<<persistent_grid(k_shadow<MODE, STATS, false>, sc->sm_count), kThreads, 0, st>>>(
@@ -2152,6 +2208,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     sc->pend_direct = direct;
     RT_CUDA(cudaEventRecord(sc->ev[5], st));
     sc->pending = true;
+    sc->pend_stats = want_stats;
     sc->pend_built = built; sc->pend_wavefront = wavefront; sc->pend_waves = waves; sc->pend_launches0 = launches0;
     if (p.flags & RT_RENDER_ASYNC) return RT_OK;  // rt_frame_finish() completes the frame
     return rt_frame_finish(sc, stats);
@@ -2207,6 +2264,12 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
             RT_CUDA(cudaEventElapsedTime(&ms, sc->cev[c][4], sc->cev[c][5])); fs.ms_bounce += ms;
         }
         fs.n_hits = (int32_t)(host_ctr[C_HITQ] >> 32);  // high word = hits, low word = queue slots
+    }
+    if (wavefront && sc->split_shade_used && n_chunks == 1 && sc->sb_choice < 0 && sc->sb_used >= 0 && !sc->pend_stats) {
+        // auto-selection of the wave-0 shadow kernel (run_wavefront, trace_shadows): best of two frames each
+        float& best = sc->sb_ms[sc->sb_used];
+        if (best <= 0.0f || fs.ms_shadow < best) best = fs.ms_shadow;
+        if (++sc->sb_frames >= 4) sc->sb_choice = sc->sb_ms[1] <= sc->sb_ms[0] ? 1 : 0;
     }
     for (int k = 0; k < 4; k++) fs.ms_wave_phase[k] = (float)host_ctr[C_PHASE_NS + k] * 1e-6f;
     fs.waves = waves >= 0 ? waves : 1 + (int)host_ctr[C_WAVES];

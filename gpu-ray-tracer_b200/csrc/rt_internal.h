@@ -102,6 +102,11 @@ struct RtScene {
     bool split_shade = false;       // RT_RENDER_SPLIT_SHADE: never use the one-kernel wave 0 (k_tile)
     bool tile_kernel_used = false;
     bool tile_kernel = false;       // RT_RENDER_TILE_KERNEL
+    // wave-0 shadow kernel auto-selection: frames timed so far, best k_shadow time per variant [per-lane, warp-coherent],
+    // the variant the pending frame used (-1: not applicable), the choice (-1: still measuring)
+    int sb_frames = 0, sb_used = -1, sb_choice = -1;
+    float sb_ms[2] = {0.0f, 0.0f};
+    bool pend_stats = false;
     int wave0_form = 0;             // 0 split, 1 tile kernels, 2 beam primary + split shading (RtFrameStats.tile_kernel)
     rth::Bvh bvh;
     bool boxes_valid = false;
