@@ -36,6 +36,7 @@ RT_RENDER_TILE_KERNEL = 16384
 RT_HITABLE_TRIMESH, RT_HITABLE_SPHERE = 0, 1
 RT_DEBUG_PREFIX_UPLOADS, RT_DEBUG_BVH8_LEVELS, RT_DEBUG_BUILD_PATH, RT_DEBUG_BUILD_LAUNCHES, RT_DEBUG_BUILD_CLUSTER = 0, 1, 2, 3, 4
 RT_DEBUG_BUILD_PHASE_NS = 16
+RT_CAST_STATIC_MAX_RAYS = 65536
 
 
 class RtMaterial(C.Structure):
@@ -187,6 +188,7 @@ def cuda_lib():
         lib.rt_tile_map.argtypes = [i32, i32, i32, i32, i32, i32, vp, C.POINTER(C.c_int64)]
         lib.rt_trace_primary.argtypes = [vp, i32, vp, vp, vp]
         lib.rt_cast_rays.argtypes = [vp, i32, vp, vp, i32, vp, vp, vp]
+        lib.rt_cast_rays_static.argtypes = [vp, i32, vp, vp, i32, vp, vp, vp]
         lib.rt_debug_cast.argtypes = [vp, i32, i32, i32, C.POINTER(RtHit)]
         lib.rt_bvh_download.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp]
         lib.rt_bvh8_download.argtypes = [vp, vp, i32, i32p, vp, vp, i32, i32p]
@@ -444,6 +446,16 @@ class Scene:
         inst = np.empty(n, np.int32); tri = np.empty(n, np.int32); t = np.empty(n, np.float32)
         _check(cuda_lib().rt_cast_rays(self._h, use_bvh, o.ctypes.data, d.ctypes.data, n, inst.ctypes.data,
                                        tri.ctypes.data, t.ctypes.data), "rt_cast_rays")
+        return inst, tri, t
+
+    def cast_rays_static(self, origins, dirs, use_bvh=1):
+        """rt_cast_rays_static: rt_cast_rays over the library's static device scratch (no allocation, at most
+        RT_CAST_STATIC_MAX_RAYS rays, an existing BVH)."""
+        o = np.ascontiguousarray(origins, np.float32); d = np.ascontiguousarray(dirs, np.float32)
+        n = o.shape[0]
+        inst = np.empty(n, np.int32); tri = np.empty(n, np.int32); t = np.empty(n, np.float32)
+        _check(cuda_lib().rt_cast_rays_static(self._h, use_bvh, o.ctypes.data, d.ctypes.data, n, inst.ctypes.data,
+                                              tri.ctypes.data, t.ctypes.data), "rt_cast_rays_static")
         return inst, tri, t
 
     def debug_cast(self, x, y, semantics=RT_SEMANTICS_GPU):

@@ -2439,3 +2439,93 @@ int rt_measure_l2_bandwidth(int64_t bytes, int32_t iters, float* gbps) {
 }
 
 }  // extern "C"
+
+// ================================================================ rt_cast_rays without any allocation
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it). rt_cast_rays stages the rays and their
+// results in RtScene::d_ids, a grow-only cudaMalloc buffer; this variant runs the same kernel (k_cast_rays) over a
+// file-scope device array instead: 36 bytes per ray (origin 12, direction 12, instance 4, triangle 4, t 4) for at most
+// RT_CAST_STATIC_MAX_RAYS rays = 2.25 MiB, held by every GPU that loads the library until the process exits.
+//   * In host code `g_cast_static` is only a host-side stand-in for the symbol, not a device address: its device address is
+//     looked up once per device with cudaGetSymbolAddress (that device current) and that pointer is what the kernel gets.
+//   * Every call — any scene, any stream, any host thread — shares the one array of its GPU. It keeps the previous call's
+//     contents; nothing in it has to start at zero, because every word a call reads was written by that same call (the
+//     inputs are copied into [0, n), the kernel stores all three results for every i < n). Calls that overlap on the GPU
+//     race; the entry point synchronises its stream before it returns and serialises its callers on the host.
+//   * No cudaMalloc / cudaFree / allocating library call: a BVH has to exist already (RT_ERR_NO_BVH otherwise).
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_cast_static[(size_t)RT_CAST_STATIC_MAX_RAYS * 36];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_cast_static_mutex;
+void* g_cast_static_ptr[kMaxDevices] = {};  // device address of g_cast_static per device ordinal, null = not looked up yet
+
+// Set-up, once per device, with that device current. Called with g_cast_static_mutex held.
+int cast_static_address(unsigned char** out) {
+    int dev = -1;
+    RT_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { set_error("device ordinal out of range for the static scratch table"); return RT_ERR_LIMIT; }
+    if (!g_cast_static_ptr[dev]) {
+        void* p = nullptr;
+        RT_CUDA(cudaGetSymbolAddress(&p, g_cast_static));
+        if (!p) { set_error("cudaGetSymbolAddress returned a null address for the static scratch array"); return RT_ERR_CUDA; }
+        g_cast_static_ptr[dev] = p;
+    }
+    *out = (unsigned char*)g_cast_static_ptr[dev];
+    return RT_OK;
+}
+}  // namespace
+
+extern "C" int rt_cast_rays_static(RtScene* sc, int32_t use_bvh, const float* origins, const float* dirs, int32_t n,
+                                   int32_t* instance, int32_t* triangle, float* t) {
+    if (!sc || n < 0 || (n && (!origins || !dirs || !instance || !triangle || !t))) { set_error("invalid argument"); return RT_ERR_INVALID_ARG; }
+    if (n > RT_CAST_STATIC_MAX_RAYS) {
+        set_error("rt_cast_rays_static: n = " + std::to_string(n) + " rays exceeds RT_CAST_STATIC_MAX_RAYS = " +
+                  std::to_string((int)RT_CAST_STATIC_MAX_RAYS) + " (the static scratch array); split the batch or use rt_cast_rays");
+        return RT_ERR_LIMIT;
+    }
+    int mode;
+    switch (use_bvh) {
+        case 1: mode = TR_BVH_BOX; break;
+        case 0: mode = TR_BRUTE; break;
+        case 2: mode = TR_BVH_NOBOX; break;
+        case 3: mode = TR_BRUTE_BOX; break;
+        default: set_error("use_bvh must be 0, 1, 2 or 3 (see rt_cast_rays)"); return RT_ERR_INVALID_ARG;
+    }
+    if (sc->pending) { set_error("a frame is pending: call rt_frame_finish first"); return RT_ERR_INVALID_ARG; }
+    if ((mode == TR_BVH_BOX || mode == TR_BVH_NOBOX) && !sc->bvh.valid) {
+        set_error("rt_cast_rays_static builds nothing: call rt_bvh_build (or render a frame) first");
+        return RT_ERR_NO_BVH;
+    }
+    if (n == 0) return RT_OK;
+    std::lock_guard<std::mutex> lock(g_cast_static_mutex);
+    unsigned char* base = nullptr;
+    if (int rc = cast_static_address(&base)) return rc;
+    if (int rc = rth::update_instance_boxes(sc)) return rc;  // one kernel when instances moved; allocates nothing
+    const size_t nn = (size_t)n;
+    int* di = (int*)base;
+    int* dt = di + nn;
+    float* dtt = (float*)(di + 2 * nn);
+    float* d_o = dtt + nn;
+    float* d_d = d_o + 3 * nn;
+    cudaStream_t st = sc->stream;
+    RT_CUDA(cudaMemcpyAsync(d_o, origins, 12 * nn, cudaMemcpyHostToDevice, st));
+    RT_CUDA(cudaMemcpyAsync(d_d, dirs, 12 * nn, cudaMemcpyHostToDevice, st));
+    SceneView v = rth::make_view(sc, true);
+    const int g = (n + kThreads - 1) / kThreads;
+    switch (mode) {
+        case TR_BVH_BOX: k_cast_rays<TR_BVH_BOX><<<g, kThreads, 0, st>>>(v, d_o, d_d, n, di, dt, dtt); break;
+        case TR_BVH_NOBOX: k_cast_rays<TR_BVH_NOBOX><<<g, kThreads, 0, st>>>(v, d_o, d_d, n, di, dt, dtt); break;
+        case TR_BRUTE: k_cast_rays<TR_BRUTE><<<g, kThreads, 0, st>>>(v, d_o, d_d, n, di, dt, dtt); break;
+        default: k_cast_rays<TR_BRUTE_BOX><<<g, kThreads, 0, st>>>(v, d_o, d_d, n, di, dt, dtt); break;
+    }
+    sc->kernel_launches++;
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(instance, di, 4 * nn, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(triangle, dt, 4 * nn, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(t, dtt, 4 * nn, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    return RT_OK;
+}

@@ -350,6 +350,20 @@ int rt_trace_primary(RtScene* scene, int32_t use_bvh, int32_t* instance, int32_t
  * directions are normalised like the rmath::Ray constructor does (include/raymath/geometry.h:216). */
 int rt_cast_rays(RtScene* scene, int32_t use_bvh, const float* origins, const float* dirs, int32_t n,
                  int32_t* instance, int32_t* triangle, float* t);
+/* rt_cast_rays for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it). It has NO counterpart in the reference.
+ * Same arguments, same results (bit for bit) as rt_cast_rays; the device staging of the rays and their results lives
+ * in a static device array inside the library instead of a grow-only cudaMalloc buffer:
+ *   - at most RT_CAST_STATIC_MAX_RAYS rays per call (36 bytes each = 2.25 MiB, held by every GPU that loads the library
+ *     until the process exits); a larger n is refused with RT_ERR_LIMIT and a message naming the limit;
+ *   - the call allocates and frees nothing and builds nothing: for use_bvh 1 / 2 a BVH must already exist (rt_bvh_build
+ *     or a rendered frame), else RT_ERR_NO_BVH; a pending asynchronous frame must be finished first;
+ *   - all calls on one GPU share the one array, which keeps the last call's contents (nothing in it has to start at zero:
+ *     a call reads only what it wrote). Calls that overlap on the GPU race; the entry point serialises its callers on the
+ *     host and synchronises the scene's stream before it returns, so calls in a row are safe. */
+#define RT_CAST_STATIC_MAX_RAYS 65536
+int rt_cast_rays_static(RtScene* scene, int32_t use_bvh, const float* origins, const float* dirs, int32_t n,
+                        int32_t* instance, int32_t* triangle, float* t);
 /* Replaces rtracer::gpu::debug_cast (src/raytracer.cu:91-100) without device printf. */
 int rt_debug_cast(RtScene* scene, int32_t x, int32_t y, int32_t semantics, RtHit* out);
 
