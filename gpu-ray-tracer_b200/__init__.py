@@ -36,6 +36,7 @@ RT_RENDER_TILE_KERNEL = 16384
 RT_HITABLE_TRIMESH, RT_HITABLE_SPHERE = 0, 1
 RT_DEBUG_PREFIX_UPLOADS, RT_DEBUG_BVH8_LEVELS, RT_DEBUG_BUILD_PATH, RT_DEBUG_BUILD_LAUNCHES, RT_DEBUG_BUILD_CLUSTER = 0, 1, 2, 3, 4
 RT_DEBUG_BUILD_PHASE_NS = 16
+RT_DEBUG_BUILD_LEVEL_NS = 32
 RT_CAST_STATIC_MAX_RAYS = 65536
 
 

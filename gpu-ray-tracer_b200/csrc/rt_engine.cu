@@ -191,6 +191,20 @@ __global__ void k_instance_boxes(InstRec* insts, int n, const MeshRec* meshes, c
     insts[i].box_ok = I.box_ok;
 }
 
+// Scene set-up: the ray-independent part of every mesh triangle's exact test (rt_exact.cuh ref_triangle_pre).
+__global__ void k_tri_precompute(const TriRec* tris, int n, const float4* verts, int n_verts, float4* tri_pre) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const TriRec T = tris[i];
+    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (T.v0 >= 0 && T.v1 >= 0 && T.v2 >= 0 && T.v0 < n_verts && T.v1 < n_verts && T.v2 < n_verts) {  // a sphere's record has no vertices
+        const float4 a = verts[T.v0], b = verts[T.v1], c = verts[T.v2];
+        const rtx::TriPre p = rtx::ref_triangle_pre(rtx::mk3(a.x, a.y, a.z), rtx::mk3(b.x, b.y, b.z), rtx::mk3(c.x, c.y, c.z));
+        o = make_float4(p.n.x, p.n.y, p.n.z, p.area);
+    }
+    tri_pre[i] = o;
+}
+
 // ---------------------------------------------------------------- tracer selection
 enum { TR_BVH_BOX = 0, TR_BRUTE = 1, TR_BVH_NOBOX = 2, TR_BRUTE_BOX = 3 };
 template <int MODE> struct TracerOf;
@@ -1235,6 +1249,8 @@ SceneView make_view(const RtScene* sc, bool with_bvh) {
     v.verts = sc->d_verts.as<float4>();
     v.norms = sc->d_norms.as<float4>();
     v.tris = sc->d_tris.as<TriRec>();
+    static const int pre_off = [] { const char* e = std::getenv("RT_TRI_PRE"); return (e && !std::atoi(e)) ? 1 : 0; }();
+    v.tri_pre = (sc->d_tri_pre.p && !pre_off) ? sc->d_tri_pre.as<float4>() : nullptr;
     v.meshes = sc->d_meshes.as<MeshRec>();
     v.insts = sc->d_insts.as<InstRec>();
     v.mats = sc->d_mats.as<MatRec>();
@@ -1379,6 +1395,13 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
         (rc = upload(sc->d_meshes, hs.meshes, sc->stream)) || (rc = upload(sc->d_mesh_box, hs.mesh_box, sc->stream)) ||
         (rc = upload(sc->d_lights, hs.lights, sc->stream)))
         return fail(rc);
+    if (sc->n_triangles > 0) {
+        if (sc->d_tri_pre.reserve(sizeof(float4) * (size_t)sc->n_triangles)) return fail(RT_ERR_OUT_OF_MEMORY);
+        k_tri_precompute<<<(sc->n_triangles + kThreads - 1) / kThreads, kThreads, 0, sc->stream>>>(
+            sc->d_tris.as<TriRec>(), sc->n_triangles, sc->d_verts.as<float4>(), sc->n_vertices, sc->d_tri_pre.as<float4>());
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return fail(rth::cuda_fail(e, "k_tri_precompute", __FILE__, __LINE__));
+    }
     sc->textured = !hs.texc.empty();
     if (sc->textured) {
         sc->atlas_w = hs.atlas_w; sc->atlas_h = hs.atlas_h;
@@ -1399,7 +1422,7 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
 int rt_scene_destroy(RtScene* sc) {
     if (!sc) return RT_OK;
     if (sc->stream) cudaStreamSynchronize(sc->stream);
-    rth::DevBuf* all[] = {&sc->d_verts, &sc->d_norms, &sc->d_tris, &sc->d_meshes, &sc->d_insts, &sc->d_mats, &sc->d_lights,
+    rth::DevBuf* all[] = {&sc->d_verts, &sc->d_norms, &sc->d_tris, &sc->d_tri_pre, &sc->d_meshes, &sc->d_insts, &sc->d_mats, &sc->d_lights,
                           &sc->d_mesh_box, &sc->d_texc, &sc->d_atlas, &sc->d_push_ctr, &sc->d_sort_keys_a, &sc->d_sort_keys_b,
                           &sc->d_sort_vals_b, &sc->d_sort_hist, &sc->d_canvas, &sc->d_counters, &sc->d_hitq, &sc->d_paths, &sc->d_queue_a,
                           &sc->d_queue_b, &sc->d_ids, &sc->d_shadowq, &sc->d_occl, &sc->d_shq_count};
@@ -2400,6 +2423,13 @@ int rt_debug_get(RtScene* sc, int32_t what, int64_t* out) {
         default:
             // RT_DEBUG_BUILD_PHASE_NS + i, i in 0..6: nanoseconds CTA 0 of the last cluster build spent in phase i (flatten +
             // bounds, Morton, sort, Karras, chunk-local boxes, spanning boxes, BVH8 collapse); needs RT_BUILD_TIMERS=1
+            if (what >= RT_DEBUG_BUILD_LEVEL_NS && what < RT_DEBUG_BUILD_LEVEL_NS + 16) {  // raw stamp i of the collapse levels
+                unsigned long long v = 0;
+                if (!sc->bvh.scene_bounds.p || sc->bvh.scene_bounds.cap < 512) { set_error("no cluster build yet"); return RT_ERR_NO_BVH; }
+                RT_CUDA(cudaMemcpy(&v, (const char*)sc->bvh.scene_bounds.p + 256 + 8 * (what - RT_DEBUG_BUILD_LEVEL_NS), 8, cudaMemcpyDeviceToHost));
+                *out = (int64_t)v;
+                break;
+            }
             if (what >= RT_DEBUG_BUILD_PHASE_NS && what < RT_DEBUG_BUILD_PHASE_NS + 7) {
                 const unsigned long long* t = sc->h_pinned + 50;
                 *out = (int64_t)(t[what - RT_DEBUG_BUILD_PHASE_NS + 1] - t[what - RT_DEBUG_BUILD_PHASE_NS]);

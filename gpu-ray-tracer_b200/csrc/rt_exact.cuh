@@ -177,6 +177,33 @@ RT_HD bool ref_triangle_hit(float3 a, float3 b, float3 c, const Ray& r, float& t
     return false;
 }
 
+// The ray-independent part of rmath::Triangle::hit: plane normal (geometry.h:276), its normalisation (Plane ctor) and the
+// triangle's area (geometry.h:282). Computed once per mesh triangle at scene set-up with the very functions
+// ref_triangle_hit uses, so ref_triangle_hit_pre returns the same bits with two square roots and a divide fewer per candidate.
+struct TriPre { float3 n; float area; };
+RT_HD TriPre ref_triangle_pre(float3 a, float3 b, float3 c) {
+    float3 plane_norm = cross3(sub3(b, a), sub3(c, a));
+    TriPre p;
+    p.n = normalized3(plane_norm);
+    p.area = len3(plane_norm);
+    return p;
+}
+RT_HD bool ref_triangle_hit_pre(float3 a, float3 b, float3 c, float3 n, float tri_area, const Ray& r, float& time, float& u, float& v) {
+    float denom = dot3(r.d, n);
+    if (fabsf(denom) < RT_THR) return false;
+    time = (1.0f / denom) * dot3(sub3(a, r.o), n);
+    float3 p = ray_at(r, time);
+    float bary0 = ref_bary_term(c, b, p, tri_area);
+    float bary1 = ref_bary_term(c, a, p, tri_area);
+    float bary2 = ref_bary_term(a, b, p, tri_area);
+    if (fabsf(bary0 + bary1 + bary2 - 1.0f) <= RT_THR) {
+        u = bary1;
+        v = bary2;
+        return true;
+    }
+    return false;
+}
+
 // ---- rmath::reflect / refract (include/raymath/linear.h:215-242) ----
 RT_HD float3 ref_reflect(float3 dir, float3 norm) {
     float d_len = len3(dir);

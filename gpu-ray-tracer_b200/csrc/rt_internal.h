@@ -83,6 +83,7 @@ struct RtScene {
     bool trace_unlit = false;       // RT_RENDER_TRACE_UNLIT
     std::vector<int> mesh_tri_count;
     // device
+    rth::DevBuf d_tri_pre;          // float4 per triangle record: unit plane normal + area (k_tri_precompute)
     rth::DevBuf d_verts, d_norms, d_tris, d_meshes, d_insts, d_mats, d_lights, d_mesh_box;
     rth::DevBuf d_texc, d_atlas;    // TextureCoords per triangle record + RGBA atlas; empty when nothing is textured
     int atlas_w = 0, atlas_h = 0;

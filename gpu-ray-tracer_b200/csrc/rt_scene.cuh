@@ -50,6 +50,7 @@ struct SceneView {
     const InstRec* insts;
     const MatRec* mats;
     const LightRec* lights;
+    const float4* tri_pre; // per triangle record: unit plane normal + area (rtx::ref_triangle_pre); null = computed per candidate
     const TexRec* texc;    // per triangle record, null when the scene has no atlas or no textured triangle
     const float4* atlas;   // RGBA texels, row-major
     int atlas_w, atlas_h;
@@ -173,9 +174,15 @@ RT_HD_NOINLINE bool exact_candidate(const SceneView& s, const rtx::Ray& r, int i
     } else {
         const TriRec T = s.tris[tri];
         float4 a4 = s.verts[T.v0], b4 = s.verts[T.v1], c4 = s.verts[T.v2];
-        if (!rtx::ref_triangle_hit(rtx::mk3(a4.x, a4.y, a4.z), rtx::mk3(b4.x, b4.y, b4.z), rtx::mk3(c4.x, c4.y, c4.z),
-                                   ctx.lray, time, u, v))
+        if (s.tri_pre) {
+            const float4 pn = s.tri_pre[tri];
+            if (!rtx::ref_triangle_hit_pre(rtx::mk3(a4.x, a4.y, a4.z), rtx::mk3(b4.x, b4.y, b4.z), rtx::mk3(c4.x, c4.y, c4.z),
+                                           rtx::mk3(pn.x, pn.y, pn.z), pn.w, ctx.lray, time, u, v))
+                return false;
+        } else if (!rtx::ref_triangle_hit(rtx::mk3(a4.x, a4.y, a4.z), rtx::mk3(b4.x, b4.y, b4.z), rtx::mk3(c4.x, c4.y, c4.z),
+                                          ctx.lray, time, u, v)) {
             return false;
+        }
     }
     if (!(time >= RT_THR)) return false;
     float t_world = (time * ctx.scale) * ctx.dir_len;

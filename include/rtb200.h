@@ -383,7 +383,8 @@ enum {
     RT_DEBUG_BUILD_PATH = 2,     /* 1 = multi-kernel pipeline, 2 = one-launch thread-block-cluster build */
     RT_DEBUG_BUILD_LAUNCHES = 3, /* kernels the last build / refit launched */
     RT_DEBUG_BUILD_CLUSTER = 4,  /* CTAs in the cluster of the last one-launch build (0: multi-kernel pipeline) */
-    RT_DEBUG_BUILD_PHASE_NS = 16 /* + i (0..6): ns per phase of the last cluster build, with RT_BUILD_TIMERS=1 in the environment */
+    RT_DEBUG_BUILD_PHASE_NS = 16, /* + i (0..6): ns per phase of the last cluster build, with RT_BUILD_TIMERS=1 in the environment */
+    RT_DEBUG_BUILD_LEVEL_NS = 32 /* + i (0..15): raw globaltimer stamp after phase A (even i) / phase B (odd i) of collapse level i / 2 */
 };
 int rt_debug_get(RtScene* scene, int32_t what, int64_t* out);
 

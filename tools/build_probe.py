@@ -27,4 +27,6 @@ for label, env in (("cluster16", {"RT_BUILD_CLUSTER": "16"}), ("cluster8", {"RT_
     if s.debug_get(pkg.RT_DEBUG_BUILD_PATH) == 2:
         ph = [s.debug_get(pkg.RT_DEBUG_BUILD_PHASE_NS + i) / 1e3 for i in range(7)]
         line += " | phases us: " + ", ".join("%s %.1f" % (n, v) for n, v in zip(PHASES, ph))
+        st = [s.debug_get(pkg.RT_DEBUG_BUILD_LEVEL_NS + i) for i in range(2 * bs["n_levels8"])]
+        line += " | collapse levels us (A, B): " + " ".join("(%.1f, %.1f)" % ((st[2 * k] - (st[2 * k - 1] if k else st[0])) / 1e3, (st[2 * k + 1] - st[2 * k]) / 1e3) for k in range(bs["n_levels8"]))
     print(line, flush=True)
