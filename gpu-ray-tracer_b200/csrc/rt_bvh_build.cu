@@ -408,6 +408,7 @@ struct CollapseArgs {
     int* result;           // [0] = n_nodes8, [1] = n_prims emitted, [2] = levels, [3] = max level width
     int* node8_root;       // out: BVH2 id each BVH8 node was collapsed from      (kept for k_refit8)
     int* node8_slot;       // out: BVH2 id in each of its 8 slots, -1 when empty
+    const uint4* rec;      // per-node records (collapse_children_rec) or null: read the separate arrays
     unsigned long long* lvl_ns;  // RT_BUILD_TIMERS: per level, time stamps of block 0 after phase A and after phase B; else null
 };
 
@@ -464,6 +465,134 @@ __device__ __forceinline__ int g_argmax(float val, int j, float& val_out) {
 // Slots: greedy assignment maximising (child centroid - node centroid) . octant direction of the
 // slot, scanning children then slots with a strict comparison. On return lane s holds the BVH2 id
 // in slot s (or -1), and n_inner / n_leaf_prims are group-uniform.
+// Greedy slot assignment over the 8 lanes of a group, one (child, slot) pair per round: lane j holds child j's cost row
+// (has_child: the lane holds a child); returns the slot of this lane's child or -1.
+__device__ __forceinline__ int greedy_slots_g(const float (&cost)[8], bool has_child, int j) {
+    unsigned slot_done = 0;
+    bool mine_done = !has_child;
+    int my_slot = -1;
+#pragma unroll 1
+    for (int it = 0; it < 8; it++) {
+        // this lane's best free slot (lowest slot on ties)
+        float bv = -INFINITY;
+        int bs = -1;
+#pragma unroll
+        for (int s = 0; s < 8; s++)
+            if (!(slot_done & (1u << s)) && (bs < 0 || cost[s] > bv)) { bv = cost[s]; bs = s; }
+        // lanes that are done or empty must never win: key below every real value, NaN-free
+        float key = mine_done ? -INFINITY : bv;
+        int cand = mine_done ? 8 + j : j;  // done lanes sort after live ones on ties at -inf
+        // argmax over lanes with ties to the lowest live lane
+        float kv = key;
+        int ki = cand;
+        for (int o = 1; o < 8; o <<= 1) {
+            float ov = __shfl_xor_sync(FULL, kv, o, 8);
+            int oi = __shfl_xor_sync(FULL, ki, o, 8);
+            if (ov > kv || (ov == kv && oi < ki)) { kv = ov; ki = oi; }
+        }
+        bool any = ki < 8;  // a live lane won
+        int wslot = g_shfl(bs, ki & 7);
+        if (any) {
+            if (j == ki) { my_slot = bs; mine_done = true; }
+            slot_done |= 1u << wslot;
+        }
+    }
+    return my_slot;
+}
+
+// ---- the same selection from per-node RECORDS (the one-launch build): 64 bytes per BVH2 node,
+//   q0 = box.lo.xyz, left      q1 = box.hi.xyz, right      q2 = lo, hi, area(left), area(right)      q3 = size(left), size(right), -, -
+// with area(c) = half-area of c's box, or -1 when c covers <= 3 triangles (cannot be opened); leaves carry left = right = -1.
+// One 64-byte load tells everything about a node AND whether its children can be opened, so an opening costs one round
+// trip to L2 (the two new children fetch their records in the same branch) instead of four or five: the child lists of a
+// level are chains of dependent loads, and those chains — not arithmetic — set the collapse's time at these scene sizes.
+struct Rec2 { uint4 q0, q1, q2, q3; };
+__device__ __forceinline__ void rec_store(uint4* rec, int id, const float* box, int left, int right, int lo, int hi, float al, float ar,
+                                          int sl, int sr) {
+    uint4* r = rec + 4 * (size_t)id;
+    r[0] = make_uint4(__float_as_uint(box[0]), __float_as_uint(box[1]), __float_as_uint(box[2]), (unsigned)left);
+    r[1] = make_uint4(__float_as_uint(box[3]), __float_as_uint(box[4]), __float_as_uint(box[5]), (unsigned)right);
+    r[2] = make_uint4((unsigned)lo, (unsigned)hi, __float_as_uint(al), __float_as_uint(ar));
+    r[3] = make_uint4((unsigned)sl, (unsigned)sr, 0u, 0u);
+}
+__device__ int collapse_children_rec(const CollapseArgs& a, int root, int j, int& n_inner, int& n_leaf_prims) {
+    const uint4* rec = a.rec;
+    int ch = -1, size = 0;
+    float area = -2.0f;   // -2: empty position, -1: cannot be opened, >= 0: half-area
+    // this lane's child: its box and what its record says about ITS children
+    float cb[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    int cl = -1, cr = -1, sl = 0, sr = 0;
+    float al = -1.0f, ar = -1.0f;
+    auto load = [&](int id) {
+        const uint4* r = rec + 4 * (size_t)id;
+        const uint4 q0 = r[0], q1 = r[1], q2 = r[2], q3 = r[3];
+        cb[0] = __uint_as_float(q0.x); cb[1] = __uint_as_float(q0.y); cb[2] = __uint_as_float(q0.z);
+        cb[3] = __uint_as_float(q1.x); cb[4] = __uint_as_float(q1.y); cb[5] = __uint_as_float(q1.z);
+        cl = (int)q0.w; cr = (int)q1.w;
+        al = __uint_as_float(q2.z); ar = __uint_as_float(q2.w);
+        sl = (int)q3.x; sr = (int)q3.y;
+    };
+    // every lane reads the root's record (one broadcast transaction): its box for the cost rows, its children to start from
+    float nb[6];
+    int root_size, nc;
+    {
+        const uint4* r = rec + 4 * (size_t)root;
+        const uint4 q0 = r[0], q1 = r[1], q2 = r[2], q3 = r[3];
+        nb[0] = __uint_as_float(q0.x); nb[1] = __uint_as_float(q0.y); nb[2] = __uint_as_float(q0.z);
+        nb[3] = __uint_as_float(q1.x); nb[4] = __uint_as_float(q1.y); nb[5] = __uint_as_float(q1.z);
+        root_size = (int)q2.y - (int)q2.x + 1;
+        const bool single = root >= a.n - 1 || root_size <= 3;  // whole scene is one leaf
+        if (single) {
+            if (j == 0) { ch = root; area = -1.0f; size = root >= a.n - 1 ? 1 : root_size; }
+            nc = 1;
+        } else {
+            if (j == 0) { ch = (int)q0.w; area = __uint_as_float(q2.z); size = (int)q3.x; }
+            if (j == 1) { ch = (int)q1.w; area = __uint_as_float(q2.w); size = (int)q3.y; }
+            nc = 2;
+        }
+        if (ch >= 0) load(ch);
+    }
+#pragma unroll 1
+    for (int it = 0; it < 6; it++) {
+        float best_area;
+        const int best = g_argmax(area, j, best_area);
+        const bool open = best_area >= 0.0f && nc < 8;  // group-uniform; the trip count stays warp-uniform (full-mask shuffles)
+        const int l = g_shfl(cl, best), r = g_shfl(cr, best);
+        const float la = __int_as_float(g_shfl(__float_as_int(al), best)), ra = __int_as_float(g_shfl(__float_as_int(ar), best));
+        const int ls = g_shfl(sl, best), rs = g_shfl(sr, best);
+        if (open) {
+            if (j == best) { ch = l; area = la; size = ls; }
+            if (j == nc) { ch = r; area = ra; size = rs; }
+            if (j == best || j == nc) load(ch);  // both new children fetch their records together: one round trip per opening
+            nc++;
+        }
+    }
+    // cost row of this lane's child
+    float cost[8];
+    {
+        float ncx = (nb[0] + nb[3]) * 0.5f, ncy = (nb[1] + nb[4]) * 0.5f, ncz = (nb[2] + nb[5]) * 0.5f;
+        float dx = 0.f, dy = 0.f, dz = 0.f;
+        if (ch >= 0) {
+            dx = (cb[0] + cb[3]) * 0.5f - ncx; dy = (cb[1] + cb[4]) * 0.5f - ncy; dz = (cb[2] + cb[5]) * 0.5f - ncz;
+        }
+#pragma unroll
+        for (int s2 = 0; s2 < 8; s2++) cost[s2] = (((s2 & 1) ? dx : -dx) + ((s2 & 2) ? dy : -dy)) + ((s2 & 4) ? dz : -dz);
+    }
+    const int my_slot = greedy_slots_g(cost, ch >= 0, j);
+    // lane s <- child assigned to slot s
+    int child_of_slot = -1, sz = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        int sk = g_shfl(my_slot, k);
+        int ck = g_shfl(ch, k);
+        int zk = g_shfl(size, k);
+        if (sk == j) { child_of_slot = ck; sz = zk; }
+    }
+    n_inner = g_sum(sz > 3 ? 1 : 0);
+    n_leaf_prims = g_sum(sz > 3 ? 0 : sz);
+    return child_of_slot;
+}
+
 __device__ int collapse_children_g(const CollapseArgs& a, int root, int j, int& n_inner, int& n_leaf_prims) {
     int ch = -1;          // BVH2 id at list position j
     int cl = -1, cr = -1; // its two children, fetched together with it (one memory round trip per opening)
@@ -517,36 +646,7 @@ __device__ int collapse_children_g(const CollapseArgs& a, int root, int j, int& 
 #pragma unroll
         for (int s = 0; s < 8; s++) cost[s] = (((s & 1) ? dx : -dx) + ((s & 2) ? dy : -dy)) + ((s & 4) ? dz : -dz);
     }
-    // greedy assignment, one (child, slot) pair per round
-    unsigned slot_done = 0;
-    bool mine_done = ch < 0;
-    int my_slot = -1;
-#pragma unroll 1
-    for (int it = 0; it < 8; it++) {
-        // this lane's best free slot (lowest slot on ties)
-        float bv = -INFINITY;
-        int bs = -1;
-#pragma unroll
-        for (int s = 0; s < 8; s++)
-            if (!(slot_done & (1u << s)) && (bs < 0 || cost[s] > bv)) { bv = cost[s]; bs = s; }
-        // lanes that are done or empty must never win: key below every real value, NaN-free
-        float key = mine_done ? -INFINITY : bv;
-        int cand = mine_done ? 8 + j : j;  // done lanes sort after live ones on ties at -inf
-        // argmax over lanes with ties to the lowest live lane
-        float kv = key;
-        int ki = cand;
-        for (int o = 1; o < 8; o <<= 1) {
-            float ov = __shfl_xor_sync(FULL, kv, o, 8);
-            int oi = __shfl_xor_sync(FULL, ki, o, 8);
-            if (ov > kv || (ov == kv && oi < ki)) { kv = ov; ki = oi; }
-        }
-        bool any = ki < 8;  // a live lane won
-        int wslot = g_shfl(bs, ki & 7);
-        if (any) {
-            if (j == ki) { my_slot = bs; mine_done = true; }
-            slot_done |= 1u << wslot;
-        }
-    }
+    const int my_slot = greedy_slots_g(cost, ch >= 0, j);
     // lane s <- child assigned to slot s
     int child_of_slot = -1;
 #pragma unroll
@@ -705,6 +805,12 @@ __device__ __forceinline__ void collapse_levels(const CollapseArgs& a, Sync& syn
         int* btot = a.block_tot + (size_t)parity * G * 2;
         int per_block = (level_n + G - 1) / G;
         int c0 = min(level_n, bid * per_block), c1 = min(level_n, c0 + per_block);
+#ifdef RT_FINE
+#define FINE(k) if (a.lvl_ns && bid == 0 && threadIdx.x == 0 && levels == 2) a.lvl_ns[16 + (k)] = collapse_ns();
+#else
+#define FINE(k)
+#endif
+        FINE(0)
         // phase A: children + counts, 8 lanes per node
         const int group = threadIdx.x >> 3, j = threadIdx.x & 7, groups = B >> 3;
         int my_inner = 0, my_prims = 0;
@@ -712,7 +818,7 @@ __device__ __forceinline__ void collapse_levels(const CollapseArgs& a, Sync& syn
             int t = base + group;
             bool valid = t < c1;
             int ni, np;
-            int child = collapse_children_g(a, cur[valid ? t : c0], j, ni, np);
+            int child = a.rec ? collapse_children_rec(a, cur[valid ? t : c0], j, ni, np) : collapse_children_g(a, cur[valid ? t : c0], j, ni, np);
             if (valid) {
                 a.slots[8 * (size_t)t + j] = child;
                 if (j == 0) {
@@ -723,12 +829,14 @@ __device__ __forceinline__ void collapse_levels(const CollapseArgs& a, Sync& syn
                 }
             }
         }
+        FINE(1)
         for (int o = 16; o; o >>= 1) {
             my_inner += __shfl_xor_sync(0xffffffffu, my_inner, o);
             my_prims += __shfl_xor_sync(0xffffffffu, my_prims, o);
         }
         if (lane == 0) { s_warp[0][warp] = my_inner; s_warp[1][warp] = my_prims; }
         __syncthreads();
+        FINE(2)
         if (threadIdx.x == 0) {
             int ti = 0, tp = 0;
             for (int w = 0; w < B / 32; w++) { ti += s_warp[0][w]; tp += s_warp[1][w]; }
@@ -736,6 +844,7 @@ __device__ __forceinline__ void collapse_levels(const CollapseArgs& a, Sync& syn
             btot[2 * bid + 1] = tp;
         }
         sync();
+        FINE(3)
         if (a.lvl_ns && bid == 0 && threadIdx.x == 0 && levels < 8) a.lvl_ns[2 * levels] = collapse_ns();
         // phase B: block offsets (every block sums the totals of the blocks before it), ordered scan, emit
         int pre_i = 0, pre_p = 0, tot_i = 0, tot_p = 0;
@@ -767,6 +876,7 @@ __device__ __forceinline__ void collapse_levels(const CollapseArgs& a, Sync& syn
             s_base[0] = ti; s_base[1] = tp;
         }
         __syncthreads();
+        FINE(4)
         const int level_inner = s_base[0], level_prims = s_base[1];
         const int next_base = level_base + level_n;
         for (int t0 = c0; t0 < c1; t0 += B) {
@@ -794,6 +904,7 @@ __device__ __forceinline__ void collapse_levels(const CollapseArgs& a, Sync& syn
             __syncthreads();
         }
         __syncthreads();
+        FINE(5)
         for (int base = c0; base < c1; base += groups) {
             int t = base + group;
             bool valid = t < c1;
@@ -802,12 +913,16 @@ __device__ __forceinline__ void collapse_levels(const CollapseArgs& a, Sync& syn
             write_node8_g<true>(a, cur[tt], level_base + tt, a.slots[8 * (size_t)tt + j], j, child_base, a.counts[2 * (size_t)tt + 1],
                           next + (child_base - next_base), valid);
         }
+        FINE(6)
         level_base = next_base;
         prim_total += level_prims;
         level_n = level_inner;
         levels++;
         if (level_n > max_width) max_width = level_n;
         sync();
+#ifdef RT_FINE
+        if (a.lvl_ns && bid == 0 && threadIdx.x == 0 && levels == 3) a.lvl_ns[16 + 7] = collapse_ns();
+#endif
         if (a.lvl_ns && bid == 0 && threadIdx.x == 0 && levels <= 8) a.lvl_ns[2 * levels - 1] = collapse_ns();
     }
     if (bid == 0 && threadIdx.x == 0) {
@@ -875,6 +990,7 @@ struct ClusterBuildArgs {
     int* left; int* right; int* parent; int* range_lo; int* range_hi;
     float* node_box;
     float* edge_box;           // 6 floats x (n prefix unions, n suffix unions, G chunk totals)
+    uint4* rec;                // 4 x uint4 per BVH2 node (collapse_children_rec), or null
     CollapseArgs c;
     unsigned long long* phase_ns;  // 12 time stamps of CTA 0 (RT_BUILD_TIMERS), else null
     int smem_words;                // dynamic shared memory, in 32-bit words
@@ -1182,6 +1298,25 @@ __global__ void __launch_bounds__(kCT, 1) k_build_cluster(ClusterBuildArgs a) {
         for (int k = 0; k < 6; k++) a.node_box[6 * (size_t)i + k] = box[k];
     }
     cluster.sync();
+    if (a.rec) {  // per-node records for the collapse (collapse_children_rec)
+        for (int id = gt; id < 2 * n - 1; id += T) {
+            float box[6];
+#pragma unroll
+            for (int k = 0; k < 6; k++) box[k] = a.node_box[6 * (size_t)id + k];
+            if (id >= n - 1) {
+                rec_store(a.rec, id, box, -1, -1, id - (n - 1), id - (n - 1), -1.0f, -1.0f, 0, 0);
+            } else {
+                const int l = a.left[id], r = a.right[id];
+                const int sl = l >= n - 1 ? 1 : a.range_hi[l] - a.range_lo[l] + 1;
+                const int sr = r >= n - 1 ? 1 : a.range_hi[r] - a.range_lo[r] + 1;
+                float bl[6], br[6];
+#pragma unroll
+                for (int k = 0; k < 6; k++) { bl[k] = a.node_box[6 * (size_t)l + k]; br[k] = a.node_box[6 * (size_t)r + k]; }
+                rec_store(a.rec, id, box, l, r, a.range_lo[id], a.range_hi[id], sl <= 3 ? -1.0f : half_area(bl), sr <= 3 ? -1.0f : half_area(br), sl, sr);
+            }
+        }
+        cluster.sync();
+    }
     if (clock) a.phase_ns[6] = build_global_ns();
 
     // ---- BVH8
@@ -1256,7 +1391,8 @@ static int launch_cluster_build(RtScene* sc, const SceneView& v, int n, int key_
     Bvh& b = sc->bvh;
     cudaStream_t st = sc->stream;
     const size_t level_cap = (size_t)n + 8;
-    if (b.edge_box.reserve(sizeof(float) * 6 * (2 * (size_t)n + 16)) ||
+    static const bool use_rec = [] { const char* e = std::getenv("RT_BUILD_RECORDS"); return !(e && !std::atoi(e)); }();
+    if (b.edge_box.reserve(sizeof(float) * 6 * (2 * (size_t)n + 16)) || (use_rec && b.rec.reserve(64 * 2 * (size_t)n)) ||
         b.collapse_scratch.reserve(sizeof(int) * (level_cap * 2 + level_cap * 8 + level_cap * 2 + (size_t)G * 4 + 16)))
         return RT_ERR_OUT_OF_MEMORY;
     int* bounds_i = b.scene_bounds.as<int>();
@@ -1280,6 +1416,7 @@ static int launch_cluster_build(RtScene* sc, const SceneView& v, int n, int key_
     a.range_lo = b.range_lo.as<int>(); a.range_hi = b.range_hi.as<int>();
     a.node_box = b.node_box.as<float>();
     a.edge_box = b.edge_box.as<float>();
+    a.rec = use_rec ? b.rec.as<uint4>() : nullptr;
     static const bool timers = [] { const char* e = std::getenv("RT_BUILD_TIMERS"); return e && std::atoi(e); }();
     a.phase_ns = timers ? (unsigned long long*)(bounds_i + 16) : nullptr;
     int* w = b.collapse_scratch.as<int>();
@@ -1301,6 +1438,7 @@ static int launch_cluster_build(RtScene* sc, const SceneView& v, int n, int key_
     c.node8_root = b.node8_root.as<int>();
     c.node8_slot = b.node8_slot.as<int>();
     c.lvl_ns = timers ? (unsigned long long*)((char*)b.scene_bounds.p + 256) : nullptr;
+    c.rec = a.rec;
     cudaLaunchConfig_t cfg;
     std::memset(&cfg, 0, sizeof cfg);
     cfg.gridDim = dim3(G); cfg.blockDim = dim3(kCT); cfg.stream = st; cfg.dynamicSmemBytes = kClusterDynSmem;
@@ -1470,6 +1608,7 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     a.node8_root = b.node8_root.as<int>();
     a.node8_slot = b.node8_slot.as<int>();
     a.lvl_ns = nullptr;
+    a.rec = nullptr;
     RT_CUDA(cudaMemsetAsync(a.result, 0, 16 * sizeof(int), st));
     void* args[] = {&a};
     RT_CUDA(cudaLaunchCooperativeKernel((void*)k_collapse, dim3(G), dim3(kThreads), args, 0, st));

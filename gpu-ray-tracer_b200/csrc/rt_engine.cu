@@ -64,7 +64,7 @@ void DevBuf::release() {
 void Bvh::release() {
     DevBuf* all[] = {&prim_world, &prim_box, &scene_bounds, &keys_a, &keys_b, &vals_a, &vals_b, &hist, &left, &right,
                      &parent, &range_lo, &range_hi, &flags, &node_box, &nodes8, &prims8, &prim_order8, &work,
-                     &collapse_scratch, &edge_box, &node8_root, &node8_slot};
+                     &collapse_scratch, &edge_box, &rec, &node8_root, &node8_slot};
     for (DevBuf* b : all) b->release();
     if (h_off) { cudaFreeHost(h_off); h_off = nullptr; h_off_cap = 0; }
     off_in_flight = false;
@@ -2423,7 +2423,7 @@ int rt_debug_get(RtScene* sc, int32_t what, int64_t* out) {
         default:
             // RT_DEBUG_BUILD_PHASE_NS + i, i in 0..6: nanoseconds CTA 0 of the last cluster build spent in phase i (flatten +
             // bounds, Morton, sort, Karras, chunk-local boxes, spanning boxes, BVH8 collapse); needs RT_BUILD_TIMERS=1
-            if (what >= RT_DEBUG_BUILD_LEVEL_NS && what < RT_DEBUG_BUILD_LEVEL_NS + 16) {  // raw stamp i of the collapse levels
+            if (what >= RT_DEBUG_BUILD_LEVEL_NS && what < RT_DEBUG_BUILD_LEVEL_NS + 32) {  // raw stamp i of the collapse levels
                 unsigned long long v = 0;
                 if (!sc->bvh.scene_bounds.p || sc->bvh.scene_bounds.cap < 512) { set_error("no cluster build yet"); return RT_ERR_NO_BVH; }
                 RT_CUDA(cudaMemcpy(&v, (const char*)sc->bvh.scene_bounds.p + 256 + 8 * (what - RT_DEBUG_BUILD_LEVEL_NS), 8, cudaMemcpyDeviceToHost));

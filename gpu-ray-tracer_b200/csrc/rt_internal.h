@@ -53,6 +53,7 @@ struct Bvh {
     const int* sorted_vals = nullptr;
     DevBuf work;         // per-instance triangle prefix
     DevBuf collapse_scratch;  // level lists, slots, counts, block totals
+    DevBuf rec;               // cluster build: 64-byte per-node records for the collapse
     DevBuf edge_box;          // cluster build: prefix / suffix unions of each CTA's leaf chunk
     int cluster_size = 0;     // CTAs of the last one-launch build
     // kept for rt_bvh_refit: which BVH2 node every BVH8 node / slot came from, and the instance layout the
