@@ -65,11 +65,16 @@ PY
       RX=${ARG%%,*}; REST=""; [[ "$ARG" == *,* ]] && REST=${ARG#*,}
       SKIP=1; CNT=2; PF="world16 3840 2160 9 3 1"
       if [ -n "$REST" ]; then SKIP=${REST%%,*}; REST2=${REST#*,}; CNT=${REST2%%,*}; [[ "$REST2" == *,* ]] && PF=${REST2#*,} && PF=${PF//,/ }; fi
-      timeout 900 ncu --set full --clock-control none --import-source on -k regex:"$RX" -s $SKIP -c $CNT -f -o gpurun_out/${TAG}_full \
+      timeout 900 env ${NCU_ENV:-} ncu --set full --clock-control none --import-source on -k regex:"$RX" -s $SKIP -c $CNT -f -o gpurun_out/${TAG}_full \
         python tools/profile_frame.py $PF > gpurun_out/${TAG}_ncu.log 2>&1
       ncu -i gpurun_out/${TAG}_full.ncu-rep --page details --csv > gpurun_out/${TAG}_ncu_details.csv 2>/dev/null
       ncu -i gpurun_out/${TAG}_full.ncu-rep --page raw --csv > gpurun_out/${TAG}_ncu_raw.csv 2>/dev/null
       ls -la gpurun_out/${TAG}_full.ncu-rep ;;
+    ncum)
+      # ncum[:<env>,...]  — byte counters of every kernel of one frame: DRAM, L2 (lts) and L1 (l1tex) traffic, duration, instructions
+      timeout 900 env ${ARGS} ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,lts__t_bytes.sum,l1tex__t_bytes.sum,smsp__inst_executed.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,lts__t_sector_hit_rate.pct,l1tex__t_sector_hit_rate.pct \
+        --clock-control none -s 5 -c 12 --csv --log-file gpurun_out/${TAG}_ncum.csv python tools/profile_frame.py world16 3840 2160 9 3 1 > gpurun_out/${TAG}_ncum.log 2>&1
+      tail -2 gpurun_out/${TAG}_ncum.log ;;
     sanitizer)
       timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -25 | tee gpurun_out/${TAG}_sanitizer.log ;;
     refcmp)
