@@ -62,6 +62,7 @@ def parse_args():
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA-build leg (N = 1)")
     ap.add_argument("--no-stress", action="store_true", help="skip the world8_stress block (N = 1)")
     ap.add_argument("--split-shade", action="store_true", help="RT_RENDER_SPLIT_SHADE: round 1's split pipeline (per-lane k_primary)")
+    ap.add_argument("--graph", action="store_true", help="RT_RENDER_GRAPH: device-resident frames captured once and replayed as one CUDA graph")
     ap.add_argument("--tile-kernel", action="store_true", help="RT_RENDER_TILE_KERNEL: wave 0 entirely in the tile kernels")
     ap.add_argument("--band-h", type=int, default=4,
                     help="N > 1, e2e: rows per full-width band dealt round-robin to the ranks (each rank copies its bands into the one shared host canvas)")
@@ -342,6 +343,9 @@ def run_ours(a):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    # everything of this rank (engine, torch kernels, NCCL, timing events) goes to ONE non-default stream: the legacy default
+    # stream cannot be captured into a CUDA graph (--graph) and synchronises implicitly with every other stream
+    torch.cuda.set_stream(torch.cuda.Stream())
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     wfile = pkg.World(os.path.join(ROOT, "scenes", a.scene + ".json"), width=a.width, height=a.height, depth=a.depth,
@@ -350,7 +354,7 @@ def run_ours(a):
     W, H = wfile.width, wfile.height
     base = (0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH) | (pkg.RT_RENDER_SORT_RAYS if a.sort_rays else 0) | \
         (pkg.RT_RENDER_SPLIT_SHADE if a.split_shade else 0) | (pkg.RT_RENDER_TILE_KERNEL if a.tile_kernel else 0)
-    dev_flags = base | pkg.RT_RENDER_CANVAS_DEVICE | (pkg.RT_RENDER_TILED_OUTPUT if world > 1 else 0)
+    dev_flags = base | pkg.RT_RENDER_CANVAS_DEVICE | (pkg.RT_RENDER_TILED_OUTPUT if world > 1 else 0) | (pkg.RT_RENDER_GRAPH if a.graph else 0)
     params = scene.params(flags=dev_flags, rank=rank, world=world, tile_w=a.tile_w, tile_h=a.tile_h)
     canvas_dev = torch.zeros(H * W, dtype=torch.int32, device="cuda")
     host_canvas = torch.zeros(H * W, dtype=torch.int32).pin_memory()
@@ -604,6 +608,7 @@ def run_ours(a):
                         "d2h_bytes_per_step": 4 * W * H,
                         "path": e2e_path(world, a, outs_e2e[0]["host_chunks"])},
                 "gpu_launches": launches_all, "clocks": clocks,
+                "graph_frames": {"replayed": sum(1 for x in st if x["graph"] == 2), "captured": sum(1 for x in st if x["graph"] == 1), "plain": sum(1 for x in st if x["graph"] == 0)},
                 "breakdown_ms": {"build": avg("ms_build"), "trace": ms_trace, "k_primary": avg("ms_primary"),
                                  "shade": avg("ms_shade"), "k_shadow": avg("ms_shadow"), "bounce_waves": avg("ms_bounce"),
                                  "waves": st[0]["waves"]},

@@ -33,8 +33,10 @@ RT_RENDER_HOST_DIRECT = 2048
 RT_RENDER_SPLIT_SHADE = 4096
 RT_RENDER_PEER_STORE = 8192
 RT_RENDER_TILE_KERNEL = 16384
+RT_RENDER_GRAPH = 32768
 RT_HITABLE_TRIMESH, RT_HITABLE_SPHERE = 0, 1
 RT_DEBUG_PREFIX_UPLOADS, RT_DEBUG_BVH8_LEVELS, RT_DEBUG_BUILD_PATH, RT_DEBUG_BUILD_LAUNCHES, RT_DEBUG_BUILD_CLUSTER = 0, 1, 2, 3, 4
+RT_DEBUG_GRAPH_REPLAYS, RT_DEBUG_GRAPH_CAPTURES = 5, 6
 RT_DEBUG_BUILD_PHASE_NS = 16
 RT_DEBUG_BUILD_LEVEL_NS = 32
 RT_CAST_STATIC_MAX_RAYS = 65536
@@ -97,7 +99,7 @@ class RtFrameStats(C.Structure):
                 ("ms_total", C.c_float), ("waves", C.c_int32), ("kernel_launches", C.c_int32),
                 ("ms_primary", C.c_float), ("ms_shade", C.c_float), ("ms_bounce", C.c_float), ("n_hits", C.c_int32), ("ms_shadow", C.c_float),
                 ("ms_wave_phase", C.c_float * 4), ("rays_culled", C.c_uint64), ("host_chunks", C.c_int32),
-                ("tile_kernel", C.c_int32), ("node_fetches", C.c_uint64)]
+                ("tile_kernel", C.c_int32), ("node_fetches", C.c_uint64), ("graph", C.c_int32)]
 
     def as_dict(self):
         return {k: (list(getattr(self, k)) if k == "ms_wave_phase" else getattr(self, k)) for k, _ in self._fields_}

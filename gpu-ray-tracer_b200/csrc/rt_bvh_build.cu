@@ -1460,7 +1460,7 @@ static int launch_cluster_build(RtScene* sc, const SceneView& v, int n, int key_
 static int finish_enqueue(RtScene* sc, RtBuildStats* stats, bool same_layout, int launches0, bool sync) {
     Bvh& b = sc->bvh;
     cudaStream_t st = sc->stream;
-    RT_CUDA(cudaEventRecord(sc->ev[1], st));
+    RT_CUDA(rth::record(sc, sc->ev[1], st));
     RT_CUDA(cudaGetLastError());
     b.valid = true;  // provisional until finish_build() has looked at the result
     b.topology_valid = true;
@@ -1501,12 +1501,12 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     b.n_bvh2_nodes = n > 0 ? 2 * n - 1 : 0;
     b.n_nodes8 = 0;
     if (stats) { stats->n_prims = n; stats->n_bvh2_nodes = b.n_bvh2_nodes; stats->n_bvh8_nodes = 0; stats->kernel_launches = 0; stats->ms_build = 0.f; }
-    RT_CUDA(cudaEventRecord(sc->ev[0], st));
+    RT_CUDA(rth::record(sc, sc->ev[0], st));
     const int cluster_G = cluster_build_size(n);  // > 0: the one-launch build, which also computes the instance boxes
     if (!cluster_G) { if (int rc = update_instance_boxes(sc)) return rc; }
     if (n == 0) {
         b.valid = true;
-        RT_CUDA(cudaEventRecord(sc->ev[1], st));
+        RT_CUDA(rth::record(sc, sc->ev[1], st));
         RT_CUDA(cudaStreamSynchronize(st));
         return RT_OK;
     }
@@ -1534,7 +1534,7 @@ int build_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
         }
         std::memcpy(b.h_off, off.data(), bytes);
         RT_CUDA(cudaMemcpyAsync(b.work.p, b.h_off, bytes, cudaMemcpyHostToDevice, st));
-        RT_CUDA(cudaEventRecord(sc->ev[11], st));
+        RT_CUDA(rth::record(sc, sc->ev[11], st));
         b.off_in_flight = true;
         b.prefix_uploads++;
     }
@@ -1639,7 +1639,7 @@ int refit_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     int launches0 = sc->kernel_launches;
     const int n = b.n_prims;
     b.valid = false;
-    RT_CUDA(cudaEventRecord(sc->ev[0], st));
+    RT_CUDA(rth::record(sc, sc->ev[0], st));
     if (int rc = update_instance_boxes(sc)) return rc;
     SceneView v = make_view(sc, false);
     int* bounds_i = b.scene_bounds.as<int>();
@@ -1662,7 +1662,7 @@ int refit_bvh(RtScene* sc, RtBuildStats* stats, bool sync) {
     a.node8_slot = b.node8_slot.as<int>();
     k_refit8<<<grid_for(b.n_nodes8 * 8), kThreads, 0, st>>>(a, b.n_nodes8);
     sc->kernel_launches += 4;
-    RT_CUDA(cudaEventRecord(sc->ev[1], st));
+    RT_CUDA(rth::record(sc, sc->ev[1], st));
     RT_CUDA(cudaGetLastError());
     b.valid = true;
     b.build_launches = sc->kernel_launches - launches0;

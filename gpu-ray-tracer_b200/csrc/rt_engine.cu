@@ -39,6 +39,7 @@ using namespace rtd;
 // ---------------------------------------------------------------- errors, buffers
 namespace rth {
 static thread_local std::string g_err;
+unsigned long long g_alloc_gen = 0;
 void set_error(const std::string& msg) { g_err = msg; }
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
     g_err = std::string(cudaGetErrorName(e)) + ": " + cudaGetErrorString(e) + " in " + what + " (" + file + ":" +
@@ -51,6 +52,7 @@ int DevBuf::reserve(size_t bytes) {
     if (bytes <= cap && p) return 0;
     if (bytes == 0) bytes = 16;
     release();
+    g_alloc_gen++;
     cudaError_t e = cudaMalloc(&p, bytes);
     if (e != cudaSuccess) { p = nullptr; cap = 0; return cuda_fail(e, "cudaMalloc", __FILE__, __LINE__); }
     cap = bytes;
@@ -743,7 +745,7 @@ __global__ void __launch_bounds__(kThreads, RT_WAVES_MIN_BLOCKS) k_bounce_waves(
 // mappings (the gathering rank's, or every rank's) instead of a local slab that a second kernel pushes; the last block
 // to finish signals the frame's epoch to their mailboxes (rt_render with RtRenderParams.peers).
 struct PeerCanvases { uint32_t* p[RT_MAX_PEERS]; int n; };
-struct PushSignal { long long mailbox_offset; unsigned epoch; unsigned* done_blocks; };
+struct PushSignal { long long mailbox_offset; unsigned epoch; unsigned* done_blocks; const unsigned* epoch_ptr; };  // epoch_ptr != null: the epoch is read from there (replayed graphs)
 struct PeerOut { PeerCanvases pc; PushSignal sg; int rank; };
 
 // PHASE 0: the whole tile in one kernel. PHASE 1 + PHASE 2: the same code cut at the hit — k_tile<1> finds the closest
@@ -907,7 +909,7 @@ k_tile(SceneView s, TileMap tm, unsigned long long* ctr, uint32_t* canvas, PeerO
             __threadfence_system();
             if ((int)threadIdx.x < po.pc.n) {
                 volatile unsigned* box = (volatile unsigned*)(po.pc.p[threadIdx.x] + po.sg.mailbox_offset);
-                box[po.rank] = po.sg.epoch;
+                box[po.rank] = po.sg.epoch_ptr ? *(volatile const unsigned*)po.sg.epoch_ptr : po.sg.epoch;
             }
             if (threadIdx.x == 0) *po.sg.done_blocks = 0u;  // ready for the next frame
         }
@@ -1106,14 +1108,15 @@ __device__ __forceinline__ void push_signal_tail(const TileMap& tm, const PeerCa
     __threadfence_system();
     if (threadIdx.x < pc.n) {
         volatile unsigned* box = (volatile unsigned*)(pc.p[threadIdx.x] + sg.mailbox_offset);
-        box[tm.rank] = sg.epoch;
+        box[tm.rank] = sg.epoch_ptr ? *(volatile const unsigned*)sg.epoch_ptr : sg.epoch;
     }
     if (threadIdx.x == 0) *sg.done_blocks = 0u;  // ready for the next frame
 }
 
 __global__ void k_wait_mailbox(const uint32_t* own_canvas, long long mailbox_offset, int n, unsigned epoch, long long timeout_cycles,
-                               unsigned* status) {
+                               unsigned* status, const unsigned* epoch_ptr) {
     if ((int)threadIdx.x >= n) return;
+    if (epoch_ptr) epoch = *(volatile const unsigned*)epoch_ptr;  // replayed graph: this frame's epoch sits in pinned memory
     volatile const unsigned* box = (volatile const unsigned*)(own_canvas + mailbox_offset);
     long long t0 = clock64();
     // epochs only grow; a peer that died would hang the GPU, so the wait gives up after timeout_cycles. The frame is then
@@ -1214,7 +1217,7 @@ static int upload_instances(RtScene* sc) {
     }
     rth::fill_instances(sc->instances.data(), (int)n, (InstRec*)sc->h_inst);
     if (n) RT_CUDA(cudaMemcpyAsync(sc->d_insts.p, sc->h_inst, sizeof(InstRec) * n, cudaMemcpyHostToDevice, sc->stream));
-    RT_CUDA(cudaEventRecord(sc->ev[10], sc->stream));
+    RT_CUDA(cudaEventRecord(sc->ev[10], sc->stream)); /* outside any frame */
     sc->boxes_valid = false;
     sc->bvh.valid = false;
     return RT_OK;
@@ -1434,6 +1437,7 @@ int rt_scene_destroy(RtScene* sc) {
         for (int i = 0; i < 6; i++) if (sc->cev[c][i]) cudaEventDestroy(sc->cev[c][i]);
         if (sc->chunk_done[c]) cudaEventDestroy(sc->chunk_done[c]);
     }
+    for (rth::FrameGraph& g : sc->graphs) if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
     if (sc->copies_done) cudaEventDestroy(sc->copies_done);
     if (sc->ev_exchange) cudaEventDestroy(sc->ev_exchange);
     if (sc->copy_stream) cudaStreamDestroy(sc->copy_stream);
@@ -1461,6 +1465,7 @@ int rt_scene_set_instances(RtScene* sc, const RtInstance* inst, int32_t n) {
         if (inst[i].mesh < 0 || inst[i].mesh >= sc->n_meshes) { set_error("instance mesh index out of range"); return RT_ERR_INVALID_ARG; }
     sc->instances.assign(inst, inst + n);
     sc->n_instances = n;
+    sc->inst_gen++;
     return upload_instances(sc);
 }
 int rt_scene_set_canvas_size(RtScene* sc, int32_t w, int32_t h) {
@@ -1524,7 +1529,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     // wave 0 shaded, bounce waves done}. peers: k_tile stores the pixels into these peer canvases and signals them
     // (only passed when the tile kernel is eligible and the frame has no secondary rays).
     cudaStream_t st = sc->stream;
-    RT_CUDA(cudaEventRecord(cev[0], st));
+    RT_CUDA(rth::record(sc, cev[0], st));
     long long n_pix = (long long)tm.n_work() * 32;
     *waves = 1;
     sc->split_shade_used = false;
@@ -1549,13 +1554,13 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         k_tile<STATS, false, false, 1><<<g0, kThreads, 0, st>>>(v, tm, ctr, canvas, po0, nullptr, 0, nullptr, sc->d_hitq.as<HitRec>());
         sc->kernel_launches++;
         sc->wave0_form = 2;
-        RT_CUDA(cudaEventRecord(cev[1], st));
+        RT_CUDA(rth::record(sc, cev[1], st));
     } else if (!use_tile) {
         int g0 = persistent_grid(k_primary<MODE, STATS, false>, sc->sm_count);
         static const int aligned_hitq = [] { const char* e = std::getenv("RT_PACKED_HITQ"); return (e && std::atoi(e)) ? 0 : 1; }();
         k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr, aligned_hitq);
         sc->kernel_launches++;
-        RT_CUDA(cudaEventRecord(cev[1], st));
+        RT_CUDA(rth::record(sc, cev[1], st));
     }
     if (secondary) {
         // Path stacks for every pixel when that is affordable (no host round trip after k_primary);
@@ -1637,15 +1642,15 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
 #undef RT_LAUNCH_TILE
         sc->kernel_launches--;  // the common tail below counts wave 0's last kernel
         sc->tile_kernel_used = true;
-        RT_CUDA(cudaEventRecord(cev[1], st));
-        RT_CUDA(cudaEventRecord(cev[2], st));
-        RT_CUDA(cudaEventRecord(cev[3], st));
+        RT_CUDA(rth::record(sc, cev[1], st));
+        RT_CUDA(rth::record(sc, cev[2], st));
+        RT_CUDA(rth::record(sc, cev[3], st));
     } else if (!sc->fused_shade) {
         k_shadow_gen<false><<<persistent_grid(k_shadow_gen<false>, sc->sm_count), kThreads, 0, st>>>(v, ctr, C_HITQ, hitq, shq, shq_count, occl, att4, nullptr, 0);
         sc->kernel_launches++;
-        RT_CUDA(cudaEventRecord(cev[2], st));
+        RT_CUDA(rth::record(sc, cev[2], st));
         trace_shadows(C_HITQ);
-        RT_CUDA(cudaEventRecord(cev[3], st));
+        RT_CUDA(rth::record(sc, cev[3], st));
         if (secondary)
             k_resolve<true><<<persistent_grid(k_resolve<true>, sc->sm_count), kThreads, 0, st>>>(
                 v, ctr, hitq, occl, att4, canvas, paths, path_stride, sc->d_queue_a.as<int>());
@@ -1661,7 +1666,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         k_shade<MODE, STATS, false><<<g1, kThreads, 0, st>>>(v, ctr, hitq, canvas, paths, path_stride, sc->d_queue_a.as<int>());
     }
     sc->kernel_launches++;
-    RT_CUDA(cudaEventRecord(cev[4], st));
+    RT_CUDA(rth::record(sc, cev[4], st));
     if (secondary) {
         int in = C_QUEUE_A, outc = C_QUEUE_B;
         int* qin = sc->d_queue_a.as<int>();
@@ -1741,7 +1746,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
             *waves = -1;  // 1 + ctr[C_WAVES], filled in by the caller after the counter read-back
         }
     }
-    RT_CUDA(cudaEventRecord(cev[5], st));
+    RT_CUDA(rth::record(sc, cev[5], st));
     RT_CUDA(cudaGetLastError());
     return RT_OK;
 }
@@ -1904,7 +1909,7 @@ static int push_tiles_impl(RtScene* sc, const RtRenderParams* p, const uint32_t*
         pc.p[r] = peer_canvases[r];
     }
     PushSignal sg;
-    sg.mailbox_offset = canvas_pixels; sg.epoch = epoch; sg.done_blocks = nullptr;
+    sg.mailbox_offset = canvas_pixels; sg.epoch = epoch; sg.done_blocks = nullptr; sg.epoch_ptr = nullptr;
     long long n_quads = (long long)tm.n_owned * tm.tile_h * (tm.tile_w / 4);
     if (signal) {
         if (!sc->d_push_ctr.p) {
@@ -1916,7 +1921,7 @@ static int push_tiles_impl(RtScene* sc, const RtRenderParams* p, const uint32_t*
         unsigned grid = (unsigned)std::max<long long>((n_quads + kThreads - 1) / kThreads, 1);
         k_push_tiles<true><<<grid, kThreads, 0, sc->stream>>>(tm, slab, pc, sg);
         k_wait_mailbox<<<1, 32, 0, sc->stream>>>(peer_canvases[tm.rank], canvas_pixels, n_peers, epoch, mailbox_timeout_cycles(),
-                                                 exchange_status(sc));
+                                                 exchange_status(sc), nullptr);
         RT_CUDA(cudaEventRecord(sc->ev_exchange, sc->stream));
         sc->exchange_pending = true;
         sc->kernel_launches += 2;
@@ -2046,8 +2051,9 @@ int rt_scene_set_stream(RtScene* sc, void* stream, int32_t external) {
     return RT_OK;
 }
 
-int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFrameStats* stats) {
-    if (!sc) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+// Enqueues one frame on the scene's stream (plain launches, or into a stream capture when sc->capturing) and leaves it
+// pending; rt_render decides between this, a capture and a replay, and finishes the frame.
+static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* canvas) {
     RtRenderParams p;
     std::memset(&p, 0, sizeof p);
     if (params) p = *params;
@@ -2089,11 +2095,14 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
             RT_CUDA(cudaMemsetAsync(sc->d_push_ctr.p, 0, 16, st));
         }
         po.sg.mailbox_offset = sc->peer_pixels; po.sg.epoch = epoch; po.sg.done_blocks = sc->d_push_ctr.as<unsigned>();
+        // under capture the kernels read the epoch from a pinned word the host rewrites before every replay
+        *(volatile unsigned*)(sc->h_pinned + 49) = epoch;
+        po.sg.epoch_ptr = sc->capturing ? (const unsigned*)(sc->h_pinned + 49) : nullptr;
         po.rank = tm.rank;
         canvas = peer_own;
     }
     bool built = false;
-    RT_CUDA(cudaEventRecord(sc->ev[2], st));
+    RT_CUDA(rth::record(sc, sc->ev[2], st));
     if (!no_bvh) {
         if (int rc = ensure_bvh(sc, (p.flags & RT_RENDER_REBUILD_BVH) != 0, &built, (p.flags & RT_RENDER_REFIT_BVH) != 0)) return rc;
     } else {
@@ -2152,7 +2161,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     // in-canvas pixel of an owned tile is written, and the slab padding beyond the canvas edge is never read.
     // (not a peer canvas either: the other ranks are storing their tiles into it)
     if (!tm.tiled_out && tm.world > 1 && !(direct && host_bands) && !peer_store) RT_CUDA(cudaMemsetAsync(dcanvas, 0, 4 * (size_t)out_pixels, st));
-    RT_CUDA(cudaEventRecord(sc->ev[3], st));
+    RT_CUDA(rth::record(sc, sc->ev[3], st));
     SceneView v = rth::make_view(sc, !no_bvh);
     int waves = 1, rc = RT_OK;
     bool canvas_copied = false, peer_direct = false;
@@ -2210,14 +2219,14 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
             sc->kernel_launches++;
         }
         if (sc->peer_root < 0 || sc->peer_root == tm.rank) {  // this rank receives the frame: wait until every rank has signalled
-            k_wait_mailbox<<<1, 32, 0, st>>>(peer_own, sc->peer_pixels, sc->peer_n, po.sg.epoch, mailbox_timeout_cycles(), exchange_status(sc));
+            k_wait_mailbox<<<1, 32, 0, st>>>(peer_own, sc->peer_pixels, sc->peer_n, po.sg.epoch, mailbox_timeout_cycles(), exchange_status(sc), po.sg.epoch_ptr);
             sc->kernel_launches++;
-            RT_CUDA(cudaEventRecord(sc->ev_exchange, st));
+            RT_CUDA(rth::record(sc, sc->ev_exchange, st));
             sc->exchange_pending = true;
         }
         RT_CUDA(cudaGetLastError());
     }
-    RT_CUDA(cudaEventRecord(sc->ev[4], st));
+    RT_CUDA(rth::record(sc, sc->ev[4], st));
     unsigned long long* host_ctr = sc->h_pinned + 64;
     RT_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof(unsigned long long) * C_N * n_chunks, cudaMemcpyDeviceToHost, st));
     if (host_canvas && !canvas_copied && !direct) {
@@ -2229,10 +2238,126 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     }
     sc->pend_chunks = n_chunks;
     sc->pend_direct = direct;
-    RT_CUDA(cudaEventRecord(sc->ev[5], st));
+    RT_CUDA(rth::record(sc, sc->ev[5], st));
     sc->pending = true;
     sc->pend_stats = want_stats;
     sc->pend_built = built; sc->pend_wavefront = wavefront; sc->pend_waves = waves; sc->pend_launches0 = launches0;
+    return RT_OK;
+}
+
+// ---- RT_RENDER_GRAPH: the frame as one CUDA graph
+// Everything a captured frame bakes into kernel parameters or launch shapes. Two frames with equal keys enqueue identical work.
+static void graph_key(const RtScene* sc, const RtRenderParams& p, const uint32_t* canvas, std::vector<unsigned char>& key) {
+    key.clear();
+    auto put = [&](const void* d, size_t n) { const unsigned char* b = (const unsigned char*)d; key.insert(key.end(), b, b + n); };
+    put(&p, sizeof p);
+    put(&canvas, sizeof canvas);
+    put(&sc->width, sizeof sc->width); put(&sc->height, sizeof sc->height);
+    put(&sc->camera, sizeof sc->camera); put(&sc->env, sizeof sc->env);
+    put(&sc->inst_gen, sizeof sc->inst_gen); put(&rth::g_alloc_gen, sizeof rth::g_alloc_gen);
+    const int st[8] = {sc->boxes_valid, sc->bvh.valid, sc->bvh.topology_valid, sc->sb_choice, sc->n_instances, sc->peer_n, sc->peer_root,
+                       (p.flags & RT_RENDER_PEER_STORE) ? (int)((sc->peer_epoch + 1u) & 1u) : 0};
+    put(st, sizeof st);
+    put(&sc->stream, sizeof sc->stream);
+    const size_t n_peer = sc->peer_canv.size();
+    if (n_peer) put(sc->peer_canv.data(), n_peer * sizeof(uint32_t*));
+}
+static rth::FrameState save_state(const RtScene* sc, int launches) {
+    rth::FrameState f;
+    f.pend_built = sc->pend_built; f.pend_wavefront = sc->pend_wavefront; f.pend_stats = sc->pend_stats; f.pend_direct = sc->pend_direct;
+    f.split_shade_used = sc->split_shade_used; f.tile_kernel_used = sc->tile_kernel_used; f.exchange_pending = sc->exchange_pending;
+    f.pend_waves = sc->pend_waves; f.pend_chunks = sc->pend_chunks; f.wave0_form = sc->wave0_form; f.sb_used = sc->sb_used; f.launches = launches;
+    return f;
+}
+static void restore_state(RtScene* sc, const rth::FrameState& f) {
+    sc->pend_built = f.pend_built; sc->pend_wavefront = f.pend_wavefront; sc->pend_stats = f.pend_stats; sc->pend_direct = f.pend_direct;
+    sc->split_shade_used = f.split_shade_used; sc->tile_kernel_used = f.tile_kernel_used; sc->exchange_pending = f.exchange_pending;
+    sc->pend_waves = f.pend_waves; sc->pend_chunks = f.pend_chunks; sc->wave0_form = f.wave0_form; sc->sb_used = f.sb_used;
+}
+
+int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFrameStats* stats) {
+    if (!sc) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+    RtRenderParams p;
+    std::memset(&p, 0, sizeof p);
+    if (params) p = *params;
+    if (sc->pending) {  // an asynchronous frame was never finished: its counters are about to be reused
+        if (int rc = rt_frame_finish(sc, nullptr)) return rc;
+    }
+    // A frame can be a graph when nothing in it needs the host in between: BVH traversal with the CUDA bounce semantics
+    // (wavefront kernels), canvas on the device or in the peers, and the wave-0 shadow kernel already chosen.
+    const bool peer_store = (p.flags & RT_RENDER_PEER_STORE) != 0;
+    static const int graph_env = [] { const char* e = std::getenv("RT_GRAPH"); return e ? (std::atoi(e) ? 1 : 0) : -1; }();
+    const bool want_graph = graph_env >= 0 ? graph_env == 1 : (p.flags & RT_RENDER_GRAPH) != 0;
+    const bool graphable = want_graph && !(p.flags & RT_RENDER_NO_BVH) && p.semantics == RT_SEMANTICS_GPU &&
+                           ((p.flags & RT_RENDER_CANVAS_DEVICE) || peer_store) && (canvas || peer_store);
+    int rc = RT_OK, pend_graph = 0;
+    bool done = false;
+    if (graphable) {
+        std::vector<unsigned char> key;
+        graph_key(sc, p, canvas, key);
+        const int launches0 = sc->kernel_launches;
+        rth::FrameGraph* hit = nullptr;
+        for (rth::FrameGraph& g : sc->graphs) if (g.exec && g.key == key) hit = &g;
+        if (hit) {
+            // replay: the host-side effects of an enqueue, then one launch
+            if (peer_store) { sc->peer_epoch++; *(volatile unsigned*)(sc->h_pinned + 49) = sc->peer_epoch; }
+            restore_state(sc, hit->state);
+            sc->boxes_valid = true;
+            if (hit->state.pend_built) { sc->bvh.valid = true; sc->bvh.topology_valid = true; }
+            RT_CUDA(cudaGraphLaunch(hit->exec, sc->stream));
+            sc->kernel_launches += hit->state.launches;
+            sc->pend_launches0 = launches0;
+            sc->pending = true;
+            hit->last_used = ++sc->graph_clock;
+            sc->graph_replays++;
+            pend_graph = 2;
+            done = true;
+        } else if (key == sc->last_key && key != sc->bad_key && (sc->sb_used < 0 || sc->sb_choice >= 0)) {
+            // second appearance of this key: every buffer has its size, capture the frame
+            const unsigned epoch0 = sc->peer_epoch;
+            const bool boxes0 = sc->boxes_valid, valid0 = sc->bvh.valid, topo0 = sc->bvh.topology_valid;
+            cudaGraph_t graph = nullptr;
+            cudaError_t e = cudaStreamBeginCapture(sc->stream, cudaStreamCaptureModeRelaxed);
+            if (e == cudaSuccess) {
+                sc->capturing = true;
+                const int rc_cap = render_enqueue(sc, &p, canvas);
+                sc->capturing = false;
+                e = cudaStreamEndCapture(sc->stream, &graph);
+                cudaGraphExec_t exec = nullptr;
+                if (rc_cap == RT_OK && e == cudaSuccess && graph) e = cudaGraphInstantiate(&exec, graph, 0);
+                if (graph) cudaGraphDestroy(graph);
+                if (rc_cap == RT_OK && e == cudaSuccess && exec) {
+                    rth::FrameGraph* slot = nullptr;  // an empty entry, else the least recently used one
+                    for (rth::FrameGraph& g : sc->graphs) if (!g.exec) { slot = &g; break; }
+                    if (!slot) { slot = &sc->graphs[0]; for (rth::FrameGraph& g : sc->graphs) if (g.last_used < slot->last_used) slot = &g; }
+                    if (slot->exec) cudaGraphExecDestroy(slot->exec);
+                    slot->exec = exec; slot->key = key; slot->state = save_state(sc, sc->kernel_launches - launches0); slot->last_used = ++sc->graph_clock;
+                    RT_CUDA(cudaGraphLaunch(exec, sc->stream));
+                    sc->graph_captures++;
+                    pend_graph = 1;
+                    done = true;
+                } else {
+                    // not capturable (an operation in this frame needs the host): plain launches for this key from now on
+                    if (exec) cudaGraphExecDestroy(exec);
+                    (void)cudaGetLastError();
+                    // nothing of the captured frame ran on the device: take back what its enqueue claimed on the host
+                    sc->pending = false;
+                    sc->exchange_pending = false;
+                    sc->peer_epoch = epoch0;
+                    sc->kernel_launches = launches0;
+                    sc->boxes_valid = boxes0; sc->bvh.valid = valid0; sc->bvh.topology_valid = topo0;
+                    sc->bad_key = key;
+                }
+            } else {
+                (void)cudaGetLastError();
+                sc->bad_key = key;
+            }
+        }
+        sc->last_key.swap(key);
+    }
+    if (!done) rc = render_enqueue(sc, &p, canvas);
+    if (rc) return rc;
+    sc->pend_graph = pend_graph;
     if (p.flags & RT_RENDER_ASYNC) return RT_OK;  // rt_frame_finish() completes the frame
     return rt_frame_finish(sc, stats);
 }
@@ -2300,6 +2425,7 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
     fs.kernel_launches = sc->kernel_launches - launches0;
     fs.host_chunks = sc->pend_direct ? 0 : n_chunks;
     fs.tile_kernel = sc->wave0_form;
+    fs.graph = sc->pend_graph;
     fs.node_fetches = host_ctr[C_FETCHES];
     if (stats) *stats = fs;
     return RT_OK;
@@ -2419,6 +2545,8 @@ int rt_debug_get(RtScene* sc, int32_t what, int64_t* out) {
         case RT_DEBUG_BVH8_LEVELS: *out = sc->bvh.n_levels8; break;
         case RT_DEBUG_BUILD_PATH: *out = sc->bvh.build_path; break;
         case RT_DEBUG_BUILD_LAUNCHES: *out = sc->bvh.build_launches; break;
+        case RT_DEBUG_GRAPH_REPLAYS: *out = sc->graph_replays; break;
+        case RT_DEBUG_GRAPH_CAPTURES: *out = sc->graph_captures; break;
         case RT_DEBUG_BUILD_CLUSTER: *out = sc->bvh.build_path == 2 ? sc->bvh.cluster_size : 0; break;
         default:
             // RT_DEBUG_BUILD_PHASE_NS + i, i in 0..6: nanoseconds CTA 0 of the last cluster build spent in phase i (flatten +

@@ -72,6 +72,24 @@ struct Bvh {
 
 }  // namespace rth
 
+namespace rth {
+extern unsigned long long g_alloc_gen;  // grows whenever a DevBuf is reallocated: device pointers baked into a captured frame are stale then
+
+// What rt_frame_finish needs to know about an enqueued frame; saved with a captured frame and restored at every replay.
+struct FrameState {
+    bool pend_built = false, pend_wavefront = false, pend_stats = false, pend_direct = false;
+    bool split_shade_used = false, tile_kernel_used = false, exchange_pending = false;
+    int pend_waves = 0, pend_chunks = 1, wave0_form = 0, sb_used = -1, launches = 0;
+};
+// One instantiated CUDA graph of a frame (RT_RENDER_GRAPH) and the key it is valid for.
+struct FrameGraph {
+    std::vector<unsigned char> key;
+    cudaGraphExec_t exec = nullptr;
+    FrameState state;
+    unsigned long long last_used = 0;
+};
+}  // namespace rth
+
 struct RtScene {
     // host copies (instances can be replaced; the rest is immutable after create)
     std::vector<RtInstance> instances;
@@ -136,6 +154,14 @@ struct RtScene {
     size_t h_inst_cap = 0;
     int sm_count = 148;
     int kernel_launches = 0;  // running count, sampled around each API call
+    // RT_RENDER_GRAPH: the frame is captured once per key (render flags, tile map, canvas, camera, environment, instance
+    // generation, buffer generation, BVH state, exchange parity) and replayed with one cudaGraphLaunch
+    bool capturing = false;              // the scene's stream is under capture: timing events become external record nodes
+    rth::FrameGraph graphs[4];
+    std::vector<unsigned char> last_key; // key of the previous frame that asked for a graph (a frame is captured on its second appearance)
+    std::vector<unsigned char> bad_key;  // a key whose capture failed: plain launches from then on
+    unsigned long long graph_clock = 0, inst_gen = 0;
+    int graph_replays = 0, graph_captures = 0, pend_graph = 0;
 };
 
 namespace rth {
@@ -150,6 +176,10 @@ size_t radix_hist_bytes(int n);
 int radix_sort_pairs(cudaStream_t st, unsigned long long*& keys_a, unsigned long long*& keys_b, int*& vals_a, int*& vals_b,
                      unsigned* hist, int n, int n_passes);
 int update_instance_boxes(RtScene* sc);                    // rt_engine.cu
+// cudaEventRecord that stays usable for timing when the stream is being captured into a graph
+inline cudaError_t record(const RtScene* sc, cudaEvent_t ev, cudaStream_t st) {
+    return cudaEventRecordWithFlags(ev, st, sc->capturing ? cudaEventRecordExternal : cudaEventRecordDefault);
+}
 rtd::SceneView make_view(const RtScene* sc, bool with_bvh);
 }  // namespace rth
 

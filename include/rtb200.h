@@ -170,6 +170,12 @@ enum {
                                     of RtRenderParams) are stored straight into the row-major peer canvases registered with
                                     rt_scene_set_peers over NVLink, and the frame's completion is signalled through their
                                     mailboxes; `canvas` is ignored (may be NULL) */
+    RT_RENDER_GRAPH = 32768,     /* the frame as ONE CUDA graph: a frame whose key (these parameters, canvas, camera, environment, instance
+                                    and buffer generation, BVH state, exchange parity) equals the previous frame's is captured from the
+                                    scene's stream — build kernel, frame kernels, counters copy, the exchange — instantiated and from then
+                                    on replayed with one cudaGraphLaunch; a changed key (camera moved, instances set) falls back to plain
+                                    launches and a new capture. Device or peer canvas, BVH traversal, RT_SEMANTICS_GPU only; frames whose
+                                    enqueue needs the host fall back silently. Per-kernel times stay available (external event nodes) */
     RT_RENDER_TRACE_UNLIT = 128  /* also trace shadow rays whose Phong weight is exactly zero (the reference does; the
                                     split pipeline skips them by default: they cannot change a pixel) */
 };
@@ -215,6 +221,7 @@ typedef struct RtFrameStats {
                                  ms_shade / ms_shadow are 0) */
     uint64_t node_fetches;    /* RT_RENDER_STATS, k_tile: 80-byte node fetches after the warp broadcast (one per warp-level
                                  visit); nodes_visited counts the same visits once per active ray */
+    int32_t graph;            /* RT_RENDER_GRAPH: 0 = plain launches, 1 = this frame was captured and launched as a graph, 2 = replayed */
 } RtFrameStats;
 
 typedef struct RtBuildStats {
@@ -382,6 +389,8 @@ enum {
     RT_DEBUG_BVH8_LEVELS = 1,    /* depth of the BVH8 of the last build */
     RT_DEBUG_BUILD_PATH = 2,     /* 1 = multi-kernel pipeline, 2 = one-launch thread-block-cluster build */
     RT_DEBUG_BUILD_LAUNCHES = 3, /* kernels the last build / refit launched */
+    RT_DEBUG_GRAPH_REPLAYS = 5,  /* frames of this scene replayed from a captured graph */
+    RT_DEBUG_GRAPH_CAPTURES = 6, /* frames captured into a graph */
     RT_DEBUG_BUILD_CLUSTER = 4,  /* CTAs in the cluster of the last one-launch build (0: multi-kernel pipeline) */
     RT_DEBUG_BUILD_PHASE_NS = 16, /* + i (0..6): ns per phase of the last cluster build, with RT_BUILD_TIMERS=1 in the environment */
     RT_DEBUG_BUILD_LEVEL_NS = 32 /* + i (0..15): raw globaltimer stamp after phase A (even i) / phase B (odd i) of collapse level i / 2 */

@@ -328,3 +328,53 @@ def test_peer_store_frames(pkg, gpu_ok, name, n, root):
         s.close()
     for p in canv:
         pkg.peer_canvas_free(p)
+
+
+# ------------------------------------------------------------------ the frame as one CUDA graph (RT_RENDER_GRAPH)
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,kw", [("world16", {"width": 1280, "height": 720}), ("world8_stress", {"depth": 9}), ("world1", {"depth": 5})])
+def test_graph_frames_equal_plain_frames(pkg, gpu_ok, name, kw):
+    """A frame captured into a CUDA graph and replayed (build kernel + frame kernels + counters copy in one cudaGraphLaunch)
+    leaves the canvas, the ray counts and the per-kernel times of a plainly launched frame; a moved camera changes the key
+    (plain frame, then a new capture) and the frames still equal the oracle's. Frames that cannot be captured fall back."""
+    import torch
+    w = pkg.World(scene_path(name), **kw)
+    s = pkg.Scene(w)
+    W, H = w.width, w.height
+    base = pkg.RT_RENDER_REBUILD_BVH | pkg.RT_RENDER_CANVAS_DEVICE
+    dev = torch.zeros(H * W, dtype=torch.int32, device="cuda")
+    ref = torch.zeros(H * W, dtype=torch.int32, device="cuda")
+    _, st0 = s.render(flags=base, out_ptr=ref.data_ptr())
+    want = ref.cpu().numpy().view(np.uint32).reshape(H, W)
+    stats = []
+    for i in range(8):
+        dev.zero_()
+        _, st = s.render(flags=base | pkg.RT_RENDER_GRAPH, out_ptr=dev.data_ptr())
+        got = dev.cpu().numpy().view(np.uint32).reshape(H, W)
+        assert (got == want).all(), (i, int((got != want).sum()))
+        for k in ("rays_total", "rays_primary", "rays_shadow", "rays_secondary", "n_hits", "waves", "kernel_launches"):
+            assert st[k] == st0[k], (i, k, st[k], st0[k])
+        assert st["ms_total"] > 0 and st["ms_primary"] > 0 and st["ms_build"] > 0
+        stats.append(st)
+    assert [x["graph"] for x in stats[:2]] == [0, 0] or stats[0]["graph"] == 0
+    caps, reps = s.debug_get(pkg.RT_DEBUG_GRAPH_CAPTURES), s.debug_get(pkg.RT_DEBUG_GRAPH_REPLAYS)
+    print(name, "captures", caps, "replays", reps)
+    assert caps >= 1 and reps >= 2, (caps, reps, [x["graph"] for x in stats])  # every one of these frames is capturable
+    assert [x["graph"] for x in stats[-3:]] == [2, 2, 2]
+    # camera moved: new key -> plain frame, capture, replays; frames equal the oracle's
+    cam = w.desc.camera
+    pkg.host_lib().rth_camera_key(C.byref(cam), b"w")
+    s.set_camera(cam)
+    o = ob.OracleScene(w)
+    o.set_camera(cam)
+    oc, ost = o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1, rows=(H // 2, H // 2 + 4))
+    for i in range(4):
+        _, st = s.render(flags=base | pkg.RT_RENDER_GRAPH, out_ptr=dev.data_ptr())
+        got = dev.cpu().numpy().view(np.uint32).reshape(H, W)
+        assert (got[H // 2:H // 2 + 4] == oc[H // 2:H // 2 + 4]).all(), i
+    # instances re-set: new key again, and a plain frame in between still works
+    s.set_instances(w.desc.instances, w.desc.n_instances)
+    c_host, _ = s.render(flags=pkg.RT_RENDER_REBUILD_BVH)
+    _, st = s.render(flags=base | pkg.RT_RENDER_GRAPH, out_ptr=dev.data_ptr())
+    assert (dev.cpu().numpy().view(np.uint32).reshape(H, W) == c_host).all()
+    s.close()
