@@ -34,6 +34,7 @@ RT_RENDER_SPLIT_SHADE = 4096
 RT_RENDER_PEER_STORE = 8192
 RT_RENDER_TILE_KERNEL = 16384
 RT_RENDER_GRAPH = 32768
+RT_RENDER_FAST_ACCEPT = 65536
 RT_HITABLE_TRIMESH, RT_HITABLE_SPHERE = 0, 1
 RT_DEBUG_PREFIX_UPLOADS, RT_DEBUG_BVH8_LEVELS, RT_DEBUG_BUILD_PATH, RT_DEBUG_BUILD_LAUNCHES, RT_DEBUG_BUILD_CLUSTER = 0, 1, 2, 3, 4
 RT_DEBUG_GRAPH_REPLAYS, RT_DEBUG_GRAPH_CAPTURES = 5, 6

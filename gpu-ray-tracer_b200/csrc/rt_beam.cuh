@@ -49,10 +49,10 @@ __device__ __forceinline__ float beam_gmax(float v) {
 }
 
 // The per-lane walk for warps whose rays do not share a direction octant: out of line, it is cold.
-template <bool STATS>
+template <bool STATS, bool FAST>
 __device__ __noinline__ bool beam_fallback(const SceneView& s, const rtx::Ray& r, bool any, bool use_box, float max_t, Hit& best, TravStats& st) {
     TravStats* stp = STATS ? &st : nullptr;
-    return any ? bvh_query<true>(s, r, use_box, max_t, best, stp) : bvh_query<false>(s, r, use_box, max_t, best, stp);
+    return any ? bvh_query<true, FAST>(s, r, use_box, max_t, best, stp) : bvh_query<false, FAST>(s, r, use_box, max_t, best, stp);
 }
 
 // Closest-hit (any == false) or occlusion (any == true) query for the rays of one warp. Every lane of the warp must
@@ -61,7 +61,7 @@ __device__ __noinline__ bool beam_fallback(const SceneView& s, const rtx::Ray& r
 // One out-of-line copy serves the camera rays and every light's shadow rays of k_tile (`any` is a run-time flag): the
 // kernel's hot loop has to fit the instruction cache (the first version inlined a closest-hit and an occlusion copy, each
 // with its per-lane fallback — 96 KB of SASS, 3.2 warps stalled on instruction fetch per issued instruction).
-template <bool STATS>
+template <bool STATS, bool FAST = false>
 __device__ __noinline__ bool beam_query(const SceneView& s, const rtx::Ray& r, bool active, const bool ANY, bool use_box, float max_t,
                                         Hit& best, TravStats& st, BeamStats& bst) {
     const unsigned FULLM = 0xffffffffu;
@@ -75,7 +75,7 @@ __device__ __noinline__ bool beam_query(const SceneView& s, const rtx::Ray& r, b
     const unsigned oct_first = __shfl_sync(FULLM, rp.octinv, __ffs((int)act0) - 1);
     if (__any_sync(FULLM, active && rp.octinv != oct_first)) {
         if (!active) return false;
-        return beam_fallback<STATS>(s, r, ANY, use_box, max_t, best, st);
+        return beam_fallback<STATS, FAST>(s, r, ANY, use_box, max_t, best, st);
     }
     const unsigned octinv = oct_first;
     // mirrored coordinates: axis k negated when the rays travel in its negative direction, so that 1 / d > 0
@@ -156,6 +156,7 @@ __device__ __noinline__ bool beam_query(const SceneView& s, const rtx::Ray& r, b
             // every lane filters the leaf's triangles for its own ray; survivors wait in `cand`
             unsigned cand = 0u;
             unsigned todo = tg.y;
+            bool fast_changed = false;
             while (todo) {
                 const unsigned k = (unsigned)__ffs((int)todo) - 1u;
                 todo &= todo - 1u;
@@ -163,11 +164,25 @@ __device__ __noinline__ bool beam_query(const SceneView& s, const rtx::Ray& r, b
                 const float4 p0 = ldg4f(pp), p1 = ldg4f(pp + 1), p2 = ldg4f(pp + 2);
                 if (active) {
                     if (STATS) st.prims++;
-                    if (tri_filter(rp.o, rp.d, p0, p1, p2, tcull)) cand |= 1u << k;
+                    if (FAST) {
+                        float ft, fu, fv;
+                        const int verdict = tri_filter_clear(rp.o, rp.d, p0, p1, p2, tcull, ft, fu, fv);
+                        if (verdict == 2 && (!ANY || ft <= max_t * 0.9999f)) {
+                            // tolerance mode: a clear hit needs no reference-exact test
+                            if (fast_candidate(__float_as_int(p0.w), __float_as_int(p1.w), ft, fu, fv, best)) {
+                                if (ANY) { occluded = true; active = false; cand = 0u; tcull = -INF; fast_changed = true; }
+                                else { tcull = fmaf(best.t, RT_TCULL_REL, RT_TCULL_ABS); fast_changed = true; }
+                            }
+                        } else if (verdict) {
+                            cand |= 1u << k;
+                        }
+                    } else if (tri_filter(rp.o, rp.d, p0, p1, p2, tcull)) {
+                        cand |= 1u << k;
+                    }
                 }
             }
             // the reference-exact test, one candidate per lane and round, all lanes that have one together
-            bool changed = false;
+            bool changed = fast_changed;
             while (__any_sync(FULLM, cand != 0u)) {
                 if (cand) {
                     const unsigned k = (unsigned)__ffs((int)cand) - 1u;

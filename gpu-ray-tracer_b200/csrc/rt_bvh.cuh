@@ -118,6 +118,36 @@ RT_HD bool tri_filter(float3 o, float3 d, float4 p0, float4 p1, float4 p2, float
     return up >= -tau && vp >= -tau && up + vp <= a + tau && tp >= -tau_t && tp <= fmaf(fminf(tcull, 3e38f), a, tau_t);
 }
 
+// The same filter with a second verdict for the opt-in tolerance mode (SceneView::fast_accept, RT_RENDER_FAST_ACCEPT):
+//   0 = reject, 1 = candidate (the reference-exact test decides), 2 = CLEAR hit: the ray crosses the triangle's plane at
+//   t >= 1e-4 (ten thresholds), not grazing (|d.n| >= 4e-5 against the reference's 1e-5), and inside all three edges by twice
+//   the margin that covers the reference's 1e-5 barycentric tolerance. The reference accepts every such hit; t = t'/|det|,
+//   uv = (u', v')/|det| then differ from its values only by rounding (measured: profiles/r2_fast_accept_parity.md).
+RT_HD int tri_filter_clear(float3 o, float3 d, float4 p0, float4 p1, float4 p2, float tcull, float& t, float& u, float& v) {
+    float3 e1 = rtx::mk3(p1.x, p1.y, p1.z), e2 = rtx::mk3(p2.x, p2.y, p2.z);
+    float3 tv = rtx::mk3(o.x - p0.x, o.y - p0.y, o.z - p0.z);
+    float3 pv = rtx::mk3(fmaf(d.y, e2.z, -d.z * e2.y), fmaf(d.z, e2.x, -d.x * e2.z), fmaf(d.x, e2.y, -d.y * e2.x));
+    float det = fmaf(e1.x, pv.x, fmaf(e1.y, pv.y, e1.z * pv.z));
+    float up = fmaf(tv.x, pv.x, fmaf(tv.y, pv.y, tv.z * pv.z));
+    float3 qv = rtx::mk3(fmaf(tv.y, e1.z, -tv.z * e1.y), fmaf(tv.z, e1.x, -tv.x * e1.z), fmaf(tv.x, e1.y, -tv.y * e1.x));
+    float vp = fmaf(d.x, qv.x, fmaf(d.y, qv.y, d.z * qv.z));
+    float tp = fmaf(e2.x, qv.x, fmaf(e2.y, qv.y, e2.z * qv.z));
+    float a = fabsf(det);
+    if (det < 0.0f) { up = -up; vp = -vp; tp = -tp; }
+    float L = p2.w;
+    float tv1 = fabsf(tv.x) + fabsf(tv.y) + fabsf(tv.z);
+    float tau = (1e-4f + 2e-5f * L + 2e-6f * tv1) * L;
+    float tau_t = fmaf(1e-4f, a, tau * (1.0f + L));
+    if (!(up >= -tau && vp >= -tau && up + vp <= a + tau && tp >= -tau_t && tp <= fmaf(fminf(tcull, 3e38f), a, tau_t))) return 0;
+    // clear? (L = +inf marks an analytic sphere: never clear)
+    if (up >= 2.0f * tau && vp >= 2.0f * tau && up + vp <= a - 2.0f * tau && a >= 1e-5f * L * L && tp >= fmaf(1e-4f, a, tau_t) && L < 3e38f) {
+        float inv = 1.0f / a;
+        t = tp * inv; u = up * inv; v = vp * inv;
+        return 2;
+    }
+    return 1;
+}
+
 struct RayPrep {
     float3 o, d, idir;
     unsigned octinv;   // 7 - octant
@@ -219,7 +249,9 @@ RT_HD unsigned node_children_hits(const uint4 q0, const uint4 q1, const uint4 q2
 
 // Closest-hit (ANY == false) or occlusion (ANY == true: stop at the first accepted hit with
 // t <= max_t) query. `use_box` applies the reference's leaf-box condition to candidates.
-template <bool ANY>
+// FAST: the opt-in tolerance mode (tri_filter_clear) as a compile-time variant, so that the default kernels carry none of it
+// (as a run-time branch it cost the bit-exact path 2.5 %).
+template <bool ANY, bool FAST = false>
 RT_HD bool bvh_query(const SceneView& s, const rtx::Ray& r, bool use_box, float max_t, Hit& best, TravStats* st) {
     hit_reset(best);
     if (s.n_prims <= 0) return false;
@@ -273,7 +305,16 @@ RT_HD bool bvh_query(const SceneView& s, const rtx::Ray& r, bool use_box, float 
             const float4* pp = s.prims + (size_t)(tg.x + k) * 3;
             float4 p0 = ldg4f(pp), p1 = ldg4f(pp + 1), p2 = ldg4f(pp + 2);
             if (st) st->prims++;
-            if (tri_filter(rp.o, rp.d, p0, p1, p2, tcull)) {
+            float ft, fu, fv;
+            const int verdict = FAST ? tri_filter_clear(rp.o, rp.d, p0, p1, p2, tcull, ft, fu, fv)
+                                     : (tri_filter(rp.o, rp.d, p0, p1, p2, tcull) ? 1 : 0);
+            if (verdict == 2 && (!ANY || ft <= max_t * 0.9999f)) {
+                // tolerance mode: a clear hit is taken as it is (fast_candidate applies the same ordering rules)
+                if (fast_candidate(hd_f2i(p0.w), hd_f2i(p1.w), ft, fu, fv, best)) {
+                    if (ANY) return true;
+                    tcull = fmaf(best.t, RT_TCULL_REL, RT_TCULL_ABS);
+                }
+            } else if (verdict) {
                 if (st) st->exact++;
                 int inst = hd_f2i(p0.w), tri = hd_f2i(p1.w);
                 if (exact_candidate(s, r, inst, tri, use_box, ctx, best)) {
@@ -294,16 +335,18 @@ RT_HD bool bvh_query(const SceneView& s, const rtx::Ray& r, bool use_box, float 
     return ANY ? false : best.inst >= 0;
 }
 
-struct BvhTracer {
+template <bool FAST>
+struct BvhTracerT {
     const SceneView* s;
     bool use_box;
     TravStats* st;
-    RT_HD bool closest(const rtx::Ray& r, Hit& best) const { return bvh_query<false>(*s, r, use_box, INFINITY, best, st); }
+    RT_HD bool closest(const rtx::Ray& r, Hit& best) const { return bvh_query<false, FAST>(*s, r, use_box, INFINITY, best, st); }
     RT_HD bool occluded(const rtx::Ray& r, float max_t) const {
         Hit h;
-        return bvh_query<true>(*s, r, use_box, max_t, h, st);
+        return bvh_query<true, FAST>(*s, r, use_box, max_t, h, st);
     }
 };
+typedef BvhTracerT<false> BvhTracer;
 
 }  // namespace rtd
 #endif

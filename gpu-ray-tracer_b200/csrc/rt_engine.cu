@@ -208,10 +208,14 @@ __global__ void k_tri_precompute(const TriRec* tris, int n, const float4* verts,
 }
 
 // ---------------------------------------------------------------- tracer selection
-enum { TR_BVH_BOX = 0, TR_BRUTE = 1, TR_BVH_NOBOX = 2, TR_BRUTE_BOX = 3 };
+enum { TR_BVH_BOX = 0, TR_BRUTE = 1, TR_BVH_NOBOX = 2, TR_BRUTE_BOX = 3, TR_BVH_BOX_FAST = 4 };  // _FAST: BVH_BOX in the opt-in tolerance mode
 template <int MODE> struct TracerOf;
 template <> struct TracerOf<TR_BVH_BOX> {
     typedef BvhTracer T;
+    __device__ static T make(const SceneView* s, TravStats* st) { T t; t.s = s; t.use_box = true; t.st = st; return t; }
+};
+template <> struct TracerOf<TR_BVH_BOX_FAST> {
+    typedef BvhTracerT<true> T;
     __device__ static T make(const SceneView* s, TravStats* st) { T t; t.s = s; t.use_box = true; t.st = st; return t; }
 };
 template <> struct TracerOf<TR_BVH_NOBOX> {
@@ -498,7 +502,7 @@ __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(Scene
 // Wave 0, opaque scenes: the shadow-ray queue of a light is slot-indexed like the tile-aligned hit queue, so 32 consecutive
 // entries are the shadow rays of ONE 8x4 tile towards ONE light (holes: misses and culled lights). Walked together by the
 // warp-coherent traversal of rt_beam.cuh instead of 32 per-lane occlusion queries; same flags out.
-template <bool STATS>
+template <bool STATS, bool FAST = false>
 __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow_beam(SceneView s, unsigned long long* ctr, int ctr_n,
                                                                                const ShadowRec* shq, unsigned char* occl,
                                                                                unsigned long long* work) {
@@ -521,7 +525,7 @@ __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow_beam(
         r.o = rtx::mk3(q.o_maxt.x, q.o_maxt.y, q.o_maxt.z);
         r.d = rtx::mk3(q.d.x, q.d.y, q.d.z);
         Hit h;
-        const bool blocked = beam_query<STATS>(s, r, trace, true, true, q.o_maxt.w, h, ts, bs);
+        const bool blocked = beam_query<STATS, FAST>(s, r, trace, true, true, q.o_maxt.w, h, ts, bs);
         if (trace) {
             rc.shadow++;
             occl[(size_t)l * n_hits + (size_t)__float_as_int(q.d.w)] = blocked ? 1 : 0;
@@ -761,7 +765,7 @@ struct PeerOut { PeerCanvases pc; PushSignal sg; int rank; };
 #ifndef RT_TILE2_MIN_BLOCKS
 #define RT_TILE2_MIN_BLOCKS 2   /* 128 registers: at 3 blocks (80) the shading phase spills 324 B and runs 6 % slower */
 #endif
-template <bool STATS, bool SECONDARY, bool PEERS, int PHASE>
+template <bool STATS, bool SECONDARY, bool PEERS, int PHASE, bool FAST = false>
 __global__ void __launch_bounds__(kThreads, PHASE == 0 ? RT_TILE_MIN_BLOCKS : PHASE == 1 ? RT_TILE1_MIN_BLOCKS : RT_TILE2_MIN_BLOCKS)
 k_tile(SceneView s, TileMap tm, unsigned long long* ctr, uint32_t* canvas, PeerOut po, unsigned char* paths, int path_stride, int* queue,
        HitRec* hitq) {
@@ -795,7 +799,7 @@ k_tile(SceneView s, TileMap tm, unsigned long long* ctr, uint32_t* canvas, PeerO
                 r = rtx::camera_ray(s.cam, (float)x, (float)y);
                 rc.primary++;
             }
-            hit = beam_query<STATS>(s, r, valid, false, true, INFINITY, h, ts, bs);
+            hit = beam_query<STATS, FAST>(s, r, valid, false, true, INFINITY, h, ts, bs);
             if (valid && !hit) store(out, 0u);  // pack_color(0,0,0,0)
             const unsigned hm = __ballot_sync(0xffffffffu, hit);
             if (!hm) continue;
@@ -852,7 +856,7 @@ k_tile(SceneView s, TileMap tm, unsigned long long* ctr, uint32_t* canvas, PeerO
                 }
             }
             Hit sh;
-            const bool blocked = beam_query<STATS>(s, sr, trace, true, true, max_t, sh, ts, bs);
+            const bool blocked = beam_query<STATS, FAST>(s, sr, trace, true, true, max_t, sh, ts, bs);
             if (trace) {
                 const LightRec& L = s.lights[l];
                 const float4 a = blocked ? rtx::mk4(0.f, 0.f, 0.f, 0.f) : L.color;
@@ -1216,6 +1220,12 @@ static int upload_instances(RtScene* sc) {
         RT_CUDA(cudaEventSynchronize(sc->ev[10]));
     }
     rth::fill_instances(sc->instances.data(), (int)n, (InstRec*)sc->h_inst);
+    {
+        bool ident = sc->meshes_identity;
+        const InstRec* ir = (const InstRec*)sc->h_inst;
+        for (size_t i = 0; ident && i < n; i++) ident = ir[i].pose.identity_rot != 0;
+        sc->all_identity = ident;
+    }
     if (n) RT_CUDA(cudaMemcpyAsync(sc->d_insts.p, sc->h_inst, sizeof(InstRec) * n, cudaMemcpyHostToDevice, sc->stream));
     RT_CUDA(cudaEventRecord(sc->ev[10], sc->stream)); /* outside any frame */
     sc->boxes_valid = false;
@@ -1282,6 +1292,13 @@ SceneView make_view(const RtScene* sc, bool with_bvh) {
     // of Light::attenuate casts, and rays_shadow must stay the reference's count
     v.cull_unlit = (sc->cull_ok && !sc->any_refractive && !sc->trace_unlit && !sc->fused_shade) ? 1 : 0;
     v.one_bits = 0x3f800000u;
+    // tolerance mode: the render flag (or RT_FAST_ACCEPT=1 for the parity hooks), only for scenes without rotated instances or
+    // meshes — the reference's leaf box of a rotated instance need not contain its geometry (from_local quirk), so there the
+    // leaf-box rule can reject hits that lie clearly inside a triangle and the exact path has to decide
+    {
+        const char* e = std::getenv("RT_FAST_ACCEPT");
+        v.fast_accept = ((sc->fast_accept || (e && std::atoi(e))) && sc->all_identity) ? 1 : 0;
+    }
     return v;
 }
 
@@ -1392,6 +1409,8 @@ int rt_scene_create(const RtSceneDesc* d, RtScene** out) {
     sc->cull_ok = hs.cull_ok;
     sc->n_materials = (int)hs.mats.size();
     sc->mesh_tri_count = hs.mesh_tri_count;
+    sc->meshes_identity = true;
+    for (const MeshRec& m : hs.meshes) if (!m.pose.identity_rot) sc->meshes_identity = false;
     int rc;
     if ((rc = upload(sc->d_verts, hs.verts, sc->stream)) || (rc = upload(sc->d_norms, hs.norms, sc->stream)) ||
         (rc = upload(sc->d_tris, hs.tris, sc->stream)) || (rc = upload(sc->d_mats, hs.mats, sc->stream)) ||
@@ -1514,12 +1533,12 @@ static int persistent_grid(K kernel, int sm_count) {
 // shadow rays are occlusion queries (no refractive material), BVH traversal with the reference's leaf-box rule.
 static bool tile_kernel_eligible(const RtScene* sc, const SceneView& v, int mode) {
     static const int env_on = [] { const char* e = std::getenv("RT_TILE_KERNEL"); return (e && std::atoi(e)) ? 1 : 0; }();
-    return mode == TR_BVH_BOX && (env_on || sc->tile_kernel) && !sc->fused_shade && !sc->split_shade && !v.any_refractive;
+    return mode == TR_BVH_BOX && (env_on || sc->tile_kernel) && !sc->fused_shade && !sc->split_shade && !v.any_refractive;  // not in the tolerance mode
 }
 // The closest hits of the camera rays by the warp-coherent k_tile<1> in front of the split shading kernels (default).
 static bool beam_primary_eligible(const RtScene* sc, int mode) {
     static const int env_off = [] { const char* e = std::getenv("RT_BEAM_PRIMARY"); return (e && !std::atoi(e)) ? 1 : 0; }();
-    return mode == TR_BVH_BOX && !env_off && !sc->fused_shade && !sc->split_shade;
+    return (mode == TR_BVH_BOX || mode == TR_BVH_BOX_FAST) && !env_off && !sc->fused_shade && !sc->split_shade;
 }
 
 template <int MODE, bool STATS>
@@ -1530,6 +1549,9 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     // (only passed when the tile kernel is eligible and the frame has no secondary rays).
     cudaStream_t st = sc->stream;
     RT_CUDA(rth::record(sc, cev[0], st));
+    // tolerance mode: only the default pipeline (k_tile<1>, k_shadow_beam / k_shadow, k_bounce_waves) has a fast variant; the
+    // other branches run their exact kernels (BM), which is always an acceptable answer
+    constexpr int BM = MODE == TR_BVH_BOX_FAST ? TR_BVH_BOX : MODE;
     long long n_pix = (long long)tm.n_work() * 32;
     *waves = 1;
     sc->split_shade_used = false;
@@ -1550,15 +1572,16 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     if (!use_tile && beam_primary_eligible(sc, MODE)) {
         PeerOut po0;
         std::memset(&po0, 0, sizeof po0);
-        static const int g0 = persistent_grid(k_tile<STATS, false, false, 1>, sc->sm_count);
-        k_tile<STATS, false, false, 1><<<g0, kThreads, 0, st>>>(v, tm, ctr, canvas, po0, nullptr, 0, nullptr, sc->d_hitq.as<HitRec>());
+        constexpr bool FAST = MODE == TR_BVH_BOX_FAST;
+        static const int g0 = persistent_grid(k_tile<STATS, false, false, 1, FAST>, sc->sm_count);
+        k_tile<STATS, false, false, 1, FAST><<<g0, kThreads, 0, st>>>(v, tm, ctr, canvas, po0, nullptr, 0, nullptr, sc->d_hitq.as<HitRec>());
         sc->kernel_launches++;
         sc->wave0_form = 2;
         RT_CUDA(rth::record(sc, cev[1], st));
     } else if (!use_tile) {
-        int g0 = persistent_grid(k_primary<MODE, STATS, false>, sc->sm_count);
+        int g0 = persistent_grid(k_primary<BM, STATS, false>, sc->sm_count);
         static const int aligned_hitq = [] { const char* e = std::getenv("RT_PACKED_HITQ"); return (e && std::atoi(e)) ? 0 : 1; }();
-        k_primary<MODE, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr, aligned_hitq);
+        k_primary<BM, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr, aligned_hitq);
         sc->kernel_launches++;
         RT_CUDA(rth::record(sc, cev[1], st));
     }
@@ -1599,8 +1622,9 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         const int beam_pick = beam_env >= 0 ? beam_env : sc->sb_choice >= 0 ? sc->sb_choice : ((sc->sb_frames & 1) ? 0 : 1);
         sc->sb_used = beam_possible ? beam_pick : -1;
         if (beam_possible && beam_pick) {
-            static const int g = persistent_grid(k_shadow_beam<STATS>, sc->sm_count);
-            k_shadow_beam<STATS><<<g, kThreads, 0, st>>>(v, ctr, ctr_n, shq, occl, ctr + C_WORK1);
+            constexpr bool FAST = MODE == TR_BVH_BOX_FAST;
+            static const int g = persistent_grid(k_shadow_beam<STATS, FAST>, sc->sm_count);
+            k_shadow_beam<STATS, FAST><<<g, kThreads, 0, st>>>(v, ctr, ctr_n, shq, occl, ctr + C_WORK1);
             sc->kernel_launches++;
             return;
         }
@@ -1659,11 +1683,11 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
                 v, ctr, hitq, occl, att4, canvas, nullptr, 0, nullptr);
         sc->split_shade_used = true;
     } else if (!v.any_secondary) {
-        int g1 = persistent_grid(k_shade<MODE, STATS, true>, sc->sm_count);
-        k_shade<MODE, STATS, true><<<g1, kThreads, 0, st>>>(v, ctr, hitq, canvas, nullptr, 0, nullptr);
+        int g1 = persistent_grid(k_shade<BM, STATS, true>, sc->sm_count);
+        k_shade<BM, STATS, true><<<g1, kThreads, 0, st>>>(v, ctr, hitq, canvas, nullptr, 0, nullptr);
     } else {
-        int g1 = persistent_grid(k_shade<MODE, STATS, false>, sc->sm_count);
-        k_shade<MODE, STATS, false><<<g1, kThreads, 0, st>>>(v, ctr, hitq, canvas, paths, path_stride, sc->d_queue_a.as<int>());
+        int g1 = persistent_grid(k_shade<BM, STATS, false>, sc->sm_count);
+        k_shade<BM, STATS, false><<<g1, kThreads, 0, st>>>(v, ctr, hitq, canvas, paths, path_stride, sc->d_queue_a.as<int>());
     }
     sc->kernel_launches++;
     RT_CUDA(rth::record(sc, cev[4], st));
@@ -1678,7 +1702,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
                 RT_CUDA(cudaStreamSynchronize(st));
                 if (live == 0) break;
                 RT_CUDA(cudaMemsetAsync(ctr + outc, 0, 8, st));
-                k_bounce<MODE, STATS><<<persistent_grid(k_bounce<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
+                k_bounce<BM, STATS><<<persistent_grid(k_bounce<BM, STATS>, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, outc, qin, qout, canvas, paths, path_stride);
                 sc->kernel_launches++;
                 (*waves)++;
@@ -1710,7 +1734,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
                 RT_CUDA(cudaMemcpyAsync(qin, va, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st));
                 RT_CUDA(cudaMemsetAsync(ctr + outc, 0, 8, st));
                 RT_CUDA(cudaMemsetAsync(shq_count, 0, sizeof(unsigned) * (size_t)std::max(v.n_lights, 1), st));
-                k_wave_trace<MODE, STATS><<<persistent_grid(k_wave_trace<MODE, STATS>, sc->sm_count), kThreads, 0, st>>>(
+                k_wave_trace<BM, STATS><<<persistent_grid(k_wave_trace<BM, STATS>, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, qin, paths, path_stride, hitq);
                 k_shadow_gen<true><<<persistent_grid(k_shadow_gen<true>, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, hitq, shq, shq_count, occl, att4, paths, path_stride);
@@ -2074,6 +2098,7 @@ static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* c
     sc->sort_rays = (p.flags & RT_RENDER_SORT_RAYS) != 0;
     sc->split_shade = (p.flags & RT_RENDER_SPLIT_SHADE) != 0;
     sc->tile_kernel = (p.flags & RT_RENDER_TILE_KERNEL) != 0;
+    sc->fast_accept = (p.flags & RT_RENDER_FAST_ACCEPT) != 0;
     // RT_RENDER_PEER_STORE: this frame's epoch and canvases (double-buffered by the parity of the epoch)
     uint32_t* peer_own = nullptr;
     PeerOut po;
@@ -2194,7 +2219,10 @@ static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* c
             static const bool env_direct = [] { const char* e = std::getenv("RT_PEER_DIRECT"); return e && std::atoi(e); }();
             peer_direct = env_direct && peer_store && !secondary && tile_kernel_eligible(sc, v, TR_BVH_BOX);
             const PeerOut* pp = peer_direct ? &po : nullptr;
-            if (want_stats) rc = run_wavefront<TR_BVH_BOX, true>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], pp);
+            if (v.fast_accept) {
+                if (want_stats) rc = run_wavefront<TR_BVH_BOX_FAST, true>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], pp);
+                else rc = run_wavefront<TR_BVH_BOX_FAST, false>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], pp);
+            } else if (want_stats) rc = run_wavefront<TR_BVH_BOX, true>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], pp);
             else rc = run_wavefront<TR_BVH_BOX, false>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], pp);
             waves = (w < 0 || waves < 0) ? -1 : std::max(waves, w);
             if (rc || n_chunks == 1) continue;
@@ -2469,7 +2497,10 @@ int rt_trace_primary(RtScene* sc, int32_t use_bvh, int32_t* instance, int32_t* t
     SceneView v = rth::make_view(sc, true);
     int g = sc->sm_count * 4;
     switch (mode) {
-        case TR_BVH_BOX: k_primary<TR_BVH_BOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0); break;
+        case TR_BVH_BOX:
+            if (v.fast_accept) k_primary<TR_BVH_BOX_FAST, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0);
+            else k_primary<TR_BVH_BOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0);
+            break;
         case TR_BVH_NOBOX: k_primary<TR_BVH_NOBOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0); break;
         case TR_BRUTE: k_primary<TR_BRUTE, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0); break;
         default: k_primary<TR_BRUTE_BOX, false, true><<<g, kThreads, 0, st>>>(v, tm, ctr, nullptr, nullptr, di, dt, dtt, 0); break;

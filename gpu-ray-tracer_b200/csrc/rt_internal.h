@@ -122,6 +122,8 @@ struct RtScene {
     bool split_shade = false;       // RT_RENDER_SPLIT_SHADE: never use the one-kernel wave 0 (k_tile)
     bool tile_kernel_used = false;
     bool tile_kernel = false;       // RT_RENDER_TILE_KERNEL
+    bool fast_accept = false;       // RT_RENDER_FAST_ACCEPT
+    bool meshes_identity = true, all_identity = false;  // no rotated mesh / instance pose (tolerance mode needs it)
     // wave-0 shadow kernel auto-selection: frames timed so far, best k_shadow time per variant [per-lane, warp-coherent],
     // the variant the pending frame used (-1: not applicable), the choice (-1: still measuring)
     int sb_frames = 0, sb_used = -1, sb_choice = -1;

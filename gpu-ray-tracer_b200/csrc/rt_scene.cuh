@@ -68,6 +68,7 @@ struct SceneView {
     int any_secondary;   // some material has Kr > 0 or Kt > 0
     int cull_unlit;      // skip shadow rays of lights with zero Phong weight (rt_shade.cuh light_unlit)
     unsigned one_bits;   // 0x3f800000, kept opaque to the compiler (rt_bvh.cuh qfloat)
+    int fast_accept;     // host-side only: the frame runs the tolerance-mode kernel variants (rt_bvh.cuh tri_filter_clear)
 };
 
 // create_boxes (src/raytracer.cu:54-74): world box of an instance = from_local(from_local(mesh box,
@@ -191,6 +192,18 @@ RT_HD_NOINLINE bool exact_candidate(const SceneView& s, const rtx::Ray& r, int i
     else better = t_world < best.t || (t_world == best.t && inst < best.inst);
     if (!better) return false;
     best.t = t_world; best.t_local = time; best.u = u; best.v = v; best.inst = inst; best.tri = tri;
+    return true;
+}
+
+// Tolerance mode (SceneView::fast_accept): a clear hit of the conservative filter, taken with the filter's own t / uv instead of
+// the reference-exact test. World-space t stands in for the mesh-local time too (the transforms are rigid: they differ by
+// rounding). Same ordering rules as exact_candidate.
+RT_HD bool fast_candidate(int inst, int tri, float t, float u, float v, Hit& best) {
+    bool better;
+    if (best.inst == inst) better = t < best.t_local || (t == best.t_local && tri < best.tri);
+    else better = t < best.t || (t == best.t && inst < best.inst);
+    if (!better) return false;
+    best.t = t; best.t_local = t; best.u = u; best.v = v; best.inst = inst; best.tri = tri;
     return true;
 }
 

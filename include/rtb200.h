@@ -176,6 +176,12 @@ enum {
                                     on replayed with one cudaGraphLaunch; a changed key (camera moved, instances set) falls back to plain
                                     launches and a new capture. Device or peer canvas, BVH traversal, RT_SEMANTICS_GPU only; frames whose
                                     enqueue needs the host fall back silently. Per-kernel times stay available (external event nodes) */
+    RT_RENDER_FAST_ACCEPT = 65536, /* OPT-IN TOLERANCE MODE (the default is bit-exact): a hit that lies clearly inside a triangle — inside
+                                    all edges by twice the filter margin, |d.n| >= 4e-5, t >= 1e-4 — is accepted with the conservative
+                                    filter's own t / uv instead of the reference-exact test (40 % of the traversal kernels' instructions);
+                                    everything near an edge, the 1e-5 threshold or the light distance still takes the exact path.
+                                    Within north_star's tolerances (ids >= 99.99 %, t 1e-4 relative, RMSE 1e-3): measured parity and speed
+                                    in profiles/r2_fast_accept_parity.md. Ignored for scenes with a rotated instance or mesh */
     RT_RENDER_TRACE_UNLIT = 128  /* also trace shadow rays whose Phong weight is exactly zero (the reference does; the
                                     split pipeline skips them by default: they cannot change a pixel) */
 };

@@ -378,3 +378,42 @@ def test_graph_frames_equal_plain_frames(pkg, gpu_ok, name, kw):
     _, st = s.render(flags=base | pkg.RT_RENDER_GRAPH, out_ptr=dev.data_ptr())
     assert (dev.cpu().numpy().view(np.uint32).reshape(H, W) == c_host).all()
     s.close()
+
+
+# ------------------------------------------------------------------ opt-in tolerance mode (RT_RENDER_FAST_ACCEPT)
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,kw", [("world16", {}), ("world8_stress", {"depth": 9}), ("world4", {"width": 1920, "height": 1080})])
+def test_fast_accept_within_north_star_tolerances(pkg, gpu_ok, monkeypatch, name, kw):
+    """The tolerance mode skips the reference-exact test for hits clearly inside a triangle. Against the oracle (= the
+    reference's serial build): ids identical on >= 99.99 % of primary rays, t within 1e-4 relative, image RMSE <= 1e-3 —
+    north_star's bars, written here. The default path stays bit-exact (every other test)."""
+    w = pkg.World(scene_path(name), **kw)
+    s = pkg.Scene(w)
+    o = ob.OracleScene(w)
+    oi, ot, ott = o.trace_primary(use_bvh=1)
+    oc, ost = o.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    c, st = s.render(flags=pkg.RT_RENDER_REBUILD_BVH | pkg.RT_RENDER_FAST_ACCEPT | pkg.RT_RENDER_STATS)
+    c_exact, st_exact = s.render(flags=pkg.RT_RENDER_STATS)
+    assert (c_exact == oc).all()
+    assert st["tris_tested"] < 0.7 * st_exact["tris_tested"]  # the mode really skips exact tests
+    ch = lambda a: np.stack([(a >> sh) & 255 for sh in (24, 16, 8, 0)], -1).astype(np.float64) / 255.0
+    rmse = float(np.sqrt(np.mean((ch(c) - ch(oc)) ** 2)))
+    monkeypatch.setenv("RT_FAST_ACCEPT", "1")
+    inst, tri, t = s.trace_primary(use_bvh=1)
+    monkeypatch.setenv("RT_FAST_ACCEPT", "0")
+    same = (inst == oi) & (tri == ot)
+    hit = same & (oi >= 0)
+    rel = np.abs(t[hit].astype(np.float64) - ott[hit]) / np.abs(ott[hit])
+    print(name, "ids %.5f %%, t max rel %.2e, rmse %.2e, %d pixels differ" % (100 * same.mean(), rel.max(), rmse, int((c != oc).sum())))
+    assert same.mean() >= 0.9999
+    assert rel.max() <= 1e-4
+    assert rmse <= 1e-3
+    assert abs(int(st["rays_total"]) - int(ost["rays_total"])) <= 1e-4 * ost["rays_total"]
+    # a rotated instance switches the mode off (the reference's leaf box of a rotated instance need not contain its geometry)
+    w.apply_moves("r:0:0:1:0:0.3")
+    s.set_instances(w.desc.instances, w.desc.n_instances)
+    o2 = ob.OracleScene(w)
+    oc2, _ = o2.render(semantics=pkg.RT_SEMANTICS_GPU, use_bvh=1)
+    c2, _ = s.render(flags=pkg.RT_RENDER_REBUILD_BVH | pkg.RT_RENDER_FAST_ACCEPT)
+    assert (c2 == oc2).all()
+    s.close()

@@ -85,7 +85,7 @@ PY
       VARS=${ARG%%;*}; BARGS=""; [[ "$ARG" == *";"* ]] && BARGS=${ARG#*;}; BARGS=${BARGS//,/ }
       for V in ${VARS//,/ }; do
         LIB=""; [ "$V" != "main" ] && LIB=gpu-ray-tracer_b200/variants/librtb200_${V}.so
-        RTB200_CUDA_LIB=$LIB timeout 600 python bench.py --steps 20 --warmup 5 --no-stress --no-ref-cuda --no-cpu-baseline $BARGS \
+        RTB200_CUDA_LIB=$LIB timeout 600 python bench.py --steps 20 --warmup 5 --no-stress --no-ref-cuda --no-cpu-baseline --no-fast-accept $BARGS \
           > gpurun_out/${TAG}_ab_${V}.json 2> gpurun_out/${TAG}_ab_${V}.err
         python - "$V" gpurun_out/${TAG}_ab_${V}.json <<'PY'
 import json, sys
@@ -104,7 +104,7 @@ PY
         LBL=${RUN%%=*}; RA=${RUN#*=}; [ "$RA" == "$RUN" ] && RA=""; RA=${RA//,/ }
         ENVS=""; BA=""
         for TOK in $RA; do if [[ "$TOK" == [A-Z_]*=* && "$TOK" != --* ]]; then ENVS="$ENVS $TOK"; else BA="$BA $TOK"; fi; done
-        env $ENVS timeout 600 python bench.py --steps 20 --warmup 5 --no-stress --no-ref-cuda --no-cpu-baseline $BA \
+        env $ENVS timeout 600 python bench.py --steps 20 --warmup 5 --no-stress --no-ref-cuda --no-cpu-baseline --no-fast-accept $BA \
           > gpurun_out/${TAG}_abf_${LBL}.json 2> gpurun_out/${TAG}_abf_${LBL}.err
         python - "$LBL" gpurun_out/${TAG}_abf_${LBL}.json <<'PY'
 import json, sys
