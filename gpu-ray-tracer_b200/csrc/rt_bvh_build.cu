@@ -1201,7 +1201,60 @@ __global__ void __launch_bounds__(kCT, 1) k_build_cluster(ClusterBuildArgs a) {
     float* suf = a.edge_box + 6 * (size_t)n;
     float* ctot = a.edge_box + 12 * (size_t)n;
     for (int i = tid; i < per; i += kCT) s_big[i] = 0u;
+    // The climb walks one tree level per step, and every step is a chain of dependent loads (parent -> range and children ->
+    // sibling box): in global memory three L2 round trips per level (38 us for world16's 15 levels). When the chunk's topology
+    // and boxes fit the CTA's dynamic shared memory (72 bytes per leaf) the whole climb runs there; global memory only gets the
+    // finished boxes. A node whose leaves lie inside [L0, L1) has its own id and its children inside the chunk too (a Karras
+    // node's id is one end of its range), so every index below stays local.
+    const bool climb_smem = (size_t)per * 72 <= (size_t)a.smem_words * 4 && n > 1;
+    int4* s_topo = (int4*)s_dyn;                        // left, right, lo, hi of internal node L0 + k
+    int* s_pint = (int*)(s_topo + per);                 // parent of internal node L0 + k
+    int* s_pleaf = s_pint + per;                        // parent of leaf L0 + k
+    volatile float* s_bint = (volatile float*)(s_pleaf + per);  // box of internal node L0 + k
+    volatile float* s_bleaf = s_bint + 6 * (size_t)per;         // box of leaf L0 + k
+    if (climb_smem) {
+        __syncthreads();  // Karras' keys in s_dyn are dead (cluster.sync above); reuse the memory
+        for (int k = tid; k < L1 - L0; k += kCT) {
+            const int i = L0 + k;
+            if (i < n - 1) {
+                s_topo[k] = make_int4(a.left[i], a.right[i], a.range_lo[i], a.range_hi[i]);
+                s_pint[k] = a.parent[i];
+            }
+            s_pleaf[k] = a.parent[n - 1 + i];
+        }
+    }
     __syncthreads();
+    if (climb_smem) {
+        for (int j = L0 + tid; j < L1; j += kCT) {
+            const int p = vin[j];
+            const int k0 = j - L0;
+            float box[6];
+#pragma unroll
+            for (int k = 0; k < 6; k++) box[k] = a.prim_box[6 * (size_t)p + k];
+            int child = n - 1 + j;
+#pragma unroll
+            for (int k = 0; k < 6; k++) { a.node_box[6 * (size_t)child + k] = box[k]; s_bleaf[6 * k0 + k] = box[k]; }
+            int cur = s_pleaf[k0];
+            while (cur >= L0 && cur < L1) {
+                const int kk = cur - L0;
+                const int4 tp = s_topo[kk];
+                if (tp.z < L0 || tp.w >= L1) break;  // spans chunks: united from prefix / suffix unions below
+                __threadfence_block();               // this thread's box of `child` is visible to the CTA before it arrives
+                if (atomicAdd(&s_big[kk], 1u) == 0u) break;  // first arrival leaves; the second unites
+                __threadfence_block();
+                const int sib = tp.x == child ? tp.y : tp.x;
+                const volatile float* sb = sib >= n - 1 ? s_bleaf + 6 * (size_t)(sib - (n - 1) - L0) : s_bint + 6 * (size_t)(sib - L0);
+                float o[6];
+#pragma unroll
+                for (int k = 0; k < 6; k++) o[k] = sb[k];
+                box_unite(box, o);
+#pragma unroll
+                for (int k = 0; k < 6; k++) { s_bint[6 * kk + k] = box[k]; a.node_box[6 * (size_t)cur + k] = box[k]; }
+                child = cur;
+                cur = s_pint[kk];
+            }
+        }
+    } else
     for (int j = L0 + tid; j < L1; j += kCT) {
         const int p = vin[j];
         float box[6];
