@@ -86,7 +86,10 @@ constexpr int kThreads = 256;
 #define RT_WAVES_MIN_BLOCKS 3
 #endif
 #ifndef RT_RESOLVE_MIN_BLOCKS
-#define RT_RESOLVE_MIN_BLOCKS 3
+#define RT_RESOLVE_MIN_BLOCKS 4   /* 64 registers, no spills: shading phase 0.905 -> 0.884 ms against 3 blocks */
+#endif
+#ifndef RT_GEN_MIN_BLOCKS
+#define RT_GEN_MIN_BLOCKS 4
 #endif
 static int g_device = -1;
 static int g_sm_count = 148;
@@ -434,7 +437,7 @@ __device__ __forceinline__ void flush_culled(const SceneView& s, unsigned long l
 }
 
 template <bool PATHS>
-__global__ void __launch_bounds__(kThreads) k_shadow_gen(SceneView s, unsigned long long* ctr, int ctr_n,
+__global__ void __launch_bounds__(kThreads, RT_GEN_MIN_BLOCKS) k_shadow_gen(SceneView s, unsigned long long* ctr, int ctr_n,
                                                         const HitRec* hitq, ShadowRec* shq, unsigned* shq_count,
                                                         unsigned char* occl, float4* att4, unsigned char* paths,
                                                         int path_stride) {
@@ -760,7 +763,7 @@ struct PeerOut { PeerCanvases pc; PushSignal sg; int rank; };
 #define RT_TILE_MIN_BLOCKS 2
 #endif
 #ifndef RT_TILE1_MIN_BLOCKS
-#define RT_TILE1_MIN_BLOCKS 3
+#define RT_TILE1_MIN_BLOCKS 4   /* 64 registers, 60 B of spills: k_tile<1> 0.727 -> 0.706 ms against 3 blocks / 80 registers (profiles/r2_summary.md) */
 #endif
 #ifndef RT_TILE2_MIN_BLOCKS
 #define RT_TILE2_MIN_BLOCKS 2   /* 128 registers: at 3 blocks (80) the shading phase spills 324 B and runs 6 % slower */
