@@ -100,6 +100,7 @@ static int g_sm_count = 148;
 struct TileMap {
     int W, H, tile_w, tile_h, tiles_x, n_tiles, rank, world, n_owned, sub_x, sub_per_tile, tiled_out;
     int k_begin, k_count;  // the owned tiles [k_begin, k_begin + k_count) this launch works on (a chunk of the frame)
+    int reverse;           // k_tile: work units are taken from the last one down (see there)
     __host__ __device__ int n_work() const { return k_count * sub_per_tile; }
     // lane -> pixel; returns false for pixels outside the canvas
     __host__ __device__ bool locate(int q, int lane, int& x, int& y, int& out) const {
@@ -137,6 +138,8 @@ static int make_tilemap(const RtScene* sc, const RtRenderParams* p, TileMap& m) 
     m.sub_per_tile = m.sub_x * (th / 4);
     m.tiled_out = tiled;
     m.k_begin = 0; m.k_count = m.n_owned;
+    static const int order_env = [] { const char* e = std::getenv("RT_TILE_ORDER"); return e ? std::atoi(e) : 0; }();
+    m.reverse = order_env;
     return RT_OK;
 }
 static long long slab_pixels(const TileMap& m) {
@@ -508,7 +511,7 @@ __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(Scene
 template <bool STATS, bool FAST = false>
 __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow_beam(SceneView s, unsigned long long* ctr, int ctr_n,
                                                                                const ShadowRec* shq, unsigned char* occl,
-                                                                               unsigned long long* work) {
+                                                                               unsigned long long* work, int from_back) {
     TravStats ts = {0, 0, 0};
     BeamStats bs = {0};
     RayCounts rc = {0, 0, 0};
@@ -520,6 +523,7 @@ __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow_beam(
         if (lane == 0) b = atomicAdd(work, 32ull);
         b = __shfl_sync(0xffffffffu, b, 0);
         if ((long long)b >= total) break;
+        if (from_back) b = (unsigned long long)(total - 32) - b;  // the queue's last groups (bottom of the image) first
         const long long f = (long long)b + lane;
         const long long l = (long long)b / n_hits;  // warp-uniform: n_hits is a multiple of 32
         const ShadowRec q = shq[f];
@@ -528,7 +532,24 @@ __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow_beam(
         r.o = rtx::mk3(q.o_maxt.x, q.o_maxt.y, q.o_maxt.z);
         r.d = rtx::mk3(q.d.x, q.d.y, q.d.z);
         Hit h;
+        unsigned long long t0 = 0;
+        const TravStats ts0 = ts;
+        const unsigned nf0 = bs.node_fetches;
+        if (STATS) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
         const bool blocked = beam_query<STATS, FAST>(s, r, trace, true, true, q.o_maxt.w, h, ts, bs);
+        if (STATS) {  // longest single work unit of the launch (RtFrameStats.ms_wave_phase[3] for frames without bounce waves)
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+            // diagnostics of that unit (racy, last writer wins): [0] = queue position, [1] = node fetches * 10000 + most exact
+            // tests of a lane, [2] = most triangle filters of a lane (overwrites k_tile<1>'s longest tile)
+            unsigned pf = ts.prims - ts0.prims, ex = ts.exact - ts0.exact;
+            for (int o = 16; o; o >>= 1) { pf = max(pf, __shfl_xor_sync(0xffffffffu, pf, o)); ex = max(ex, __shfl_xor_sync(0xffffffffu, ex, o)); }
+            if (lane == 0 && atomicMax(&ctr[C_PHASE_NS + 3], t1 - t0) < t1 - t0) {
+                ctr[C_PHASE_NS + 0] = b;
+                ctr[C_PHASE_NS + 1] = (unsigned long long)(bs.node_fetches - nf0) * 10000ull + ex;  // small integers: exact as floats
+                ctr[C_PHASE_NS + 2] = pf;
+            }
+        }
         if (trace) {
             rc.shadow++;
             occl[(size_t)l * n_hits + (size_t)__float_as_int(q.d.w)] = blocked ? 1 : 0;
@@ -797,12 +818,26 @@ k_tile(SceneView s, TileMap tm, unsigned long long* ctr, uint32_t* canvas, PeerO
         bool hit;
         if (PHASE != 2) {
             if (q >= n_work) break;
+            // Bottom of the image first: tiles are enumerated from the top (sky: one node test) to the bottom (terrain near the
+            // camera: the most expensive tiles). A persistent kernel that meets its heaviest units last ends with a few warps
+            // still walking them (SMs finished up to 0.04 ms apart; that imbalance does not shrink when the frame is sharded
+            // over more GPUs). Reversed, the cheap units come last and even the end out; the hit queue — filled in completion
+            // order — then hands the shadow kernel its heavy units first as well. RT_TILE_ORDER=0 restores the old order.
+            if (tm.reverse == 1) q = n_work - 1 - q;
+            else if (tm.reverse == 2) { q += n_work >> 1; if (q >= n_work) q -= n_work; }  // lower half of the image first, in natural order
             const bool valid = tm.locate(q, lane, x, y, out);
             if (valid) {
                 r = rtx::camera_ray(s.cam, (float)x, (float)y);
                 rc.primary++;
             }
+            unsigned long long t0 = 0;
+            if (STATS) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
             hit = beam_query<STATS, FAST>(s, r, valid, false, true, INFINITY, h, ts, bs);
+            if (STATS) {  // longest single tile (ms_wave_phase[2])
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+                if (lane == 0) atomicMax(&ctr[C_PHASE_NS + 2], t1 - t0);
+            }
             if (valid && !hit) store(out, 0u);  // pack_color(0,0,0,0)
             const unsigned hm = __ballot_sync(0xffffffffu, hit);
             if (!hm) continue;
@@ -1494,7 +1529,7 @@ int rt_scene_set_canvas_size(RtScene* sc, int32_t w, int32_t h) {
     if (!sc || w <= 0 || h <= 0 || w > 65535 || h > 65535) { set_error("invalid canvas size"); return RT_ERR_INVALID_ARG; }
     if ((long long)w * h > (1ll << 30)) { set_error("canvas larger than 2^30 pixels"); return RT_ERR_LIMIT; }
     sc->width = w; sc->height = h;
-    sc->sb_choice = -1; sc->sb_frames = 0; sc->sb_ms[0] = sc->sb_ms[1] = 0.0f;
+    for (RtScene::SbTuner& t : sc->tuners) t = RtScene::SbTuner();
     sc->camera.canvas_width = (float)w;
     sc->camera.canvas_height = (float)h;
     return RT_OK;
@@ -1618,16 +1653,19 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         // Wave 0 of an opaque scene behind k_tile<1>: the queues are tile-aligned, so one warp-coherent occlusion walk per
         // tile and light is possible (k_shadow_beam). Which kernel wins depends on the scene (world16 at 4K: 0.61 ms against
         // 0.70 per lane; world8_stress: 0.40 against 0.31, where most shadow rays are blocked at once and a lane-wise walk
-        // stops early), so a scene times both on its first four frames (same flags either way) and keeps the faster;
-        // RT_BEAM_SHADOW=0|1 forces one.
-        static const int beam_env = [] { const char* e = std::getenv("RT_BEAM_SHADOW"); return e ? (std::atoi(e) ? 1 : 0) : -1; }();
+        // stops early), and so does the order the beam kernel takes the queue in: front to back wins on the whole 4K frame
+        // (0.606 ms against 0.658), back to front (the image's lower rows, its longest units, first) on an eighth of it
+        // (0.133 against 0.162). A scene therefore times the three on its first six frames of a tile shape (same flags
+        // each time) and keeps the fastest; RT_BEAM_SHADOW=0|1|2 forces lane-wise / beam / beam from the back.
+        static const int beam_env = [] { const char* e = std::getenv("RT_BEAM_SHADOW"); return e ? std::min(std::max(std::atoi(e), 0), 2) : -1; }();
         const bool beam_possible = !loop && sc->wave0_form == 2 && ctr_n == C_HITQ && v.n_lights > 0;
-        const int beam_pick = beam_env >= 0 ? beam_env : sc->sb_choice >= 0 ? sc->sb_choice : ((sc->sb_frames & 1) ? 0 : 1);
+        const RtScene::SbTuner& tuner = sc->tuners[sc->sb_cur];
+        const int beam_pick = beam_env >= 0 ? beam_env : tuner.choice >= 0 ? tuner.choice : (tuner.frames + 1) % 3;
         sc->sb_used = beam_possible ? beam_pick : -1;
         if (beam_possible && beam_pick) {
             constexpr bool FAST = MODE == TR_BVH_BOX_FAST;
             static const int g = persistent_grid(k_shadow_beam<STATS, FAST>, sc->sm_count);
-            k_shadow_beam<STATS, FAST><<<g, kThreads, 0, st>>>(v, ctr, ctr_n, shq, occl, ctr + C_WORK1);
+            k_shadow_beam<STATS, FAST><<<g, kThreads, 0, st>>>(v, ctr, ctr_n, shq, occl, ctr + C_WORK1, beam_pick == 2);
             sc->kernel_launches++;
             return;
         }
@@ -2286,7 +2324,7 @@ static void graph_key(const RtScene* sc, const RtRenderParams& p, const uint32_t
     put(&sc->width, sizeof sc->width); put(&sc->height, sizeof sc->height);
     put(&sc->camera, sizeof sc->camera); put(&sc->env, sizeof sc->env);
     put(&sc->inst_gen, sizeof sc->inst_gen); put(&rth::g_alloc_gen, sizeof rth::g_alloc_gen);
-    const int st[8] = {sc->boxes_valid, sc->bvh.valid, sc->bvh.topology_valid, sc->sb_choice, sc->n_instances, sc->peer_n, sc->peer_root,
+    const int st[8] = {sc->boxes_valid, sc->bvh.valid, sc->bvh.topology_valid, sc->tuners[sc->sb_cur].choice, sc->n_instances, sc->peer_n, sc->peer_root,
                        (p.flags & RT_RENDER_PEER_STORE) ? (int)((sc->peer_epoch + 1u) & 1u) : 0};
     put(st, sizeof st);
     put(&sc->stream, sizeof sc->stream);
@@ -2313,6 +2351,19 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
     if (params) p = *params;
     if (sc->pending) {  // an asynchronous frame was never finished: its counters are about to be reused
         if (int rc = rt_frame_finish(sc, nullptr)) return rc;
+    }
+    {   // the shadow-kernel tuner of this frame's tile shape
+        const int shape[5] = {p.tile_w, p.tile_h, p.world > 1 ? p.world : 1, sc->width, sc->height};
+        int found = -1;
+        for (int i = 0; i < 6 && found < 0; i++) if (sc->tuners[i].used && std::memcmp(sc->tuners[i].shape, shape, sizeof shape) == 0) found = i;
+        if (found < 0) {
+            found = sc->sb_next;
+            sc->sb_next = (sc->sb_next + 1) % 6;
+            sc->tuners[found] = RtScene::SbTuner();
+            std::memcpy(sc->tuners[found].shape, shape, sizeof shape);
+            sc->tuners[found].used = true;
+        }
+        sc->sb_cur = found;
     }
     // A frame can be a graph when nothing in it needs the host in between: BVH traversal with the CUDA bounce semantics
     // (wavefront kernels), canvas on the device or in the peers, and the wave-0 shadow kernel already chosen.
@@ -2343,7 +2394,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
             sc->graph_replays++;
             pend_graph = 2;
             done = true;
-        } else if (key == sc->last_key && key != sc->bad_key && (sc->sb_used < 0 || sc->sb_choice >= 0)) {
+        } else if (key == sc->last_key && key != sc->bad_key && (sc->sb_used < 0 || sc->tuners[sc->sb_cur].choice >= 0)) {
             // second appearance of this key: every buffer has its size, capture the frame
             const unsigned epoch0 = sc->peer_epoch;
             const bool boxes0 = sc->boxes_valid, valid0 = sc->bvh.valid, topo0 = sc->bvh.topology_valid;
@@ -2444,11 +2495,16 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
         }
         fs.n_hits = (int32_t)(host_ctr[C_HITQ] >> 32);  // high word = hits, low word = queue slots
     }
-    if (wavefront && sc->split_shade_used && n_chunks == 1 && sc->sb_choice < 0 && sc->sb_used >= 0 && !sc->pend_stats) {
-        // auto-selection of the wave-0 shadow kernel (run_wavefront, trace_shadows): best of two frames each
-        float& best = sc->sb_ms[sc->sb_used];
+    RtScene::SbTuner& tuner = sc->tuners[sc->sb_cur];
+    if (wavefront && sc->split_shade_used && n_chunks == 1 && tuner.choice < 0 && sc->sb_used >= 0 && !sc->pend_stats) {
+        // auto-selection of the wave-0 shadow kernel (run_wavefront, trace_shadows): best of two frames each, per tile shape
+        float& best = tuner.ms[sc->sb_used];
         if (best <= 0.0f || fs.ms_shadow < best) best = fs.ms_shadow;
-        if (++sc->sb_frames >= 4) sc->sb_choice = sc->sb_ms[1] <= sc->sb_ms[0] ? 1 : 0;
+        if (++tuner.frames >= 6) {
+            tuner.choice = 1;
+            if (tuner.ms[2] < tuner.ms[tuner.choice]) tuner.choice = 2;
+            if (tuner.ms[0] < tuner.ms[tuner.choice]) tuner.choice = 0;
+        }
     }
     for (int k = 0; k < 4; k++) fs.ms_wave_phase[k] = (float)host_ctr[C_PHASE_NS + k] * 1e-6f;
     fs.waves = waves >= 0 ? waves : 1 + (int)host_ctr[C_WAVES];

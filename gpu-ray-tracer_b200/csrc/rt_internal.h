@@ -126,8 +126,11 @@ struct RtScene {
     bool meshes_identity = true, all_identity = false;  // no rotated mesh / instance pose (tolerance mode needs it)
     // wave-0 shadow kernel auto-selection: frames timed so far, best k_shadow time per variant [per-lane, warp-coherent],
     // the variant the pending frame used (-1: not applicable), the choice (-1: still measuring)
-    int sb_frames = 0, sb_used = -1, sb_choice = -1;
-    float sb_ms[2] = {0.0f, 0.0f};
+    // One tuner per tile shape (tile size, world size, canvas size): frames with different tilings — e.g. the 32x16 tiles of a
+    // device-resident frame and the 4-row full-width bands of a host frame — time the two kernels differently.
+    struct SbTuner { int shape[5] = {0, 0, 0, 0, 0}; int frames = 0, choice = -1; float ms[3] = {0.0f, 0.0f, 0.0f}; bool used = false; };
+    SbTuner tuners[6];
+    int sb_cur = 0, sb_next = 0, sb_used = -1;
     bool pend_stats = false;
     int wave0_form = 0;             // 0 split, 1 tile kernels, 2 beam primary + split shading (RtFrameStats.tile_kernel)
     rth::Bvh bvh;
