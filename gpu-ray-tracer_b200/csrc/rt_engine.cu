@@ -1155,18 +1155,40 @@ __device__ __forceinline__ void push_signal_tail(const TileMap& tm, const PeerCa
     if (threadIdx.x == 0) *sg.done_blocks = 0u;  // ready for the next frame
 }
 
+// ack.n > 0 (gather to one rank): once every rank has signalled, the gathering rank acknowledges the epoch in each sender's own
+// mailbox (slot ack_slot = the gathering rank's id; k_wait_ack is the other end).
 __global__ void k_wait_mailbox(const uint32_t* own_canvas, long long mailbox_offset, int n, unsigned epoch, long long timeout_cycles,
-                               unsigned* status, const unsigned* epoch_ptr) {
-    if ((int)threadIdx.x >= n) return;
+                               unsigned* status, const unsigned* epoch_ptr, PeerCanvases ack, int ack_slot) {
     if (epoch_ptr) epoch = *(volatile const unsigned*)epoch_ptr;  // replayed graph: this frame's epoch sits in pinned memory
     volatile const unsigned* box = (volatile const unsigned*)(own_canvas + mailbox_offset);
-    long long t0 = clock64();
     // epochs only grow; a peer that died would hang the GPU, so the wait gives up after timeout_cycles. The frame is then
     // incomplete: the slot that timed out is recorded in *status (pinned host memory, bit r = rank r never signalled) and
     // the host turns it into RT_ERR_CUDA at the next synchronisation point of this scene (rt_frame_finish / the
     // blocking rt_push_tiles_signal).
-    while ((int)(box[threadIdx.x] - epoch) < 0) {
-        if (clock64() - t0 > timeout_cycles) { atomicOr(status, 1u << threadIdx.x); break; }
+    if ((int)threadIdx.x < n) {
+        const long long t0 = clock64();
+        while ((int)(box[threadIdx.x] - epoch) < 0) {
+            if (clock64() - t0 > timeout_cycles) { atomicOr(status, 1u << threadIdx.x); break; }
+        }
+    }
+    __threadfence_system();
+    __syncwarp();  // every slot has been seen (or given up on) before any acknowledgement leaves
+    if ((int)threadIdx.x < ack.n && (int)threadIdx.x != ack_slot)
+        *((volatile unsigned*)(ack.p[threadIdx.x] + mailbox_offset) + ack_slot) = epoch;
+}
+
+// Sender side of a gather to one rank: before this rank stores frame `epoch` into the gathering rank's canvas of that parity
+// (which still holds frame epoch - 2), the gathering rank must have finished gathering frame epoch - 1 — its wait kernel for
+// that frame runs behind everything its stream did with frame epoch - 2. Without this a sender that never waits for anyone
+// could run any number of frames ahead of the receiver. In step the acknowledgement is a frame old when it is looked at.
+__global__ void k_wait_ack(const uint32_t* own_canvas0, long long mailbox_offset, int slot, unsigned epoch, long long timeout_cycles,
+                           unsigned* status, const unsigned* epoch_ptr) {
+    if (threadIdx.x) return;
+    if (epoch_ptr) epoch = *(volatile const unsigned*)epoch_ptr;
+    volatile const unsigned* box = (volatile const unsigned*)(own_canvas0 + mailbox_offset) + slot;
+    const long long t0 = clock64();
+    while ((int)(*box - (epoch - 1u)) < 0) {
+        if (clock64() - t0 > timeout_cycles) { atomicOr(status, 1u << slot); break; }
     }
     __threadfence_system();
 }
@@ -1952,7 +1974,7 @@ static int check_exchange(RtScene* sc) {
     if (!missing) return RT_OK;
     *st = 0u;
     char buf[160];
-    std::snprintf(buf, sizeof buf, "peer exchange timed out: ranks with mask 0x%x never signalled this frame (canvas incomplete)", missing);
+    std::snprintf(buf, sizeof buf, "peer exchange timed out: ranks with mask 0x%x never signalled (or, gathering rank, never acknowledged) this frame", missing);
     set_error(buf);
     return RT_ERR_CUDA;
 }
@@ -1985,8 +2007,10 @@ static int push_tiles_impl(RtScene* sc, const RtRenderParams* p, const uint32_t*
         // a rank that owns no tile still has to signal: one block, no quads
         unsigned grid = (unsigned)std::max<long long>((n_quads + kThreads - 1) / kThreads, 1);
         k_push_tiles<true><<<grid, kThreads, 0, sc->stream>>>(tm, slab, pc, sg);
+        PeerCanvases no_ack;
+        std::memset(&no_ack, 0, sizeof no_ack);
         k_wait_mailbox<<<1, 32, 0, sc->stream>>>(peer_canvases[tm.rank], canvas_pixels, n_peers, epoch, mailbox_timeout_cycles(),
-                                                 exchange_status(sc), nullptr);
+                                                 exchange_status(sc), nullptr, no_ack, 0);
         RT_CUDA(cudaEventRecord(sc->ev_exchange, sc->stream));
         sc->exchange_pending = true;
         sc->kernel_launches += 2;
@@ -2167,6 +2191,17 @@ static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* c
         po.rank = tm.rank;
         canvas = peer_own;
     }
+    const bool gather_sender = peer_store && sc->peer_root >= 0 && sc->peer_root != tm.rank && sc->peer_n > 1;
+    bool ack_waited = false;
+    {
+        static const bool env_direct = [] { const char* e = std::getenv("RT_PEER_DIRECT"); return e && std::atoi(e); }();
+        if (gather_sender && env_direct) {  // the frame kernels may store into the gathering rank themselves: wait in front of them
+            k_wait_ack<<<1, 32, 0, st>>>(sc->peer_canv[tm.rank], sc->peer_pixels, sc->peer_root, po.sg.epoch, mailbox_timeout_cycles(),
+                                         exchange_status(sc), po.sg.epoch_ptr);
+            sc->kernel_launches++;
+            ack_waited = true;
+        }
+    }
     bool built = false;
     RT_CUDA(rth::record(sc, sc->ev[2], st));
     if (!no_bvh) {
@@ -2284,11 +2319,24 @@ static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* c
             if (tm.tile_w % 4) { set_error("tile_w must be a multiple of 4"); return RT_ERR_INVALID_ARG; }
             const long long n_quads = (long long)tm.n_owned * tm.tile_h * (tm.tile_w / 4);
             const unsigned grid = (unsigned)std::max<long long>((n_quads + kThreads - 1) / kThreads, 1);
+            if (gather_sender && !ack_waited) {  // sender of a gather: not more than one frame ahead of the gathering rank
+                k_wait_ack<<<1, 32, 0, st>>>(sc->peer_canv[tm.rank], sc->peer_pixels, sc->peer_root, po.sg.epoch, mailbox_timeout_cycles(),
+                                             exchange_status(sc), po.sg.epoch_ptr);
+                sc->kernel_launches++;
+            }
             k_forward_tiles<<<grid, kThreads, 0, st>>>(tm, peer_own, po.pc, po.sg);
             sc->kernel_launches++;
         }
+        if (gather_sender) {  // rt_frame_finish looks at the time-out word of the acknowledgement wait
+            RT_CUDA(rth::record(sc, sc->ev_exchange, st));
+            sc->exchange_pending = true;
+        }
         if (sc->peer_root < 0 || sc->peer_root == tm.rank) {  // this rank receives the frame: wait until every rank has signalled
-            k_wait_mailbox<<<1, 32, 0, st>>>(peer_own, sc->peer_pixels, sc->peer_n, po.sg.epoch, mailbox_timeout_cycles(), exchange_status(sc), po.sg.epoch_ptr);
+            PeerCanvases ack;
+            std::memset(&ack, 0, sizeof ack);
+            if (sc->peer_root >= 0 && sc->peer_n > 1) { ack.n = sc->peer_n; for (int r = 0; r < sc->peer_n; r++) ack.p[r] = sc->peer_canv[r]; }  // parity-0 canvases hold the acknowledgement words
+            k_wait_mailbox<<<1, 32, 0, st>>>(peer_own, sc->peer_pixels, sc->peer_n, po.sg.epoch, mailbox_timeout_cycles(), exchange_status(sc), po.sg.epoch_ptr,
+                                             ack, std::max(sc->peer_root, 0));
             sc->kernel_launches++;
             RT_CUDA(rth::record(sc, sc->ev_exchange, st));
             sc->exchange_pending = true;

@@ -330,6 +330,54 @@ def test_peer_store_frames(pkg, gpu_ok, name, n, root):
         pkg.peer_canvas_free(p)
 
 
+@pytest.mark.gpu
+def test_gather_sender_cannot_run_ahead(pkg, gpu_ok):
+    """Gather to one rank: a sender stores frame e into the gathering rank's canvas of that parity only once the gathering
+    rank has acknowledged frame e - 1 (k_wait_ack / the acknowledgement k_wait_mailbox sends). A sender whose receiver is
+    not rendering gets a time-out error on its second frame instead of overwriting a frame nobody has gathered yet; once
+    the receiver has caught up the exchange works again and the gathered frame is the single-rank frame."""
+    env = dict(os.environ, RT_MAILBOX_TIMEOUT_MS="20")
+    code = r"""
+import sys, numpy as np
+sys.path.insert(0, %r)
+import rtb200_loader
+pkg = rtb200_loader.load()
+w = pkg.World(%r, width=256, height=128)
+W, H = 256, 128
+ref = pkg.Scene(w)
+full, _ = ref.render()
+ref.close()
+canv = [pkg.peer_canvas_alloc(W * H)[0] for _ in range(4)]
+ranks = [pkg.Scene(w) for _ in range(2)]
+for s in ranks:
+    s.set_peers(canv, 2, W * H, 0)
+F = pkg.RT_RENDER_PEER_STORE | pkg.RT_RENDER_ASYNC | pkg.RT_RENDER_REBUILD_BVH
+def frame(r):
+    ranks[r].render(flags=F, rank=r, world=2, tile_w=32, tile_h=16, out_ptr=0)
+    try:
+        ranks[r].finish()
+        return "ok"
+    except RuntimeError as e:
+        return "error: " + str(e)
+print("SENDER-1", frame(1))   # nothing to wait for
+print("SENDER-2", frame(1))   # frame 1 was never gathered
+print("ROOT-1", frame(0))     # sees the sender's signal (epoch 2 >= 1), acknowledges 1
+print("ROOT-2", frame(0))     # acknowledges 2
+print("SENDER-3", frame(1))   # allowed: frame 2 is acknowledged
+print("ROOT-3", frame(0))
+ptr, epoch = ranks[0].peer_frame_canvas(0)
+got = ranks[0].copy_to_host(ptr, np.empty(W * H, np.uint32)).reshape(H, W)
+print("FRAME-EQUAL", epoch, bool((got == full).all()))
+""" % (ROOT, scene_path("world4"))
+    out = subprocess.run(["python", "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    lines = dict(l.split(" ", 1) for l in out.stdout.strip().splitlines())
+    assert lines["SENDER-1"] == "ok", out.stdout
+    assert lines["SENDER-2"].startswith("error") and "timed out" in lines["SENDER-2"] and "0x1" in lines["SENDER-2"], out.stdout
+    assert lines["ROOT-1"] == "ok" and lines["ROOT-2"] == "ok" and lines["SENDER-3"] == "ok" and lines["ROOT-3"] == "ok", out.stdout
+    assert lines["FRAME-EQUAL"] == "3 True", out.stdout
+
+
 # ------------------------------------------------------------------ the frame as one CUDA graph (RT_RENDER_GRAPH)
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,kw", [("world16", {"width": 1280, "height": 720}), ("world8_stress", {"depth": 9}), ("world1", {"depth": 5})])
