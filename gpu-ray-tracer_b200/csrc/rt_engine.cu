@@ -2442,8 +2442,9 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
             sc->graph_replays++;
             pend_graph = 2;
             done = true;
-        } else if (key == sc->last_key && key != sc->bad_key && (sc->sb_used < 0 || sc->tuners[sc->sb_cur].choice >= 0)) {
-            // second appearance of this key: every buffer has its size, capture the frame
+        } else if ((key == sc->last_key || key == sc->prev_key) && key != sc->bad_key && (sc->sb_used < 0 || sc->tuners[sc->sb_cur].choice >= 0)) {
+            // second appearance of this key (peer frames alternate between the keys of the two canvas parities, hence the last two
+            // frames): every buffer has its size, capture the frame
             const unsigned epoch0 = sc->peer_epoch;
             const bool boxes0 = sc->boxes_valid, valid0 = sc->bvh.valid, topo0 = sc->bvh.topology_valid;
             cudaGraph_t graph = nullptr;
@@ -2483,6 +2484,7 @@ int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFra
                 sc->bad_key = key;
             }
         }
+        sc->prev_key.swap(sc->last_key);
         sc->last_key.swap(key);
     }
     if (!done) rc = render_enqueue(sc, &p, canvas);

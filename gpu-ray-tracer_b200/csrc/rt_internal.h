@@ -163,7 +163,7 @@ struct RtScene {
     // generation, buffer generation, BVH state, exchange parity) and replayed with one cudaGraphLaunch
     bool capturing = false;              // the scene's stream is under capture: timing events become external record nodes
     rth::FrameGraph graphs[4];
-    std::vector<unsigned char> last_key; // key of the previous frame that asked for a graph (a frame is captured on its second appearance)
+    std::vector<unsigned char> last_key, prev_key; // keys of the last two frames that asked for a graph (a frame is captured on its second appearance)
     std::vector<unsigned char> bad_key;  // a key whose capture failed: plain launches from then on
     unsigned long long graph_clock = 0, inst_gen = 0;
     int graph_replays = 0, graph_captures = 0, pend_graph = 0;

@@ -290,13 +290,15 @@ def test_refractive_scene_beam_primary(pkg, gpu_ok):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name,n,root", [("world16", 2, -1), ("world16", 4, 0), ("world16", 8, 3), ("world8_stress", 2, -1),
-                                         ("world8_stress", 4, 1), ("world1", 2, 0)])
-def test_peer_store_frames(pkg, gpu_ok, name, n, root):
+@pytest.mark.parametrize("name,n,root,graph", [("world16", 2, -1, 0), ("world16", 4, 0, 0), ("world16", 8, 3, 0), ("world8_stress", 2, -1, 0),
+                                               ("world8_stress", 4, 1, 0), ("world1", 2, 0, 0), ("world16", 4, 0, 1), ("world8_stress", 2, -1, 1)])
+def test_peer_store_frames(pkg, gpu_ok, name, n, root, graph):
     """RT_RENDER_PEER_STORE with n ranks emulated on one device (one Scene per rank, each on its own stream): the tiles
     every rank's kernels store into the shared row-major canvases reassemble the single-rank frame — on every rank
     (root = -1) or on the gathering rank only — for two consecutive frames (both parities). world16: k_tile stores and
-    signals itself; world8_stress (secondary rays) and world1 (refractive: split pipeline) forward their own canvas."""
+    signals itself; world8_stress (secondary rays) and world1 (refractive: split pipeline) forward their own canvas.
+    graph = 1: the same with RT_RENDER_GRAPH for 14 frames — the two canvas parities are two keys, each captured on its second
+    appearance once the shadow-kernel choice (part of the key) has settled, then replayed with the epoch read from pinned memory."""
     w = pkg.World(scene_path(name), width=512, height=272)
     W, H = w.width, w.height
     ref = pkg.Scene(w)
@@ -306,12 +308,13 @@ def test_peer_store_frames(pkg, gpu_ok, name, n, root):
     ranks = [pkg.Scene(w) for _ in range(n)]
     for s in ranks:
         s.set_peers(canv, n, W * H, root)
-    for frame in (1, 2, 3):
+    extra = pkg.RT_RENDER_GRAPH if graph else 0
+    for frame in range(1, 15 if graph else 4):
         # on real hardware every rank has its own GPU; here the ranks share one, so the gathering rank's frame (whose last
         # kernel spins on its mailbox) is enqueued last
         order = [r for r in range(n) if r != root] + ([root] if root >= 0 else [])
         for r in order:
-            ranks[r].render(flags=pkg.RT_RENDER_PEER_STORE | pkg.RT_RENDER_ASYNC | pkg.RT_RENDER_REBUILD_BVH, rank=r, world=n, tile_w=32,
+            ranks[r].render(flags=pkg.RT_RENDER_PEER_STORE | pkg.RT_RENDER_ASYNC | pkg.RT_RENDER_REBUILD_BVH | extra, rank=r, world=n, tile_w=32,
                             tile_h=16, out_ptr=0)
         rays = 0
         for r, s in enumerate(ranks):
@@ -324,6 +327,10 @@ def test_peer_store_frames(pkg, gpu_ok, name, n, root):
             if root < 0 or root == r:
                 got = s.copy_to_host(ptr, np.empty(W * H, np.uint32)).reshape(H, W)
                 assert (got == full).all(), (frame, r, int((got != full).sum()))
+    if graph:
+        for r, s in enumerate(ranks):
+            caps, reps = s.debug_get(pkg.RT_DEBUG_GRAPH_CAPTURES), s.debug_get(pkg.RT_DEBUG_GRAPH_REPLAYS)
+            assert caps == 2 and reps >= 2, (r, caps, reps)
     for s in ranks:
         s.close()
     for p in canv:
