@@ -458,7 +458,7 @@ __global__ void __launch_bounds__(kThreads, RT_GEN_MIN_BLOCKS) k_shadow_gen(Scen
 template <bool LOOP, class Tracer>
 __device__ __forceinline__ void phase_shadow(const SceneView& s, const Tracer& tr, RayCounts& rc, const long long n_hits,
                                              const ShadowRec* shq, const unsigned* shq_count, unsigned char* occl,
-                                             float4* att4, unsigned long long* work = nullptr) {
+                                             float4* att4, unsigned long long* work = nullptr, const bool from_back = false) {
     long long total = 0;
     for (int l = 0; l < s.n_lights; l++) total += shq_count[l];
     long long f0 = 0, fstep = 0;
@@ -471,6 +471,7 @@ __device__ __forceinline__ void phase_shadow(const SceneView& s, const Tracer& t
             if (lane == 0) b = atomicAdd(work, 32ull);
             b = __shfl_sync(0xffffffffu, b, 0);
             if ((long long)b >= total) break;
+            if (from_back) b = (unsigned long long)(((total + 31) & ~31ll) - 32) - b;  // the queues' last entries first
             f = (long long)b + lane;
             if (f >= total) continue;
         } else if (f >= total) {
@@ -497,11 +498,11 @@ __device__ __forceinline__ void phase_shadow(const SceneView& s, const Tracer& t
 template <int MODE, bool STATS, bool LOOP>
 __global__ void __launch_bounds__(kThreads, RT_SHADOW_MIN_BLOCKS) k_shadow(SceneView s, unsigned long long* ctr, int ctr_n, const ShadowRec* shq,
                                                        const unsigned* shq_count, unsigned char* occl, float4* att4,
-                                                       unsigned long long* work) {
+                                                       unsigned long long* work, int from_back) {
     TravStats ts = {0, 0, 0};
     RayCounts rc = {0, 0, 0};
     typename TracerOf<MODE>::T tr = TracerOf<MODE>::make(&s, STATS ? &ts : nullptr);
-    phase_shadow<LOOP>(s, tr, rc, (long long)(unsigned)ctr[ctr_n], shq, shq_count, occl, att4, work);
+    phase_shadow<LOOP>(s, tr, rc, (long long)(unsigned)ctr[ctr_n], shq, shq_count, occl, att4, work, from_back != 0);
     flush_counts(ctr, rc, ts, STATS);
 }
 
@@ -1691,10 +1692,12 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
             sc->kernel_launches++;
             return;
         }
+        static const int lane_back_env = [] { const char* e = std::getenv("RT_SHADOW_LANE_ORDER"); return (e && std::atoi(e)) ? 1 : 0; }();
+        const int lane_back = (beam_possible && lane_back_env && !static_split) ? 1 : 0;
         if (loop) k_shadow<MODE, STATS, true><<<persistent_grid(k_shadow<MODE, STATS, true>, sc->sm_count), kThreads, 0, st>>>(
-            v, ctr, ctr_n, shq, shq_count, occl, att4, work);
+            v, ctr, ctr_n, shq, shq_count, occl, att4, work, 0);
         else k_shadow<MODE, STATS, false><<<persistent_grid(k_shadow<MODE, STATS, false>, sc->sm_count), kThreads, 0, st>>>(
-            v, ctr, ctr_n, shq, shq_count, occl, att4, work);
+            v, ctr, ctr_n, shq, shq_count, occl, att4, work, lane_back);
         sc->kernel_launches++;
     };
     HitRec* hitq = sc->d_hitq.as<HitRec>();
@@ -1802,9 +1805,9 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
                 k_shadow_gen<true><<<persistent_grid(k_shadow_gen<true>, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, hitq, shq, shq_count, occl, att4, paths, path_stride);
                 if (loop) k_shadow<MODE, STATS, true><<<persistent_grid(k_shadow<MODE, STATS, true>, sc->sm_count), kThreads, 0, st>>>(
-                    v, ctr, in, shq, shq_count, occl, att4, nullptr);
+                    v, ctr, in, shq, shq_count, occl, att4, nullptr, 0);
                 else k_shadow<MODE, STATS, false><<<persistent_grid(k_shadow<MODE, STATS, false>, sc->sm_count), kThreads, 0, st>>>(
-                    v, ctr, in, shq, shq_count, occl, att4, nullptr);
+                    v, ctr, in, shq, shq_count, occl, att4, nullptr, 0);
                 k_wave_advance<<<persistent_grid(k_wave_advance, sc->sm_count), kThreads, 0, st>>>(
                     v, ctr, in, outc, hitq, occl, att4, qout, canvas, paths, path_stride);
                 sc->kernel_launches += 4;
