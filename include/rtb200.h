@@ -331,6 +331,12 @@ int rt_push_tiles_signal(RtScene* scene, const RtRenderParams* params, const uin
  *                which in stream order is after its consumers of frame e.
  *   gather_root  r >= 0: only rank r receives the frame (north_star's "framebuffer gathered": 4 bytes per pixel cross
  *                NVLink once); -1: every rank receives it (all-gather: every pixel is stored n_ranks times).
+ *                With one receiver the senders wait for nobody's signal, so rank r acknowledges every gathered epoch in
+ *                each sender's own mailbox (slot r of its parity-0 canvas) and a sender stores frame e only after the
+ *                acknowledgement of frame e - 1: it is never more than one frame ahead of the gathering rank, and a
+ *                gathering rank that stopped rendering makes the sender's frame RT_ERR_CUDA after the time-out.
+ *                The consumer's side of the contract: reads of frame e are enqueued on the scene's stream (or complete)
+ *                before rt_render is called for frame e + 1.
  * A receiving rank's rt_render ends with a one-warp wait on its own mailbox (all ranks' epochs), so when the call — or
  * rt_frame_finish after RT_RENDER_ASYNC — returns RT_OK the frame in rt_peer_frame_canvas() is complete; a peer that never
  * signals makes it RT_ERR_CUDA after the time-out instead. Frames with secondary rays or refractive materials render into
