@@ -46,6 +46,67 @@ rtb::Float3 read_vec3(const mini_json::Value& v) { return {v.at(0).as_float(), v
 rtb::Float4 read_vec4(const mini_json::Value& v) {
     return {v.at(0).as_float(), v.at(1).as_float(), v.at(2).as_float(), v.at(3).as_float()};
 }
+
+const float kInv255 = 1.0f / UINT8_MAX;
+
+// Top-level scalars of a world file (src/procedural/cube_world.cc:39-61,141-144), then the caller's overrides.
+struct WorldSettings {
+    int seed = kDefaultSeed, grid_size = kDefaultGridSize, width = kDefaultWidth, height = kDefaultHeight;
+    float fov = kDefaultFov, unit_length = kDefaultUnitLen, amplitude = kDefaultAmplitude;
+    WorldSettings(const mini_json::Value& doc, const WorldOverrides& ov) {
+        struct { const char* key; int* dst; } ints[] = {{"seed", &seed}, {"grid_size", &grid_size}, {"width", &width}, {"height", &height}};
+        for (auto& e : ints) if (doc.has(e.key)) *e.dst = doc.at(e.key).as_int();
+        if (doc.has("fov")) fov = (float)(doc.at("fov").as_double() * M_PI) / 180;  // degrees -> radians (:57)
+        if (doc.has("unit_length")) unit_length = (float)doc.at("unit_length").as_double();
+        if (doc.has("amplitude")) amplitude = (float)doc.at("amplitude").as_double();
+        if (ov.width > 0) width = ov.width;
+        if (ov.height > 0) height = ov.height;
+        if (ov.grid_size > 0) grid_size = ov.grid_size;
+    }
+};
+
+// Material keys of a "cubes" (or "spheres") entry (:82-105): the four colour terms are 0-255 in the file, Kt / Kr are not.
+rtracer::Material read_material(const mini_json::Value& e) {
+    rtracer::Material mat;
+    if (e.has("Ke")) mat.set_Ke(kInv255 * read_vec4(e.at("Ke")));
+    if (e.has("Ka")) mat.set_Ka(kInv255 * read_vec4(e.at("Ka")));
+    if (e.has("Kd")) mat.set_Kd(kInv255 * read_vec4(e.at("Kd")));
+    if (e.has("Ks")) mat.set_Ks(kInv255 * read_vec4(e.at("Ks")));
+    if (e.has("Kt")) mat.set_Kt(read_vec4(e.at("Kt")));
+    if (e.has("Kr")) mat.set_Kr(read_vec4(e.at("Kr")));
+    if (e.has("alpha")) mat.set_alpha((float)e.at("alpha").as_double());
+    if (e.has("eta")) mat.set_eta((float)e.at("eta").as_double());
+    return mat;
+}
+
+// The terrain (:145-170): for every cube mesh a fresh height field with the SAME seed (so every layer has the same relief),
+// sampled on the integer grid; floor(0.5 (noise + amplitude)) + 1 cubes of that mesh are stacked on the column, on top of
+// what the meshes before it left there. Instances are created in mesh / row / column / bottom-up order — the order is
+// the instance id. Returns the highest column.
+float stack_terrain(rtracer::SceneBuilder& builder, const WorldSettings& ws, int n_meshes) {
+    const int g = ws.grid_size;
+    std::vector<float> column_top((size_t)g * g, 0.0f);
+    float highest = 0.0f;
+    for (int mesh = 0; mesh < n_meshes; mesh++) {
+        Perlin relief(ws.seed, (g + 4) / 5);
+        relief.set_amplitude(ws.amplitude);
+        relief.set_period((float)g);
+        for (int row = 0; row < g; row++) {
+            for (int col = 0; col < g; col++) {
+                float& top = column_top[(size_t)row * g + col];
+                const float x = row - g / 2.0f, z = col - g / 2.0f;
+                const float layers = std::floor(0.5f * (relief.sample((float)row, (float)col, 0.0f) + ws.amplitude)) + 1;
+                for (int k = 0; k < layers; k++) {
+                    const int id = builder.add_trans(builder.get_mesh_builder(mesh));
+                    builder.get_transformation(id).set_position({x, top + k, z});
+                }
+                top += layers;
+                highest = std::max(highest, top);
+            }
+        }
+    }
+    return highest;
+}
 }  // namespace
 
 rtracer::FlatScene generate_from_text(const std::string& json_text, const WorldOverrides& ov) {
@@ -53,46 +114,27 @@ rtracer::FlatScene generate_from_text(const std::string& json_text, const WorldO
     const mini_json::Value& doc = *root;
     if (!doc.is_object()) throw std::runtime_error("world json: top level is not an object");
 
-    int seed = kDefaultSeed, grid_size = kDefaultGridSize, width = kDefaultWidth, height = kDefaultHeight;
-    float fov = kDefaultFov, unit_length = kDefaultUnitLen;
-    if (doc.has("seed")) seed = doc.at("seed").as_int();
-    if (doc.has("grid_size")) grid_size = doc.at("grid_size").as_int();
-    if (doc.has("width")) width = doc.at("width").as_int();
-    if (doc.has("height")) height = doc.at("height").as_int();
-    if (doc.has("fov")) fov = (float)(doc.at("fov").as_double() * M_PI) / 180;  // degrees -> radians (:57)
-    if (doc.has("unit_length")) unit_length = (float)doc.at("unit_length").as_double();
-    if (ov.width > 0) width = ov.width;
-    if (ov.height > 0) height = ov.height;
-    if (ov.grid_size > 0) grid_size = ov.grid_size;
+    const WorldSettings ws(doc, ov);
+    const int grid_size = ws.grid_size, width = ws.width, height = ws.height;
 
     (void)doc.at("atlas").as_string();  // required key in the reference (:64); the atlas is never sampled
-    rtracer::Camera cam(fov, unit_length, width, height);
+    rtracer::Camera cam(ws.fov, ws.unit_length, width, height);
     rtracer::SceneBuilder builder;
 
     // cube meshes, one per "cubes" entry (:70-114)
     int n_cubes = 0;
-    const float inv255 = 1.0f / UINT8_MAX;
     if (doc.has("cubes")) {
         const mini_json::Value& cubes = doc.at("cubes");
         n_cubes = (int)cubes.size();
         for (int i = 0; i < n_cubes; i++) {
             const mini_json::Value& cube = cubes.at((size_t)i);
-            rtracer::Material mat;
-            rtracer::TextureCoords coords;  // degenerate: texture mapping is a TODO in the reference (:79-81)
-            if (cube.has("Ke")) mat.set_Ke(inv255 * read_vec4(cube.at("Ke")));
-            if (cube.has("Ka")) mat.set_Ka(inv255 * read_vec4(cube.at("Ka")));
-            if (cube.has("Kd")) mat.set_Kd(inv255 * read_vec4(cube.at("Kd")));
-            if (cube.has("Ks")) mat.set_Ks(inv255 * read_vec4(cube.at("Ks")));
-            if (cube.has("Kt")) mat.set_Kt(read_vec4(cube.at("Kt")));
-            if (cube.has("Kr")) mat.set_Kr(read_vec4(cube.at("Kr")));
-            if (cube.has("alpha")) mat.set_alpha((float)cube.at("alpha").as_double());
-            if (cube.has("eta")) mat.set_eta((float)cube.at("eta").as_double());
+            const rtracer::Material mat = read_material(cube);
             // "texture": [tile_x, tile_y, tile_size] — schema extension: every face shows that atlas tile
             if (cube.has("texture")) {
                 const mini_json::Value& t = cube.at("texture");
                 builder.build_textured_cube(.999f, t.at(0).as_int(), t.at(1).as_int(), t.at(2).as_int(), mat);
             } else {
-                builder.build_cube(.999f, coords, mat);
+                builder.build_cube(.999f, rtracer::TextureCoords(), mat);  // degenerate coordinates: texture mapping is a TODO in the reference (:79-81)
             }
         }
     }
@@ -114,16 +156,8 @@ rtracer::FlatScene generate_from_text(const std::string& json_text, const WorldO
         const mini_json::Value& sp = doc.at("spheres");
         for (size_t i = 0; i < sp.size(); i++) {
             const mini_json::Value& e = sp.at(i);
-            rtracer::Material mat;
+            const rtracer::Material mat = read_material(e);
             rtracer::TextureCoords coords;
-            if (e.has("Ke")) mat.set_Ke(inv255 * read_vec4(e.at("Ke")));
-            if (e.has("Ka")) mat.set_Ka(inv255 * read_vec4(e.at("Ka")));
-            if (e.has("Kd")) mat.set_Kd(inv255 * read_vec4(e.at("Kd")));
-            if (e.has("Ks")) mat.set_Ks(inv255 * read_vec4(e.at("Ks")));
-            if (e.has("Kt")) mat.set_Kt(read_vec4(e.at("Kt")));
-            if (e.has("Kr")) mat.set_Kr(read_vec4(e.at("Kr")));
-            if (e.has("alpha")) mat.set_alpha((float)e.at("alpha").as_double());
-            if (e.has("eta")) mat.set_eta((float)e.at("eta").as_double());
             spheres.push_back({builder.build_sphere((float)e.at("radius").as_double(), coords, mat), read_vec3(e.at("pos"))});
         }
     }
@@ -134,39 +168,16 @@ rtracer::FlatScene generate_from_text(const std::string& json_text, const WorldO
         if (lights.has("directional")) {
             const mini_json::Value& d = lights.at("directional");
             for (size_t i = 0; i < d.size(); i++)
-                builder.add_directional_light(read_vec3(d.at(i).at("dir")), inv255 * read_vec4(d.at(i).at("col")));
+                builder.add_directional_light(read_vec3(d.at(i).at("dir")), kInv255 * read_vec4(d.at(i).at("col")));
         }
         if (lights.has("point")) {
             const mini_json::Value& p = lights.at("point");
             for (size_t i = 0; i < p.size(); i++)
-                builder.add_point_light(read_vec3(p.at(i).at("pos")), inv255 * read_vec4(p.at(i).at("col")));
+                builder.add_point_light(read_vec3(p.at(i).at("pos")), kInv255 * read_vec4(p.at(i).at("col")));
         }
     }
 
-    // Perlin height field -> stacked unit cubes (:140-170)
-    float amplitude = kDefaultAmplitude;
-    if (doc.has("amplitude")) amplitude = (float)doc.at("amplitude").as_double();
-    std::vector<float> last_heights((size_t)grid_size * grid_size, 0.0f);
-    float max_height = 0.0f;
-    for (int c = 0; c < n_cubes; c++) {
-        Perlin perlin(seed, (grid_size + 4) / 5);
-        perlin.set_amplitude(amplitude);
-        perlin.set_period((float)grid_size);
-        for (int i = 0; i < grid_size; i++) {
-            for (int j = 0; j < grid_size; j++) {
-                float x = i - grid_size / 2.0f;
-                float z = j - grid_size / 2.0f;
-                float y_off = std::floor(0.5f * (perlin.sample((float)i, (float)j, 0.0f) + amplitude)) + 1;
-                for (int d = 0; d < y_off; d++) {
-                    float y = last_heights[(size_t)i * grid_size + j] + d;
-                    int tid = builder.add_trans(builder.get_mesh_builder(c));
-                    builder.get_transformation(tid).set_position({x, y, z});
-                }
-                last_heights[(size_t)i * grid_size + j] += y_off;
-                max_height = std::max(max_height, last_heights[(size_t)i * grid_size + j]);
-            }
-        }
-    }
+    const float max_height = stack_terrain(builder, ws, n_cubes);
 
     for (const SphereAt& sa : spheres) {
         int tid = builder.add_trans(builder.get_mesh_builder(sa.hitable));

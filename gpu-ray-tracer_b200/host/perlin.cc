@@ -3,69 +3,73 @@
 #include <cmath>
 #include <functional>
 #include <random>
+#include <utility>
 
 namespace procedural {
 
+namespace {
+
+// point on the unit sphere from a polar and an azimuth angle, renormalised like the reference does (perlin.cu:90-92)
+rtb::Float3 direction(float polar, float azimuth) {
+    const float ring = std::sin(polar);
+    const rtb::Float3 v = {std::cos(azimuth) * ring, std::sin(azimuth) * ring, std::cos(polar)};
+    return rtb::normalized(v);
+}
+
+// the reference's blend puts the weight on its FIRST operand (perlin.cu:8-10)
+float blend(float first, float second, float w) { return w * first + (1 - w) * second; }
+
+// smoothstep of the position inside a lattice cell (perlin.cu:35-37)
+float fade(float d) { return d * d * (3 - 2 * d); }
+
+struct Axis {  // one coordinate, scaled to lattice units: cell index and faded fraction
+    int cell;
+    float frac;
+    Axis(float scaled, int n) : cell((int)std::floor(scaled) % n), frac(fade(scaled - std::floor(scaled))) {}
+};
+
+}  // namespace
+
 Perlin::Perlin(int seed, int n_sample_vecs) : amplitude_(1.0f), period_(1.0f), n_(n_sample_vecs) {
-    std::mt19937 generator{(std::mt19937::result_type)seed};
-    auto rng = std::bind(std::uniform_real_distribution<float>{}, generator);  // copies the generator
-    sample_vecs_.resize(n_);
-    permutation_.resize(n_);
-    for (int i = 0; i < n_; i++) {
-        float theta = std::acos(2 * rng() - 1);
-        float phi = 2 * rng() * M_PI;
-        rtb::Float3 v = {std::cos(phi) * std::sin(theta), std::sin(phi) * std::sin(theta), std::cos(theta)};
-        sample_vecs_[i] = rtb::normalized(v);
-        permutation_[i] = i;
+    std::mt19937 engine{(std::mt19937::result_type)seed};
+    // std::bind stores a COPY of the engine: the integer stream below starts from the seed state again (perlin.cu:85,96)
+    auto uniform01 = std::bind(std::uniform_real_distribution<float>{}, engine);
+    gradients_.reserve(n_);
+    perm_.reserve(n_);
+    for (int k = 0; k < n_; k++) {
+        const float polar = std::acos(2 * uniform01() - 1);
+        const float azimuth = 2 * uniform01() * M_PI;
+        gradients_.push_back(direction(polar, azimuth));
+        perm_.push_back(k);
     }
-    auto rng_int = std::bind(std::uniform_int_distribution<unsigned>{}, generator);  // seed state again
-    for (int i = 0; i < n_; i++) {
-        int swap_idx = rng_int() % n_;
-        int temp = permutation_[i];
-        permutation_[i] = permutation_[swap_idx];
-        permutation_[swap_idx] = temp;
+    auto any_unsigned = std::bind(std::uniform_int_distribution<unsigned>{}, engine);
+    for (int k = 0; k < n_; k++) {
+        const int other = any_unsigned() % n_;
+        std::swap(perm_[k], perm_[other]);
     }
 }
 
-const rtb::Float3& Perlin::hash(int x, int y, int z) const {
-    int hx = x % n_;
-    int hxy = (permutation_[hx] + y) % n_;
-    int hxyz = (permutation_[hxy] + z) % n_;
-    return sample_vecs_[permutation_[hxyz]];
-}
-
-static float smoothstep_remap(float d) { return d * d * (3 - 2 * d); }
-static float interpolate(float a, float b, float w) { return w * a + (1 - w) * b; }
-
-float Perlin::weight(int ix, int iy, int iz, float mx, float my, float mz, int dx, int dy, int dz) const {
-    float cx = ix + dx, cy = iy + dy, cz = iz + dz;
-    rtb::Float3 offset = {dx - mx, dy - my, dz - mz};
-    const rtb::Float3& wv = hash((int)cx, (int)cy, (int)cz);
-    return rtb::dot(wv, rtb::normalized(offset));
+const rtb::Float3& Perlin::gradient_at(int x, int y, int z) const {
+    int h = x % n_;
+    h = (perm_[h] + y) % n_;
+    h = (perm_[h] + z) % n_;
+    return gradients_[perm_[h]];
 }
 
 float Perlin::sample(float x, float y, float z) const {
-    float sx = x * n_ / period_, sy = y * n_ / period_, sz = z * n_ / period_;
-    int ix = (int)std::floor(sx) % n_, iy = (int)std::floor(sy) % n_, iz = (int)std::floor(sz) % n_;
-    float mx = smoothstep_remap(sx - std::floor(sx));
-    float my = smoothstep_remap(sy - std::floor(sy));
-    float mz = smoothstep_remap(sz - std::floor(sz));
-    float w000 = weight(ix, iy, iz, mx, my, mz, 0, 0, 0);
-    float w001 = weight(ix, iy, iz, mx, my, mz, 0, 0, 1);
-    float w010 = weight(ix, iy, iz, mx, my, mz, 0, 1, 0);
-    float w011 = weight(ix, iy, iz, mx, my, mz, 0, 1, 1);
-    float w100 = weight(ix, iy, iz, mx, my, mz, 1, 0, 0);
-    float w101 = weight(ix, iy, iz, mx, my, mz, 1, 0, 1);
-    float w110 = weight(ix, iy, iz, mx, my, mz, 1, 1, 0);
-    float w111 = weight(ix, iy, iz, mx, my, mz, 1, 1, 1);
-    float x00 = interpolate(w000, w100, mx);
-    float x01 = interpolate(w001, w101, mx);
-    float x10 = interpolate(w010, w110, mx);
-    float x11 = interpolate(w011, w111, mx);
-    float xy0 = interpolate(x00, x10, my);
-    float xy1 = interpolate(x01, x11, my);
-    float xyz = interpolate(xy0, xy1, mz);
-    return amplitude_ * xyz;
+    const Axis ax(x * n_ / period_, n_), ay(y * n_ / period_, n_), az(z * n_ / period_, n_);
+    // gradient . unit offset at the eight corners of the cell, corner (dx, dy, dz) at index 4 dx + 2 dy + dz (perlin.cu:49-57)
+    float corner[8];
+    for (int c = 0; c < 8; c++) {
+        const int dx = c >> 2, dy = (c >> 1) & 1, dz = c & 1;
+        const rtb::Float3 to_corner = {dx - ax.frac, dy - ay.frac, dz - az.frac};
+        corner[c] = rtb::dot(gradient_at(ax.cell + dx, ay.cell + dy, az.cell + dz), rtb::normalized(to_corner));
+    }
+    // fold the cube along x, then y, then z (perlin.cu:73-80)
+    float face[4], edge[2];
+    for (int k = 0; k < 4; k++) face[k] = blend(corner[k], corner[4 + k], ax.frac);
+    for (int k = 0; k < 2; k++) edge[k] = blend(face[k], face[2 + k], ay.frac);
+    return amplitude_ * blend(edge[0], edge[1], az.frac);
 }
 
 }  // namespace procedural
