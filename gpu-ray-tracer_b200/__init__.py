@@ -37,7 +37,7 @@ RT_RENDER_GRAPH = 32768
 RT_RENDER_FAST_ACCEPT = 65536
 RT_HITABLE_TRIMESH, RT_HITABLE_SPHERE = 0, 1
 RT_DEBUG_PREFIX_UPLOADS, RT_DEBUG_BVH8_LEVELS, RT_DEBUG_BUILD_PATH, RT_DEBUG_BUILD_LAUNCHES, RT_DEBUG_BUILD_CLUSTER = 0, 1, 2, 3, 4
-RT_DEBUG_GRAPH_REPLAYS, RT_DEBUG_GRAPH_CAPTURES = 5, 6
+RT_DEBUG_GRAPH_REPLAYS, RT_DEBUG_GRAPH_CAPTURES, RT_DEBUG_FRAME_LANES = 5, 6, 7
 RT_DEBUG_BUILD_PHASE_NS = 16
 RT_DEBUG_BUILD_LEVEL_NS = 32
 RT_CAST_STATIC_MAX_RAYS = 65536
@@ -177,6 +177,7 @@ def cuda_lib():
         lib.rt_tiled_slab_pixels.argtypes = [vp, C.POINTER(RtRenderParams), C.POINTER(C.c_int64)]
         lib.rt_untile.argtypes = [vp, C.POINTER(RtRenderParams), vp, vp]
         lib.rt_scene_set_stream.argtypes = [vp, vp, i32]
+        lib.rt_scene_set_lanes.argtypes = [vp, i32]
         lib.rt_peer_canvas_alloc.argtypes = [C.c_int64, C.POINTER(vp), vp]
         lib.rt_peer_canvas_free.argtypes = [vp]
         lib.rt_peer_canvas_open.argtypes = [vp, C.POINTER(vp)]
@@ -394,6 +395,10 @@ class Scene:
         """Enqueue all later work of this scene on the caller's CUDA stream (an int handle, e.g.
         torch.cuda.current_stream().cuda_stream); None returns to the scene's own stream."""
         _check(cuda_lib().rt_scene_set_stream(self._h, cuda_stream or None, 0 if cuda_stream is None else 1), "rt_scene_set_stream")
+
+    def set_lanes(self, lanes):
+        """rt_scene_set_lanes: concurrent lanes of a device-resident frame (0 = library default, RT_FRAME_LANES or 1)."""
+        _check(cuda_lib().rt_scene_set_lanes(self._h, lanes), "rt_scene_set_lanes")
 
     def finish(self):
         """Waits for the frame started with RT_RENDER_ASYNC and returns its statistics."""

@@ -1520,6 +1520,11 @@ int rt_scene_destroy(RtScene* sc) {
     for (rth::FrameGraph& g : sc->graphs) if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
     if (sc->copies_done) cudaEventDestroy(sc->copies_done);
     if (sc->ev_exchange) cudaEventDestroy(sc->ev_exchange);
+    if (sc->lane_fork) cudaEventDestroy(sc->lane_fork);
+    for (int c = 0; c < RtScene::kMaxChunks - 1; c++) {
+        if (sc->lane_join[c]) cudaEventDestroy(sc->lane_join[c]);
+        if (sc->lane_stream[c]) { cudaStreamSynchronize(sc->lane_stream[c]); cudaStreamDestroy(sc->lane_stream[c]); }
+    }
     if (sc->copy_stream) cudaStreamDestroy(sc->copy_stream);
     if (sc->own_stream) cudaStreamDestroy(sc->own_stream);
     if (sc->h_pinned) cudaFreeHost(sc->h_pinned);
@@ -1608,7 +1613,8 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     // ctr: this chunk's counter block; cev: its events {start, primary done, shadow rays generated, shadow rays traced,
     // wave 0 shaded, bounce waves done}. peers: k_tile stores the pixels into these peer canvases and signals them
     // (only passed when the tile kernel is eligible and the frame has no secondary rays).
-    cudaStream_t st = sc->stream;
+    cudaStream_t st = sc->cur_stream ? sc->cur_stream : sc->stream;  // a lane's stream (render_enqueue) or the scene's
+    const size_t q_off = (size_t)sc->cur_off;  // this lane's first slot of the hit / shadow queues (0 without lanes)
     RT_CUDA(rth::record(sc, cev[0], st));
     // tolerance mode: only the default pipeline (k_tile<1>, k_shadow_beam / k_shadow, k_bounce_waves) has a fast variant; the
     // other branches run their exact kernels (BM), which is always an acceptable answer
@@ -1627,7 +1633,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     bool use_tile = tile_kernel_eligible(sc, v, MODE) && !(secondary && hit_cap * (size_t)path_stride > ((size_t)32 << 30));
     if (peers && !(use_tile && !secondary)) { set_error("internal: peer stores need the tile kernel"); return RT_ERR_INVALID_ARG; }
     if (!use_tile || secondary) {
-        if (sc->d_hitq.reserve(sizeof(HitRec) * (size_t)std::max<long long>(n_pix, 1))) return RT_ERR_OUT_OF_MEMORY;
+        if (sc->d_hitq.reserve(sizeof(HitRec) * (q_off + (size_t)std::max<long long>(n_pix, 1)))) return RT_ERR_OUT_OF_MEMORY;
     }
     sc->wave0_form = use_tile ? 1 : 0;
     if (!use_tile && beam_primary_eligible(sc, MODE)) {
@@ -1635,14 +1641,14 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
         std::memset(&po0, 0, sizeof po0);
         constexpr bool FAST = MODE == TR_BVH_BOX_FAST;
         static const int g0 = persistent_grid(k_tile<STATS, false, false, 1, FAST>, sc->sm_count);
-        k_tile<STATS, false, false, 1, FAST><<<g0, kThreads, 0, st>>>(v, tm, ctr, canvas, po0, nullptr, 0, nullptr, sc->d_hitq.as<HitRec>());
+        k_tile<STATS, false, false, 1, FAST><<<g0, kThreads, 0, st>>>(v, tm, ctr, canvas, po0, nullptr, 0, nullptr, sc->d_hitq.as<HitRec>() + q_off);
         sc->kernel_launches++;
         sc->wave0_form = 2;
         RT_CUDA(rth::record(sc, cev[1], st));
     } else if (!use_tile) {
         int g0 = persistent_grid(k_primary<BM, STATS, false>, sc->sm_count);
         static const int aligned_hitq = [] { const char* e = std::getenv("RT_PACKED_HITQ"); return (e && std::atoi(e)) ? 0 : 1; }();
-        k_primary<BM, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>(), canvas, nullptr, nullptr, nullptr, aligned_hitq);
+        k_primary<BM, STATS, false><<<g0, kThreads, 0, st>>>(v, tm, ctr, sc->d_hitq.as<HitRec>() + q_off, canvas, nullptr, nullptr, nullptr, aligned_hitq);
         sc->kernel_launches++;
         RT_CUDA(rth::record(sc, cev[1], st));
     }
@@ -1661,14 +1667,15 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
     float4* att4 = nullptr;
     ShadowRec* shq = nullptr;
     if (!sc->fused_shade && (!use_tile || secondary)) {
-        size_t cap = hit_cap * (size_t)std::max(v.n_lights, 1);
+        const size_t nl = (size_t)std::max(v.n_lights, 1);
+        size_t cap = (q_off + hit_cap) * nl;
         if (sc->d_shadowq.reserve(sizeof(ShadowRec) * cap) || sc->d_occl.reserve((loop ? sizeof(float4) : 1) * cap) ||
-            sc->d_shq_count.reserve(sizeof(unsigned) * (size_t)std::max(v.n_lights, 1)))
+            sc->d_shq_count.reserve(sizeof(unsigned) * nl * (size_t)(sc->cur_lane + 1)))
             return RT_ERR_OUT_OF_MEMORY;
-        shq = sc->d_shadowq.as<ShadowRec>();
-        if (loop) att4 = sc->d_occl.as<float4>(); else occl = sc->d_occl.as<unsigned char>();
+        shq = sc->d_shadowq.as<ShadowRec>() + q_off * nl;
+        if (loop) att4 = sc->d_occl.as<float4>() + q_off * nl; else occl = sc->d_occl.as<unsigned char>() + q_off * nl;
     }
-    unsigned* shq_count = sc->d_shq_count.as<unsigned>();
+    unsigned* shq_count = sc->d_shq_count.as<unsigned>() + (size_t)std::max(v.n_lights, 1) * (size_t)sc->cur_lane;
     // one any-hit / closest-loop traversal of the shadow rays queued in shq
     auto trace_shadows = [&](int ctr_n) {
         static const int static_split = [] { const char* e = std::getenv("RT_SHADOW_STATIC"); return (e && std::atoi(e)) ? 1 : 0; }();
@@ -1700,7 +1707,7 @@ static int run_wavefront(RtScene* sc, const SceneView& v, const TileMap& tm, uin
             v, ctr, ctr_n, shq, shq_count, occl, att4, work, lane_back);
         sc->kernel_launches++;
     };
-    HitRec* hitq = sc->d_hitq.as<HitRec>();
+    HitRec* hitq = sc->d_hitq.as<HitRec>() + q_off;
     unsigned char* paths = sc->d_paths.as<unsigned char>();
     if (use_tile) {
         PeerOut po;
@@ -2143,6 +2150,26 @@ int rt_scene_set_stream(RtScene* sc, void* stream, int32_t external) {
     return RT_OK;
 }
 
+// RT_FRAME_LANES=n (1..8, default 1): how many concurrent lanes a device-resident frame without secondary rays is cut into.
+static int frame_lanes_env() {
+    static const int n = [] { const char* e = std::getenv("RT_FRAME_LANES"); int v = e ? std::atoi(e) : 1; return std::min(std::max(v, 1), (int)RtScene::kMaxChunks); }();
+    return n;
+}
+static int ensure_lane_streams(RtScene* sc, int n_lanes) {
+    if (!sc->lane_fork) RT_CUDA(cudaEventCreateWithFlags(&sc->lane_fork, cudaEventDisableTiming));
+    for (int c = 1; c < n_lanes; c++) {
+        if (!sc->lane_stream[c - 1]) RT_CUDA(cudaStreamCreateWithFlags(&sc->lane_stream[c - 1], cudaStreamNonBlocking));
+        if (!sc->lane_join[c - 1]) RT_CUDA(cudaEventCreateWithFlags(&sc->lane_join[c - 1], cudaEventDisableTiming));
+    }
+    return RT_OK;
+}
+
+int rt_scene_set_lanes(RtScene* sc, int32_t lanes) {
+    if (!sc || lanes < 0 || lanes > RtScene::kMaxChunks) { set_error("lanes must be in 0..8"); return RT_ERR_INVALID_ARG; }
+    sc->lanes_req = lanes;
+    return RT_OK;
+}
+
 // Enqueues one frame on the scene's stream (plain launches, or into a stream capture when sc->capturing) and leaves it
 // pending; rt_render decides between this, a capture and a replay, and finishes the frame.
 static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* canvas) {
@@ -2158,6 +2185,7 @@ static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* c
     TileMap tm;
     if (int rc = make_tilemap(sc, &p, tm)) return rc;
     cudaStream_t st = sc->stream;
+    sc->cur_stream = nullptr; sc->cur_off = 0; sc->cur_lane = 0;
     int launches0 = sc->kernel_launches;
     const bool no_bvh = (p.flags & RT_RENDER_NO_BVH) != 0;
     const bool want_stats = (p.flags & RT_RENDER_STATS) != 0;
@@ -2259,8 +2287,42 @@ static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* c
                    : (!bounces && 4 * (size_t)out_pixels >= ((size_t)16 << 20) ? 2 : 1);
         n_chunks = std::max(1, std::min(std::min(n_chunks, (int)RtScene::kMaxChunks), units));
     }
+    // Concurrent lanes (RT_FRAME_LANES=n, default 1 = off): the owned tiles are cut into n contiguous ranges; each range runs
+    // the wave-0 pipeline (k_tile<1> -> k_shadow_gen -> shadow kernel -> k_resolve) on its own stream with its own counter
+    // block, events and slice of the queues. A traversal kernel ends with a few SMs finishing their longest work units while
+    // the others idle (0.04-0.07 ms per kernel at any frame size, profiles/r2_summary.md section 5); with lanes the next
+    // lane's kernel takes the SMs the tail leaves free. Same kernels, same arguments up to the tile range: same frame.
+    // Only for the default pipeline of a device-resident frame without secondary rays, outside graph capture and stats
+    // frames, and once the shadow-kernel tuner of this tile shape has settled (its timings need frames without overlap).
+    int n_lanes = 1;
+    int lane_bounds[RtScene::kMaxChunks + 1] = {0};
+    {
+        static const bool tile_env = [] { const char* e = std::getenv("RT_TILE_KERNEL"); return e && std::atoi(e); }();
+        static const bool direct_env = [] { const char* e = std::getenv("RT_PEER_DIRECT"); return e && std::atoi(e); }();
+        static const bool shadow_forced = std::getenv("RT_BEAM_SHADOW") != nullptr;
+        static const int first_pct = [] { const char* e = std::getenv("RT_LANE_FIRST_PCT"); int v = e ? std::atoi(e) : 0; return (v > 0 && v < 100) ? v : 0; }();
+        const int want = sc->lanes_req > 0 ? sc->lanes_req : frame_lanes_env();
+        const bool bounces = sc->any_secondary && sc->env.depth > 0;
+        if (want > 1 && wavefront && n_chunks == 1 && (p.flags & RT_RENDER_CANVAS_DEVICE) && !direct && !sc->capturing &&
+            !(p.flags & RT_RENDER_GRAPH) && !want_stats && !bounces && !sc->any_refractive && !sc->fused_shade && !sc->sort_rays &&
+            !sc->split_shade && !sc->tile_kernel && !tile_env && !direct_env && beam_primary_eligible(sc, TR_BVH_BOX) &&
+            (shadow_forced || sc->tuners[sc->sb_cur].choice >= 0) && sc->n_lights > 0) {
+            n_lanes = std::min(want, std::max(tm.n_owned / 64, 1));  // a lane is worth its launches from ~64 screen tiles on
+            for (int c = 0; c <= n_lanes; c++) lane_bounds[c] = (int)((long long)tm.n_owned * c / n_lanes);
+            if (n_lanes == 2 && first_pct) lane_bounds[1] = std::min(std::max((int)((long long)tm.n_owned * first_pct / 100), 1), tm.n_owned - 1);
+        }
+        if (n_lanes > 1) {
+            if (int rc_l = ensure_lane_streams(sc, n_lanes)) return rc_l;
+            // the queues of all lanes at once: a lane must not reallocate what another lane is using
+            const size_t tot = (size_t)tm.n_work() * 32, nl = (size_t)std::max(sc->n_lights, 1);
+            if (sc->d_hitq.reserve(sizeof(HitRec) * std::max<size_t>(tot, 1)) || sc->d_shadowq.reserve(sizeof(ShadowRec) * std::max<size_t>(tot, 1) * nl) ||
+                sc->d_occl.reserve(std::max<size_t>(tot, 1) * nl) || sc->d_shq_count.reserve(sizeof(unsigned) * nl * (size_t)n_lanes))
+                return RT_ERR_OUT_OF_MEMORY;
+        }
+    }
+    const int n_blocks = std::max(n_chunks, n_lanes);  // counter blocks of this frame
     unsigned long long* ctr = sc->d_counters.as<unsigned long long>();
-    RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long) * C_N * n_chunks, st));
+    RT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long) * C_N * n_blocks, st));
     // row-major canvas shared with other ranks' tiles: clear them. A tile slab needs no clearing: every
     // in-canvas pixel of an owned tile is written, and the slab padding beyond the canvas edge is never read.
     // (not a peer canvas either: the other ranks are storing their tiles into it)
@@ -2271,7 +2333,29 @@ static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* c
     bool canvas_copied = false, peer_direct = false;
     if (no_bvh) rc = run_mega<TR_BRUTE>(sc, v, tm, dcanvas, p.semantics);
     else if (p.semantics == RT_SEMANTICS_CPU) rc = run_mega<TR_BVH_BOX>(sc, v, tm, dcanvas, p.semantics);
-    else {
+    else if (n_lanes > 1) {
+        // RT_LANE_ORDER=1: the last lane (the bottom of the image, where the long work units are) is enqueued first
+        static const bool bottom_first = [] { const char* e = std::getenv("RT_LANE_ORDER"); return e && std::atoi(e); }();
+        RT_CUDA(cudaEventRecord(sc->lane_fork, st));
+        for (int i = 0; i < n_lanes && !rc; i++) {
+            const int c = bottom_first ? n_lanes - 1 - i : i;
+            cudaStream_t ls = c == 0 ? st : sc->lane_stream[c - 1];
+            if (c > 0) RT_CUDA(cudaStreamWaitEvent(ls, sc->lane_fork, 0));
+            TileMap tc = tm;
+            tc.k_begin = lane_bounds[c]; tc.k_count = lane_bounds[c + 1] - lane_bounds[c];
+            sc->cur_stream = ls; sc->cur_lane = c;
+            sc->cur_off = (long long)tc.k_begin * tm.sub_per_tile * 32;
+            int w = 1;
+            if (v.fast_accept) rc = run_wavefront<TR_BVH_BOX_FAST, false>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], nullptr);
+            else rc = run_wavefront<TR_BVH_BOX, false>(sc, v, tc, dcanvas, &w, ctr + (size_t)C_N * c, sc->cev[c], nullptr);
+            if (!rc && c > 0) {
+                cudaError_t e_j = cudaEventRecord(sc->lane_join[c - 1], ls);
+                if (e_j != cudaSuccess) rc = rth::cuda_fail(e_j, "cudaEventRecord(lane_join)", __FILE__, __LINE__);
+            }
+        }
+        sc->cur_stream = nullptr; sc->cur_off = 0; sc->cur_lane = 0;
+        for (int c = 1; c < n_lanes && !rc; c++) RT_CUDA(cudaStreamWaitEvent(st, sc->lane_join[c - 1], 0));
+    } else {
         // chunk sizes fall geometrically (1, 1/4, 1/16, ...): only the last chunk's copy is not hidden behind rendering
         // (world16 at 4K, two chunks: e2e 2.496 ms at ratio 1/2, 2.457 at 1/4, 2.461 at 0.18).
         // Every chunk gets at least one unit (n_chunks <= units).
@@ -2348,7 +2432,7 @@ static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* c
     }
     RT_CUDA(rth::record(sc, sc->ev[4], st));
     unsigned long long* host_ctr = sc->h_pinned + 64;
-    RT_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof(unsigned long long) * C_N * n_chunks, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof(unsigned long long) * C_N * n_blocks, cudaMemcpyDeviceToHost, st));
     if (host_canvas && !canvas_copied && !direct) {
         if (host_bands) {
             if (int rc2 = copy_rows_to_host(sc, tm, 0, tm.n_owned, dcanvas, canvas, true, st)) return rc2;
@@ -2356,7 +2440,8 @@ static int render_enqueue(RtScene* sc, const RtRenderParams* params, uint32_t* c
             RT_CUDA(cudaMemcpyAsync(canvas, dcanvas, 4 * (size_t)out_pixels, cudaMemcpyDeviceToHost, st));
         }
     }
-    sc->pend_chunks = n_chunks;
+    sc->pend_chunks = n_blocks;
+    sc->pend_lanes = n_lanes;
     sc->pend_direct = direct;
     RT_CUDA(rth::record(sc, sc->ev[5], st));
     sc->pending = true;
@@ -2393,6 +2478,7 @@ static void restore_state(RtScene* sc, const rth::FrameState& f) {
     sc->pend_built = f.pend_built; sc->pend_wavefront = f.pend_wavefront; sc->pend_stats = f.pend_stats; sc->pend_direct = f.pend_direct;
     sc->split_shade_used = f.split_shade_used; sc->tile_kernel_used = f.tile_kernel_used; sc->exchange_pending = f.exchange_pending;
     sc->pend_waves = f.pend_waves; sc->pend_chunks = f.pend_chunks; sc->wave0_form = f.wave0_form; sc->sb_used = f.sb_used;
+    sc->pend_lanes = 1;  // captured frames never use lanes
 }
 
 int rt_render(RtScene* sc, const RtRenderParams* params, uint32_t* canvas, RtFrameStats* stats) {
@@ -2563,7 +2649,7 @@ int rt_frame_finish(RtScene* sc, RtFrameStats* stats) {
     fs.waves = waves >= 0 ? waves : 1 + (int)host_ctr[C_WAVES];
     if (fs.waves > 4096) { set_error("bounce waves did not terminate"); return RT_ERR_LIMIT; }
     fs.kernel_launches = sc->kernel_launches - launches0;
-    fs.host_chunks = sc->pend_direct ? 0 : n_chunks;
+    fs.host_chunks = sc->pend_direct ? 0 : sc->pend_lanes > 1 ? 1 : n_chunks;
     fs.tile_kernel = sc->wave0_form;
     fs.graph = sc->pend_graph;
     fs.node_fetches = host_ctr[C_FETCHES];
@@ -2690,6 +2776,7 @@ int rt_debug_get(RtScene* sc, int32_t what, int64_t* out) {
         case RT_DEBUG_BUILD_LAUNCHES: *out = sc->bvh.build_launches; break;
         case RT_DEBUG_GRAPH_REPLAYS: *out = sc->graph_replays; break;
         case RT_DEBUG_GRAPH_CAPTURES: *out = sc->graph_captures; break;
+        case RT_DEBUG_FRAME_LANES: *out = sc->pend_lanes; break;
         case RT_DEBUG_BUILD_CLUSTER: *out = sc->bvh.build_path == 2 ? sc->bvh.cluster_size : 0; break;
         default:
             // RT_DEBUG_BUILD_PHASE_NS + i, i in 0..6: nanoseconds CTA 0 of the last cluster build spent in phase i (flatten +

@@ -152,6 +152,16 @@ struct RtScene {
     bool exchange_pending = false;      // ... whose outcome (h_pinned[48]) rt_frame_finish still has to look at
     int pend_chunks = 1;
     bool pend_direct = false;
+    // Concurrent lanes (RT_FRAME_LANES, render_enqueue): a device-resident frame without secondary rays is cut into up to
+    // kMaxChunks contiguous ranges of owned tiles; lane c > 0 runs its wave-0 kernels on lane_stream[c - 1], forked from and
+    // joined back into the scene's stream, with its own counter block, events and slice of the hit / shadow queues, so that
+    // the tail of one lane's kernel (a few SMs finishing their longest work units) is filled by the next lane's kernel.
+    cudaStream_t lane_stream[kMaxChunks - 1] = {};
+    cudaEvent_t lane_fork = nullptr, lane_join[kMaxChunks - 1] = {};
+    cudaStream_t cur_stream = nullptr;  // stream of the lane run_wavefront is enqueuing (nullptr: the scene's stream)
+    long long cur_off = 0;              // first hit-queue slot of that lane
+    int cur_lane = 0, pend_lanes = 1;
+    int lanes_req = 0;                  // rt_scene_set_lanes (0: RT_FRAME_LANES / 1)
     // pinned host memory, u64 units: [32,36) build result, [48] exchange time-out mask, [50,58) phase time stamps of the cluster build (RT_BUILD_TIMERS), [40,42) live counts of the bounce waves,
     // [64 + 32 c, 96 + 32 c) counters of chunk c
     unsigned long long* h_pinned = nullptr;

@@ -295,6 +295,14 @@ int rt_render(RtScene* scene, const RtRenderParams* params, uint32_t* canvas, Rt
  * pending per scene; starting another finishes the pending one first. */
 int rt_scene_set_stream(RtScene* scene, void* cuda_stream, int32_t external);
 int rt_frame_finish(RtScene* scene, RtFrameStats* stats);
+/* Concurrent lanes (no counterpart in the reference, whose trace is one kernel, src/raytracer.cu:108-113): a device-resident
+ * frame without secondary rays is cut into `lanes` (1..8) contiguous ranges of its screen tiles, and every range runs the
+ * frame's kernels on a stream of its own, forked from and joined back into the scene's stream, with its own slice of the
+ * queues — the tail of one range's traversal kernel (a few SMs finishing their longest work units) is filled by the next
+ * range's kernel. Same kernels, same frame, bit for bit. 0 = the library default (RT_FRAME_LANES in the environment, else 1).
+ * Frames that cannot use lanes (host canvas in chunks, secondary rays, graph capture, statistics, the opt-in kernel
+ * variants) run as before; RT_DEBUG_FRAME_LANES tells how many the last frame used. */
+int rt_scene_set_lanes(RtScene* scene, int32_t lanes);
 
 /* Multi-GPU helper: number of uint32 pixels rt_render writes with RT_RENDER_TILED_OUTPUT, and the
  * de-interleave of `world` gathered slabs back into a row-major canvas (both device pointers). */
@@ -403,6 +411,7 @@ enum {
     RT_DEBUG_BUILD_LAUNCHES = 3, /* kernels the last build / refit launched */
     RT_DEBUG_GRAPH_REPLAYS = 5,  /* frames of this scene replayed from a captured graph */
     RT_DEBUG_GRAPH_CAPTURES = 6, /* frames captured into a graph */
+    RT_DEBUG_FRAME_LANES = 7,    /* concurrent lanes the last frame was cut into (RT_FRAME_LANES; 1 = none) */
     RT_DEBUG_BUILD_CLUSTER = 4,  /* CTAs in the cluster of the last one-launch build (0: multi-kernel pipeline) */
     RT_DEBUG_BUILD_PHASE_NS = 16, /* + i (0..6): ns per phase of the last cluster build, with RT_BUILD_TIMERS=1 in the environment */
     RT_DEBUG_BUILD_LEVEL_NS = 32 /* + i (0..15): raw globaltimer stamp after phase A (even i) / phase B (odd i) of collapse level i / 2 */
