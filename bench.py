@@ -64,6 +64,8 @@ def parse_args():
     ap.add_argument("--no-stress", action="store_true", help="skip the world8_stress block (N = 1)")
     ap.add_argument("--split-shade", action="store_true", help="RT_RENDER_SPLIT_SHADE: round 1's split pipeline (per-lane k_primary)")
     ap.add_argument("--graph", action="store_true", help="RT_RENDER_GRAPH: device-resident frames captured once and replayed as one CUDA graph")
+    ap.add_argument("--lanes", type=int, default=0,
+                    help="rt_scene_set_lanes: concurrent lanes of the device-resident frame (0 = library default, i.e. RT_FRAME_LANES or one stream; measured neutral, profiles/r2_lanes_ab.txt)")
     ap.add_argument("--tile-kernel", action="store_true", help="RT_RENDER_TILE_KERNEL: wave 0 entirely in the tile kernels")
     ap.add_argument("--band-h", type=int, default=4,
                     help="N > 1, e2e: rows per full-width band dealt round-robin to the ranks (each rank copies its bands into the one shared host canvas)")
@@ -352,6 +354,8 @@ def run_ours(a):
     wfile = pkg.World(os.path.join(ROOT, "scenes", a.scene + ".json"), width=a.width, height=a.height, depth=a.depth,
                       grid_size=a.grid_size)
     scene = pkg.Scene(wfile, device=local_rank)
+    if a.lanes:
+        scene.set_lanes(a.lanes)
     W, H = wfile.width, wfile.height
     base = (0 if a.keep_bvh else pkg.RT_RENDER_REBUILD_BVH) | (pkg.RT_RENDER_SORT_RAYS if a.sort_rays else 0) | \
         (pkg.RT_RENDER_SPLIT_SHADE if a.split_shade else 0) | (pkg.RT_RENDER_TILE_KERNEL if a.tile_kernel else 0)
@@ -599,6 +603,7 @@ def run_ours(a):
                            "culled_frac": sst["rays_culled"] / max(sst["rays_total"], 1), "instances": desc.n_instances,
                            "triangles": sst_prims(scene), "step": "BVH rebuild + trace" if not a.keep_bvh else "trace (BVH kept)",
                            "l2": "flushed between timed iterations (256 MiB write)",
+                           "lanes": a.lanes if a.lanes else "library default (one stream unless RT_FRAME_LANES is set)",
                            "sharding": "screen tiles %dx%d round-robin over %d rank(s)" % (a.tile_w, a.tile_h, world),
                            "exchange": {"fused-root": "RT_RENDER_PEER_STORE: the frame's kernels store every pixel into rank 0's row-major canvas over NVLink peer memory (double-buffered by frame parity) and signal its mailbox; rank 0 waits for all ranks (the framebuffer gathered: no slab, no push kernel, no collective call)",
                                         "fused-all": "RT_RENDER_PEER_STORE into every rank's canvas (all ranks receive the frame)",
