@@ -214,6 +214,8 @@ extern "C" {
 
 // Camera rays through beam_query as k_tile<1> calls it (closest hit, leaf-box rule on, tolerance mode off).
 // stats4: nodes visited (per active ray), triangle filters, exact tests, node fetches (per warp).
+// use_box: 0 = BVH8 only, 1 = with the reference's leaf-box rule, 2 = leaf-box rule + the opt-in tolerance mode
+// (beam_query<.., FAST = true>: clear filter hits skip the reference-exact test; scenes without rotations only).
 int emu_beam_primary(const RtSceneDesc* d, const uint32_t* nodes8, const float* prims8, int n_prims, int use_box,
                      int32_t* inst, int32_t* tri, float* t, uint64_t* stats4, int threads) {
     WScene e;
@@ -231,7 +233,8 @@ int emu_beam_primary(const RtSceneDesc* d, const uint32_t* nodes8, const float* 
         Hit h;
         TravStats ts = {0, 0, 0};
         BeamStats bs = {0};
-        const bool hit = beam_query<true, false>(v, r, valid, false, use_box != 0, INFINITY, h, ts, bs);
+        const bool hit = use_box == 2 ? beam_query<true, true>(v, r, valid, false, true, INFINITY, h, ts, bs)
+                                      : beam_query<true, false>(v, r, valid, false, use_box != 0, INFINITY, h, ts, bs);
         if (valid) {
             const size_t p = (size_t)y * v.width + x;
             inst[p] = hit ? h.inst : -1;

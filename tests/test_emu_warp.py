@@ -121,3 +121,20 @@ def test_beam_on_a_deep_tree_of_coincident_triangles(pkg):
     li, lt, ltime, _ = eb.trace_primary(w, bvh, 1)
     assert ((gi >= 0) == (oi >= 0)).all() and (gt == ot).all() and (bits(gtime) == bits(otime)).all()
     assert (gi == li).all() and (gi >= 0).sum() > 50
+
+
+@pytest.mark.parametrize("name", ["world4", "world16", "world8_stress"])
+def test_beam_primary_tolerance_mode(pkg, name):
+    """The opt-in tolerance mode of the same walk (beam_query<.., FAST>: hits clearly inside a triangle skip the
+    reference-exact test): north_star's bars against the oracle — ids on >= 99.99 % of the rays, t within 1e-4 relative —
+    and it really skips exact tests."""
+    w = pkg.World(scene_path(name), width=320, height=240)
+    bvh = ob.OracleBvh(w)
+    oi, ot, otime = ob.OracleScene(w).trace_primary(use_bvh=1)
+    inst, tri, t, st = eb.beam_primary(w, bvh, use_box=2)
+    _, _, _, st_exact = eb.beam_primary(w, bvh, use_box=1)
+    same = (inst == oi) & (tri == ot)
+    hit = same & (oi >= 0)
+    rel = np.abs(t[hit].astype(np.float64) - otime[hit]) / np.abs(otime[hit])
+    assert same.mean() >= 0.9999 and rel.max() <= 1e-4
+    assert st["exact"] < 0.7 * st_exact["exact"]
